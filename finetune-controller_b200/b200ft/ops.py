@@ -1,0 +1,200 @@
+"""Thin torch-tensor front ends for the C ABI: they only pull out device pointers, leading
+dimensions and the current stream.  torch is plumbing here (memory + streams), not compute.
+
+`LAUNCHES` counts kernels of THIS library enqueued through these wrappers (bench.py reports
+it as `gpu_launches`).
+"""
+from __future__ import annotations
+
+import ctypes
+
+import torch
+
+from . import _lib
+from ._lib import (A_MN_MAJOR, B_MN_MAJOR, EPI_DGELU, EPI_GELU, EPI_NONE, EPI_RESIDUAL, GemmArgs,
+                   check, lib)
+
+LAUNCHES = 0
+
+
+def _p(t):
+    return None if t is None else ctypes.c_void_p(t.data_ptr())
+
+
+def _stream():
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _need_cuda(*ts):
+    for t in ts:
+        if t is not None and not t.is_cuda:
+            raise _lib.B200FTError("b200ft ops take CUDA tensors only (no CPU path exists)")
+
+
+def gemm(a, b, out, *, a_mn=False, b_mn=False, a2=None, b2=None, bias=None, epilogue=EPI_NONE,
+         aux=None, out2=None, alpha=1.0, block_n=0, max_ctas=0, m=None, n=None, k=None, k2=None):
+    """out[m,n] = epi(alpha * (A.B^T + A2.B2^T) + bias).  A: [M,K] (K-major) or [K,M] (a_mn);
+    B: [N,K] or [K,N] (b_mn); A2 [M,K2], B2 [N,K2].  Row pitch = stride(0)."""
+    global LAUNCHES
+    _need_cuda(a, b, out, a2, b2, bias, aux, out2)
+    assert a.dtype == b.dtype == out.dtype == torch.bfloat16
+    assert a.stride(-1) == 1 and b.stride(-1) == 1 and out.stride(-1) == 1
+    if m is None:
+        m = a.shape[1] if a_mn else a.shape[0]
+    if k is None:
+        k = a.shape[0] if a_mn else a.shape[1]
+    if n is None:
+        n = b.shape[1] if b_mn else b.shape[0]
+    kb = b.shape[0] if b_mn else b.shape[1]
+    assert kb >= k or True
+    args = GemmArgs()
+    args.m, args.n = m, n
+    args.a1, args.lda1 = a.data_ptr(), a.stride(0)
+    args.b1, args.ldb1 = b.data_ptr(), b.stride(0)
+    args.k1 = k
+    if a2 is not None:
+        assert a2.dtype == b2.dtype == torch.bfloat16
+        args.a2, args.lda2 = a2.data_ptr(), a2.stride(0)
+        args.b2, args.ldb2 = b2.data_ptr(), b2.stride(0)
+        args.k2 = k2 if k2 is not None else a2.shape[1]
+    args.layout = (A_MN_MAJOR if a_mn else 0) | (B_MN_MAJOR if b_mn else 0)
+    args.epilogue = epilogue
+    args.alpha = alpha
+    if bias is not None:
+        assert bias.dtype == torch.float32
+        args.bias = bias.data_ptr()
+    if aux is not None:
+        args.aux, args.ld_aux = aux.data_ptr(), aux.stride(0)
+    args.c, args.ldc = out.data_ptr(), out.stride(0)
+    if out2 is not None:
+        args.c2, args.ldc2 = out2.data_ptr(), out2.stride(0)
+    args.block_n, args.max_ctas = block_n, max_ctas
+    check(lib().b200ft_gemm_bf16(ctypes.byref(args), _stream()), "gemm_bf16")
+    LAUNCHES += 1
+    return out
+
+
+def lora_grad(s, t, out, *, r, cols, alpha=1.0, m=None):
+    """out[i,c] += alpha * sum_m s[m,i] t[m,c]  (fp32 out, bf16 s/t)."""
+    global LAUNCHES
+    _need_cuda(s, t, out)
+    assert s.dtype == t.dtype == torch.bfloat16 and out.dtype == torch.float32
+    m = s.shape[0] if m is None else m
+    check(lib().b200ft_lora_grad(_p(s), s.stride(0), r, _p(t), t.stride(0), cols, m, _p(out), out.stride(0),
+                                 alpha, _stream()), "lora_grad")
+    LAUNCHES += 1
+    return out
+
+
+def softmax_xent_workspace(rows, device):
+    nbytes = lib().b200ft_softmax_xent_workspace_bytes(rows)
+    return torch.empty(nbytes, dtype=torch.uint8, device=device)
+
+
+def softmax_xent_fwd_bwd(logits, targets, loss_out, workspace, *, vocab, grad_scale=1.0, ignore_index=-100):
+    """In place: logits [rows, ld] bf16 -> d loss / d logits; loss_out[0] = mean loss."""
+    global LAUNCHES
+    _need_cuda(logits, targets, loss_out, workspace)
+    assert logits.dtype == torch.bfloat16 and targets.dtype == torch.int64 and loss_out.dtype == torch.float32
+    rows = logits.shape[0]
+    check(lib().b200ft_softmax_xent_fwd_bwd(_p(logits), rows, vocab, logits.stride(0), _p(targets), ignore_index,
+                                            grad_scale, _p(loss_out), _p(workspace), workspace.numel(),
+                                            _stream()), "softmax_xent_fwd_bwd")
+    LAUNCHES += 2
+    return loss_out
+
+
+def shift_targets(labels, targets, ignore_index=-100):
+    global LAUNCHES
+    _need_cuda(labels, targets)
+    b, t = labels.shape
+    check(lib().b200ft_shift_targets(_p(labels), _p(targets), b, t, ignore_index, _stream()), "shift_targets")
+    LAUNCHES += 1
+    return targets
+
+
+def adamw_step(p, m, v, g, *, step, lr, beta1, beta2, eps, weight_decay, shadow=None, grad_scale=1.0,
+               grad_scale_dev=None):
+    global LAUNCHES
+    _need_cuda(p, m, v, g, shadow, grad_scale_dev)
+    assert p.dtype == m.dtype == v.dtype == torch.float32
+    assert g.dtype in (torch.bfloat16, torch.float32)
+    n = p.numel()
+    assert m.numel() == n and v.numel() == n and g.numel() == n
+    check(lib().b200ft_adamw_step(_p(p), _p(m), _p(v), _p(g), int(g.dtype == torch.bfloat16), _p(shadow), n, lr,
+                                  beta1, beta2, eps, weight_decay, step, grad_scale, _p(grad_scale_dev),
+                                  _stream()), "adamw_step")
+    LAUNCHES += 1
+
+
+def gradnorm_workspace(n, device):
+    return torch.zeros(lib().b200ft_gradnorm_sq_workspace_bytes(n), dtype=torch.uint8, device=device)
+
+
+def gradnorm_sq(g, out_sq, workspace):
+    global LAUNCHES
+    _need_cuda(g, out_sq, workspace)
+    check(lib().b200ft_gradnorm_sq(_p(g), int(g.dtype == torch.bfloat16), g.numel(), _p(out_sq), _p(workspace),
+                                   workspace.numel(), _stream()), "gradnorm_sq")
+    LAUNCHES += 1
+    return out_sq
+
+
+def clip_coef(norm_sq, coef, *, max_norm, pre_scale=1.0):
+    global LAUNCHES
+    check(lib().b200ft_clip_coef(_p(norm_sq), max_norm, pre_scale, _p(coef), _stream()), "clip_coef")
+    LAUNCHES += 1
+    return coef
+
+
+def layernorm_fwd(x, gamma, beta, y, mean, rstd, eps):
+    global LAUNCHES
+    _need_cuda(x, gamma, beta, y, mean, rstd)
+    rows, d = x.shape
+    assert x.is_contiguous() and y.is_contiguous()
+    check(lib().b200ft_layernorm_fwd(_p(x), _p(gamma), _p(beta), _p(y), _p(mean), _p(rstd), rows, d, eps,
+                                     _stream()), "layernorm_fwd")
+    LAUNCHES += 1
+    return y
+
+
+def layernorm_bwd_dx(dy, x, gamma, mean, rstd, dx, dres=None):
+    global LAUNCHES
+    _need_cuda(dy, x, gamma, mean, rstd, dx, dres)
+    rows, d = x.shape
+    assert dy.is_contiguous() and x.is_contiguous() and dx.is_contiguous()
+    check(lib().b200ft_layernorm_bwd_dx(_p(dy), _p(x), _p(gamma), _p(mean), _p(rstd), _p(dres), _p(dx), rows, d,
+                                        _stream()), "layernorm_bwd_dx")
+    LAUNCHES += 1
+    return dx
+
+
+def embed_fwd(ids, wte, wpe, x, *, seq, vocab):
+    global LAUNCHES
+    _need_cuda(ids, wte, wpe, x)
+    rows, d = x.shape
+    assert wte.stride(0) == d and wpe.stride(0) == d
+    check(lib().b200ft_embed_fwd(_p(ids), _p(wte), _p(wpe), _p(x), rows, seq, d, vocab, _stream()), "embed_fwd")
+    LAUNCHES += 1
+    return x
+
+
+def transpose(inp, out, rows=None, cols=None):
+    """out[c, r] = inp[r, c] (bf16)."""
+    global LAUNCHES
+    _need_cuda(inp, out)
+    rows = inp.shape[0] if rows is None else rows
+    cols = inp.shape[1] if cols is None else cols
+    check(lib().b200ft_transpose_bf16(_p(inp), inp.stride(0), _p(out), out.stride(0), rows, cols, _stream()),
+          "transpose_bf16")
+    LAUNCHES += 1
+    return out
+
+
+def cast_f32_to_bf16(inp, out):
+    global LAUNCHES
+    _need_cuda(inp, out)
+    assert inp.dtype == torch.float32 and out.dtype == torch.bfloat16 and inp.numel() == out.numel()
+    check(lib().b200ft_cast_f32_to_bf16(_p(inp), _p(out), inp.numel(), _stream()), "cast_f32_to_bf16")
+    LAUNCHES += 1
+    return out

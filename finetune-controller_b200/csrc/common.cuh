@@ -1,0 +1,125 @@
+// Shared device/host helpers for libb200ft (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#ifndef B200FT_NUM_SMS
+#define B200FT_NUM_SMS 148  // B200: 2 dies x 74 SMs; grids below are sized in multiples of this
+#endif
+
+// ----------------------------------------------------------------------------------
+// error plumbing: nothing throws across the C boundary; the last message is kept
+// per host thread and handed out by b200ft_last_error_string().
+// ----------------------------------------------------------------------------------
+void b200ft_set_error(const char* fmt, ...);
+
+#define B200FT_ERR_ARG (-1)
+#define B200FT_ERR_UNSUPPORTED (-2)
+#define B200FT_ERR_WORKSPACE (-3)
+
+#define B200FT_CHECK_ARG(cond, ...)              \
+  do {                                           \
+    if (!(cond)) {                               \
+      b200ft_set_error(__VA_ARGS__);             \
+      return B200FT_ERR_ARG;                     \
+    }                                            \
+  } while (0)
+
+#define B200FT_CUDA(call)                                                            \
+  do {                                                                               \
+    cudaError_t e__ = (call);                                                        \
+    if (e__ != cudaSuccess) {                                                        \
+      b200ft_set_error("%s failed: %s (%s:%d)", #call, cudaGetErrorString(e__),      \
+                       __FILE__, __LINE__);                                          \
+      return (int)e__;                                                               \
+    }                                                                                \
+  } while (0)
+
+#define B200FT_LAUNCH_CHECK()                                                        \
+  do {                                                                               \
+    cudaError_t e__ = cudaGetLastError();                                            \
+    if (e__ != cudaSuccess) {                                                        \
+      b200ft_set_error("kernel launch failed: %s (%s:%d)", cudaGetErrorString(e__),  \
+                       __FILE__, __LINE__);                                          \
+      return (int)e__;                                                               \
+    }                                                                                \
+  } while (0)
+
+// ----------------------------------------------------------------------------------
+// device helpers
+// ----------------------------------------------------------------------------------
+#ifdef __CUDACC__
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+// 16-byte streaming load / store (data touched once: keep it out of L1)
+__device__ __forceinline__ uint4 ld_stream16(const void* p) {
+  uint4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p));
+  return r;
+}
+__device__ __forceinline__ void st_stream16(void* p, uint4 v) {
+  asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x),
+               "r"(v.y), "r"(v.z), "r"(v.w)
+               : "memory");
+}
+// plain (coherent) 16-byte load: for data another kernel phase of the SAME launch wrote
+__device__ __forceinline__ uint4 ld_cg16(const void* p) {
+  uint4 r;
+  asm volatile("ld.global.cg.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p));
+  return r;
+}
+
+__device__ __forceinline__ float bf16lo(uint32_t w) { return __uint_as_float(w << 16); }
+__device__ __forceinline__ float bf16hi(uint32_t w) { return __uint_as_float(w & 0xffff0000u); }
+__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
+  __nv_bfloat162 t = __floats2bfloat162_rn(lo, hi);  // .x = lo (low 16 bits)
+  return *reinterpret_cast<uint32_t*>(&t);
+}
+__device__ __forceinline__ void unpack8(const uint4& q, float* f) {
+  f[0] = bf16lo(q.x); f[1] = bf16hi(q.x); f[2] = bf16lo(q.y); f[3] = bf16hi(q.y);
+  f[4] = bf16lo(q.z); f[5] = bf16hi(q.z); f[6] = bf16lo(q.w); f[7] = bf16hi(q.w);
+}
+__device__ __forceinline__ uint4 pack8(const float* f) {
+  uint4 q;
+  q.x = pack_bf16x2(f[0], f[1]); q.y = pack_bf16x2(f[2], f[3]);
+  q.z = pack_bf16x2(f[4], f[5]); q.w = pack_bf16x2(f[6], f[7]);
+  return q;
+}
+
+__device__ __forceinline__ float tanh_approx(float x) {
+  float y;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+// GPT-2 "gelu_new" and its derivative (tanh form)
+__device__ __forceinline__ float gelu_new_f(float x) {
+  const float k0 = 0.7978845608028654f, k1 = 0.044715f;
+  float t = tanh_approx(k0 * (x + k1 * x * x * x));
+  return 0.5f * x * (1.f + t);
+}
+__device__ __forceinline__ float gelu_new_grad_f(float x) {
+  const float k0 = 0.7978845608028654f, k1 = 0.044715f;
+  float x2 = x * x;
+  float t = tanh_approx(k0 * (x + k1 * x * x2));
+  float dt = (1.f - t * t) * k0 * (1.f + 3.f * k1 * x2);
+  return 0.5f * (1.f + t) + 0.5f * x * dt;
+}
+
+#endif  // __CUDACC__

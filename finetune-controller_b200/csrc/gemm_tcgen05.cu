@@ -1,0 +1,493 @@
+// bf16 GEMM on Blackwell 5th-gen tensor cores: TMA -> shared memory (128B swizzle) ->
+// tcgen05.mma (fp32 accumulators in TMEM) -> tcgen05.ld epilogue.
+//
+// Persistent, warp-specialised, one CTA per SM (256 threads):
+//   warp 0 : TMA producer (one lane)          smem ring of kStages {A 128x64, B BNx64} slabs
+//   warp 1 : MMA issuer (one lane)            128 x BN x 16 UMMAs, 4 per K slab
+//   warp 2 : TMEM allocator (512 columns = two 128 x 256 fp32 accumulators)
+//   warps 4-7 : epilogue, one TMEM lane quarter each; runs on accumulator `a` while the MMA
+//               warp fills accumulator `a^1` for the next tile.
+// Three mbarrier pipelines: smem full/empty (TMA <-> MMA), TMEM full/empty (MMA <-> epilogue).
+//
+// The K loop runs over up to two operand segments.  Segment 2 is how a LoRA branch is
+// fused: A2 = s*(X*A_lora) [M, r_pad], B2 = B_lora^T [N, r_pad] accumulate into the same
+// TMEM tile as the frozen projection, and only ceil(r_pad/16) UMMAs are issued for it.
+//
+// Operand layouts.  K-major (reduction index contiguous): one TMA box of {64 k, rows} per slab,
+// UMMA descriptor SW128 / SBO = 1024 B, K advance = 32 B inside the swizzle row.  MN-major
+// (M or N index contiguous): TMA boxes of {64 mn, 64 k} (8 KB each), UMMA descriptor SW128 /
+// LBO = 8192 B between 64-wide MN chunks / SBO = 1024 B between 8-row K groups, K advance =
+// 2048 B.  Descriptor bit layouts follow the PTX ISA "tcgen05 matrix / instruction descriptor"
+// tables.
+#include <cuda.h>
+#include <map>
+#include <mutex>
+#include <tuple>
+#include "common.cuh"
+#include "../../include/b200ft.h"
+
+namespace {
+
+constexpr int kBlockM = 128;
+constexpr int kBlockK = 64;  // 64 bf16 = 128 B = one swizzle row
+constexpr int kMaxBN = 256;
+constexpr int kStages = 4;
+constexpr int kAStageBytes = kBlockM * kBlockK * 2;  // 16 KB
+constexpr int kBStageBytes = kMaxBN * kBlockK * 2;   // 32 KB
+constexpr int kTileBytes = kStages * (kAStageBytes + kBStageBytes);
+constexpr int kBarrierBytes = 256;
+constexpr int kSmemBytes = kTileBytes + kBarrierBytes + 1024;  // + slack to align to 1024
+constexpr int kThreads = 256;
+constexpr int kTmemCols = 512;
+constexpr int kAccStride = 256;  // TMEM columns per accumulator stage
+constexpr long long kWaitLimitCycles = 4000000000ll;  // ~2 s: deadlock guard, trap instead of hanging the GPU
+
+struct GemmParams {
+  int M, N, BN;
+  int k1, k2, kblocks1, kblocks2;
+  int a_mn, b_mn;
+  int tiles_m, tiles_n;
+  int epilogue;
+  float alpha;
+  const float* bias;
+  const __nv_bfloat16* aux; int64_t ld_aux;
+  __nv_bfloat16* c; int64_t ldc;
+  __nv_bfloat16* c2; int64_t ldc2;
+};
+
+// ---------------------------------------------------------------------------------------
+// PTX wrappers
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  uint32_t done = 0;
+  long long t0 = 0;
+  while (true) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    if (done) break;
+    if (t0 == 0) t0 = clock64();
+    else if (clock64() - t0 > kWaitLimitCycles) __trap();
+  }
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, int c0, int c1, uint32_t bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+      ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(c0), "r"(c1), "r"(bar)
+      : "memory");
+}
+__device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* map) {
+  asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(map)) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tmem_alloc(uint32_t smem_dst, uint32_t ncols) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_dst), "r"(ncols) : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t* r) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// shared-memory matrix descriptor (PTX ISA, tcgen05 "matrix descriptor"): start>>4 [0,14),
+// LBO>>4 [16,30), SBO>>4 [32,46), version=1 [46,48), swizzle mode [61,64) (2 = 128B)
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  uint64_t d = 0;
+  d |= (uint64_t)((addr & 0x3FFFFu) >> 4);
+  d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFFu) << 16;
+  d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFFu) << 32;
+  d |= 1ull << 46;
+  d |= 2ull << 61;
+  return d;
+}
+// instruction descriptor (kind::f16): D fp32 [4,6)=1, A bf16 [7,10)=1, B bf16 [10,13)=1,
+// A major [15], B major [16] (1 = MN-major), N>>3 [17,23), M>>4 [24,29)
+__device__ __forceinline__ uint32_t make_idesc(int n, int a_mn, int b_mn) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)a_mn << 15) | ((uint32_t)b_mn << 16) |
+         ((uint32_t)(n >> 3) << 17) | ((uint32_t)(kBlockM >> 4) << 24);
+}
+
+// ---------------------------------------------------------------------------------------
+// the kernel
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreads, 1)
+gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmB1,
+                         const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmB2,
+                         const GemmParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw = smem_u32(smem_raw);
+  const uint32_t base = (raw + 1023u) & ~1023u;
+  const uint32_t sA = base;
+  const uint32_t sB = base + kStages * kAStageBytes;
+  const uint32_t bars = base + kTileBytes;
+  auto full_bar = [&](int s) { return bars + 8u * s; };
+  auto empty_bar = [&](int s) { return bars + 8u * (kStages + s); };
+  auto tfull_bar = [&](int a) { return bars + 8u * (2 * kStages + a); };
+  auto tempty_bar = [&](int a) { return bars + 8u * (2 * kStages + 2 + a); };
+  const uint32_t tmem_slot = bars + 8u * (2 * kStages + 4);
+  volatile uint32_t* tmem_slot_ptr =
+      reinterpret_cast<volatile uint32_t*>(smem_raw + (base - raw) + kTileBytes + 8 * (2 * kStages + 4));
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA1);
+    tma_prefetch_desc(&tmB1);
+    if (p.kblocks2 > 0) { tma_prefetch_desc(&tmA2); tma_prefetch_desc(&tmB2); }
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < kStages; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
+    for (int a = 0; a < 2; ++a) { mbar_init(tfull_bar(a), 1); mbar_init(tempty_bar(a), 4); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 2) tmem_alloc(tmem_slot, kTmemCols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot_ptr;
+
+  const int num_tiles = p.tiles_m * p.tiles_n;
+  const int kb_total = p.kblocks1 + p.kblocks2;
+  const int BN = p.BN;
+
+  if (warp == 0) {
+    // =============================== TMA producer ===============================
+    if (lane == 0) {
+      const uint32_t b_bytes = p.b_mn ? (uint32_t)((BN + 63) / 64) * 8192u : (uint32_t)BN * 128u;
+      const uint32_t b2_bytes = (uint32_t)BN * 128u;
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int m0 = (tile / p.tiles_n) * kBlockM;
+        const int n0 = (tile % p.tiles_n) * BN;
+        for (int kb = 0; kb < kb_total; ++kb) {
+          mbar_wait(empty_bar(stage), phase ^ 1u);
+          const bool seg2 = kb >= p.kblocks1;
+          const int kk = (seg2 ? kb - p.kblocks1 : kb) * kBlockK;
+          const uint32_t a_dst = sA + stage * kAStageBytes;
+          const uint32_t b_dst = sB + stage * kBStageBytes;
+          const uint32_t fb = full_bar(stage);
+          mbar_expect_tx(fb, (uint32_t)kAStageBytes + (seg2 ? b2_bytes : b_bytes));
+          if (seg2) {
+            tma_load_2d(a_dst, &tmA2, kk, m0, fb);
+            tma_load_2d(b_dst, &tmB2, kk, n0, fb);
+          } else {
+            if (p.a_mn) {
+              tma_load_2d(a_dst, &tmA1, m0, kk, fb);
+              tma_load_2d(a_dst + 8192u, &tmA1, m0 + 64, kk, fb);
+            } else {
+              tma_load_2d(a_dst, &tmA1, kk, m0, fb);
+            }
+            if (p.b_mn) {
+              for (int j = 0; j * 64 < BN; ++j) tma_load_2d(b_dst + 8192u * j, &tmB1, n0 + 64 * j, kk, fb);
+            } else {
+              tma_load_2d(b_dst, &tmB1, kk, n0, fb);
+            }
+          }
+          if (++stage == kStages) { stage = 0; phase ^= 1u; }
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // =============================== MMA issuer ===============================
+    if (lane == 0) {
+      const uint32_t idesc1 = make_idesc(BN, p.a_mn, p.b_mn);
+      const uint32_t idesc2 = make_idesc(BN, 0, 0);
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        mbar_wait(tempty_bar(acc), acc_phase ^ 1u);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + (uint32_t)(acc * kAccStride);
+        for (int kb = 0; kb < kb_total; ++kb) {
+          mbar_wait(full_bar(stage), phase);
+          tc_fence_after();
+          const bool seg2 = kb >= p.kblocks1;
+          const int kk = (seg2 ? kb - p.kblocks1 : kb) * kBlockK;
+          const int kleft = (seg2 ? p.k2 : p.k1) - kk;
+          const int nmma = kleft >= kBlockK ? 4 : (kleft + 15) / 16;
+          const bool amn = !seg2 && p.a_mn, bmn = !seg2 && p.b_mn;
+          const uint32_t a_base = sA + stage * kAStageBytes;
+          const uint32_t b_base = sB + stage * kBStageBytes;
+          const uint32_t idesc = seg2 ? idesc2 : idesc1;
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            if (j < nmma) {
+              const uint64_t ad = amn ? make_smem_desc(a_base + 2048u * j, 8192u, 1024u)
+                                      : make_smem_desc(a_base + 32u * j, 16u, 1024u);
+              const uint64_t bd = bmn ? make_smem_desc(b_base + 2048u * j, 8192u, 1024u)
+                                      : make_smem_desc(b_base + 32u * j, 16u, 1024u);
+              umma_bf16(d_tmem, ad, bd, idesc, (kb > 0 || j > 0) ? 1u : 0u);
+            }
+          }
+          umma_commit(empty_bar(stage));  // frees the smem slot when these MMAs retire
+          if (++stage == kStages) { stage = 0; phase ^= 1u; }
+        }
+        umma_commit(tfull_bar(acc));  // accumulator complete -> epilogue
+        acc ^= 1;
+        if (acc == 0) acc_phase ^= 1u;
+      }
+    }
+    __syncwarp();
+  } else if (warp >= 4) {
+    // =============================== epilogue ===============================
+    const int q = warp - 4;  // TMEM lane quarter == warp % 4
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      const int m0 = (tile / p.tiles_n) * kBlockM;
+      const int n0 = (tile % p.tiles_n) * BN;
+      mbar_wait(tfull_bar(acc), acc_phase);
+      tc_fence_after();
+      const int row = m0 + q * 32 + lane;
+      const bool row_ok = row < p.M;
+      const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * kAccStride);
+      for (int c = 0; c < BN; c += 32) {
+        uint32_t r[32];
+        tmem_ld16(t_row + c, r);
+        const bool second = (c + 16 < BN);
+        if (second) tmem_ld16(t_row + c + 16, r + 16);
+        tmem_wait_ld();
+        const int nvec = second ? 4 : 2;
+#pragma unroll
+        for (int v = 0; v < 4; ++v) {
+          if (v < nvec) {
+            const int col = n0 + c + v * 8;
+            if (row_ok && col < p.N) {
+              float f[8];
+#pragma unroll
+              for (int j = 0; j < 8; ++j) f[j] = __uint_as_float(r[v * 8 + j]) * p.alpha;
+              if (p.bias) {
+                const float4 b0 = __ldg(reinterpret_cast<const float4*>(p.bias + col));
+                const float4 b1 = __ldg(reinterpret_cast<const float4*>(p.bias + col + 4));
+                f[0] += b0.x; f[1] += b0.y; f[2] += b0.z; f[3] += b0.w;
+                f[4] += b1.x; f[5] += b1.y; f[6] += b1.z; f[7] += b1.w;
+              }
+              if (p.epilogue == B200FT_EPI_RESIDUAL) {
+                float a[8];  // plain (coherent) load: aux may alias c for an in-place residual add
+                unpack8(*reinterpret_cast<const uint4*>(p.aux + (int64_t)row * p.ld_aux + col), a);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) f[j] += a[j];
+              } else if (p.epilogue == B200FT_EPI_DGELU) {
+                float a[8];
+                unpack8(ld_stream16(p.aux + (int64_t)row * p.ld_aux + col), a);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) f[j] *= gelu_new_grad_f(a[j]);
+              }
+              *reinterpret_cast<uint4*>(p.c + (int64_t)row * p.ldc + col) = pack8(f);
+              if (p.epilogue == B200FT_EPI_GELU) {
+                // gelu of the bf16-ROUNDED pre-activation, so that backward (which only has
+                // the stored bf16 value) differentiates exactly the function applied here
+                float g[8];
+                unpack8(pack8(f), g);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) g[j] = gelu_new_f(g[j]);
+                *reinterpret_cast<uint4*>(p.c2 + (int64_t)row * p.ldc2 + col) = pack8(g);
+              }
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(tempty_bar(acc));
+      acc ^= 1;
+      if (acc == 0) acc_phase ^= 1u;
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, kTmemCols);
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// host side: TMA descriptors (cached), tile-shape choice, launch
+// ---------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
+                                  CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                  CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* f = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = (EncodeTiledFn)f;
+  });
+  return fn;
+}
+
+using MapKey = std::tuple<const void*, uint64_t, uint64_t, uint64_t, uint32_t, uint32_t>;
+std::mutex g_map_mu;
+std::map<MapKey, CUtensorMap> g_maps;
+
+// 2-D bf16 tensor {inner, outer} with row pitch ld (elements), box {box_inner, box_outer}, SW128
+int get_tensor_map(const void* ptr, uint64_t inner, uint64_t outer, uint64_t ld, uint32_t box_inner,
+                   uint32_t box_outer, CUtensorMap* out) {
+  MapKey key{ptr, inner, outer, ld, box_inner, box_outer};
+  {
+    std::lock_guard<std::mutex> lk(g_map_mu);
+    auto it = g_maps.find(key);
+    if (it != g_maps.end()) { *out = it->second; return 0; }
+  }
+  EncodeTiledFn enc = get_encode_fn();
+  if (!enc) { b200ft_set_error("gemm: cuTensorMapEncodeTiled unavailable (no CUDA driver?)"); return B200FT_ERR_UNSUPPORTED; }
+  cuuint64_t dims[2] = {inner, outer};
+  cuuint64_t strides[1] = {ld * 2};
+  cuuint32_t box[2] = {box_inner, box_outer};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    b200ft_set_error("gemm: cuTensorMapEncodeTiled failed (%d) ptr=%p dims=(%llu,%llu) ld=%llu box=(%u,%u)", (int)r,
+                     ptr, (unsigned long long)inner, (unsigned long long)outer, (unsigned long long)ld, box_inner,
+                     box_outer);
+    return B200FT_ERR_ARG;
+  }
+  std::lock_guard<std::mutex> lk(g_map_mu);
+  if (g_maps.size() > 4096) g_maps.clear();
+  g_maps[key] = *out;
+  return 0;
+}
+
+int choose_block_n(int M, int N, int ctas) {
+  if (N <= kMaxBN) return (N + 15) / 16 * 16;
+  const int tiles_m = (M + kBlockM - 1) / kBlockM;
+  int best = 256;
+  long best_cost = -1;
+  for (int bn : {256, 192, 128}) {
+    long tiles = (long)tiles_m * ((N + bn - 1) / bn);
+    long waves = (tiles + ctas - 1) / ctas;
+    long cost = waves * (bn + 24);  // + fixed per-tile overhead (pipeline fill, epilogue tail)
+    if (best_cost < 0 || cost < best_cost) { best_cost = cost; best = bn; }
+  }
+  return best;
+}
+
+}  // namespace
+
+extern "C" int b200ft_gemm_bf16(const b200ft_gemm_args* a, void* stream) {
+  B200FT_CHECK_ARG(a != nullptr, "gemm: null args");
+  B200FT_CHECK_ARG(a->m > 0 && a->n > 0 && a->k1 > 0, "gemm: m=%d n=%d k1=%d", a->m, a->n, a->k1);
+  B200FT_CHECK_ARG(a->a1 && a->b1 && a->c, "gemm: null operand");
+  B200FT_CHECK_ARG(a->n % 8 == 0 && a->ldc % 8 == 0 && a->ldc >= a->n, "gemm: n=%d ldc=%lld must be multiples of 8", a->n,
+                   (long long)a->ldc);
+  B200FT_CHECK_ARG(a->lda1 % 8 == 0 && a->ldb1 % 8 == 0, "gemm: lda1=%lld ldb1=%lld must be multiples of 8",
+                   (long long)a->lda1, (long long)a->ldb1);
+  B200FT_CHECK_ARG(((uintptr_t)a->a1 | (uintptr_t)a->b1 | (uintptr_t)a->c) % 16 == 0, "gemm: 16-byte alignment required");
+  const bool seg2 = a->a2 != nullptr;
+  if (seg2) {
+    B200FT_CHECK_ARG(a->b2 && a->k2 > 0 && a->lda2 % 8 == 0 && a->ldb2 % 8 == 0 &&
+                         ((uintptr_t)a->a2 | (uintptr_t)a->b2) % 16 == 0,
+                     "gemm: bad second segment (k2=%d lda2=%lld ldb2=%lld)", a->k2, (long long)a->lda2,
+                     (long long)a->ldb2);
+  }
+  B200FT_CHECK_ARG(a->epilogue >= 0 && a->epilogue <= 3, "gemm: epilogue=%d", a->epilogue);
+  if (a->epilogue == B200FT_EPI_RESIDUAL || a->epilogue == B200FT_EPI_DGELU)
+    B200FT_CHECK_ARG(a->aux && a->ld_aux % 8 == 0 && (uintptr_t)a->aux % 16 == 0, "gemm: epilogue needs aux");
+  if (a->epilogue == B200FT_EPI_GELU)
+    B200FT_CHECK_ARG(a->c2 && a->ldc2 % 8 == 0 && (uintptr_t)a->c2 % 16 == 0, "gemm: GELU epilogue needs c2");
+  if (a->bias) B200FT_CHECK_ARG((uintptr_t)a->bias % 16 == 0, "gemm: bias must be 16-byte aligned");
+
+  const int ctas_max = a->max_ctas > 0 ? a->max_ctas : B200FT_NUM_SMS;
+  int BN = a->block_n > 0 ? a->block_n : choose_block_n(a->m, a->n, ctas_max);
+  B200FT_CHECK_ARG(BN % 16 == 0 && BN >= 16 && BN <= kMaxBN, "gemm: block_n=%d", BN);
+
+  GemmParams p;
+  memset(&p, 0, sizeof(p));
+  p.M = a->m; p.N = a->n; p.BN = BN;
+  p.k1 = a->k1; p.k2 = seg2 ? a->k2 : 0;
+  p.kblocks1 = (a->k1 + kBlockK - 1) / kBlockK;
+  p.kblocks2 = seg2 ? (a->k2 + kBlockK - 1) / kBlockK : 0;
+  p.a_mn = (a->layout & B200FT_A_MN_MAJOR) ? 1 : 0;
+  p.b_mn = (a->layout & B200FT_B_MN_MAJOR) ? 1 : 0;
+  p.tiles_m = (a->m + kBlockM - 1) / kBlockM;
+  p.tiles_n = (a->n + BN - 1) / BN;
+  p.epilogue = a->epilogue;
+  p.alpha = a->alpha;
+  p.bias = a->bias;
+  p.aux = (const __nv_bfloat16*)a->aux; p.ld_aux = a->ld_aux;
+  p.c = (__nv_bfloat16*)a->c; p.ldc = a->ldc;
+  p.c2 = (__nv_bfloat16*)a->c2; p.ldc2 = a->ldc2;
+
+  CUtensorMap tA1, tB1, tA2, tB2;
+  int rc;
+  if (p.a_mn) rc = get_tensor_map(a->a1, (uint64_t)a->m, (uint64_t)a->k1, (uint64_t)a->lda1, 64, 64, &tA1);
+  else        rc = get_tensor_map(a->a1, (uint64_t)a->k1, (uint64_t)a->m, (uint64_t)a->lda1, 64, kBlockM, &tA1);
+  if (rc) return rc;
+  if (p.b_mn) rc = get_tensor_map(a->b1, (uint64_t)a->n, (uint64_t)a->k1, (uint64_t)a->ldb1, 64, 64, &tB1);
+  else        rc = get_tensor_map(a->b1, (uint64_t)a->k1, (uint64_t)a->n, (uint64_t)a->ldb1, 64, (uint32_t)BN, &tB1);
+  if (rc) return rc;
+  if (seg2) {
+    rc = get_tensor_map(a->a2, (uint64_t)a->k2, (uint64_t)a->m, (uint64_t)a->lda2, 64, kBlockM, &tA2);
+    if (rc) return rc;
+    rc = get_tensor_map(a->b2, (uint64_t)a->k2, (uint64_t)a->n, (uint64_t)a->ldb2, 64, (uint32_t)BN, &tB2);
+    if (rc) return rc;
+  } else {
+    tA2 = tA1; tB2 = tB1;
+  }
+
+  // the opt-in shared-memory size is a per-device function attribute
+  static thread_local int attr_dev = -1;
+  int dev = -1;
+  B200FT_CUDA(cudaGetDevice(&dev));
+  if (dev != attr_dev) {
+    B200FT_CUDA(cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+    attr_dev = dev;
+  }
+  const int num_tiles = p.tiles_m * p.tiles_n;
+  const int grid = num_tiles < ctas_max ? num_tiles : ctas_max;
+  gemm_bf16_tcgen05_kernel<<<grid, kThreads, kSmemBytes, (cudaStream_t)stream>>>(tA1, tB1, tA2, tB2, p);
+  B200FT_LAUNCH_CHECK();
+  return 0;
+}

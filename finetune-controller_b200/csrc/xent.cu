@@ -1,0 +1,203 @@
+// Fused softmax-cross-entropy forward + backward over bf16 logits, in place.
+//
+// One CTA per row.  Sweep 1 streams the row from HBM with 16-byte loads keeping an online
+// (max, sum-of-exp2) pair per thread, folded with warp shuffles and one shared-memory hop.
+// Sweep 2 re-reads the row (it is still in the 126 MB L2: 148 SMs x resident CTAs x 100 KB)
+// and overwrites it with (softmax - onehot) * grad_scale / n_valid.  Algorithmic HBM traffic is
+// therefore one read + one write of the row: 2*rows*ld*2 bytes, plus 12 bytes per row.
+//
+// Scratch (the caller's workspace): [0] number of valid targets, [1] completion ticket,
+// [16 .. 16+rows) per-row losses.  The last CTA to finish folds the row losses in a fixed
+// order, so the loss is bit-reproducible from run to run.
+#include "common.cuh"
+#include "../../include/b200ft.h"
+
+namespace {
+
+constexpr int kThreads = 256;
+constexpr float kLog2e = 1.4426950408889634f;
+constexpr float kLn2 = 0.6931471805599453f;
+
+__global__ void __launch_bounds__(256)
+count_valid_kernel(const int64_t* __restrict__ targets, int64_t rows, int64_t ignore_index,
+                   unsigned int* __restrict__ ws) {
+  // single CTA: rows is at most a few 10^5, this is ~1 us and keeps the count exact
+  unsigned int c = 0;
+  for (int64_t i = threadIdx.x; i < rows; i += blockDim.x) c += (targets[i] != ignore_index);
+  __shared__ unsigned int red[8];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = c;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    unsigned int t = 0;
+    for (int w = 0; w < 8; ++w) t += red[w];
+    ws[0] = t;
+    ws[1] = 0;  // ticket
+  }
+}
+
+struct MS { float m, s; };
+__device__ __forceinline__ MS ms_merge(MS a, MS b) {
+  float M = fmaxf(a.m, b.m);
+  MS r;
+  r.m = M;
+  // guard (-inf) - (-inf): a fully masked partial contributes 0
+  float ea = (a.m == -INFINITY) ? 0.f : exp2f(a.m - M);
+  float eb = (b.m == -INFINITY) ? 0.f : exp2f(b.m - M);
+  r.s = a.s * ea + b.s * eb;
+  return r;
+}
+
+__global__ void __launch_bounds__(kThreads)
+softmax_xent_kernel(__nv_bfloat16* __restrict__ logits, int64_t rows, int vocab, int64_t ld,
+                    const int64_t* __restrict__ targets, int64_t ignore_index, float grad_scale,
+                    float* __restrict__ loss_out, unsigned int* __restrict__ ws) {
+  const int64_t row = blockIdx.x;
+  __nv_bfloat16* z = logits + row * ld;
+  const int nvec = (int)(ld >> 3);  // the whole padded row is rewritten
+  const int64_t tgt = targets[row];
+  const bool valid = (tgt != ignore_index);
+  float* row_loss = reinterpret_cast<float*>(ws + 16);
+  __shared__ MS red[kThreads / 32];
+  __shared__ float s_lse2;
+  __shared__ bool s_last;
+
+  if (valid) {
+    // ---- sweep 1: online max / sum in the log2 domain ----
+    MS acc{-INFINITY, 0.f};
+    for (int i = threadIdx.x; i < nvec; i += kThreads) {
+      float f[8];
+      unpack8(ld_cg16(z + ((int64_t)i << 3)), f);
+      const int c0 = i << 3;
+      float vmax = -INFINITY;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        f[j] = (c0 + j < vocab) ? f[j] * kLog2e : -INFINITY;
+        vmax = fmaxf(vmax, f[j]);
+      }
+      if (vmax > acc.m) {  // rare after the first few vectors
+        acc.s *= exp2f(acc.m - vmax);  // exp2f(-inf) = 0 on the first hit
+        acc.m = vmax;
+      }
+      if (acc.m != -INFINITY) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc.s += exp2f(f[j] - acc.m);
+      }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      MS other;
+      other.m = __shfl_xor_sync(0xffffffffu, acc.m, o);
+      other.s = __shfl_xor_sync(0xffffffffu, acc.s, o);
+      acc = ms_merge(acc, other);
+    }
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      MS t = red[0];
+      for (int w = 1; w < kThreads / 32; ++w) t = ms_merge(t, red[w]);
+      float lse2 = t.m + log2f(t.s);
+      s_lse2 = lse2;
+      float zt = __bfloat162float(z[tgt]) * kLog2e;
+      row_loss[row] = (lse2 - zt) * kLn2;
+    }
+    __syncthreads();
+  } else if (threadIdx.x == 0) {
+    row_loss[row] = 0.f;
+  }
+
+  // ---- sweep 2: write the gradient in place ----
+  const unsigned int n_valid = ws[0];
+  const float scale = valid ? grad_scale / (float)(n_valid > 0 ? n_valid : 1) : 0.f;
+  const float lse2 = valid ? s_lse2 : 0.f;
+  const int tcol = valid ? (int)tgt : -1;
+  for (int i = threadIdx.x; i < nvec; i += kThreads) {
+    __nv_bfloat16* pz = z + ((int64_t)i << 3);
+    float f[8];
+    if (valid) {
+      unpack8(ld_cg16(pz), f);
+      const int c0 = i << 3;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float p = exp2f(f[j] * kLog2e - lse2);
+        p = (c0 + j == tcol) ? p - 1.f : p;
+        f[j] = (c0 + j < vocab) ? p * scale : 0.f;
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) f[j] = 0.f;
+    }
+    st_stream16(pz, pack8(f));
+  }
+
+  // ---- last CTA folds the per-row losses ----
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    s_last = (atomicAdd(ws + 1, 1u) == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (s_last) {
+    __threadfence();
+    float t = 0.f;
+    for (int64_t i = threadIdx.x; i < rows; i += kThreads) t += __ldcg(row_loss + i);
+    t = warp_sum(t);
+    __shared__ float fr[kThreads / 32];
+    if ((threadIdx.x & 31) == 0) fr[threadIdx.x >> 5] = t;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      float sum = 0.f;
+      for (int w = 0; w < kThreads / 32; ++w) sum += fr[w];
+      loss_out[0] = sum / (float)(n_valid > 0 ? n_valid : 1);
+    }
+  }
+}
+
+__global__ void shift_targets_kernel(const int64_t* __restrict__ labels, int64_t* __restrict__ targets,
+                                     int64_t total, int seq, int64_t ignore_index) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= total) return;
+  int t = (int)(i % seq);
+  targets[i] = (t == seq - 1) ? ignore_index : labels[i + 1];
+}
+
+}  // namespace
+
+extern "C" size_t b200ft_softmax_xent_workspace_bytes(int64_t rows) {
+  return (size_t)(rows + 16) * sizeof(float);
+}
+
+extern "C" int b200ft_softmax_xent_fwd_bwd(void* logits, int64_t rows, int vocab, int64_t ld,
+                                           const int64_t* targets, int64_t ignore_index,
+                                           float grad_scale, float* loss_out, void* workspace,
+                                           size_t workspace_bytes, void* stream) {
+  B200FT_CHECK_ARG(logits && targets && loss_out && workspace, "softmax_xent: null buffer");
+  B200FT_CHECK_ARG(rows > 0 && rows < (1ll << 31) && vocab > 0 && ld >= vocab && ld % 8 == 0,
+                   "softmax_xent: rows=%lld vocab=%d ld=%lld (ld must be a multiple of 8 and >= vocab)",
+                   (long long)rows, vocab, (long long)ld);
+  B200FT_CHECK_ARG((uintptr_t)logits % 16 == 0, "softmax_xent: logits must be 16-byte aligned");
+  if (workspace_bytes < b200ft_softmax_xent_workspace_bytes(rows)) {
+    b200ft_set_error("softmax_xent: workspace %zu < %zu", workspace_bytes,
+                     b200ft_softmax_xent_workspace_bytes(rows));
+    return B200FT_ERR_WORKSPACE;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  unsigned int* ws = (unsigned int*)workspace;
+  count_valid_kernel<<<1, 256, 0, st>>>(targets, rows, ignore_index, ws);
+  B200FT_LAUNCH_CHECK();
+  softmax_xent_kernel<<<(unsigned)rows, kThreads, 0, st>>>((__nv_bfloat16*)logits, rows, vocab, ld, targets,
+                                                           ignore_index, grad_scale, loss_out, ws);
+  B200FT_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int b200ft_shift_targets(const int64_t* labels, int64_t* targets, int64_t batch, int seq,
+                                    int64_t ignore_index, void* stream) {
+  B200FT_CHECK_ARG(labels && targets && batch > 0 && seq > 0, "shift_targets: bad arguments");
+  int64_t total = batch * seq;
+  shift_targets_kernel<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+      labels, targets, total, seq, ignore_index);
+  B200FT_LAUNCH_CHECK();
+  return 0;
+}

@@ -1,0 +1,163 @@
+/*
+ * libb200ft — C ABI of the B200-native fine-tuning step.
+ *
+ * What this boundary replaces.  The reference (acceleratedscience/finetune-controller) has
+ * no FFI and no compute code: its model plugin names a container image and a shell command
+ * (reference app/models/base/finetuning.py:51-108, app/models/examples/mnist.py:41-99) and
+ * app/jobs/kubeflow/PyTorchJobDeployer.py:93-119 runs that command in the "pytorch"
+ * container.  The arithmetic the command performs lives in an external image that is absent
+ * from the reference tree, so there is no reference symbol to bind one-to-one.  Each entry
+ * point below therefore cites the op of the training step it implements (the row of
+ * SURVEY.md §8(a2), restated on CPU in oracle/gpt2_lora_ref.py) instead of a reference
+ * function; INTEGRATION.md shows the ctypes binding the payload uses.
+ *
+ * Conventions (all entry points):
+ *   - return 0 on success; a negative B200FT_ERR_* for rejected arguments; a positive
+ *     cudaError_t for a CUDA failure.  b200ft_last_error_string() describes the last failure
+ *     on the calling host thread.  Nothing throws across the boundary.
+ *   - every pointer is a DEVICE pointer unless its name ends in _host.  The caller owns all
+ *     memory; the library allocates none on the device.  Scratch is passed in as
+ *     (workspace, workspace_bytes) sized by the matching *_workspace_bytes().
+ *   - `stream` is a cudaStream_t passed as void*; work is enqueued and the call returns
+ *     without synchronising.
+ *   - bf16 tensors are row-major with an explicit leading dimension in ELEMENTS; bases are
+ *     16-byte aligned and leading dimensions are multiples of 8 elements.
+ *   - there is no CPU fallback: on a machine without an sm_100 GPU the calls fail.
+ */
+#ifndef B200FT_H_
+#define B200FT_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200FT_ERR_ARG (-1)
+#define B200FT_ERR_UNSUPPORTED (-2)
+#define B200FT_ERR_WORKSPACE (-3)
+
+/* library identity / diagnostics */
+const char* b200ft_version(void);
+const char* b200ft_last_error_string(void);
+
+/* ---------------------------------------------------------------------------------------
+ * Projection / LoRA GEMM on tcgen05 tensor cores (SURVEY.md §8 a2.1, a2.2, a2.3, a2.5;
+ * oracle/gpt2_lora_ref.py:_linear and its autograd transpose).
+ *
+ *   acc[m,n] = sum_{k<k1} A1[m,k]*B1[n,k]  +  sum_{k<k2} A2[m,k]*B2[n,k]      (fp32 in TMEM)
+ *   v        = alpha*acc + bias[n]
+ *   epilogue NONE     : C = v
+ *            RESIDUAL : C = v + AUX[m,n]
+ *            GELU     : C = v, C2 = gelu_new(v)
+ *            DGELU    : C = v * gelu_new'(AUX[m,n])
+ *
+ * The second K segment is how a LoRA branch is fused: with A2 = s*(X*A_lora) and
+ * B2 = B_lora^T it adds the rank-r product into the same TMEM accumulator as the frozen
+ * projection.  Operands are bf16.  "K-major" = the reduction index is contiguous
+ * (A: [M, lda], B: [N, ldb]); "MN-major" = the M (resp. N) index is contiguous
+ * (A: [K, lda], B: [K, ldb]).  Segment 2 is always K-major.
+ * ------------------------------------------------------------------------------------- */
+enum {
+  B200FT_EPI_NONE = 0,
+  B200FT_EPI_RESIDUAL = 1,
+  B200FT_EPI_GELU = 2,
+  B200FT_EPI_DGELU = 3
+};
+enum { B200FT_A_MN_MAJOR = 1, B200FT_B_MN_MAJOR = 2 };
+
+typedef struct b200ft_gemm_args {
+  int32_t m, n;
+  const void* a1; int64_t lda1;
+  const void* b1; int64_t ldb1;
+  int32_t k1;
+  const void* a2; int64_t lda2;   /* NULL when there is no second segment */
+  const void* b2; int64_t ldb2;
+  int32_t k2;
+  int32_t layout;                 /* B200FT_A_MN_MAJOR | B200FT_B_MN_MAJOR, segment 1 only */
+  int32_t epilogue;               /* B200FT_EPI_* */
+  float alpha;
+  const float* bias;              /* [n] fp32 or NULL */
+  const void* aux; int64_t ld_aux;/* bf16 [m, ld_aux] for RESIDUAL / DGELU */
+  void* c; int64_t ldc;           /* bf16 [m, ldc] */
+  void* c2; int64_t ldc2;         /* bf16 [m, ldc2], GELU only */
+  int32_t block_n;                /* 0 = choose; else multiple of 16 in [16,256] */
+  int32_t max_ctas;               /* 0 = one per SM */
+} b200ft_gemm_args;
+
+int b200ft_gemm_bf16(const b200ft_gemm_args* args_host, void* stream);
+
+/* ---------------------------------------------------------------------------------------
+ * Adapter-gradient contraction over tokens (dB = s*(XA)^T*dY,
+ * dA = X^T*(s*dY*B^T)):   out[i, c] += alpha * sum_m S[m, i] * T[m, c],  i < r, c < cols.
+ * S, T bf16; out fp32 [r, ld_out], accumulated into (zero it first).  r <= 16.
+ * ------------------------------------------------------------------------------------- */
+int b200ft_lora_grad(const void* s, int64_t ld_s, int r, const void* t, int64_t ld_t, int cols,
+                     int64_t m, float* out, int64_t ld_out, float alpha, void* stream);
+
+/* ---------------------------------------------------------------------------------------
+ * Fused softmax-cross-entropy forward+backward (SURVEY.md §8 a2.4;
+ * oracle/gpt2_lora_ref.py:softmax_xent_ref).  logits bf16 [rows, ld], the first `vocab`
+ * columns valid; overwritten in place with d(loss)/d(logits) * grad_scale (padding columns
+ * and ignored rows get 0).  loss_out[0] = mean over rows whose target != ignore_index.
+ * Scratch: b200ft_softmax_xent_workspace_bytes(rows) bytes.
+ * ------------------------------------------------------------------------------------- */
+size_t b200ft_softmax_xent_workspace_bytes(int64_t rows);
+int b200ft_softmax_xent_fwd_bwd(void* logits, int64_t rows, int vocab, int64_t ld,
+                                const int64_t* targets, int64_t ignore_index, float grad_scale,
+                                float* loss_out, void* workspace, size_t workspace_bytes,
+                                void* stream);
+
+/* HF causal-LM target shift (oracle/gpt2_lora_ref.py:causal_lm_loss):
+ * targets[b, t] = labels[b, t+1] for t < seq-1, ignore_index at t = seq-1. */
+int b200ft_shift_targets(const int64_t* labels, int64_t* targets, int64_t batch, int seq,
+                         int64_t ignore_index, void* stream);
+
+/* ---------------------------------------------------------------------------------------
+ * Fused AdamW + gradient scale (oracle/gpt2_lora_ref.py:adamw_ref, the
+ * formula of torch.optim.AdamW).  Flat buffers of n elements: p, m, v fp32; g bf16 or fp32;
+ * optional bf16 shadow of the updated p.  g is multiplied by grad_scale and, when
+ * grad_scale_dev != NULL, also by *grad_scale_dev (a device scalar, e.g. a clip factor).
+ * 28 bytes of HBM traffic per element with a bf16 g and a shadow.
+ * ------------------------------------------------------------------------------------- */
+int b200ft_adamw_step(float* p, float* m, float* v, const void* g, int g_is_bf16, void* shadow_bf16,
+                      int64_t n, float lr, float beta1, float beta2, float eps,
+                      float weight_decay, int step, float grad_scale,
+                      const float* grad_scale_dev, void* stream);
+
+/* Sum of squares of a flat gradient buffer -> out_sq[0] (fp32), and the clip factor
+ * coef[0] = min(1, max_norm / (pre_scale*sqrt(norm_sq) + 1e-6))  (torch clip_grad_norm_). */
+size_t b200ft_gradnorm_sq_workspace_bytes(int64_t n);
+int b200ft_gradnorm_sq(const void* g, int g_is_bf16, int64_t n, float* out_sq, void* workspace,
+                       size_t workspace_bytes, void* stream);
+int b200ft_clip_coef(const float* norm_sq, float max_norm, float pre_scale, float* coef, void* stream);
+
+/* ---------------------------------------------------------------------------------------
+ * LayerNorm (F.layer_norm in oracle forward()).  x, y, dy, dx, dres bf16
+ * [rows, d]; gamma/beta fp32 [d]; mean/rstd fp32 [rows].  bwd_dx: dx = dres + dLN/dx
+ * (dres may be NULL): the residual-stream gradient add is fused.
+ * d must be a multiple of 8 and <= 8192.
+ * ------------------------------------------------------------------------------------- */
+int b200ft_layernorm_fwd(const void* x, const float* gamma, const float* beta, void* y, float* mean,
+                         float* rstd, int64_t rows, int d, float eps, void* stream);
+int b200ft_layernorm_bwd_dx(const void* dy, const void* x, const float* gamma, const float* mean,
+                            const float* rstd, const void* dres, void* dx, int64_t rows, int d,
+                            void* stream);
+
+/* Token + position embedding (oracle forward(): F.embedding(ids,wte)+F.embedding(pos,wpe)).
+ * wte bf16 [vocab, d], wpe bf16 [ctx, d], x bf16 [rows, d], position = row % seq. */
+int b200ft_embed_fwd(const int64_t* ids, const void* wte, const void* wpe, void* x, int64_t rows,
+                     int seq, int d, int vocab, void* stream);
+
+/* out[c, r] = in[r, c] for bf16 matrices (weight re-layout at load; adapter shadows). */
+int b200ft_transpose_bf16(const void* in, int64_t ld_in, void* out, int64_t ld_out, int rows,
+                          int cols, void* stream);
+
+/* fp32 -> bf16 cast of a flat buffer (parameter upload). */
+int b200ft_cast_f32_to_bf16(const float* in, void* out, int64_t n, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200FT_H_ */
