@@ -162,6 +162,10 @@ class GPT2LoRAStep:
             out[f"h{l}.c_attn.lora_B"] = self.gB_all[l * R_PAD: l * R_PAD + r].contiguous().cpu()
         return out
 
+    def grad_views(self, lo: int, hi: int) -> list:
+        """Contiguous gradient slices of layers [lo, hi) (what one all-reduce bucket covers)."""
+        return [self.gAt_all[lo * R_PAD: hi * R_PAD], self.gB_all[lo * R_PAD: hi * R_PAD]]
+
     # ------------------------------------------------------------------ activations
     def _alloc_activations(self) -> None:
         D, dev, M = self.dims, self.dev, self.M
@@ -285,6 +289,21 @@ class GPT2LoRAStep:
                        beta2=o.beta2, eps=o.eps, weight_decay=o.weight_decay, shadow=self.S, grad_scale=gs,
                        grad_scale_dev=coef)
         self._refresh_shadows(cast=False)
+
+    def step_host(self, ids_host: torch.Tensor, labels_host: torch.Tensor) -> float:
+        """The call a user of the package makes: HOST int64 [batch, seq] tensors in (pinned
+        memory makes the copies asynchronous), python float loss out.  Copies the inputs to
+        the device, runs one full step, reads the loss back."""
+        if not hasattr(self, "_ids_dev"):
+            self._ids_dev = torch.empty(self.B, self.T, dtype=torch.int64, device=self.dev)
+            self._labels_dev = torch.empty(self.B, self.T, dtype=torch.int64, device=self.dev)
+            self._loss_host = torch.empty(1, dtype=torch.float32).pin_memory()
+        self._ids_dev.copy_(ids_host, non_blocking=True)
+        self._labels_dev.copy_(labels_host, non_blocking=True)
+        self.step(self._ids_dev, self._labels_dev)
+        self._loss_host.copy_(self.loss, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        return float(self._loss_host[0])
 
     def step(self, ids: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:
         """ids, labels: int64 [batch, seq] on the device.  Returns the (device) loss scalar."""

@@ -16,6 +16,29 @@ from ._lib import (A_MN_MAJOR, B_MN_MAJOR, EPI_DGELU, EPI_GELU, EPI_NONE, EPI_RE
 
 LAUNCHES = 0
 
+# Optional per-kernel-class timing (bench.py's instrumented pass): when PROFILE is a dict,
+# every wrapper brackets its launch with CUDA events on the launching stream and appends
+# (start, end, algorithmic_work) under its class name.  Off (None) in normal operation.
+PROFILE = None
+
+
+class _timed:
+    def __init__(self, name, work):
+        self.name, self.work = name, work
+
+    def __enter__(self):
+        if PROFILE is not None:
+            self.e0 = torch.cuda.Event(enable_timing=True)
+            self.e1 = torch.cuda.Event(enable_timing=True)
+            self.e0.record()
+        return self
+
+    def __exit__(self, *exc):
+        if PROFILE is not None:
+            self.e1.record()
+            PROFILE.setdefault(self.name, []).append((self.e0, self.e1, self.work))
+        return False
+
 
 def _p(t):
     return None if t is None else ctypes.c_void_p(t.data_ptr())
@@ -69,7 +92,9 @@ def gemm(a, b, out, *, a_mn=False, b_mn=False, a2=None, b2=None, bias=None, epil
     if out2 is not None:
         args.c2, args.ldc2 = out2.data_ptr(), out2.stride(0)
     args.block_n, args.max_ctas = block_n, max_ctas
-    check(lib().b200ft_gemm_bf16(ctypes.byref(args), _stream()), "gemm_bf16")
+    kk = k + (args.k2 if a2 is not None else 0)
+    with _timed("gemm", 2.0 * m * n * kk):
+        check(lib().b200ft_gemm_bf16(ctypes.byref(args), _stream()), "gemm_bf16")
     LAUNCHES += 1
     return out
 
@@ -80,8 +105,9 @@ def lora_grad(s, t, out, *, r, cols, alpha=1.0, m=None):
     _need_cuda(s, t, out)
     assert s.dtype == t.dtype == torch.bfloat16 and out.dtype == torch.float32
     m = s.shape[0] if m is None else m
-    check(lib().b200ft_lora_grad(_p(s), s.stride(0), r, _p(t), t.stride(0), cols, m, _p(out), out.stride(0),
-                                 alpha, _stream()), "lora_grad")
+    with _timed("lora_grad", 2.0 * m * (cols + r)):
+        check(lib().b200ft_lora_grad(_p(s), s.stride(0), r, _p(t), t.stride(0), cols, m, _p(out), out.stride(0),
+                                     alpha, _stream()), "lora_grad")
     LAUNCHES += 1
     return out
 
@@ -97,9 +123,10 @@ def softmax_xent_fwd_bwd(logits, targets, loss_out, workspace, *, vocab, grad_sc
     _need_cuda(logits, targets, loss_out, workspace)
     assert logits.dtype == torch.bfloat16 and targets.dtype == torch.int64 and loss_out.dtype == torch.float32
     rows = logits.shape[0]
-    check(lib().b200ft_softmax_xent_fwd_bwd(_p(logits), rows, vocab, logits.stride(0), _p(targets), ignore_index,
-                                            grad_scale, _p(loss_out), _p(workspace), workspace.numel(),
-                                            _stream()), "softmax_xent_fwd_bwd")
+    with _timed("softmax_xent", 2.0 * rows * vocab * 2 + 12.0 * rows):
+        check(lib().b200ft_softmax_xent_fwd_bwd(_p(logits), rows, vocab, logits.stride(0), _p(targets),
+                                                ignore_index, grad_scale, _p(loss_out), _p(workspace),
+                                                workspace.numel(), _stream()), "softmax_xent_fwd_bwd")
     LAUNCHES += 2
     return loss_out
 
@@ -121,9 +148,11 @@ def adamw_step(p, m, v, g, *, step, lr, beta1, beta2, eps, weight_decay, shadow=
     assert g.dtype in (torch.bfloat16, torch.float32)
     n = p.numel()
     assert m.numel() == n and v.numel() == n and g.numel() == n
-    check(lib().b200ft_adamw_step(_p(p), _p(m), _p(v), _p(g), int(g.dtype == torch.bfloat16), _p(shadow), n, lr,
-                                  beta1, beta2, eps, weight_decay, step, grad_scale, _p(grad_scale_dev),
-                                  _stream()), "adamw_step")
+    per = 24 + g.element_size() + (2 if shadow is not None else 0)
+    with _timed("adamw", float(per) * n):
+        check(lib().b200ft_adamw_step(_p(p), _p(m), _p(v), _p(g), int(g.dtype == torch.bfloat16), _p(shadow), n,
+                                      lr, beta1, beta2, eps, weight_decay, step, grad_scale, _p(grad_scale_dev),
+                                      _stream()), "adamw_step")
     LAUNCHES += 1
 
 
@@ -152,8 +181,9 @@ def layernorm_fwd(x, gamma, beta, y, mean, rstd, eps):
     _need_cuda(x, gamma, beta, y, mean, rstd)
     rows, d = x.shape
     assert x.is_contiguous() and y.is_contiguous()
-    check(lib().b200ft_layernorm_fwd(_p(x), _p(gamma), _p(beta), _p(y), _p(mean), _p(rstd), rows, d, eps,
-                                     _stream()), "layernorm_fwd")
+    with _timed("layernorm_fwd", 4.0 * rows * d):
+        check(lib().b200ft_layernorm_fwd(_p(x), _p(gamma), _p(beta), _p(y), _p(mean), _p(rstd), rows, d, eps,
+                                         _stream()), "layernorm_fwd")
     LAUNCHES += 1
     return y
 
@@ -163,8 +193,9 @@ def layernorm_bwd_dx(dy, x, gamma, mean, rstd, dx, dres=None):
     _need_cuda(dy, x, gamma, mean, rstd, dx, dres)
     rows, d = x.shape
     assert dy.is_contiguous() and x.is_contiguous() and dx.is_contiguous()
-    check(lib().b200ft_layernorm_bwd_dx(_p(dy), _p(x), _p(gamma), _p(mean), _p(rstd), _p(dres), _p(dx), rows, d,
-                                        _stream()), "layernorm_bwd_dx")
+    with _timed("layernorm_bwd", (8.0 if dres is not None else 6.0) * rows * d):
+        check(lib().b200ft_layernorm_bwd_dx(_p(dy), _p(x), _p(gamma), _p(mean), _p(rstd), _p(dres), _p(dx), rows,
+                                            d, _stream()), "layernorm_bwd_dx")
     LAUNCHES += 1
     return dx
 
