@@ -1,0 +1,175 @@
+"""Container entrypoint of the fine-tune job: ``python -m b200ft.train --k=v ...``.
+
+This is what the plugin's ``run_cmd()`` (finetune-controller_b200/plugin/b200_lora.py) starts
+inside the controller's ``pytorch`` container (reference
+app/jobs/kubeflow/PyTorchJobDeployer.py:93-119).  Contract with the controller:
+
+  * flags: exactly those ``run_cmd()`` emits, incl. ``--dataset_path`` / ``--checkpoint_path``
+    (reference app/models/examples/mnist.py:93-95);
+  * stdout: a line containing ``Epoch`` before anything the log stream should show
+    (reference app/utils/stream_logger.py:404-418, app/core/config.py:26);
+  * ``<checkpoint_path>/metrics.csv`` readable by ``pd.read_csv`` (reference
+    app/utils/S3Handler.py:252-286), plus ``adapter.pt`` / ``adapter_config.json`` which match
+    the default ``store_asset_patterns`` (reference app/models/base/finetuning.py:94-97);
+  * exit code 0 on success only — the controller appends ``&& touch done.txt``
+    (reference PyTorchJobDeployer.py:30-32); any CUDA/NCCL error propagates as non-zero so the
+    operator's restart policy applies.
+
+The pod gets ``--gpus`` devices; the operator's RANK/WORLD_SIZE describe pods, so this process
+spawns one worker per local GPU itself unless it is already running under torchrun.
+"""
+from __future__ import annotations
+
+import argparse
+import csv
+import json
+import os
+import sys
+import time
+
+
+def build_parser() -> argparse.ArgumentParser:
+    ap = argparse.ArgumentParser(prog="b200ft.train")
+    ap.add_argument("--model", default="gpt2-124m")
+    ap.add_argument("--mode", default="lora", choices=["lora"])
+    ap.add_argument("--lora_r", type=int, default=8)
+    ap.add_argument("--lora_alpha", type=float, default=16.0)
+    ap.add_argument("--seq_len", type=int, default=1024)
+    ap.add_argument("--batch_size", type=int, default=32)
+    ap.add_argument("--epochs", type=int, default=1)
+    ap.add_argument("--steps_per_epoch", type=int, default=100)
+    ap.add_argument("--lr", type=float, default=1e-4)
+    ap.add_argument("--weight_decay", type=float, default=0.01)
+    ap.add_argument("--beta1", type=float, default=0.9)
+    ap.add_argument("--beta2", type=float, default=0.999)
+    ap.add_argument("--eps", type=float, default=1e-8)
+    ap.add_argument("--max_grad_norm", type=float, default=0.0)
+    ap.add_argument("--seed", type=int, default=0)
+    ap.add_argument("--log_interval", type=int, default=10)
+    ap.add_argument("--save_model", action="store_true")
+    ap.add_argument("--synthetic", action="store_true")
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--dataset_path", default="/data/dataset")
+    ap.add_argument("--checkpoint_path", default="/data/artifacts")
+    return ap
+
+
+def load_token_stream(dataset_path: str):
+    """tokens.pt (1-D int tensor) or tokens.bin (little-endian uint16/int32 ids) if present."""
+    import numpy as np
+    import torch
+    pt, bn = os.path.join(dataset_path, "tokens.pt"), os.path.join(dataset_path, "tokens.bin")
+    if os.path.exists(pt):
+        return torch.load(pt).to(torch.int64).flatten()
+    if os.path.exists(bn):
+        raw = np.fromfile(bn, dtype=np.uint16)
+        return torch.from_numpy(raw.astype(np.int64))
+    return None
+
+
+def worker(args, rank: int, world: int, local: int) -> None:
+    import torch
+    from . import ddp, gpt2, params
+
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dims = params.MODELS[args.model]
+    lora = gpt2.LoRASpec(args.lora_r, args.lora_alpha)
+    opt = gpt2.OptSpec(args.lr, args.beta1, args.beta2, args.eps, args.weight_decay, args.max_grad_norm)
+    base = params.init_gpt2(dims, args.seed, device=dev)          # identical on every rank (same seed)
+    ad = params.init_lora(dims, lora, args.seed + 1, device=dev)
+    sync = ddp.BucketedGradSync(dims.n_layer, n_buckets=2) if world > 1 else None
+    eng = gpt2.GPT2LoRAStep(dims, lora, opt, base, ad, batch=args.batch_size, seq=args.seq_len, device=dev,
+                            world_size=world, grad_sync=sync)
+    del base
+    stream = None if args.synthetic else load_token_stream(args.dataset_path)
+    gen = torch.Generator().manual_seed(1234 + args.seed + rank)
+    B, T = args.batch_size, args.seq_len
+    ids_host = torch.empty(B, T, dtype=torch.int64).pin_memory()
+
+    def next_batch(global_step: int):
+        if stream is None:
+            ids_host.copy_(torch.randint(0, dims.vocab, (B, T), generator=gen, dtype=torch.int64))
+        else:
+            span = B * T
+            n_chunks = max(1, (stream.numel() - 1) // span)
+            off = ((global_step * world + rank) % n_chunks) * span
+            chunk = stream[off: off + span]
+            if chunk.numel() < span:
+                chunk = torch.cat([chunk, stream[: span - chunk.numel()]])
+            ids_host.copy_(chunk.view(B, T).clamp_(0, dims.vocab - 1))
+        return ids_host
+
+    os.makedirs(args.checkpoint_path, exist_ok=True)
+    metrics_path = os.path.join(args.checkpoint_path, "metrics.csv")
+    writer = fh = None
+    if rank == 0:
+        fh = open(metrics_path, "w", newline="")
+        writer = csv.writer(fh)
+        writer.writerow(["epoch", "step", "loss", "lr", "tokens_per_sec", "elapsed_s"])
+        print(f"Epoch 0/{args.epochs} starting: model={args.model} lora_r={args.lora_r} world={world} "
+              f"batch/gpu={B} seq={T}", flush=True)
+    t_start = time.time()
+    gstep = 0
+    for epoch in range(1, args.epochs + 1):
+        t0, tok0 = time.time(), 0
+        loss = float("nan")
+        for it in range(1, args.steps_per_epoch + 1):
+            batch = next_batch(gstep)
+            loss = eng.step_host(batch, batch)
+            gstep += 1
+            tok0 += B * T * world
+            if rank == 0 and (it % args.log_interval == 0 or it == args.steps_per_epoch):
+                tps = tok0 / max(time.time() - t0, 1e-9)
+                print(f"Epoch {epoch}/{args.epochs} step {it}/{args.steps_per_epoch} loss {loss:.4f} "
+                      f"tokens/s {tps:.0f}", flush=True)
+                writer.writerow([epoch, gstep, f"{loss:.6f}", args.lr, f"{tps:.1f}", f"{time.time() - t_start:.2f}"])
+                fh.flush()
+        if loss != loss:
+            raise RuntimeError("loss is NaN")
+    if rank == 0:
+        fh.close()
+        if args.save_model:
+            torch.save({k: v for k, v in eng.adapters_state().items()}, os.path.join(args.checkpoint_path, "adapter.pt"))
+            with open(os.path.join(args.checkpoint_path, "adapter_config.json"), "w") as f:
+                json.dump({"peft_type": "LORA", "base_model": args.model, "r": args.lora_r,
+                           "lora_alpha": args.lora_alpha, "target_modules": ["c_attn"], "fan_in_fan_out": True,
+                           "lora_dropout": 0.0, "steps": gstep}, f, indent=1)
+        print(f"Epoch {args.epochs}/{args.epochs} done: {gstep} steps in {time.time() - t_start:.1f}s", flush=True)
+
+
+def _spawned(local: int, args, world: int, port: int) -> None:
+    os.environ.update(RANK=str(local), LOCAL_RANK=str(local), WORLD_SIZE=str(world),
+                      MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    from . import ddp
+    rank, world, local = ddp.init_process_group_from_env("nccl")
+    try:
+        worker(args, rank, world, local)
+    finally:
+        import torch.distributed as dist
+        if dist.is_initialized():
+            dist.destroy_process_group()
+
+
+def main(argv=None) -> int:
+    args = build_parser().parse_args(argv)
+    import torch
+    if not torch.cuda.is_available():
+        print("b200ft.train: no CUDA device visible; this payload has no CPU path", file=sys.stderr)
+        return 2
+    if "LOCAL_RANK" in os.environ and int(os.environ.get("WORLD_SIZE", "1")) > 1 and args.gpus > 1:
+        from . import ddp  # already under torchrun: one process per GPU exists
+        rank, world, local = ddp.init_process_group_from_env("nccl")
+        worker(args, rank, world, local)
+        return 0
+    if args.gpus <= 1:
+        worker(args, 0, 1, 0)
+        return 0
+    import torch.multiprocessing as mp
+    from . import ddp
+    mp.spawn(_spawned, args=(args, args.gpus, ddp.free_port()), nprocs=args.gpus, join=True)
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -5,8 +5,12 @@
 //   warp 0 : TMA producer (one lane)          smem ring of kStages {A 128x64, B BNx64} slabs
 //   warp 1 : MMA issuer (one lane)            128 x BN x 16 UMMAs, 4 per K slab
 //   warp 2 : TMEM allocator (512 columns = two 128 x 256 fp32 accumulators)
-//   warps 4-7 : epilogue, one TMEM lane quarter each; runs on accumulator `a` while the MMA
-//               warp fills accumulator `a^1` for the next tile.
+//   warps 4-7 : epilogue, one TMEM lane quarter (32 rows) each; runs on accumulator `a` while
+//               the MMA warp fills accumulator `a^1` for the next tile.  Per 64-column chunk:
+//               tcgen05.ld -> registers -> (alpha, bias, residual / gelu / dgelu) -> bf16 into a
+//               128B-swizzled 32x64 smem tile -> one TMA store (coalesced, asynchronous, clipped
+//               at the matrix edge).  The residual / dgelu operand arrives by TMA load into the
+//               same tile one chunk ahead and is updated in place.
 // Three mbarrier pipelines: smem full/empty (TMA <-> MMA), TMEM full/empty (MMA <-> epilogue).
 //
 // The K loop runs over up to two operand segments.  Segment 2 is how a LoRA branch is
@@ -35,8 +39,11 @@ constexpr int kStages = 4;
 constexpr int kAStageBytes = kBlockM * kBlockK * 2;  // 16 KB
 constexpr int kBStageBytes = kMaxBN * kBlockK * 2;   // 32 KB
 constexpr int kTileBytes = kStages * (kAStageBytes + kBStageBytes);
+constexpr int kEpiBufBytes = 32 * 64 * 2;              // one 32-row x 64-col bf16 staging tile
+constexpr int kEpiBytes = 4 * 2 * kEpiBufBytes;        // 4 epilogue warps x 2 tiles = 32 KB
 constexpr int kBarrierBytes = 256;
-constexpr int kSmemBytes = kTileBytes + kBarrierBytes + 1024;  // + slack to align to 1024
+constexpr int kSmemBytes = kTileBytes + kEpiBytes + kBarrierBytes + 1024;  // + slack to align to 1024
+static_assert(kSmemBytes <= 227 * 1024, "shared memory budget");
 constexpr int kThreads = 256;
 constexpr int kTmemCols = 512;
 constexpr int kAccStride = 256;  // TMEM columns per accumulator stage
@@ -48,6 +55,7 @@ struct GemmParams {
   int a_mn, b_mn;
   int tiles_m, tiles_n;
   int epilogue;
+  int cw;  // epilogue chunk width in columns: 64 (swizzled staging tile), 32 or 16 (dense)
   float alpha;
   const float* bias;
   const __nv_bfloat16* aux; int64_t ld_aux;
@@ -92,6 +100,26 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map
       ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(c0), "r"(c1), "r"(bar)
       : "memory");
 }
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, uint32_t src, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+               ::"l"(reinterpret_cast<uint64_t>(map)), "r"(src), "r"(c0), "r"(c1)
+               : "memory");
+  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+template <int N>
+__device__ __forceinline__ void tma_store_wait_read() {
+  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ uint4 lds16(uint32_t addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ void sts16(uint32_t addr, uint4 v) {
+  asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* map) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(map)) : "memory");
 }
@@ -124,6 +152,18 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t* r) {
       : "r"(taddr)
       : "memory");
 }
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* r) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,"
+      "%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+        "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+        "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr)
+      : "memory");
+}
 __device__ __forceinline__ void tmem_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 // shared-memory matrix descriptor (PTX ISA, tcgen05 "matrix descriptor"): start>>4 [0,14),
@@ -144,26 +184,156 @@ __device__ __forceinline__ uint32_t make_idesc(int n, int a_mn, int b_mn) {
          ((uint32_t)(n >> 3) << 17) | ((uint32_t)(kBlockM >> 4) << 24);
 }
 
+
+// ---------------------------------------------------------------------------------------
+// epilogue of one warp: TMEM lane quarter q (rows m0 + 32q .. +31) of every tile this CTA owns
+// ---------------------------------------------------------------------------------------
+// address of the 16-byte vector `v` of row `lane` inside a staging tile of CW columns
+template <int CW>
+__device__ __forceinline__ uint32_t epi_vec_addr(uint32_t buf, int lane, int v) {
+  if constexpr (CW == 64) return buf + lane * 128 + ((v ^ (lane & 7)) << 4);  // TMA SWIZZLE_128B pattern
+  else return buf + lane * (CW * 2) + (v << 4);                               // dense rows (SWIZZLE_NONE)
+}
+
+template <int CW>
+__device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtensorMap* tmC, const CUtensorMap* tmC2,
+                                              const CUtensorMap* tmAux, int q, int lane, uint32_t tmem_base,
+                                              uint32_t ebuf, uint32_t abar0, uint32_t abar1, uint32_t tfull0,
+                                              uint32_t tempty0, int num_tiles) {
+  const int BN = p.BN;
+  const int nchunks = BN / CW;
+  const bool has_aux = (p.epilogue == B200FT_EPI_RESIDUAL) || (p.epilogue == B200FT_EPI_DGELU);
+  const uint32_t aux_bytes = 32u * CW * 2u;
+  uint32_t slot = 0;          // running count of staged tiles: buffer = slot & 1
+  uint32_t aux_phase = 0;     // bit b = parity to wait for on aux barrier b
+  int acc = 0;
+  uint32_t acc_phase = 0;
+  for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+    const int m0 = (tile / p.tiles_n) * kBlockM;
+    const int n0 = (tile % p.tiles_n) * BN;
+    const int row0 = m0 + q * 32;
+    if (has_aux && lane == 0) {  // first chunk's operand: in flight while the MMAs of this tile finish
+      const uint32_t b = slot & 1u;
+      tma_store_wait_read<1>();  // the store that last used this buffer has drained it
+      const uint32_t bar = b ? abar1 : abar0;
+      mbar_expect_tx(bar, aux_bytes);
+      tma_load_2d(ebuf + b * kEpiBufBytes, tmAux, n0, row0, bar);
+    }
+    mbar_wait(tfull0 + 8u * acc, acc_phase);
+    tc_fence_after();
+    const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * kAccStride);
+    for (int c = 0; c < nchunks; ++c) {
+      const uint32_t b = slot & 1u;
+      const uint32_t buf = ebuf + b * kEpiBufBytes;
+      uint32_t r[CW];
+      if constexpr (CW == 64) { tmem_ld32(t_row + c * CW, r); tmem_ld32(t_row + c * CW + 32, r + 32); }
+      else if constexpr (CW == 32) { tmem_ld32(t_row + c * CW, r); }
+      else { tmem_ld16(t_row + c * CW, r); }
+      if (has_aux) {
+        mbar_wait(b ? abar1 : abar0, (aux_phase >> b) & 1u);
+        aux_phase ^= (1u << b);
+      } else {
+        if (lane == 0) tma_store_wait_read<1>();
+        __syncwarp();
+      }
+      tmem_wait_ld();
+      const int colbase = n0 + c * CW;
+#pragma unroll
+      for (int v = 0; v < CW / 8; ++v) {
+        float f[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) f[j] = __uint_as_float(r[v * 8 + j]) * p.alpha;
+        const int col = colbase + v * 8;
+        if (p.bias && col < p.N) {
+          const float4 b0 = __ldg(reinterpret_cast<const float4*>(p.bias + col));
+          const float4 b1 = __ldg(reinterpret_cast<const float4*>(p.bias + col + 4));
+          f[0] += b0.x; f[1] += b0.y; f[2] += b0.z; f[3] += b0.w;
+          f[4] += b1.x; f[5] += b1.y; f[6] += b1.z; f[7] += b1.w;
+        }
+        const uint32_t addr = epi_vec_addr<CW>(buf, lane, v);
+        if (has_aux) {
+          float a[8];
+          unpack8(lds16(addr), a);
+          if (p.epilogue == B200FT_EPI_RESIDUAL) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) f[j] += a[j];
+          } else {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) f[j] *= gelu_new_grad_f(a[j]);
+          }
+        }
+        const uint4 packed = pack8(f);
+        sts16(addr, packed);
+        if (p.epilogue == B200FT_EPI_GELU) {  // keep the bf16-rounded pre-activation for pass 2
+          r[v * 8 + 0] = packed.x; r[v * 8 + 1] = packed.y; r[v * 8 + 2] = packed.z; r[v * 8 + 3] = packed.w;
+        }
+      }
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) tma_store_2d(tmC, buf, colbase, row0);
+      ++slot;
+      if (p.epilogue == B200FT_EPI_GELU) {
+        // second output: gelu of the bf16-ROUNDED pre-activation, so that backward (which only
+        // has the stored bf16 value) differentiates exactly the function applied here
+        const uint32_t buf2 = ebuf + (slot & 1u) * kEpiBufBytes;
+        if (lane == 0) tma_store_wait_read<1>();
+        __syncwarp();
+#pragma unroll
+        for (int v = 0; v < CW / 8; ++v) {
+          uint4 pk;
+          pk.x = r[v * 8 + 0]; pk.y = r[v * 8 + 1]; pk.z = r[v * 8 + 2]; pk.w = r[v * 8 + 3];
+          float g[8];
+          unpack8(pk, g);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) g[j] = gelu_new_f(g[j]);
+          sts16(epi_vec_addr<CW>(buf2, lane, v), pack8(g));
+        }
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) tma_store_2d(tmC2, buf2, colbase, row0);
+        ++slot;
+      }
+      if (has_aux && c + 1 < nchunks && lane == 0) {  // next chunk's operand, one chunk ahead
+        const uint32_t nb = slot & 1u;
+        tma_store_wait_read<1>();
+        const uint32_t bar = nb ? abar1 : abar0;
+        mbar_expect_tx(bar, aux_bytes);
+        tma_load_2d(ebuf + nb * kEpiBufBytes, tmAux, colbase + CW, row0, bar);
+      }
+    }
+    tc_fence_before();
+    __syncwarp();
+    if (lane == 0) mbar_arrive(tempty0 + 8u * acc);
+    acc ^= 1;
+    if (acc == 0) acc_phase ^= 1u;
+  }
+  if (lane == 0) tma_store_wait_all();  // smem must outlive the bulk stores reading it
+  __syncwarp();
+}
+
 // ---------------------------------------------------------------------------------------
 // the kernel
 // ---------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmB1,
                          const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmB2,
-                         const GemmParams p) {
+                         const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmC2,
+                         const __grid_constant__ CUtensorMap tmAux, const GemmParams p) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
   const uint32_t base = (raw + 1023u) & ~1023u;
   const uint32_t sA = base;
   const uint32_t sB = base + kStages * kAStageBytes;
-  const uint32_t bars = base + kTileBytes;
+  const uint32_t sEpi = base + kTileBytes;
+  const uint32_t bars = sEpi + kEpiBytes;
   auto full_bar = [&](int s) { return bars + 8u * s; };
   auto empty_bar = [&](int s) { return bars + 8u * (kStages + s); };
   auto tfull_bar = [&](int a) { return bars + 8u * (2 * kStages + a); };
   auto tempty_bar = [&](int a) { return bars + 8u * (2 * kStages + 2 + a); };
-  const uint32_t tmem_slot = bars + 8u * (2 * kStages + 4);
-  volatile uint32_t* tmem_slot_ptr =
-      reinterpret_cast<volatile uint32_t*>(smem_raw + (base - raw) + kTileBytes + 8 * (2 * kStages + 4));
+  auto aux_bar = [&](int q, int b) { return bars + 8u * (2 * kStages + 4 + 2 * q + b); };
+  const uint32_t tmem_slot = bars + 8u * (2 * kStages + 12);
+  volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(
+      smem_raw + (base - raw) + kTileBytes + kEpiBytes + 8 * (2 * kStages + 12));
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -172,10 +342,12 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
     tma_prefetch_desc(&tmA1);
     tma_prefetch_desc(&tmB1);
     if (p.kblocks2 > 0) { tma_prefetch_desc(&tmA2); tma_prefetch_desc(&tmB2); }
+    tma_prefetch_desc(&tmC);
   }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < kStages; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
     for (int a = 0; a < 2; ++a) { mbar_init(tfull_bar(a), 1); mbar_init(tempty_bar(a), 4); }
+    for (int q = 0; q < 4; ++q) { mbar_init(aux_bar(q, 0), 1); mbar_init(aux_bar(q, 1), 1); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 2) tmem_alloc(tmem_slot, kTmemCols);
@@ -273,68 +445,12 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
   } else if (warp >= 4) {
     // =============================== epilogue ===============================
     const int q = warp - 4;  // TMEM lane quarter == warp % 4
-    int acc = 0;
-    uint32_t acc_phase = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-      const int m0 = (tile / p.tiles_n) * kBlockM;
-      const int n0 = (tile % p.tiles_n) * BN;
-      mbar_wait(tfull_bar(acc), acc_phase);
-      tc_fence_after();
-      const int row = m0 + q * 32 + lane;
-      const bool row_ok = row < p.M;
-      const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * kAccStride);
-      for (int c = 0; c < BN; c += 32) {
-        uint32_t r[32];
-        tmem_ld16(t_row + c, r);
-        const bool second = (c + 16 < BN);
-        if (second) tmem_ld16(t_row + c + 16, r + 16);
-        tmem_wait_ld();
-        const int nvec = second ? 4 : 2;
-#pragma unroll
-        for (int v = 0; v < 4; ++v) {
-          if (v < nvec) {
-            const int col = n0 + c + v * 8;
-            if (row_ok && col < p.N) {
-              float f[8];
-#pragma unroll
-              for (int j = 0; j < 8; ++j) f[j] = __uint_as_float(r[v * 8 + j]) * p.alpha;
-              if (p.bias) {
-                const float4 b0 = __ldg(reinterpret_cast<const float4*>(p.bias + col));
-                const float4 b1 = __ldg(reinterpret_cast<const float4*>(p.bias + col + 4));
-                f[0] += b0.x; f[1] += b0.y; f[2] += b0.z; f[3] += b0.w;
-                f[4] += b1.x; f[5] += b1.y; f[6] += b1.z; f[7] += b1.w;
-              }
-              if (p.epilogue == B200FT_EPI_RESIDUAL) {
-                float a[8];  // plain (coherent) load: aux may alias c for an in-place residual add
-                unpack8(*reinterpret_cast<const uint4*>(p.aux + (int64_t)row * p.ld_aux + col), a);
-#pragma unroll
-                for (int j = 0; j < 8; ++j) f[j] += a[j];
-              } else if (p.epilogue == B200FT_EPI_DGELU) {
-                float a[8];
-                unpack8(ld_stream16(p.aux + (int64_t)row * p.ld_aux + col), a);
-#pragma unroll
-                for (int j = 0; j < 8; ++j) f[j] *= gelu_new_grad_f(a[j]);
-              }
-              *reinterpret_cast<uint4*>(p.c + (int64_t)row * p.ldc + col) = pack8(f);
-              if (p.epilogue == B200FT_EPI_GELU) {
-                // gelu of the bf16-ROUNDED pre-activation, so that backward (which only has
-                // the stored bf16 value) differentiates exactly the function applied here
-                float g[8];
-                unpack8(pack8(f), g);
-#pragma unroll
-                for (int j = 0; j < 8; ++j) g[j] = gelu_new_f(g[j]);
-                *reinterpret_cast<uint4*>(p.c2 + (int64_t)row * p.ldc2 + col) = pack8(g);
-              }
-            }
-          }
-        }
-      }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(tempty_bar(acc));
-      acc ^= 1;
-      if (acc == 0) acc_phase ^= 1u;
-    }
+    if (p.cw == 64)      epilogue_loop<64>(p, &tmC, &tmC2, &tmAux, q, lane, tmem_base, sEpi + q * 2 * kEpiBufBytes,
+                                           aux_bar(q, 0), aux_bar(q, 1), tfull_bar(0), tempty_bar(0), num_tiles);
+    else if (p.cw == 32) epilogue_loop<32>(p, &tmC, &tmC2, &tmAux, q, lane, tmem_base, sEpi + q * 2 * kEpiBufBytes,
+                                           aux_bar(q, 0), aux_bar(q, 1), tfull_bar(0), tempty_bar(0), num_tiles);
+    else                 epilogue_loop<16>(p, &tmC, &tmC2, &tmAux, q, lane, tmem_base, sEpi + q * 2 * kEpiBufBytes,
+                                           aux_bar(q, 0), aux_bar(q, 1), tfull_bar(0), tempty_bar(0), num_tiles);
   }
 
   tc_fence_before();
@@ -366,14 +482,14 @@ EncodeTiledFn get_encode_fn() {
   return fn;
 }
 
-using MapKey = std::tuple<const void*, uint64_t, uint64_t, uint64_t, uint32_t, uint32_t>;
+using MapKey = std::tuple<const void*, uint64_t, uint64_t, uint64_t, uint32_t, uint32_t, int>;
 std::mutex g_map_mu;
 std::map<MapKey, CUtensorMap> g_maps;
 
 // 2-D bf16 tensor {inner, outer} with row pitch ld (elements), box {box_inner, box_outer}, SW128
 int get_tensor_map(const void* ptr, uint64_t inner, uint64_t outer, uint64_t ld, uint32_t box_inner,
-                   uint32_t box_outer, CUtensorMap* out) {
-  MapKey key{ptr, inner, outer, ld, box_inner, box_outer};
+                   uint32_t box_outer, CUtensorMap* out, bool swizzle128 = true) {
+  MapKey key{ptr, inner, outer, ld, box_inner, box_outer, swizzle128 ? 1 : 0};
   {
     std::lock_guard<std::mutex> lk(g_map_mu);
     auto it = g_maps.find(key);
@@ -386,7 +502,8 @@ int get_tensor_map(const void* ptr, uint64_t inner, uint64_t outer, uint64_t ld,
   cuuint32_t box[2] = {box_inner, box_outer};
   cuuint32_t estr[2] = {1, 1};
   CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
-                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     b200ft_set_error("gemm: cuTensorMapEncodeTiled failed (%d) ptr=%p dims=(%llu,%llu) ld=%llu box=(%u,%u)", (int)r,
@@ -460,8 +577,21 @@ extern "C" int b200ft_gemm_bf16(const b200ft_gemm_args* a, void* stream) {
   p.c = (__nv_bfloat16*)a->c; p.ldc = a->ldc;
   p.c2 = (__nv_bfloat16*)a->c2; p.ldc2 = a->ldc2;
 
-  CUtensorMap tA1, tB1, tA2, tB2;
+  p.cw = (BN % 64 == 0) ? 64 : (BN % 32 == 0 ? 32 : 16);
+  CUtensorMap tA1, tB1, tA2, tB2, tC, tC2, tAux;
   int rc;
+  // epilogue staging tiles: {cw columns, 32 rows}; the 64-wide one is 128B-swizzled
+  rc = get_tensor_map(a->c, (uint64_t)a->n, (uint64_t)a->m, (uint64_t)a->ldc, (uint32_t)p.cw, 32, &tC, p.cw == 64);
+  if (rc) return rc;
+  tC2 = tC; tAux = tC;
+  if (a->epilogue == B200FT_EPI_GELU) {
+    rc = get_tensor_map(a->c2, (uint64_t)a->n, (uint64_t)a->m, (uint64_t)a->ldc2, (uint32_t)p.cw, 32, &tC2, p.cw == 64);
+    if (rc) return rc;
+  }
+  if (a->epilogue == B200FT_EPI_RESIDUAL || a->epilogue == B200FT_EPI_DGELU) {
+    rc = get_tensor_map(a->aux, (uint64_t)a->n, (uint64_t)a->m, (uint64_t)a->ld_aux, (uint32_t)p.cw, 32, &tAux, p.cw == 64);
+    if (rc) return rc;
+  }
   if (p.a_mn) rc = get_tensor_map(a->a1, (uint64_t)a->m, (uint64_t)a->k1, (uint64_t)a->lda1, 64, 64, &tA1);
   else        rc = get_tensor_map(a->a1, (uint64_t)a->k1, (uint64_t)a->m, (uint64_t)a->lda1, 64, kBlockM, &tA1);
   if (rc) return rc;
@@ -487,7 +617,7 @@ extern "C" int b200ft_gemm_bf16(const b200ft_gemm_args* a, void* stream) {
   }
   const int num_tiles = p.tiles_m * p.tiles_n;
   const int grid = num_tiles < ctas_max ? num_tiles : ctas_max;
-  gemm_bf16_tcgen05_kernel<<<grid, kThreads, kSmemBytes, (cudaStream_t)stream>>>(tA1, tB1, tA2, tB2, p);
+  gemm_bf16_tcgen05_kernel<<<grid, kThreads, kSmemBytes, (cudaStream_t)stream>>>(tA1, tB1, tA2, tB2, tC, tC2, tAux, p);
   B200FT_LAUNCH_CHECK();
   return 0;
 }

@@ -39,7 +39,7 @@ def main():
         "adapters_after": {k: v.detach().clone() for k, v in tr.trainable.items()},
         "xent": {"z": z, "targets": tg, "loss": float(xl), "dz": xdz},
         "adamw": {"p0": p0, "g0": g0, "p1": p1, "m1": m1, "v1": v1, "grad_scale": 0.5},
-        "torch_version": torch.__version__,
+        "torch_version": str(torch.__version__),
     }
     path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "gpt2_tiny_lora_step.pt")
     torch.save(out, path)
