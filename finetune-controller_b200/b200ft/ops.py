@@ -23,8 +23,8 @@ PROFILE = None
 
 
 class _timed:
-    def __init__(self, name, work):
-        self.name, self.work = name, work
+    def __init__(self, name, work, label=None):
+        self.name, self.work, self.label = name, work, label
 
     def __enter__(self):
         if PROFILE is not None:
@@ -36,7 +36,7 @@ class _timed:
     def __exit__(self, *exc):
         if PROFILE is not None:
             self.e1.record()
-            PROFILE.setdefault(self.name, []).append((self.e0, self.e1, self.work))
+            PROFILE.setdefault(self.name, []).append((self.e0, self.e1, self.work, self.label))
         return False
 
 
@@ -93,7 +93,7 @@ def gemm(a, b, out, *, a_mn=False, b_mn=False, a2=None, b2=None, bias=None, epil
         args.c2, args.ldc2 = out2.data_ptr(), out2.stride(0)
     args.block_n, args.max_ctas = block_n, max_ctas
     kk = k + (args.k2 if a2 is not None else 0)
-    with _timed("gemm", 2.0 * m * n * kk):
+    with _timed("gemm", 2.0 * m * n * kk, (m, n, kk, int(a_mn), int(b_mn), epilogue)):
         check(lib().b200ft_gemm_bf16(ctypes.byref(args), _stream()), "gemm_bf16")
     LAUNCHES += 1
     return out
