@@ -49,6 +49,9 @@ SIGNATURES = {
     "b200ft_softmax_xent_workspace_bytes": (c_size_t, [c_int64]),
     "b200ft_softmax_xent_fwd_bwd": (c_int, [c_void_p, c_int64, c_int, c_int64, c_void_p, c_int64, c_float,
                                             c_void_p, c_void_p, c_size_t, c_void_p]),
+    "b200ft_softmax_xent_noalloc_max_rows": (c_int64, []),
+    "b200ft_softmax_xent_fwd_bwd_noalloc": (c_int, [c_void_p, c_int64, c_int, c_int64, c_void_p, c_int64, c_float,
+                                                    c_void_p, c_void_p]),
     "b200ft_shift_targets": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_int64, c_void_p]),
     "b200ft_adamw_step": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_int64, c_float,
                                   c_float, c_float, c_float, c_float, c_int, c_float, c_void_p, c_void_p]),

@@ -9,6 +9,7 @@
 // Scratch (the caller's workspace): [0] number of valid targets, [1] completion ticket,
 // [16 .. 16+rows) per-row losses.  The last CTA to finish folds the row losses in a fixed
 // order, so the loss is bit-reproducible from run to run.
+#include <mutex>
 #include "common.cuh"
 #include "../../include/b200ft.h"
 
@@ -184,6 +185,73 @@ extern "C" int b200ft_softmax_xent_fwd_bwd(void* logits, int64_t rows, int vocab
   }
   cudaStream_t st = (cudaStream_t)stream;
   unsigned int* ws = (unsigned int*)workspace;
+  count_valid_kernel<<<1, 256, 0, st>>>(targets, rows, ignore_index, ws);
+  B200FT_LAUNCH_CHECK();
+  softmax_xent_kernel<<<(unsigned)rows, kThreads, 0, st>>>((__nv_bfloat16*)logits, rows, vocab, ld, targets,
+                                                           ignore_index, grad_scale, loss_out, ws);
+  B200FT_LAUNCH_CHECK();
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------
+// Allocation-free variant.  Some callers of this library are not in a position to hand over a
+// workspace: a host that has given every byte of device memory to its own pool and may not
+// call cudaMalloc again, or a plug-in running inside another framework's allocator where a
+// fresh allocation would fragment or stall it.  For them the scratch of the cross-entropy
+// kernel (valid-target count, completion ticket, one loss per row) lives in this file-scope
+// device array instead.  It costs (kNoAllocMaxRows + 16) * 4 bytes on every GPU that loads the
+// library, until the process exits.
+//
+// The array's name is only a host-side handle; the kernels need its device address, which
+// cudaGetSymbolAddress() yields for the device that is current at the time.  That look-up is
+// done once per device, on the first call made with that device current.
+// ---------------------------------------------------------------------------------------
+namespace {
+constexpr int64_t kNoAllocMaxRows = 65536;
+static __device__ __align__(256) unsigned int g_xent_static_scratch[kNoAllocMaxRows + 16];
+
+constexpr int kMaxDevices = 64;
+std::mutex g_scratch_mu;
+unsigned int* g_scratch_addr[kMaxDevices] = {nullptr};
+
+// Device address of the static scratch on the CURRENT device (resolved once per device).
+int static_scratch_for_current_device(unsigned int** out) {
+  int dev = -1;
+  B200FT_CUDA(cudaGetDevice(&dev));
+  B200FT_CHECK_ARG(dev >= 0 && dev < kMaxDevices, "softmax_xent_noalloc: device ordinal %d unsupported", dev);
+  std::lock_guard<std::mutex> lk(g_scratch_mu);
+  if (g_scratch_addr[dev] == nullptr) {
+    unsigned int* ptr = nullptr;
+    B200FT_CUDA(cudaGetSymbolAddress((void**)&ptr, g_xent_static_scratch));
+    g_scratch_addr[dev] = ptr;
+  }
+  *out = g_scratch_addr[dev];
+  return 0;
+}
+}  // namespace
+
+extern "C" int64_t b200ft_softmax_xent_noalloc_max_rows(void) { return kNoAllocMaxRows; }
+
+extern "C" int b200ft_softmax_xent_fwd_bwd_noalloc(void* logits, int64_t rows, int vocab, int64_t ld,
+                                                   const int64_t* targets, int64_t ignore_index,
+                                                   float grad_scale, float* loss_out, void* stream) {
+  B200FT_CHECK_ARG(logits && targets && loss_out, "softmax_xent_noalloc: null buffer");
+  B200FT_CHECK_ARG(rows > 0 && vocab > 0 && ld >= vocab && ld % 8 == 0,
+                   "softmax_xent_noalloc: rows=%lld vocab=%d ld=%lld (ld must be a multiple of 8 and >= vocab)",
+                   (long long)rows, vocab, (long long)ld);
+  if (rows > kNoAllocMaxRows) {
+    b200ft_set_error("softmax_xent_noalloc: rows=%lld exceeds the built-in scratch (max %lld rows); split the "
+                     "batch or use b200ft_softmax_xent_fwd_bwd with a caller workspace",
+                     (long long)rows, (long long)kNoAllocMaxRows);
+    return B200FT_ERR_WORKSPACE;
+  }
+  B200FT_CHECK_ARG((uintptr_t)logits % 16 == 0, "softmax_xent_noalloc: logits must be 16-byte aligned");
+  unsigned int* ws = nullptr;
+  int rc = static_scratch_for_current_device(&ws);
+  if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  // count_valid_kernel rewrites the count and zeroes the ticket; every row's loss slot is
+  // rewritten by its CTA, so nothing of the previous call's contents is read.
   count_valid_kernel<<<1, 256, 0, st>>>(targets, rows, ignore_index, ws);
   B200FT_LAUNCH_CHECK();
   softmax_xent_kernel<<<(unsigned)rows, kThreads, 0, st>>>((__nv_bfloat16*)logits, rows, vocab, ld, targets,

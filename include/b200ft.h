@@ -109,6 +109,24 @@ int b200ft_softmax_xent_fwd_bwd(void* logits, int64_t rows, int vocab, int64_t l
                                 float* loss_out, void* workspace, size_t workspace_bytes,
                                 void* stream);
 
+/* Allocation-free form of b200ft_softmax_xent_fwd_bwd (no counterpart in the reference; it
+ * exists for this library's own callers).  Same arguments minus the workspace: the scratch
+ * is a fixed array inside the library's device image, so a caller that cannot allocate device
+ * memory at this point (its pool owns all of it, or it runs inside another framework's
+ * allocator) can still compute the loss.  Limits and rules:
+ *   - rows <= b200ft_softmax_xent_noalloc_max_rows() (65536); more is refused with
+ *     B200FT_ERR_WORKSPACE and a message, nothing is launched;
+ *   - the array (about 256 KB) is resident on every GPU that loads the library until exit;
+ *   - the first call made with a given device current resolves the array's device address
+ *     (cudaGetSymbolAddress); make that first call outside any stream capture;
+ *   - all calls on a device share the one array: two calls that may overlap on the GPU
+ *     (different streams, no dependency) race and give wrong losses — serialise them;
+ *   - the call itself allocates and frees nothing, on the host or the device. */
+int64_t b200ft_softmax_xent_noalloc_max_rows(void);
+int b200ft_softmax_xent_fwd_bwd_noalloc(void* logits, int64_t rows, int vocab, int64_t ld,
+                                        const int64_t* targets, int64_t ignore_index, float grad_scale,
+                                        float* loss_out, void* stream);
+
 /* HF causal-LM target shift (oracle/gpt2_lora_ref.py:causal_lm_loss):
  * targets[b, t] = labels[b, t+1] for t < seq-1, ignore_index at t = seq-1. */
 int b200ft_shift_targets(const int64_t* labels, int64_t* targets, int64_t batch, int seq,
