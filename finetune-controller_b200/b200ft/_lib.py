@@ -13,7 +13,7 @@ from ctypes import POINTER, c_char_p, c_float, c_int, c_int32, c_int64, c_size_t
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libb200ft.so")
 
-EPI_NONE, EPI_RESIDUAL, EPI_GELU, EPI_DGELU = 0, 1, 2, 3
+EPI_NONE, EPI_RESIDUAL, EPI_GELU, EPI_DGELU, EPI_ATOMIC_F32_T = 0, 1, 2, 3, 4
 A_MN_MAJOR, B_MN_MAJOR = 1, 2
 
 
@@ -36,6 +36,7 @@ class GemmArgs(ctypes.Structure):
         ("c2", c_void_p), ("ldc2", c_int64),
         ("block_n", c_int32),
         ("max_ctas", c_int32),
+        ("split_k", c_int32),
     ]
 
 

@@ -11,8 +11,8 @@ import ctypes
 import torch
 
 from . import _lib
-from ._lib import (A_MN_MAJOR, B_MN_MAJOR, EPI_DGELU, EPI_GELU, EPI_NONE, EPI_RESIDUAL, GemmArgs,
-                   check, lib)
+from ._lib import (A_MN_MAJOR, B_MN_MAJOR, EPI_ATOMIC_F32_T, EPI_DGELU, EPI_GELU, EPI_NONE, EPI_RESIDUAL,
+                   GemmArgs, check, lib)
 
 LAUNCHES = 0
 
@@ -55,12 +55,13 @@ def _need_cuda(*ts):
 
 
 def gemm(a, b, out, *, a_mn=False, b_mn=False, a2=None, b2=None, bias=None, epilogue=EPI_NONE,
-         aux=None, out2=None, alpha=1.0, block_n=0, max_ctas=0, m=None, n=None, k=None, k2=None):
+         aux=None, out2=None, alpha=1.0, block_n=0, max_ctas=0, split_k=0, m=None, n=None, k=None, k2=None):
     """out[m,n] = epi(alpha * (A.B^T + A2.B2^T) + bias).  A: [M,K] (K-major) or [K,M] (a_mn);
     B: [N,K] or [K,N] (b_mn); A2 [M,K2], B2 [N,K2].  Row pitch = stride(0)."""
     global LAUNCHES
     _need_cuda(a, b, out, a2, b2, bias, aux, out2)
-    assert a.dtype == b.dtype == out.dtype == torch.bfloat16
+    assert a.dtype == b.dtype == torch.bfloat16
+    assert out.dtype == (torch.float32 if epilogue == EPI_ATOMIC_F32_T else torch.bfloat16)
     assert a.stride(-1) == 1 and b.stride(-1) == 1 and out.stride(-1) == 1
     if m is None:
         m = a.shape[1] if a_mn else a.shape[0]
@@ -68,8 +69,6 @@ def gemm(a, b, out, *, a_mn=False, b_mn=False, a2=None, b2=None, bias=None, epil
         k = a.shape[0] if a_mn else a.shape[1]
     if n is None:
         n = b.shape[1] if b_mn else b.shape[0]
-    kb = b.shape[0] if b_mn else b.shape[1]
-    assert kb >= k or True
     args = GemmArgs()
     args.m, args.n = m, n
     args.a1, args.lda1 = a.data_ptr(), a.stride(0)
@@ -91,7 +90,7 @@ def gemm(a, b, out, *, a_mn=False, b_mn=False, a2=None, b2=None, bias=None, epil
     args.c, args.ldc = out.data_ptr(), out.stride(0)
     if out2 is not None:
         args.c2, args.ldc2 = out2.data_ptr(), out2.stride(0)
-    args.block_n, args.max_ctas = block_n, max_ctas
+    args.block_n, args.max_ctas, args.split_k = block_n, max_ctas, split_k
     kk = k + (args.k2 if a2 is not None else 0)
     with _timed("gemm", 2.0 * m * n * kk, (m, n, kk, int(a_mn), int(b_mn), epilogue)):
         check(lib().b200ft_gemm_bf16(ctypes.byref(args), _stream()), "gemm_bf16")

@@ -54,6 +54,7 @@ struct GemmParams {
   int k1, k2, kblocks1, kblocks2;
   int a_mn, b_mn;
   int tiles_m, tiles_n;
+  int splits, kb_per_split;  // split-K: work item w -> (tile = w / splits, K slabs of split w % splits)
   int epilogue;
   int cw;  // epilogue chunk width in columns: 64 (swizzled staging tile), 32 or 16 (dense)
   float alpha;
@@ -61,6 +62,7 @@ struct GemmParams {
   const __nv_bfloat16* aux; int64_t ld_aux;
   __nv_bfloat16* c; int64_t ldc;
   __nv_bfloat16* c2; int64_t ldc2;
+  float* cf;  // ATOMIC_F32_T: fp32 [N, ldc], cf[n, m] += alpha * acc[m, n]
 };
 
 // ---------------------------------------------------------------------------------------
@@ -199,7 +201,7 @@ template <int CW>
 __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtensorMap* tmC, const CUtensorMap* tmC2,
                                               const CUtensorMap* tmAux, int q, int lane, uint32_t tmem_base,
                                               uint32_t ebuf, uint32_t abar0, uint32_t abar1, uint32_t tfull0,
-                                              uint32_t tempty0, int num_tiles) {
+                                              uint32_t tempty0, int num_work) {
   const int BN = p.BN;
   const int nchunks = BN / CW;
   const bool has_aux = (p.epilogue == B200FT_EPI_RESIDUAL) || (p.epilogue == B200FT_EPI_DGELU);
@@ -208,7 +210,9 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtenso
   uint32_t aux_phase = 0;     // bit b = parity to wait for on aux barrier b
   int acc = 0;
   uint32_t acc_phase = 0;
-  for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+  const bool atomic_t = (p.epilogue == B200FT_EPI_ATOMIC_F32_T);
+  for (int w = blockIdx.x; w < num_work; w += gridDim.x) {
+    const int tile = w / p.splits;
     const int m0 = (tile / p.tiles_n) * kBlockM;
     const int n0 = (tile % p.tiles_n) * BN;
     const int row0 = m0 + q * 32;
@@ -229,6 +233,21 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtenso
       if constexpr (CW == 64) { tmem_ld32(t_row + c * CW, r); tmem_ld32(t_row + c * CW + 32, r + 32); }
       else if constexpr (CW == 32) { tmem_ld32(t_row + c * CW, r); }
       else { tmem_ld16(t_row + c * CW, r); }
+      const int colbase = n0 + c * CW;
+      if (atomic_t) {
+        // split-K partial: fp32 reduction into the transposed output (lanes = consecutive m,
+        // so every red.global.add of a warp hits one 128-byte line)
+        tmem_wait_ld();
+        const int mrow = row0 + lane;
+        if (mrow < p.M) {
+#pragma unroll
+          for (int j = 0; j < CW; ++j) {
+            if (colbase + j < p.N)
+              atomicAdd(p.cf + (int64_t)(colbase + j) * p.ldc + mrow, __uint_as_float(r[j]) * p.alpha);
+          }
+        }
+        continue;
+      }
       if (has_aux) {
         mbar_wait(b ? abar1 : abar0, (aux_phase >> b) & 1u);
         aux_phase ^= (1u << b);
@@ -237,7 +256,6 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtenso
         __syncwarp();
       }
       tmem_wait_ld();
-      const int colbase = n0 + c * CW;
 #pragma unroll
       for (int v = 0; v < CW / 8; ++v) {
         float f[8];
@@ -356,7 +374,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot_ptr;
 
-  const int num_tiles = p.tiles_m * p.tiles_n;
+  const int num_work = p.tiles_m * p.tiles_n * p.splits;
   const int kb_total = p.kblocks1 + p.kblocks2;
   const int BN = p.BN;
 
@@ -367,10 +385,13 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
       const uint32_t b2_bytes = (uint32_t)BN * 128u;
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      for (int w = blockIdx.x; w < num_work; w += gridDim.x) {
+        const int tile = w / p.splits;
         const int m0 = (tile / p.tiles_n) * kBlockM;
         const int n0 = (tile % p.tiles_n) * BN;
-        for (int kb = 0; kb < kb_total; ++kb) {
+        const int kb_begin = (w % p.splits) * p.kb_per_split;
+        const int kb_end = min(kb_total, kb_begin + p.kb_per_split);
+        for (int kb = kb_begin; kb < kb_end; ++kb) {
           mbar_wait(empty_bar(stage), phase ^ 1u);
           const bool seg2 = kb >= p.kblocks1;
           const int kk = (seg2 ? kb - p.kblocks1 : kb) * kBlockK;
@@ -408,11 +429,13 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      for (int w = blockIdx.x; w < num_work; w += gridDim.x) {
         mbar_wait(tempty_bar(acc), acc_phase ^ 1u);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + (uint32_t)(acc * kAccStride);
-        for (int kb = 0; kb < kb_total; ++kb) {
+        const int kb_begin = (w % p.splits) * p.kb_per_split;
+        const int kb_end = min(kb_total, kb_begin + p.kb_per_split);
+        for (int kb = kb_begin; kb < kb_end; ++kb) {
           mbar_wait(full_bar(stage), phase);
           tc_fence_after();
           const bool seg2 = kb >= p.kblocks1;
@@ -430,7 +453,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
                                       : make_smem_desc(a_base + 32u * j, 16u, 1024u);
               const uint64_t bd = bmn ? make_smem_desc(b_base + 2048u * j, 8192u, 1024u)
                                       : make_smem_desc(b_base + 32u * j, 16u, 1024u);
-              umma_bf16(d_tmem, ad, bd, idesc, (kb > 0 || j > 0) ? 1u : 0u);
+              umma_bf16(d_tmem, ad, bd, idesc, (kb > kb_begin || j > 0) ? 1u : 0u);
             }
           }
           umma_commit(empty_bar(stage));  // frees the smem slot when these MMAs retire
@@ -446,11 +469,11 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
     // =============================== epilogue ===============================
     const int q = warp - 4;  // TMEM lane quarter == warp % 4
     if (p.cw == 64)      epilogue_loop<64>(p, &tmC, &tmC2, &tmAux, q, lane, tmem_base, sEpi + q * 2 * kEpiBufBytes,
-                                           aux_bar(q, 0), aux_bar(q, 1), tfull_bar(0), tempty_bar(0), num_tiles);
+                                           aux_bar(q, 0), aux_bar(q, 1), tfull_bar(0), tempty_bar(0), num_work);
     else if (p.cw == 32) epilogue_loop<32>(p, &tmC, &tmC2, &tmAux, q, lane, tmem_base, sEpi + q * 2 * kEpiBufBytes,
-                                           aux_bar(q, 0), aux_bar(q, 1), tfull_bar(0), tempty_bar(0), num_tiles);
+                                           aux_bar(q, 0), aux_bar(q, 1), tfull_bar(0), tempty_bar(0), num_work);
     else                 epilogue_loop<16>(p, &tmC, &tmC2, &tmAux, q, lane, tmem_base, sEpi + q * 2 * kEpiBufBytes,
-                                           aux_bar(q, 0), aux_bar(q, 1), tfull_bar(0), tempty_bar(0), num_tiles);
+                                           aux_bar(q, 0), aux_bar(q, 1), tfull_bar(0), tempty_bar(0), num_work);
   }
 
   tc_fence_before();
@@ -537,8 +560,13 @@ extern "C" int b200ft_gemm_bf16(const b200ft_gemm_args* a, void* stream) {
   B200FT_CHECK_ARG(a != nullptr, "gemm: null args");
   B200FT_CHECK_ARG(a->m > 0 && a->n > 0 && a->k1 > 0, "gemm: m=%d n=%d k1=%d", a->m, a->n, a->k1);
   B200FT_CHECK_ARG(a->a1 && a->b1 && a->c, "gemm: null operand");
-  B200FT_CHECK_ARG(a->n % 8 == 0 && a->ldc % 8 == 0 && a->ldc >= a->n, "gemm: n=%d ldc=%lld must be multiples of 8", a->n,
-                   (long long)a->ldc);
+  const bool atomic_t = a->epilogue == B200FT_EPI_ATOMIC_F32_T;
+  if (atomic_t)
+    B200FT_CHECK_ARG(a->n % 8 == 0 && a->ldc >= a->m, "gemm: ATOMIC_F32_T needs n %% 8 == 0 and ldc >= m (n=%d m=%d ldc=%lld)",
+                     a->n, a->m, (long long)a->ldc);
+  else
+    B200FT_CHECK_ARG(a->n % 8 == 0 && a->ldc % 8 == 0 && a->ldc >= a->n, "gemm: n=%d ldc=%lld must be multiples of 8", a->n,
+                     (long long)a->ldc);
   B200FT_CHECK_ARG(a->lda1 % 8 == 0 && a->ldb1 % 8 == 0, "gemm: lda1=%lld ldb1=%lld must be multiples of 8",
                    (long long)a->lda1, (long long)a->ldb1);
   B200FT_CHECK_ARG(((uintptr_t)a->a1 | (uintptr_t)a->b1 | (uintptr_t)a->c) % 16 == 0, "gemm: 16-byte alignment required");
@@ -549,7 +577,9 @@ extern "C" int b200ft_gemm_bf16(const b200ft_gemm_args* a, void* stream) {
                      "gemm: bad second segment (k2=%d lda2=%lld ldb2=%lld)", a->k2, (long long)a->lda2,
                      (long long)a->ldb2);
   }
-  B200FT_CHECK_ARG(a->epilogue >= 0 && a->epilogue <= 3, "gemm: epilogue=%d", a->epilogue);
+  B200FT_CHECK_ARG(a->epilogue >= 0 && a->epilogue <= 4, "gemm: epilogue=%d", a->epilogue);
+  B200FT_CHECK_ARG(a->split_k >= 0 && (a->split_k <= 1 || atomic_t), "gemm: split_k=%d needs the ATOMIC_F32_T epilogue",
+                   a->split_k);
   if (a->epilogue == B200FT_EPI_RESIDUAL || a->epilogue == B200FT_EPI_DGELU)
     B200FT_CHECK_ARG(a->aux && a->ld_aux % 8 == 0 && (uintptr_t)a->aux % 16 == 0, "gemm: epilogue needs aux");
   if (a->epilogue == B200FT_EPI_GELU)
@@ -576,14 +606,28 @@ extern "C" int b200ft_gemm_bf16(const b200ft_gemm_args* a, void* stream) {
   p.aux = (const __nv_bfloat16*)a->aux; p.ld_aux = a->ld_aux;
   p.c = (__nv_bfloat16*)a->c; p.ldc = a->ldc;
   p.c2 = (__nv_bfloat16*)a->c2; p.ldc2 = a->ldc2;
+  p.cf = (float*)a->c;
+  {
+    const int kb_total = p.kblocks1 + p.kblocks2;
+    int splits = a->split_k > 0 ? a->split_k : 1;
+    if (atomic_t && a->split_k == 0) {  // fill the machine: tiles * splits ~ one wave of CTAs
+      const int tiles = p.tiles_m * p.tiles_n;
+      splits = ctas_max / (tiles < 1 ? 1 : tiles);
+    }
+    if (splits < 1) splits = 1;
+    if (splits > kb_total) splits = kb_total;
+    p.kb_per_split = (kb_total + splits - 1) / splits;
+    p.splits = (kb_total + p.kb_per_split - 1) / p.kb_per_split;  // no empty split
+  }
 
   p.cw = (BN % 64 == 0) ? 64 : (BN % 32 == 0 ? 32 : 16);
   CUtensorMap tA1, tB1, tA2, tB2, tC, tC2, tAux;
   int rc;
   // epilogue staging tiles: {cw columns, 32 rows}; the 64-wide one is 128B-swizzled
-  rc = get_tensor_map(a->c, (uint64_t)a->n, (uint64_t)a->m, (uint64_t)a->ldc, (uint32_t)p.cw, 32, &tC, p.cw == 64);
-  if (rc) return rc;
-  tC2 = tC; tAux = tC;
+  if (!atomic_t) {
+    rc = get_tensor_map(a->c, (uint64_t)a->n, (uint64_t)a->m, (uint64_t)a->ldc, (uint32_t)p.cw, 32, &tC, p.cw == 64);
+    if (rc) return rc;
+  }
   if (a->epilogue == B200FT_EPI_GELU) {
     rc = get_tensor_map(a->c2, (uint64_t)a->n, (uint64_t)a->m, (uint64_t)a->ldc2, (uint32_t)p.cw, 32, &tC2, p.cw == 64);
     if (rc) return rc;
@@ -606,6 +650,9 @@ extern "C" int b200ft_gemm_bf16(const b200ft_gemm_args* a, void* stream) {
   } else {
     tA2 = tA1; tB2 = tB1;
   }
+  if (atomic_t) tC = tA1;  // unused by this epilogue; any valid descriptor
+  if (a->epilogue != B200FT_EPI_GELU) tC2 = tC;
+  if (!(a->epilogue == B200FT_EPI_RESIDUAL || a->epilogue == B200FT_EPI_DGELU)) tAux = tC;
 
   // the opt-in shared-memory size is a per-device function attribute
   static thread_local int attr_dev = -1;
@@ -615,8 +662,8 @@ extern "C" int b200ft_gemm_bf16(const b200ft_gemm_args* a, void* stream) {
     B200FT_CUDA(cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
     attr_dev = dev;
   }
-  const int num_tiles = p.tiles_m * p.tiles_n;
-  const int grid = num_tiles < ctas_max ? num_tiles : ctas_max;
+  const int num_work = p.tiles_m * p.tiles_n * p.splits;
+  const int grid = num_work < ctas_max ? num_work : ctas_max;
   gemm_bf16_tcgen05_kernel<<<grid, kThreads, kSmemBytes, (cudaStream_t)stream>>>(tA1, tB1, tA2, tB2, tC, tC2, tAux, p);
   B200FT_LAUNCH_CHECK();
   return 0;

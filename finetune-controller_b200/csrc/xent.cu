@@ -16,6 +16,13 @@
 namespace {
 
 constexpr int kThreads = 256;
+constexpr int kUnroll = 4;
+
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kLn2 = 0.6931471805599453f;
 
@@ -65,25 +72,48 @@ softmax_xent_kernel(__nv_bfloat16* __restrict__ logits, int64_t rows, int vocab,
   __shared__ bool s_last;
 
   if (valid) {
-    // ---- sweep 1: online max / sum in the log2 domain ----
+    // ---- sweep 1: online max / sum in the log2 domain, kUnroll independent 16-byte loads in
+    // flight per thread (the running max is revisited once per 8*kUnroll elements) ----
     MS acc{-INFINITY, 0.f};
-    for (int i = threadIdx.x; i < nvec; i += kThreads) {
-      float f[8];
-      unpack8(ld_cg16(z + ((int64_t)i << 3)), f);
-      const int c0 = i << 3;
+    for (int i0 = threadIdx.x; i0 < nvec; i0 += kThreads * kUnroll) {
+      uint4 q[kUnroll];
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) {
+        const int i = i0 + u * kThreads;
+        if (i < nvec) q[u] = ld_cg16(z + ((int64_t)i << 3));
+      }
+      float f[kUnroll][8];
       float vmax = -INFINITY;
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        f[j] = (c0 + j < vocab) ? f[j] * kLog2e : -INFINITY;
-        vmax = fmaxf(vmax, f[j]);
+      for (int u = 0; u < kUnroll; ++u) {
+        const int i = i0 + u * kThreads;
+        const int c0 = i << 3;
+        if (i < nvec) {
+          unpack8(q[u], f[u]);
+          if (c0 + 8 <= vocab) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) { f[u][j] *= kLog2e; vmax = fmaxf(vmax, f[u][j]); }
+          } else {  // the vector straddling (or beyond) the end of the vocabulary
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              f[u][j] = (c0 + j < vocab) ? f[u][j] * kLog2e : -INFINITY;
+              vmax = fmaxf(vmax, f[u][j]);
+            }
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) f[u][j] = -INFINITY;
+        }
       }
-      if (vmax > acc.m) {  // rare after the first few vectors
-        acc.s *= exp2f(acc.m - vmax);  // exp2f(-inf) = 0 on the first hit
+      if (vmax > acc.m) {  // rare after the first few iterations
+        acc.s *= ex2_approx(acc.m - vmax);  // ex2(-inf) = 0 on the first hit
         acc.m = vmax;
       }
       if (acc.m != -INFINITY) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j) acc.s += exp2f(f[j] - acc.m);
+        for (int u = 0; u < kUnroll; ++u)
+#pragma unroll
+          for (int j = 0; j < 8; ++j) acc.s += ex2_approx(f[u][j] - acc.m);
       }
     }
 #pragma unroll
@@ -100,7 +130,8 @@ softmax_xent_kernel(__nv_bfloat16* __restrict__ logits, int64_t rows, int vocab,
       for (int w = 1; w < kThreads / 32; ++w) t = ms_merge(t, red[w]);
       float lse2 = t.m + log2f(t.s);
       s_lse2 = lse2;
-      float zt = __bfloat162float(z[tgt]) * kLog2e;
+      const int64_t tsafe = tgt < 0 ? 0 : (tgt >= vocab ? vocab - 1 : tgt);  // never read out of the row
+      float zt = __bfloat162float(z[tsafe]) * kLog2e;
       row_loss[row] = (lse2 - zt) * kLn2;
     }
     __syncthreads();
@@ -108,28 +139,43 @@ softmax_xent_kernel(__nv_bfloat16* __restrict__ logits, int64_t rows, int vocab,
     row_loss[row] = 0.f;
   }
 
-  // ---- sweep 2: write the gradient in place ----
+  // ---- sweep 2: write the gradient in place (row re-read from L2) ----
   const unsigned int n_valid = ws[0];
   const float scale = valid ? grad_scale / (float)(n_valid > 0 ? n_valid : 1) : 0.f;
   const float lse2 = valid ? s_lse2 : 0.f;
   const int tcol = valid ? (int)tgt : -1;
-  for (int i = threadIdx.x; i < nvec; i += kThreads) {
-    __nv_bfloat16* pz = z + ((int64_t)i << 3);
-    float f[8];
-    if (valid) {
-      unpack8(ld_cg16(pz), f);
-      const int c0 = i << 3;
+  if (valid) {
+    for (int i0 = threadIdx.x; i0 < nvec; i0 += kThreads * kUnroll) {
+      uint4 q[kUnroll];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        float p = exp2f(f[j] * kLog2e - lse2);
-        p = (c0 + j == tcol) ? p - 1.f : p;
-        f[j] = (c0 + j < vocab) ? p * scale : 0.f;
+      for (int u = 0; u < kUnroll; ++u) {
+        const int i = i0 + u * kThreads;
+        if (i < nvec) q[u] = ld_cg16(z + ((int64_t)i << 3));
       }
-    } else {
 #pragma unroll
-      for (int j = 0; j < 8; ++j) f[j] = 0.f;
+      for (int u = 0; u < kUnroll; ++u) {
+        const int i = i0 + u * kThreads;
+        if (i < nvec) {
+          const int c0 = i << 3;
+          float f[8];
+          unpack8(q[u], f);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) f[j] = ex2_approx(f[j] * kLog2e - lse2) * scale;
+          if (tcol >= c0 && tcol < c0 + 8) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) if (c0 + j == tcol) f[j] -= scale;
+          }
+          if (c0 + 8 > vocab) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) if (c0 + j >= vocab) f[j] = 0.f;
+          }
+          st_stream16(z + ((int64_t)i << 3), pack8(f));
+        }
+      }
     }
-    st_stream16(pz, pack8(f));
+  } else {
+    const uint4 zero = make_uint4(0u, 0u, 0u, 0u);
+    for (int i = threadIdx.x; i < nvec; i += kThreads) st_stream16(z + ((int64_t)i << 3), zero);
   }
 
   // ---- last CTA folds the per-row losses ----

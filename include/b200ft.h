@@ -52,6 +52,9 @@ const char* b200ft_last_error_string(void);
  *            RESIDUAL : C = v + AUX[m,n]
  *            GELU     : C = v, C2 = gelu_new(v)
  *            DGELU    : C = v * gelu_new'(AUX[m,n])
+ *            ATOMIC_F32_T : C is fp32 [n, ldc]; C[n_i, m_i] += alpha*acc[m_i, n_i] (atomic), so
+ *                       the reduction can be split over K slabs (split_k) across CTAs; no bias.
+ *                       Used for the adapter-gradient contractions over tokens.
  *
  * The second K segment is how a LoRA branch is fused: with A2 = s*(X*A_lora) and
  * B2 = B_lora^T it adds the rank-r product into the same TMEM accumulator as the frozen
@@ -63,7 +66,8 @@ enum {
   B200FT_EPI_NONE = 0,
   B200FT_EPI_RESIDUAL = 1,
   B200FT_EPI_GELU = 2,
-  B200FT_EPI_DGELU = 3
+  B200FT_EPI_DGELU = 3,
+  B200FT_EPI_ATOMIC_F32_T = 4
 };
 enum { B200FT_A_MN_MAJOR = 1, B200FT_B_MN_MAJOR = 2 };
 
@@ -84,6 +88,7 @@ typedef struct b200ft_gemm_args {
   void* c2; int64_t ldc2;         /* bf16 [m, ldc2], GELU only */
   int32_t block_n;                /* 0 = choose; else multiple of 16 in [16,256] */
   int32_t max_ctas;               /* 0 = one per SM */
+  int32_t split_k;                /* ATOMIC_F32_T only: 0 = choose, else number of K splits */
 } b200ft_gemm_args;
 
 int b200ft_gemm_bf16(const b200ft_gemm_args* args_host, void* stream);
@@ -91,7 +96,10 @@ int b200ft_gemm_bf16(const b200ft_gemm_args* args_host, void* stream);
 /* ---------------------------------------------------------------------------------------
  * Adapter-gradient contraction over tokens (dB = s*(XA)^T*dY,
  * dA = X^T*(s*dY*B^T)):   out[i, c] += alpha * sum_m S[m, i] * T[m, c],  i < r, c < cols.
- * S, T bf16; out fp32 [r, ld_out], accumulated into (zero it first).  r <= 16.
+ * S, T bf16; out fp32 [r, ld_out], accumulated into (zero it first).  r = 8 or 16; ld_s, ld_t
+ * multiples of 8.  Runs on the tcgen05 GEMM (both operands MN-major, split-K over tokens,
+ * ATOMIC_F32_T epilogue): the sum order across splits is not fixed, results are reproducible
+ * to fp32 rounding, not bitwise.
  * ------------------------------------------------------------------------------------- */
 int b200ft_lora_grad(const void* s, int64_t ld_s, int r, const void* t, int64_t ld_t, int cols,
                      int64_t m, float* out, int64_t ld_out, float alpha, void* stream);

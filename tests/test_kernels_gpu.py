@@ -280,6 +280,19 @@ def test_gemm_persistent_many_tiles(ops):
     _gemm_case(ops, 4096, 2304, 256)
 
 
+@pytest.mark.parametrize("M,N,K,split_k", [(256, 16, 4096, 0), (200, 8, 1000, 3), (768, 16, 32768, 0), (128, 64, 640, 5)])
+def test_gemm_splitk_atomic_transposed(ops, M, N, K, split_k):
+    # the adapter-gradient shape: both operands MN-major, long reduction, fp32 C^T accumulated
+    g = torch.Generator().manual_seed(M + K)
+    A = bf16_round(torch.randn(K, M, generator=g))       # [K, M]: M contiguous
+    Bm = bf16_round(torch.randn(K, N, generator=g))      # [K, N]: N contiguous
+    out = torch.ones(N, M, device=DEV)                   # accumulates on top of what is there
+    ops.gemm(A.to(DEV, torch.bfloat16), Bm.to(DEV, torch.bfloat16), out, a_mn=True, b_mn=True, epilogue=4,
+             alpha=0.5, split_k=split_k)
+    exp = 1.0 + 0.5 * (Bm.double().t() @ A.double())
+    torch.testing.assert_close(out.cpu().double(), exp, rtol=1e-4, atol=1e-3 * (K ** 0.5))
+
+
 def test_gemm_rejects_bad_arguments(ops):
     from b200ft._lib import B200FTError
     a = torch.zeros(128, 60, dtype=torch.bfloat16, device=DEV)  # K pitch 60 is not a multiple of 8
