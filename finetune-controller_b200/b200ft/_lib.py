@@ -37,6 +37,7 @@ class GemmArgs(ctypes.Structure):
         ("block_n", c_int32),
         ("max_ctas", c_int32),
         ("split_k", c_int32),
+        ("cta_group", c_int32),
     ]
 
 

@@ -55,7 +55,7 @@ def _need_cuda(*ts):
 
 
 def gemm(a, b, out, *, a_mn=False, b_mn=False, a2=None, b2=None, bias=None, epilogue=EPI_NONE,
-         aux=None, out2=None, alpha=1.0, block_n=0, max_ctas=0, split_k=0, m=None, n=None, k=None, k2=None):
+         aux=None, out2=None, alpha=1.0, block_n=0, max_ctas=0, split_k=0, cta_group=0, m=None, n=None, k=None, k2=None):
     """out[m,n] = epi(alpha * (A.B^T + A2.B2^T) + bias).  A: [M,K] (K-major) or [K,M] (a_mn);
     B: [N,K] or [K,N] (b_mn); A2 [M,K2], B2 [N,K2].  Row pitch = stride(0)."""
     global LAUNCHES
@@ -90,7 +90,7 @@ def gemm(a, b, out, *, a_mn=False, b_mn=False, a2=None, b2=None, bias=None, epil
     args.c, args.ldc = out.data_ptr(), out.stride(0)
     if out2 is not None:
         args.c2, args.ldc2 = out2.data_ptr(), out2.stride(0)
-    args.block_n, args.max_ctas, args.split_k = block_n, max_ctas, split_k
+    args.block_n, args.max_ctas, args.split_k, args.cta_group = block_n, max_ctas, split_k, cta_group
     kk = k + (args.k2 if a2 is not None else 0)
     with _timed("gemm", 2.0 * m * n * kk, (m, n, kk, int(a_mn), int(b_mn), epilogue)):
         check(lib().b200ft_gemm_bf16(ctypes.byref(args), _stream()), "gemm_bf16")

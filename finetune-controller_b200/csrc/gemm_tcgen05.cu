@@ -1,6 +1,16 @@
 // bf16 GEMM on Blackwell 5th-gen tensor cores: TMA -> shared memory (128B swizzle) ->
 // tcgen05.mma (fp32 accumulators in TMEM) -> tcgen05.ld epilogue.
 //
+// Two instantiations of one kernel template:
+//   CG = 1  one CTA per 128 x BN tile (cta_group::1), 4-stage ring.  Handles every layout
+//           (K-major / MN-major operands), split-K, tiny N.
+//   CG = 2  a cluster of two CTAs (one TPC) per 256 x BN tile (cta_group::2): each CTA stages
+//           its own 128 rows of A and HALF of the B tile, the leader CTA issues 256 x BN x 16
+//           UMMAs that read both CTAs' shared memory and write both CTAs' TMEM.  Per FLOP this
+//           moves 2/3 of the operand bytes of CG = 1 from L2 into the SMs — and the L2->SM
+//           fabric (~42 B/clk/SM), not the tensor pipe, is what bounds CG = 1 (measured:
+//           profiles/README.md) — and the halved B stage allows a 6-stage ring.
+//
 // Persistent, warp-specialised, one CTA per SM (256 threads):
 //   warp 0 : TMA producer (one lane)          smem ring of kStages {A 128x64, B BNx64} slabs
 //   warp 1 : MMA issuer (one lane)            128 x BN x 16 UMMAs, 4 per K slab
@@ -35,10 +45,15 @@ namespace {
 constexpr int kBlockM = 128;
 constexpr int kBlockK = 64;  // 64 bf16 = 128 B = one swizzle row
 constexpr int kMaxBN = 256;
-constexpr int kStages = 4;
 constexpr int kAStageBytes = kBlockM * kBlockK * 2;  // 16 KB
-constexpr int kBStageBytes = kMaxBN * kBlockK * 2;   // 32 KB
-constexpr int kTileBytes = kStages * (kAStageBytes + kBStageBytes);
+constexpr int kTileBytes = 4 * (kAStageBytes + kMaxBN * kBlockK * 2);  // 192 KB of operand ring either way
+template <int CG> struct RingCfg {
+  static constexpr int kStages = CG == 1 ? 4 : 6;
+  static constexpr int kBStageBytes = kMaxBN / CG * kBlockK * 2;  // 32 KB, or 16 KB (half of B per CTA)
+  static_assert(kStages * (kAStageBytes + kBStageBytes) == kTileBytes, "ring size");
+};
+constexpr int kMaxStages = 6;
+constexpr uint32_t kPeerBitMask = 0xFEFFFFFFu;  // clears the CTA-rank bit of a shared::cluster address -> CTA 0
 constexpr int kEpiBufBytes = 32 * 64 * 2;              // one 32-row x 64-col bf16 staging tile
 constexpr int kEpiBytes = 4 * 2 * kEpiBufBytes;        // 4 epilogue warps x 2 tiles = 32 KB
 constexpr int kBarrierBytes = 256;
@@ -102,6 +117,55 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map
       ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(c0), "r"(c1), "r"(bar)
       : "memory");
 }
+// cta_group::2 forms -------------------------------------------------------------------
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// arrive on the barrier at the same offset in CTA `cta` of the cluster
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t bar, uint32_t cta) {
+  asm volatile(
+      "{\n\t.reg .b32 remote;\n\t"
+      "mapa.shared::cluster.u32 remote, %0, %1;\n\t"
+      "mbarrier.arrive.shared::cluster.b64 _, [remote];\n\t}"
+      ::"r"(bar), "r"(cta)
+      : "memory");
+}
+// TMA load issued by either CTA of a pair; completion bytes are credited to CTA 0's barrier
+__device__ __forceinline__ void tma_load_2d_cg2(uint32_t dst, const CUtensorMap* map, int c0, int c1, uint32_t bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+      ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(c0), "r"(c1), "r"(bar & kPeerBitMask)
+      : "memory");
+}
+__device__ __forceinline__ void umma_bf16_cg2(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// commit: arrive on the barrier at this offset in BOTH CTAs of the pair when the MMAs retire
+__device__ __forceinline__ void umma_commit_cg2(uint32_t bar) {
+  asm volatile(
+      "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+      ::"r"(bar), "h"((uint16_t)3)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_alloc_cg2(uint32_t smem_dst, uint32_t ncols) {
+  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_dst), "r"(ncols) : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc_cg2(uint32_t taddr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+
 __device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, uint32_t src, int c0, int c1) {
   asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
                ::"l"(reinterpret_cast<uint64_t>(map)), "r"(src), "r"(c0), "r"(c1)
@@ -181,9 +245,9 @@ __device__ __forceinline__ uint64_t make_smem_desc(uint32_t addr, uint32_t lbo_b
 }
 // instruction descriptor (kind::f16): D fp32 [4,6)=1, A bf16 [7,10)=1, B bf16 [10,13)=1,
 // A major [15], B major [16] (1 = MN-major), N>>3 [17,23), M>>4 [24,29)
-__device__ __forceinline__ uint32_t make_idesc(int n, int a_mn, int b_mn) {
+__device__ __forceinline__ uint32_t make_idesc(int m, int n, int a_mn, int b_mn) {
   return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)a_mn << 15) | ((uint32_t)b_mn << 16) |
-         ((uint32_t)(n >> 3) << 17) | ((uint32_t)(kBlockM >> 4) << 24);
+         ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
 }
 
 
@@ -197,11 +261,12 @@ __device__ __forceinline__ uint32_t epi_vec_addr(uint32_t buf, int lane, int v) 
   else return buf + lane * (CW * 2) + (v << 4);                               // dense rows (SWIZZLE_NONE)
 }
 
-template <int CW>
+template <int CW, int CG>
 __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtensorMap* tmC, const CUtensorMap* tmC2,
                                               const CUtensorMap* tmAux, int q, int lane, uint32_t tmem_base,
                                               uint32_t ebuf, uint32_t abar0, uint32_t abar1, uint32_t tfull0,
-                                              uint32_t tempty0, int num_work) {
+                                              uint32_t tempty0, int num_work, int w_begin, int w_stride,
+                                              int cta_rank) {
   const int BN = p.BN;
   const int nchunks = BN / CW;
   const bool has_aux = (p.epilogue == B200FT_EPI_RESIDUAL) || (p.epilogue == B200FT_EPI_DGELU);
@@ -211,9 +276,9 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtenso
   int acc = 0;
   uint32_t acc_phase = 0;
   const bool atomic_t = (p.epilogue == B200FT_EPI_ATOMIC_F32_T);
-  for (int w = blockIdx.x; w < num_work; w += gridDim.x) {
+  for (int w = w_begin; w < num_work; w += w_stride) {
     const int tile = w / p.splits;
-    const int m0 = (tile / p.tiles_n) * kBlockM;
+    const int m0 = (tile / p.tiles_n) * (kBlockM * CG) + cta_rank * kBlockM;
     const int n0 = (tile % p.tiles_n) * BN;
     const int row0 = m0 + q * 32;
     if (has_aux && lane == 0) {  // first chunk's operand: in flight while the MMAs of this tile finish
@@ -321,7 +386,10 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtenso
     }
     tc_fence_before();
     __syncwarp();
-    if (lane == 0) mbar_arrive(tempty0 + 8u * acc);
+    if (lane == 0) {  // accumulator drained: tell the MMA issuer (it lives in CTA 0 of the pair)
+      if constexpr (CG == 1) mbar_arrive(tempty0 + 8u * acc);
+      else mbar_arrive_cluster(tempty0 + 8u * acc, 0);
+    }
     acc ^= 1;
     if (acc == 0) acc_phase ^= 1u;
   }
@@ -332,29 +400,35 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtenso
 // ---------------------------------------------------------------------------------------
 // the kernel
 // ---------------------------------------------------------------------------------------
+template <int CG>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmB1,
                          const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmB2,
                          const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmC2,
                          const __grid_constant__ CUtensorMap tmAux, const GemmParams p) {
+  constexpr int kStages = RingCfg<CG>::kStages;
+  constexpr int kBStageBytes = RingCfg<CG>::kBStageBytes;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
-  const uint32_t base = (raw + 1023u) & ~1023u;
+  const uint32_t base = (raw + 1023u) & ~1023u;  // identical in both CTAs of a pair (same kernel, same layout)
   const uint32_t sA = base;
   const uint32_t sB = base + kStages * kAStageBytes;
   const uint32_t sEpi = base + kTileBytes;
   const uint32_t bars = sEpi + kEpiBytes;
   auto full_bar = [&](int s) { return bars + 8u * s; };
-  auto empty_bar = [&](int s) { return bars + 8u * (kStages + s); };
-  auto tfull_bar = [&](int a) { return bars + 8u * (2 * kStages + a); };
-  auto tempty_bar = [&](int a) { return bars + 8u * (2 * kStages + 2 + a); };
-  auto aux_bar = [&](int q, int b) { return bars + 8u * (2 * kStages + 4 + 2 * q + b); };
-  const uint32_t tmem_slot = bars + 8u * (2 * kStages + 12);
+  auto empty_bar = [&](int s) { return bars + 8u * (kMaxStages + s); };
+  auto tfull_bar = [&](int a) { return bars + 8u * (2 * kMaxStages + a); };
+  auto tempty_bar = [&](int a) { return bars + 8u * (2 * kMaxStages + 2 + a); };
+  auto aux_bar = [&](int q, int b) { return bars + 8u * (2 * kMaxStages + 4 + 2 * q + b); };
+  const uint32_t tmem_slot = bars + 8u * (2 * kMaxStages + 12);
   volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(
-      smem_raw + (base - raw) + kTileBytes + kEpiBytes + 8 * (2 * kStages + 12));
+      smem_raw + (base - raw) + kTileBytes + kEpiBytes + 8 * (2 * kMaxStages + 12));
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  const int cta_rank = CG == 1 ? 0 : (int)cluster_ctarank();
+  const int w_begin = blockIdx.x / CG;   // work items are handed to CTA pairs when CG == 2
+  const int w_stride = gridDim.x / CG;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA1);
@@ -363,14 +437,18 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
     tma_prefetch_desc(&tmC);
   }
   if (warp == 1 && lane == 0) {
-    for (int s = 0; s < kStages; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
-    for (int a = 0; a < 2; ++a) { mbar_init(tfull_bar(a), 1); mbar_init(tempty_bar(a), 4); }
+    for (int s = 0; s < kStages; ++s) { mbar_init(full_bar(s), CG); mbar_init(empty_bar(s), 1); }
+    for (int a = 0; a < 2; ++a) { mbar_init(tfull_bar(a), 1); mbar_init(tempty_bar(a), 4 * CG); }
     for (int q = 0; q < 4; ++q) { mbar_init(aux_bar(q, 0), 1); mbar_init(aux_bar(q, 1), 1); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (warp == 2) tmem_alloc(tmem_slot, kTmemCols);
+  if (warp == 2) {
+    if constexpr (CG == 1) tmem_alloc(tmem_slot, kTmemCols);
+    else tmem_alloc_cg2(tmem_slot, kTmemCols);
+  }
   tc_fence_before();
-  __syncthreads();
+  if constexpr (CG == 1) __syncthreads();
+  else cluster_sync_all();  // the peer's barriers must be initialised before anything remote touches them
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot_ptr;
 
@@ -379,16 +457,17 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
   const int BN = p.BN;
 
   if (warp == 0) {
-    // =============================== TMA producer ===============================
+    // =============================== TMA producer (every CTA) ===============================
     if (lane == 0) {
-      const uint32_t b_bytes = p.b_mn ? (uint32_t)((BN + 63) / 64) * 8192u : (uint32_t)BN * 128u;
-      const uint32_t b2_bytes = (uint32_t)BN * 128u;
+      const uint32_t b_rows = (uint32_t)BN / CG;  // CG == 2: this CTA stages half of the B tile
+      const uint32_t b_bytes = (CG == 1 && p.b_mn) ? (uint32_t)((BN + 63) / 64) * 8192u : b_rows * 128u;
+      const uint32_t b2_bytes = b_rows * 128u;
       int stage = 0;
       uint32_t phase = 0;
-      for (int w = blockIdx.x; w < num_work; w += gridDim.x) {
+      for (int w = w_begin; w < num_work; w += w_stride) {
         const int tile = w / p.splits;
-        const int m0 = (tile / p.tiles_n) * kBlockM;
-        const int n0 = (tile % p.tiles_n) * BN;
+        const int m0 = (tile / p.tiles_n) * (kBlockM * CG) + cta_rank * kBlockM;
+        const int n0 = (tile % p.tiles_n) * BN + cta_rank * (int)b_rows;
         const int kb_begin = (w % p.splits) * p.kb_per_split;
         const int kb_end = min(kb_total, kb_begin + p.kb_per_split);
         for (int kb = kb_begin; kb < kb_end; ++kb) {
@@ -398,22 +477,32 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
           const uint32_t a_dst = sA + stage * kAStageBytes;
           const uint32_t b_dst = sB + stage * kBStageBytes;
           const uint32_t fb = full_bar(stage);
-          mbar_expect_tx(fb, (uint32_t)kAStageBytes + (seg2 ? b2_bytes : b_bytes));
-          if (seg2) {
-            tma_load_2d(a_dst, &tmA2, kk, m0, fb);
-            tma_load_2d(b_dst, &tmB2, kk, n0, fb);
+          const uint32_t bytes = (uint32_t)kAStageBytes + (seg2 ? b2_bytes : b_bytes);
+          if constexpr (CG == 1) {
+            mbar_expect_tx(fb, bytes);
+            if (seg2) {
+              tma_load_2d(a_dst, &tmA2, kk, m0, fb);
+              tma_load_2d(b_dst, &tmB2, kk, n0, fb);
+            } else {
+              if (p.a_mn) {
+                tma_load_2d(a_dst, &tmA1, m0, kk, fb);
+                tma_load_2d(a_dst + 8192u, &tmA1, m0 + 64, kk, fb);
+              } else {
+                tma_load_2d(a_dst, &tmA1, kk, m0, fb);
+              }
+              if (p.b_mn) {
+                for (int j = 0; j * 64 < BN; ++j) tma_load_2d(b_dst + 8192u * j, &tmB1, n0 + 64 * j, kk, fb);
+              } else {
+                tma_load_2d(b_dst, &tmB1, kk, n0, fb);
+              }
+            }
           } else {
-            if (p.a_mn) {
-              tma_load_2d(a_dst, &tmA1, m0, kk, fb);
-              tma_load_2d(a_dst + 8192u, &tmA1, m0 + 64, kk, fb);
-            } else {
-              tma_load_2d(a_dst, &tmA1, kk, m0, fb);
-            }
-            if (p.b_mn) {
-              for (int j = 0; j * 64 < BN; ++j) tma_load_2d(b_dst + 8192u * j, &tmB1, n0 + 64 * j, kk, fb);
-            } else {
-              tma_load_2d(b_dst, &tmB1, kk, n0, fb);
-            }
+            // both CTAs' bytes land on CTA 0's barrier: the leader arms it with the pair's total,
+            // the peer adds its (byte-less) arrival
+            if (cta_rank == 0) mbar_expect_tx(fb, 2u * bytes);
+            else mbar_arrive_cluster(fb, 0);
+            tma_load_2d_cg2(a_dst, seg2 ? &tmA2 : &tmA1, kk, m0, fb);
+            tma_load_2d_cg2(b_dst, seg2 ? &tmB2 : &tmB1, kk, n0, fb);
           }
           if (++stage == kStages) { stage = 0; phase ^= 1u; }
         }
@@ -421,15 +510,15 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
     }
     __syncwarp();
   } else if (warp == 1) {
-    // =============================== MMA issuer ===============================
-    if (lane == 0) {
-      const uint32_t idesc1 = make_idesc(BN, p.a_mn, p.b_mn);
-      const uint32_t idesc2 = make_idesc(BN, 0, 0);
+    // =============================== MMA issuer (CTA 0 of a pair) ===============================
+    if (lane == 0 && cta_rank == 0) {
+      const uint32_t idesc1 = make_idesc(kBlockM * CG, BN, p.a_mn, p.b_mn);
+      const uint32_t idesc2 = make_idesc(kBlockM * CG, BN, 0, 0);
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
-      for (int w = blockIdx.x; w < num_work; w += gridDim.x) {
+      for (int w = w_begin; w < num_work; w += w_stride) {
         mbar_wait(tempty_bar(acc), acc_phase ^ 1u);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + (uint32_t)(acc * kAccStride);
@@ -442,7 +531,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
           const int kk = (seg2 ? kb - p.kblocks1 : kb) * kBlockK;
           const int kleft = (seg2 ? p.k2 : p.k1) - kk;
           const int nmma = kleft >= kBlockK ? 4 : (kleft + 15) / 16;
-          const bool amn = !seg2 && p.a_mn, bmn = !seg2 && p.b_mn;
+          const bool amn = CG == 1 && !seg2 && p.a_mn, bmn = CG == 1 && !seg2 && p.b_mn;
           const uint32_t a_base = sA + stage * kAStageBytes;
           const uint32_t b_base = sB + stage * kBStageBytes;
           const uint32_t idesc = seg2 ? idesc2 : idesc1;
@@ -453,34 +542,45 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
                                       : make_smem_desc(a_base + 32u * j, 16u, 1024u);
               const uint64_t bd = bmn ? make_smem_desc(b_base + 2048u * j, 8192u, 1024u)
                                       : make_smem_desc(b_base + 32u * j, 16u, 1024u);
-              umma_bf16(d_tmem, ad, bd, idesc, (kb > kb_begin || j > 0) ? 1u : 0u);
+              if constexpr (CG == 1) umma_bf16(d_tmem, ad, bd, idesc, (kb > kb_begin || j > 0) ? 1u : 0u);
+              else umma_bf16_cg2(d_tmem, ad, bd, idesc, (kb > kb_begin || j > 0) ? 1u : 0u);
             }
           }
-          umma_commit(empty_bar(stage));  // frees the smem slot when these MMAs retire
+          // frees the smem slot (in both CTAs when CG == 2) once these MMAs retire
+          if constexpr (CG == 1) umma_commit(empty_bar(stage));
+          else umma_commit_cg2(empty_bar(stage));
           if (++stage == kStages) { stage = 0; phase ^= 1u; }
         }
-        umma_commit(tfull_bar(acc));  // accumulator complete -> epilogue
+        // accumulator complete -> epilogue warps (of both CTAs)
+        if constexpr (CG == 1) umma_commit(tfull_bar(acc));
+        else umma_commit_cg2(tfull_bar(acc));
         acc ^= 1;
         if (acc == 0) acc_phase ^= 1u;
       }
     }
     __syncwarp();
   } else if (warp >= 4) {
-    // =============================== epilogue ===============================
+    // =============================== epilogue (every CTA: its own 128 rows) ===============================
     const int q = warp - 4;  // TMEM lane quarter == warp % 4
-    if (p.cw == 64)      epilogue_loop<64>(p, &tmC, &tmC2, &tmAux, q, lane, tmem_base, sEpi + q * 2 * kEpiBufBytes,
-                                           aux_bar(q, 0), aux_bar(q, 1), tfull_bar(0), tempty_bar(0), num_work);
-    else if (p.cw == 32) epilogue_loop<32>(p, &tmC, &tmC2, &tmAux, q, lane, tmem_base, sEpi + q * 2 * kEpiBufBytes,
-                                           aux_bar(q, 0), aux_bar(q, 1), tfull_bar(0), tempty_bar(0), num_work);
-    else                 epilogue_loop<16>(p, &tmC, &tmC2, &tmAux, q, lane, tmem_base, sEpi + q * 2 * kEpiBufBytes,
-                                           aux_bar(q, 0), aux_bar(q, 1), tfull_bar(0), tempty_bar(0), num_work);
+    const uint32_t eb = sEpi + q * 2 * kEpiBufBytes;
+    if (p.cw == 64)
+      epilogue_loop<64, CG>(p, &tmC, &tmC2, &tmAux, q, lane, tmem_base, eb, aux_bar(q, 0), aux_bar(q, 1),
+                            tfull_bar(0), tempty_bar(0), num_work, w_begin, w_stride, cta_rank);
+    else if (p.cw == 32)
+      epilogue_loop<32, CG>(p, &tmC, &tmC2, &tmAux, q, lane, tmem_base, eb, aux_bar(q, 0), aux_bar(q, 1),
+                            tfull_bar(0), tempty_bar(0), num_work, w_begin, w_stride, cta_rank);
+    else
+      epilogue_loop<16, CG>(p, &tmC, &tmC2, &tmAux, q, lane, tmem_base, eb, aux_bar(q, 0), aux_bar(q, 1),
+                            tfull_bar(0), tempty_bar(0), num_work, w_begin, w_stride, cta_rank);
   }
 
   tc_fence_before();
-  __syncthreads();
+  if constexpr (CG == 1) __syncthreads();
+  else cluster_sync_all();  // neither CTA may free TMEM / exit while the other still reads its smem
   if (warp == 2) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, kTmemCols);
+    if constexpr (CG == 1) tmem_dealloc(tmem_base, kTmemCols);
+    else tmem_dealloc_cg2(tmem_base, kTmemCols);
   }
 }
 
@@ -540,9 +640,11 @@ int get_tensor_map(const void* ptr, uint64_t inner, uint64_t outer, uint64_t ld,
   return 0;
 }
 
-int choose_block_n(int M, int N, int ctas) {
+// units = CTAs (CG == 1) or CTA pairs (CG == 2) working concurrently; tile_m = rows per unit tile
+int choose_block_n(int M, int N, int units, int tile_m) {
   if (N <= kMaxBN) return (N + 15) / 16 * 16;
-  const int tiles_m = (M + kBlockM - 1) / kBlockM;
+  const int tiles_m = (M + tile_m - 1) / tile_m;
+  const int ctas = units < 1 ? 1 : units;
   int best = 256;
   long best_cost = -1;
   for (int bn : {256, 192, 128}) {
@@ -587,7 +689,13 @@ extern "C" int b200ft_gemm_bf16(const b200ft_gemm_args* a, void* stream) {
   if (a->bias) B200FT_CHECK_ARG((uintptr_t)a->bias % 16 == 0, "gemm: bias must be 16-byte aligned");
 
   const int ctas_max = a->max_ctas > 0 ? a->max_ctas : B200FT_NUM_SMS;
-  int BN = a->block_n > 0 ? a->block_n : choose_block_n(a->m, a->n, ctas_max);
+  const bool kmajor = (a->layout & (B200FT_A_MN_MAJOR | B200FT_B_MN_MAJOR)) == 0;
+  B200FT_CHECK_ARG(a->cta_group >= 0 && a->cta_group <= 2, "gemm: cta_group=%d", a->cta_group);
+  int cg = a->cta_group;
+  if (cg == 0) cg = (kmajor && !atomic_t && a->m > kBlockM && a->n >= 128 && ctas_max >= 2) ? 2 : 1;
+  B200FT_CHECK_ARG(cg == 1 || (kmajor && !atomic_t && ctas_max >= 2),
+                   "gemm: cta_group=2 needs K-major operands, a non-atomic epilogue and >= 2 CTAs");
+  int BN = a->block_n > 0 ? a->block_n : choose_block_n(a->m, a->n, ctas_max / cg, kBlockM * cg);
   B200FT_CHECK_ARG(BN % 16 == 0 && BN >= 16 && BN <= kMaxBN, "gemm: block_n=%d", BN);
 
   GemmParams p;
@@ -598,7 +706,7 @@ extern "C" int b200ft_gemm_bf16(const b200ft_gemm_args* a, void* stream) {
   p.kblocks2 = seg2 ? (a->k2 + kBlockK - 1) / kBlockK : 0;
   p.a_mn = (a->layout & B200FT_A_MN_MAJOR) ? 1 : 0;
   p.b_mn = (a->layout & B200FT_B_MN_MAJOR) ? 1 : 0;
-  p.tiles_m = (a->m + kBlockM - 1) / kBlockM;
+  p.tiles_m = (a->m + kBlockM * cg - 1) / (kBlockM * cg);
   p.tiles_n = (a->n + BN - 1) / BN;
   p.epilogue = a->epilogue;
   p.alpha = a->alpha;
@@ -640,12 +748,12 @@ extern "C" int b200ft_gemm_bf16(const b200ft_gemm_args* a, void* stream) {
   else        rc = get_tensor_map(a->a1, (uint64_t)a->k1, (uint64_t)a->m, (uint64_t)a->lda1, 64, kBlockM, &tA1);
   if (rc) return rc;
   if (p.b_mn) rc = get_tensor_map(a->b1, (uint64_t)a->n, (uint64_t)a->k1, (uint64_t)a->ldb1, 64, 64, &tB1);
-  else        rc = get_tensor_map(a->b1, (uint64_t)a->k1, (uint64_t)a->n, (uint64_t)a->ldb1, 64, (uint32_t)BN, &tB1);
+  else        rc = get_tensor_map(a->b1, (uint64_t)a->k1, (uint64_t)a->n, (uint64_t)a->ldb1, 64, (uint32_t)(BN / cg), &tB1);
   if (rc) return rc;
   if (seg2) {
     rc = get_tensor_map(a->a2, (uint64_t)a->k2, (uint64_t)a->m, (uint64_t)a->lda2, 64, kBlockM, &tA2);
     if (rc) return rc;
-    rc = get_tensor_map(a->b2, (uint64_t)a->k2, (uint64_t)a->n, (uint64_t)a->ldb2, 64, (uint32_t)BN, &tB2);
+    rc = get_tensor_map(a->b2, (uint64_t)a->k2, (uint64_t)a->n, (uint64_t)a->ldb2, 64, (uint32_t)(BN / cg), &tB2);
     if (rc) return rc;
   } else {
     tA2 = tA1; tB2 = tB1;
@@ -659,12 +767,30 @@ extern "C" int b200ft_gemm_bf16(const b200ft_gemm_args* a, void* stream) {
   int dev = -1;
   B200FT_CUDA(cudaGetDevice(&dev));
   if (dev != attr_dev) {
-    B200FT_CUDA(cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+    B200FT_CUDA(cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+    B200FT_CUDA(cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
     attr_dev = dev;
   }
   const int num_work = p.tiles_m * p.tiles_n * p.splits;
-  const int grid = num_work < ctas_max ? num_work : ctas_max;
-  gemm_bf16_tcgen05_kernel<<<grid, kThreads, kSmemBytes, (cudaStream_t)stream>>>(tA1, tB1, tA2, tB2, tC, tC2, tAux, p);
-  B200FT_LAUNCH_CHECK();
+  if (cg == 1) {
+    const int grid = num_work < ctas_max ? num_work : ctas_max;
+    gemm_bf16_tcgen05_kernel<1><<<grid, kThreads, kSmemBytes, (cudaStream_t)stream>>>(tA1, tB1, tA2, tB2, tC, tC2, tAux, p);
+    B200FT_LAUNCH_CHECK();
+    return 0;
+  }
+  // cta_group::2: clusters of two CTAs (one TPC); work items go to pairs
+  const int pairs_max = ctas_max / 2;
+  const int pairs = num_work < pairs_max ? num_work : pairs_max;
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3(2 * pairs);
+  cfg.blockDim = dim3(kThreads);
+  cfg.dynamicSmemBytes = kSmemBytes;
+  cfg.stream = (cudaStream_t)stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr; cfg.numAttrs = 1;
+  B200FT_CUDA(cudaLaunchKernelEx(&cfg, gemm_bf16_tcgen05_kernel<2>, tA1, tB1, tA2, tB2, tC, tC2, tAux, p));
   return 0;
 }

@@ -198,7 +198,8 @@ def test_lora_grad(ops, M, r, cols):
 
 
 # ----------------------------------------------------------------------------- tcgen05 GEMM
-def _gemm_case(ops, M, N, K, a_mn=False, b_mn=False, K2=0, epilogue=0, bias=False, alpha=1.0, block_n=0, seed=0):
+def _gemm_case(ops, M, N, K, a_mn=False, b_mn=False, K2=0, epilogue=0, bias=False, alpha=1.0, block_n=0, seed=0,
+               cta_group=0):
     g = torch.Generator().manual_seed(seed + M + 3 * N + 7 * K)
     A = bf16_round(torch.randn(M, K, generator=g))
     Bm = bf16_round(torch.randn(N, K, generator=g))
@@ -234,7 +235,8 @@ def _gemm_case(ops, M, N, K, a_mn=False, b_mn=False, K2=0, epilogue=0, bias=Fals
         kw["aux"] = aux.to(DEV, torch.bfloat16)
     else:
         exp = v
-    ops.gemm(Ad, Bd, out, a_mn=a_mn, b_mn=b_mn, epilogue=epilogue, alpha=alpha, block_n=block_n, **kw)
+    ops.gemm(Ad, Bd, out, a_mn=a_mn, b_mn=b_mn, epilogue=epilogue, alpha=alpha, block_n=block_n,
+             cta_group=cta_group, **kw)
     torch.cuda.synchronize()
     got = out.cpu().double()
     assert not torch.isnan(got).any(), "GEMM left output elements unwritten"
@@ -259,25 +261,38 @@ def test_gemm_mn_major(ops, M, N, K, a_mn, b_mn):
     _gemm_case(ops, M, N, K, a_mn=a_mn, b_mn=b_mn)
 
 
+@pytest.mark.parametrize("cta_group", [1, 2])
+@pytest.mark.parametrize("M,N,K", [(256, 256, 64), (256, 256, 768), (512, 512, 128), (300, 200, 136), (129, 256, 768),
+                                   (1000, 768, 3072), (2048, 2304, 768), (4096, 768, 256), (200, 128, 72)])
+def test_gemm_cta_groups(ops, M, N, K, cta_group):
+    # cta_group 2 = CTA pairs on 256-row tiles (ragged M: second CTA's rows partly / wholly out of range)
+    _gemm_case(ops, M, N, K, cta_group=cta_group)
+
+
+@pytest.mark.parametrize("cta_group", [1, 2])
 @pytest.mark.parametrize("epilogue", [0, 1, 2, 3])
-def test_gemm_epilogues_bias_alpha(ops, epilogue):
-    _gemm_case(ops, 384, 512, 192, epilogue=epilogue, bias=True, alpha=0.5)
+def test_gemm_epilogues_bias_alpha(ops, epilogue, cta_group):
+    _gemm_case(ops, 384, 512, 192, epilogue=epilogue, bias=True, alpha=0.5, cta_group=cta_group)
 
 
+@pytest.mark.parametrize("cta_group", [1, 2])
 @pytest.mark.parametrize("K2", [16, 8, 64, 80])
-def test_gemm_second_segment(ops, K2):
+def test_gemm_second_segment(ops, K2, cta_group):
     # the LoRA slab: a rank-K2 product accumulated into the same TMEM tile
-    _gemm_case(ops, 512, 768, 256, K2=K2, bias=True)
+    _gemm_case(ops, 512, 768, 256, K2=K2, bias=True, cta_group=cta_group)
 
 
+@pytest.mark.parametrize("cta_group", [1, 2])
 @pytest.mark.parametrize("block_n", [16, 64, 128, 192, 256])
-def test_gemm_block_n(ops, block_n):
-    _gemm_case(ops, 640, 768, 320, block_n=block_n)
+def test_gemm_block_n(ops, block_n, cta_group):
+    _gemm_case(ops, 640, 768, 320, block_n=block_n, cta_group=cta_group)
 
 
-def test_gemm_persistent_many_tiles(ops):
+@pytest.mark.parametrize("cta_group", [1, 2])
+def test_gemm_persistent_many_tiles(ops, cta_group):
     # more tiles than SMs so every CTA loops and both TMEM accumulator stages wrap
-    _gemm_case(ops, 4096, 2304, 256)
+    _gemm_case(ops, 4096, 2304, 256, cta_group=cta_group)
+    _gemm_case(ops, 8192, 3072, 768, epilogue=2, bias=True, cta_group=cta_group)
 
 
 @pytest.mark.parametrize("M,N,K,split_k", [(256, 16, 4096, 0), (200, 8, 1000, 3), (768, 16, 32768, 0), (128, 64, 640, 5)])
