@@ -15,12 +15,15 @@
 //   warp 0 : TMA producer (one lane)          smem ring of kStages {A 128x64, B BNx64} slabs
 //   warp 1 : MMA issuer (one lane)            128 x BN x 16 UMMAs, 4 per K slab
 //   warp 2 : TMEM allocator (512 columns = two 128 x 256 fp32 accumulators)
-//   warps 4-7 : epilogue, one TMEM lane quarter (32 rows) each; runs on accumulator `a` while
-//               the MMA warp fills accumulator `a^1` for the next tile.  Per 64-column chunk:
-//               tcgen05.ld -> registers -> (alpha, bias, residual / gelu / dgelu) -> bf16 into a
-//               128B-swizzled 32x64 smem tile -> one TMA store (coalesced, asynchronous, clipped
-//               at the matrix edge).  The residual / dgelu operand arrives by TMA load into the
-//               same tile one chunk ahead and is updated in place.
+//   warps 4-11 : epilogue, two warps per TMEM lane quarter (32 rows), taking alternate
+//               32-column chunks; runs on accumulator `a` while the MMA warp fills accumulator
+//               `a^1` for the next tile.  Per chunk: tcgen05.ld -> registers -> (alpha, bias from
+//               a per-tile smem copy, residual / gelu / dgelu) -> bf16 into a 64B-swizzled 32x32
+//               smem tile -> one TMA store (coalesced, asynchronous, clipped at the matrix edge).
+//               The residual / dgelu operand arrives by TMA load into the same tile one chunk
+//               ahead and is updated in place.  (Two warps per scheduler, a 32-column body: the
+//               first version — one warp per quarter, 64-column chunks, bias from global — was
+//               bound by instruction issue, i-cache misses and LDG latency; profiles/README.md.)
 // Three mbarrier pipelines: smem full/empty (TMA <-> MMA), TMEM full/empty (MMA <-> epilogue).
 //
 // The K loop runs over up to two operand segments.  Segment 2 is how a LoRA branch is
@@ -54,12 +57,14 @@ template <int CG> struct RingCfg {
 };
 constexpr int kMaxStages = 6;
 constexpr uint32_t kPeerBitMask = 0xFEFFFFFFu;  // clears the CTA-rank bit of a shared::cluster address -> CTA 0
-constexpr int kEpiBufBytes = 32 * 64 * 2;              // one 32-row x 64-col bf16 staging tile
-constexpr int kEpiBytes = 4 * 2 * kEpiBufBytes;        // 4 epilogue warps x 2 tiles = 32 KB
-constexpr int kBarrierBytes = 256;
-constexpr int kSmemBytes = kTileBytes + kEpiBytes + kBarrierBytes + 1024;  // + slack to align to 1024
+constexpr int kEpiWarps = 8;                           // two per TMEM lane quarter
+constexpr int kEpiBufBytes = 32 * 32 * 2;              // one 32-row x 32-col bf16 staging tile (2 KB)
+constexpr int kEpiBytes = kEpiWarps * 2 * kEpiBufBytes;  // 8 epilogue warps x 2 tiles = 32 KB
+constexpr int kBiasBytes = kMaxBN * 4;                 // the tile's bias slice, fp32
+constexpr int kBarrierBytes = 384;
+constexpr int kSmemBytes = kTileBytes + kEpiBytes + kBiasBytes + kBarrierBytes + 1024;  // + slack to align to 1024
 static_assert(kSmemBytes <= 227 * 1024, "shared memory budget");
-constexpr int kThreads = 256;
+constexpr int kThreads = 128 + 32 * kEpiWarps;         // 4 control warps + 8 epilogue warps
 constexpr int kTmemCols = 512;
 constexpr int kAccStride = 256;  // TMEM columns per accumulator stage
 constexpr long long kWaitLimitCycles = 4000000000ll;  // ~2 s: deadlock guard, trap instead of hanging the GPU
@@ -232,17 +237,22 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* r) {
 }
 __device__ __forceinline__ void tmem_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
-// shared-memory matrix descriptor (PTX ISA, tcgen05 "matrix descriptor"): start>>4 [0,14),
-// LBO>>4 [16,30), SBO>>4 [32,46), version=1 [46,48), swizzle mode [61,64) (2 = 128B)
-__device__ __forceinline__ uint64_t make_smem_desc(uint32_t addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
-  uint64_t d = 0;
-  d |= (uint64_t)((addr & 0x3FFFFu) >> 4);
-  d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFFu) << 16;
-  d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFFu) << 32;
-  d |= 1ull << 46;
-  d |= 2ull << 61;
-  return d;
+// The descriptor's upper word is constant per layout; only the start-address field of the lower
+// word moves (per stage, per K step), so the issue loop adds small integers to `lo`.
+__device__ __forceinline__ uint32_t smem_desc_hi(uint32_t sbo_bytes) {
+  return ((sbo_bytes >> 4) & 0x3FFFu) | (1u << 14) | (2u << 29);
 }
+__device__ __forceinline__ uint32_t smem_desc_lo(uint32_t addr, uint32_t lbo_bytes) {
+  return ((addr & 0x3FFFFu) >> 4) | (((lbo_bytes >> 4) & 0x3FFFu) << 16);
+}
+__device__ __forceinline__ uint64_t desc64(uint32_t lo, uint32_t hi) { return ((uint64_t)hi << 32) | lo; }
+// one lane of a converged warp (the same lane every time for a full mask)
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+  return pred != 0;
+}
+
 // instruction descriptor (kind::f16): D fp32 [4,6)=1, A bf16 [7,10)=1, B bf16 [10,13)=1,
 // A major [15], B major [16] (1 = MN-major), N>>3 [17,23), M>>4 [24,29)
 __device__ __forceinline__ uint32_t make_idesc(int m, int n, int a_mn, int b_mn) {
@@ -257,47 +267,67 @@ __device__ __forceinline__ uint32_t make_idesc(int m, int n, int a_mn, int b_mn)
 // address of the 16-byte vector `v` of row `lane` inside a staging tile of CW columns
 template <int CW>
 __device__ __forceinline__ uint32_t epi_vec_addr(uint32_t buf, int lane, int v) {
-  if constexpr (CW == 64) return buf + lane * 128 + ((v ^ (lane & 7)) << 4);  // TMA SWIZZLE_128B pattern
-  else return buf + lane * (CW * 2) + (v << 4);                               // dense rows (SWIZZLE_NONE)
+  if constexpr (CW == 32) return buf + lane * 64 + ((v ^ ((lane >> 1) & 3)) << 4);  // TMA SWIZZLE_64B pattern
+  else return buf + lane * (CW * 2) + (v << 4);                                     // dense rows (SWIZZLE_NONE)
+}
+__device__ __forceinline__ void epi_bar_sync() {  // the 8 epilogue warps only
+  asm volatile("bar.sync 1, %0;" ::"n"(32 * kEpiWarps) : "memory");
+}
+__device__ __forceinline__ float4 lds_f4(uint32_t addr) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+  return v;
 }
 
+// q = TMEM lane quarter, h = which of the quarter's two warps (takes chunks h, h+2, ...),
+// et = index among the 256 epilogue threads
 template <int CW, int CG>
 __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtensorMap* tmC, const CUtensorMap* tmC2,
-                                              const CUtensorMap* tmAux, int q, int lane, uint32_t tmem_base,
-                                              uint32_t ebuf, uint32_t abar0, uint32_t abar1, uint32_t tfull0,
-                                              uint32_t tempty0, int num_work, int w_begin, int w_stride,
-                                              int cta_rank) {
+                                              const CUtensorMap* tmAux, int q, int h, int lane, int et,
+                                              uint32_t tmem_base, uint32_t ebuf, uint32_t sbias, uint32_t abar0,
+                                              uint32_t abar1, uint32_t tfull0, uint32_t tempty0, int num_work,
+                                              int w_begin, int w_stride, int cta_rank) {
   const int BN = p.BN;
   const int nchunks = BN / CW;
   const bool has_aux = (p.epilogue == B200FT_EPI_RESIDUAL) || (p.epilogue == B200FT_EPI_DGELU);
+  const bool atomic_t = (p.epilogue == B200FT_EPI_ATOMIC_F32_T);
+  const bool has_bias = p.bias != nullptr;
+  const bool scale = p.alpha != 1.0f;
   const uint32_t aux_bytes = 32u * CW * 2u;
   uint32_t slot = 0;          // running count of staged tiles: buffer = slot & 1
   uint32_t aux_phase = 0;     // bit b = parity to wait for on aux barrier b
   int acc = 0;
   uint32_t acc_phase = 0;
-  const bool atomic_t = (p.epilogue == B200FT_EPI_ATOMIC_F32_T);
   for (int w = w_begin; w < num_work; w += w_stride) {
     const int tile = w / p.splits;
     const int m0 = (tile / p.tiles_n) * (kBlockM * CG) + cta_rank * kBlockM;
     const int n0 = (tile % p.tiles_n) * BN;
     const int row0 = m0 + q * 32;
-    if (has_aux && lane == 0) {  // first chunk's operand: in flight while the MMAs of this tile finish
+    if (has_bias) {  // this tile's bias slice -> smem, once, while the MMAs of the tile still run
+      epi_bar_sync();  // everyone is done with the previous tile's slice
+      if (et < BN) {
+        const int col = n0 + et;
+        const float bv = col < p.N ? __ldg(p.bias + col) : 0.f;
+        asm volatile("st.shared.f32 [%0], %1;" ::"r"(sbias + 4u * et), "f"(bv) : "memory");
+      }
+      epi_bar_sync();
+    }
+    if (has_aux && h < nchunks && lane == 0) {  // first chunk's operand, in flight during the tfull wait
       const uint32_t b = slot & 1u;
       tma_store_wait_read<1>();  // the store that last used this buffer has drained it
       const uint32_t bar = b ? abar1 : abar0;
       mbar_expect_tx(bar, aux_bytes);
-      tma_load_2d(ebuf + b * kEpiBufBytes, tmAux, n0, row0, bar);
+      tma_load_2d(ebuf + b * kEpiBufBytes, tmAux, n0 + h * CW, row0, bar);
     }
     mbar_wait(tfull0 + 8u * acc, acc_phase);
     tc_fence_after();
     const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * kAccStride);
-    for (int c = 0; c < nchunks; ++c) {
+    for (int c = h; c < nchunks; c += 2) {
       const uint32_t b = slot & 1u;
       const uint32_t buf = ebuf + b * kEpiBufBytes;
       uint32_t r[CW];
-      if constexpr (CW == 64) { tmem_ld32(t_row + c * CW, r); tmem_ld32(t_row + c * CW + 32, r + 32); }
-      else if constexpr (CW == 32) { tmem_ld32(t_row + c * CW, r); }
-      else { tmem_ld16(t_row + c * CW, r); }
+      if constexpr (CW == 32) tmem_ld32(t_row + c * CW, r);
+      else tmem_ld16(t_row + c * CW, r);
       const int colbase = n0 + c * CW;
       if (atomic_t) {
         // split-K partial: fp32 reduction into the transposed output (lanes = consecutive m,
@@ -321,15 +351,18 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtenso
         __syncwarp();
       }
       tmem_wait_ld();
+      if (scale) {
+#pragma unroll
+        for (int j = 0; j < CW; ++j) r[j] = __float_as_uint(__uint_as_float(r[j]) * p.alpha);
+      }
 #pragma unroll
       for (int v = 0; v < CW / 8; ++v) {
         float f[8];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) f[j] = __uint_as_float(r[v * 8 + j]) * p.alpha;
-        const int col = colbase + v * 8;
-        if (p.bias && col < p.N) {
-          const float4 b0 = __ldg(reinterpret_cast<const float4*>(p.bias + col));
-          const float4 b1 = __ldg(reinterpret_cast<const float4*>(p.bias + col + 4));
+        for (int j = 0; j < 8; ++j) f[j] = __uint_as_float(r[v * 8 + j]);
+        if (has_bias) {
+          const float4 b0 = lds_f4(sbias + 4u * (c * CW + v * 8));
+          const float4 b1 = lds_f4(sbias + 4u * (c * CW + v * 8 + 4));
           f[0] += b0.x; f[1] += b0.y; f[2] += b0.z; f[3] += b0.w;
           f[4] += b1.x; f[5] += b1.y; f[6] += b1.z; f[7] += b1.w;
         }
@@ -376,12 +409,12 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtenso
         if (lane == 0) tma_store_2d(tmC2, buf2, colbase, row0);
         ++slot;
       }
-      if (has_aux && c + 1 < nchunks && lane == 0) {  // next chunk's operand, one chunk ahead
+      if (has_aux && c + 2 < nchunks && lane == 0) {  // this warp's next chunk's operand
         const uint32_t nb = slot & 1u;
         tma_store_wait_read<1>();
         const uint32_t bar = nb ? abar1 : abar0;
         mbar_expect_tx(bar, aux_bytes);
-        tma_load_2d(ebuf + nb * kEpiBufBytes, tmAux, colbase + CW, row0, bar);
+        tma_load_2d(ebuf + nb * kEpiBufBytes, tmAux, colbase + 2 * CW, row0, bar);
       }
     }
     tc_fence_before();
@@ -414,15 +447,17 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
   const uint32_t sA = base;
   const uint32_t sB = base + kStages * kAStageBytes;
   const uint32_t sEpi = base + kTileBytes;
-  const uint32_t bars = sEpi + kEpiBytes;
+  const uint32_t sBias = sEpi + kEpiBytes;
+  const uint32_t bars = sBias + kBiasBytes;
   auto full_bar = [&](int s) { return bars + 8u * s; };
   auto empty_bar = [&](int s) { return bars + 8u * (kMaxStages + s); };
   auto tfull_bar = [&](int a) { return bars + 8u * (2 * kMaxStages + a); };
   auto tempty_bar = [&](int a) { return bars + 8u * (2 * kMaxStages + 2 + a); };
-  auto aux_bar = [&](int q, int b) { return bars + 8u * (2 * kMaxStages + 4 + 2 * q + b); };
-  const uint32_t tmem_slot = bars + 8u * (2 * kMaxStages + 12);
+  auto aux_bar = [&](int ew, int b) { return bars + 8u * (2 * kMaxStages + 4 + 2 * ew + b); };
+  const uint32_t tmem_slot = bars + 8u * (2 * kMaxStages + 4 + 2 * kEpiWarps);
   volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(
-      smem_raw + (base - raw) + kTileBytes + kEpiBytes + 8 * (2 * kMaxStages + 12));
+      smem_raw + (base - raw) + kTileBytes + kEpiBytes + kBiasBytes + 8 * (2 * kMaxStages + 4 + 2 * kEpiWarps));
+  static_assert(8 * (2 * kMaxStages + 4 + 2 * kEpiWarps) + 4 <= kBarrierBytes, "barrier area");
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -438,8 +473,8 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
   }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < kStages; ++s) { mbar_init(full_bar(s), CG); mbar_init(empty_bar(s), 1); }
-    for (int a = 0; a < 2; ++a) { mbar_init(tfull_bar(a), 1); mbar_init(tempty_bar(a), 4 * CG); }
-    for (int q = 0; q < 4; ++q) { mbar_init(aux_bar(q, 0), 1); mbar_init(aux_bar(q, 1), 1); }
+    for (int a = 0; a < 2; ++a) { mbar_init(tfull_bar(a), 1); mbar_init(tempty_bar(a), kEpiWarps * CG); }
+    for (int ew = 0; ew < kEpiWarps; ++ew) { mbar_init(aux_bar(ew, 0), 1); mbar_init(aux_bar(ew, 1), 1); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 2) {
@@ -458,39 +493,43 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
 
   if (warp == 0) {
     // =============================== TMA producer (every CTA) ===============================
-    if (lane == 0) {
-      const uint32_t b_rows = (uint32_t)BN / CG;  // CG == 2: this CTA stages half of the B tile
-      const uint32_t b_bytes = (CG == 1 && p.b_mn) ? (uint32_t)((BN + 63) / 64) * 8192u : b_rows * 128u;
-      const uint32_t b2_bytes = b_rows * 128u;
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int w = w_begin; w < num_work; w += w_stride) {
-        const int tile = w / p.splits;
-        const int m0 = (tile / p.tiles_n) * (kBlockM * CG) + cta_rank * kBlockM;
-        const int n0 = (tile % p.tiles_n) * BN + cta_rank * (int)b_rows;
-        const int kb_begin = (w % p.splits) * p.kb_per_split;
-        const int kb_end = min(kb_total, kb_begin + p.kb_per_split);
-        for (int kb = kb_begin; kb < kb_end; ++kb) {
-          mbar_wait(empty_bar(stage), phase ^ 1u);
-          const bool seg2 = kb >= p.kblocks1;
-          const int kk = (seg2 ? kb - p.kblocks1 : kb) * kBlockK;
-          const uint32_t a_dst = sA + stage * kAStageBytes;
-          const uint32_t b_dst = sB + stage * kBStageBytes;
-          const uint32_t fb = full_bar(stage);
-          const uint32_t bytes = (uint32_t)kAStageBytes + (seg2 ? b2_bytes : b_bytes);
+    // The whole warp walks the loop (warp-uniform control flow keeps addresses and coordinates in
+    // uniform registers); one elected lane arms the barrier and issues the copies.
+    const bool issuer = elect_one();
+    const uint32_t b_rows = (uint32_t)BN / CG;  // CG == 2: this CTA stages half of the B tile
+    const uint32_t b_bytes = (CG == 1 && p.b_mn) ? (uint32_t)((BN + 63) / 64) * 8192u : b_rows * 128u;
+    const uint32_t b2_bytes = b_rows * 128u;
+    const bool a_mn = CG == 1 && p.a_mn, b_mn = CG == 1 && p.b_mn;
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int w = w_begin; w < num_work; w += w_stride) {
+      const int tile = w / p.splits;
+      const int m0 = (tile / p.tiles_n) * (kBlockM * CG) + cta_rank * kBlockM;
+      const int n0 = (tile % p.tiles_n) * BN + cta_rank * (int)b_rows;
+      const int kb_begin = (w % p.splits) * p.kb_per_split;
+      const int kb_end = min(kb_total, kb_begin + p.kb_per_split);
+      for (int kb = kb_begin; kb < kb_end; ++kb) {
+        mbar_wait(empty_bar(stage), phase ^ 1u);
+        const bool seg2 = kb >= p.kblocks1;
+        const int kk = (seg2 ? kb - p.kblocks1 : kb) * kBlockK;
+        const uint32_t a_dst = sA + stage * kAStageBytes;
+        const uint32_t b_dst = sB + stage * kBStageBytes;
+        const uint32_t fb = full_bar(stage);
+        const uint32_t bytes = (uint32_t)kAStageBytes + (seg2 ? b2_bytes : b_bytes);
+        if (issuer) {
           if constexpr (CG == 1) {
             mbar_expect_tx(fb, bytes);
             if (seg2) {
               tma_load_2d(a_dst, &tmA2, kk, m0, fb);
               tma_load_2d(b_dst, &tmB2, kk, n0, fb);
             } else {
-              if (p.a_mn) {
+              if (a_mn) {
                 tma_load_2d(a_dst, &tmA1, m0, kk, fb);
                 tma_load_2d(a_dst + 8192u, &tmA1, m0 + 64, kk, fb);
               } else {
                 tma_load_2d(a_dst, &tmA1, kk, m0, fb);
               }
-              if (p.b_mn) {
+              if (b_mn) {
                 for (int j = 0; j * 64 < BN; ++j) tma_load_2d(b_dst + 8192u * j, &tmB1, n0 + 64 * j, kk, fb);
               } else {
                 tma_load_2d(b_dst, &tmB1, kk, n0, fb);
@@ -504,16 +543,26 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
             tma_load_2d_cg2(a_dst, seg2 ? &tmA2 : &tmA1, kk, m0, fb);
             tma_load_2d_cg2(b_dst, seg2 ? &tmB2 : &tmB1, kk, n0, fb);
           }
-          if (++stage == kStages) { stage = 0; phase ^= 1u; }
         }
+        __syncwarp();
+        if (++stage == kStages) { stage = 0; phase ^= 1u; }
       }
     }
-    __syncwarp();
   } else if (warp == 1) {
     // =============================== MMA issuer (CTA 0 of a pair) ===============================
-    if (lane == 0 && cta_rank == 0) {
-      const uint32_t idesc1 = make_idesc(kBlockM * CG, BN, p.a_mn, p.b_mn);
+    // Warp-uniform loop; one elected lane issues every tcgen05.mma / tcgen05.commit (a commit only
+    // tracks the MMAs of the thread that executes it).
+    if (cta_rank == 0) {
+      const bool issuer = elect_one();
+      const bool a_mn = CG == 1 && p.a_mn, b_mn = CG == 1 && p.b_mn;
+      const uint32_t idesc1 = make_idesc(kBlockM * CG, BN, a_mn, b_mn);
       const uint32_t idesc2 = make_idesc(kBlockM * CG, BN, 0, 0);
+      // descriptor words: K-major SW128 (LBO 16, SBO 1024, +32 B per K step) or MN-major SW128
+      // (LBO 8192, SBO 1024, +2048 B per K step)
+      const uint32_t hi = smem_desc_hi(1024u);
+      const uint32_t a_lo1 = smem_desc_lo(sA, a_mn ? 8192u : 16u), a_step1 = a_mn ? 128u : 2u;
+      const uint32_t b_lo1 = smem_desc_lo(sB, b_mn ? 8192u : 16u), b_step1 = b_mn ? 128u : 2u;
+      const uint32_t a_lo2 = smem_desc_lo(sA, 16u), b_lo2 = smem_desc_lo(sB, 16u);
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
@@ -528,49 +577,63 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
           mbar_wait(full_bar(stage), phase);
           tc_fence_after();
           const bool seg2 = kb >= p.kblocks1;
-          const int kk = (seg2 ? kb - p.kblocks1 : kb) * kBlockK;
-          const int kleft = (seg2 ? p.k2 : p.k1) - kk;
-          const int nmma = kleft >= kBlockK ? 4 : (kleft + 15) / 16;
-          const bool amn = CG == 1 && !seg2 && p.a_mn, bmn = CG == 1 && !seg2 && p.b_mn;
-          const uint32_t a_base = sA + stage * kAStageBytes;
-          const uint32_t b_base = sB + stage * kBStageBytes;
+          const int kleft = seg2 ? p.k2 - (kb - p.kblocks1) * kBlockK : p.k1 - kb * kBlockK;
+          const uint32_t a_lo = (seg2 ? a_lo2 : a_lo1) + (uint32_t)stage * (kAStageBytes >> 4);
+          const uint32_t b_lo = (seg2 ? b_lo2 : b_lo1) + (uint32_t)stage * (kBStageBytes >> 4);
+          const uint32_t a_step = seg2 ? 2u : a_step1, b_step = seg2 ? 2u : b_step1;
           const uint32_t idesc = seg2 ? idesc2 : idesc1;
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            if (j < nmma) {
-              const uint64_t ad = amn ? make_smem_desc(a_base + 2048u * j, 8192u, 1024u)
-                                      : make_smem_desc(a_base + 32u * j, 16u, 1024u);
-              const uint64_t bd = bmn ? make_smem_desc(b_base + 2048u * j, 8192u, 1024u)
-                                      : make_smem_desc(b_base + 32u * j, 16u, 1024u);
-              if constexpr (CG == 1) umma_bf16(d_tmem, ad, bd, idesc, (kb > kb_begin || j > 0) ? 1u : 0u);
-              else umma_bf16_cg2(d_tmem, ad, bd, idesc, (kb > kb_begin || j > 0) ? 1u : 0u);
+          const uint32_t first = kb > kb_begin ? 1u : 0u;
+          if (issuer) {
+            if (kleft >= kBlockK) {  // the common case: four K steps, no per-step predicate
+              if constexpr (CG == 1) {
+                umma_bf16(d_tmem, desc64(a_lo, hi), desc64(b_lo, hi), idesc, first);
+                umma_bf16(d_tmem, desc64(a_lo + a_step, hi), desc64(b_lo + b_step, hi), idesc, 1u);
+                umma_bf16(d_tmem, desc64(a_lo + 2 * a_step, hi), desc64(b_lo + 2 * b_step, hi), idesc, 1u);
+                umma_bf16(d_tmem, desc64(a_lo + 3 * a_step, hi), desc64(b_lo + 3 * b_step, hi), idesc, 1u);
+              } else {
+                umma_bf16_cg2(d_tmem, desc64(a_lo, hi), desc64(b_lo, hi), idesc, first);
+                umma_bf16_cg2(d_tmem, desc64(a_lo + a_step, hi), desc64(b_lo + b_step, hi), idesc, 1u);
+                umma_bf16_cg2(d_tmem, desc64(a_lo + 2 * a_step, hi), desc64(b_lo + 2 * b_step, hi), idesc, 1u);
+                umma_bf16_cg2(d_tmem, desc64(a_lo + 3 * a_step, hi), desc64(b_lo + 3 * b_step, hi), idesc, 1u);
+              }
+            } else {                 // K tail / the LoRA slab: ceil(kleft / 16) steps
+              const int nmma = (kleft + 15) / 16;
+              for (int j = 0; j < nmma; ++j) {
+                const uint32_t accf = (j > 0) ? 1u : first;
+                if constexpr (CG == 1)
+                  umma_bf16(d_tmem, desc64(a_lo + j * a_step, hi), desc64(b_lo + j * b_step, hi), idesc, accf);
+                else
+                  umma_bf16_cg2(d_tmem, desc64(a_lo + j * a_step, hi), desc64(b_lo + j * b_step, hi), idesc, accf);
+              }
             }
+            // frees the smem slot (in both CTAs when CG == 2) once these MMAs retire
+            if constexpr (CG == 1) umma_commit(empty_bar(stage));
+            else umma_commit_cg2(empty_bar(stage));
           }
-          // frees the smem slot (in both CTAs when CG == 2) once these MMAs retire
-          if constexpr (CG == 1) umma_commit(empty_bar(stage));
-          else umma_commit_cg2(empty_bar(stage));
+          __syncwarp();
           if (++stage == kStages) { stage = 0; phase ^= 1u; }
         }
-        // accumulator complete -> epilogue warps (of both CTAs)
-        if constexpr (CG == 1) umma_commit(tfull_bar(acc));
-        else umma_commit_cg2(tfull_bar(acc));
+        if (issuer) {  // accumulator complete -> epilogue warps (of both CTAs)
+          if constexpr (CG == 1) umma_commit(tfull_bar(acc));
+          else umma_commit_cg2(tfull_bar(acc));
+        }
+        __syncwarp();
         acc ^= 1;
         if (acc == 0) acc_phase ^= 1u;
       }
     }
-    __syncwarp();
   } else if (warp >= 4) {
     // =============================== epilogue (every CTA: its own 128 rows) ===============================
-    const int q = warp - 4;  // TMEM lane quarter == warp % 4
-    const uint32_t eb = sEpi + q * 2 * kEpiBufBytes;
-    if (p.cw == 64)
-      epilogue_loop<64, CG>(p, &tmC, &tmC2, &tmAux, q, lane, tmem_base, eb, aux_bar(q, 0), aux_bar(q, 1),
-                            tfull_bar(0), tempty_bar(0), num_work, w_begin, w_stride, cta_rank);
-    else if (p.cw == 32)
-      epilogue_loop<32, CG>(p, &tmC, &tmC2, &tmAux, q, lane, tmem_base, eb, aux_bar(q, 0), aux_bar(q, 1),
+    const int ew = warp - 4;      // 0..7
+    const int q = warp & 3;       // TMEM lane quarter this warp may touch (== warp % 4)
+    const int h = ew >> 2;        // first or second warp of the quarter
+    const int et = threadIdx.x - 128;
+    const uint32_t eb = sEpi + ew * 2 * kEpiBufBytes;
+    if (p.cw == 32)
+      epilogue_loop<32, CG>(p, &tmC, &tmC2, &tmAux, q, h, lane, et, tmem_base, eb, sBias, aux_bar(ew, 0), aux_bar(ew, 1),
                             tfull_bar(0), tempty_bar(0), num_work, w_begin, w_stride, cta_rank);
     else
-      epilogue_loop<16, CG>(p, &tmC, &tmC2, &tmAux, q, lane, tmem_base, eb, aux_bar(q, 0), aux_bar(q, 1),
+      epilogue_loop<16, CG>(p, &tmC, &tmC2, &tmAux, q, h, lane, et, tmem_base, eb, sBias, aux_bar(ew, 0), aux_bar(ew, 1),
                             tfull_bar(0), tempty_bar(0), num_work, w_begin, w_stride, cta_rank);
   }
 
@@ -611,8 +674,8 @@ std::map<MapKey, CUtensorMap> g_maps;
 
 // 2-D bf16 tensor {inner, outer} with row pitch ld (elements), box {box_inner, box_outer}, SW128
 int get_tensor_map(const void* ptr, uint64_t inner, uint64_t outer, uint64_t ld, uint32_t box_inner,
-                   uint32_t box_outer, CUtensorMap* out, bool swizzle128 = true) {
-  MapKey key{ptr, inner, outer, ld, box_inner, box_outer, swizzle128 ? 1 : 0};
+                   uint32_t box_outer, CUtensorMap* out, int swizzle = 2 /* 0 none, 1 = 64B, 2 = 128B */) {
+  MapKey key{ptr, inner, outer, ld, box_inner, box_outer, swizzle};
   {
     std::lock_guard<std::mutex> lk(g_map_mu);
     auto it = g_maps.find(key);
@@ -625,7 +688,8 @@ int get_tensor_map(const void* ptr, uint64_t inner, uint64_t outer, uint64_t ld,
   cuuint32_t box[2] = {box_inner, box_outer};
   cuuint32_t estr[2] = {1, 1};
   CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
-                   CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   swizzle == 2 ? CU_TENSOR_MAP_SWIZZLE_128B : (swizzle == 1 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_NONE),
                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
@@ -728,20 +792,21 @@ extern "C" int b200ft_gemm_bf16(const b200ft_gemm_args* a, void* stream) {
     p.splits = (kb_total + p.kb_per_split - 1) / p.kb_per_split;  // no empty split
   }
 
-  p.cw = (BN % 64 == 0) ? 64 : (BN % 32 == 0 ? 32 : 16);
+  p.cw = (BN % 32 == 0) ? 32 : 16;
+  const int esw = p.cw == 32 ? 1 : 0;  // staging tile swizzle: 64B for the 32-column tile, none for 16
   CUtensorMap tA1, tB1, tA2, tB2, tC, tC2, tAux;
   int rc;
-  // epilogue staging tiles: {cw columns, 32 rows}; the 64-wide one is 128B-swizzled
+  // epilogue staging tiles: {cw columns, 32 rows}
   if (!atomic_t) {
-    rc = get_tensor_map(a->c, (uint64_t)a->n, (uint64_t)a->m, (uint64_t)a->ldc, (uint32_t)p.cw, 32, &tC, p.cw == 64);
+    rc = get_tensor_map(a->c, (uint64_t)a->n, (uint64_t)a->m, (uint64_t)a->ldc, (uint32_t)p.cw, 32, &tC, esw);
     if (rc) return rc;
   }
   if (a->epilogue == B200FT_EPI_GELU) {
-    rc = get_tensor_map(a->c2, (uint64_t)a->n, (uint64_t)a->m, (uint64_t)a->ldc2, (uint32_t)p.cw, 32, &tC2, p.cw == 64);
+    rc = get_tensor_map(a->c2, (uint64_t)a->n, (uint64_t)a->m, (uint64_t)a->ldc2, (uint32_t)p.cw, 32, &tC2, esw);
     if (rc) return rc;
   }
   if (a->epilogue == B200FT_EPI_RESIDUAL || a->epilogue == B200FT_EPI_DGELU) {
-    rc = get_tensor_map(a->aux, (uint64_t)a->n, (uint64_t)a->m, (uint64_t)a->ld_aux, (uint32_t)p.cw, 32, &tAux, p.cw == 64);
+    rc = get_tensor_map(a->aux, (uint64_t)a->n, (uint64_t)a->m, (uint64_t)a->ld_aux, (uint32_t)p.cw, 32, &tAux, esw);
     if (rc) return rc;
   }
   if (p.a_mn) rc = get_tensor_map(a->a1, (uint64_t)a->m, (uint64_t)a->k1, (uint64_t)a->lda1, 64, 64, &tA1);
