@@ -27,6 +27,12 @@ class GemmArgs(ctypes.Structure):
         ("a2", c_void_p), ("lda2", c_int64),
         ("b2", c_void_p), ("ldb2", c_int64),
         ("k2", c_int32),
+        ("a3", c_void_p), ("lda3", c_int64),
+        ("b3", c_void_p), ("ldb3", c_int64),
+        ("k3", c_int32),
+        ("a4", c_void_p), ("lda4", c_int64),
+        ("b4", c_void_p), ("ldb4", c_int64),
+        ("k4", c_int32),
         ("layout", c_int32),
         ("epilogue", c_int32),
         ("alpha", c_float),

@@ -192,7 +192,6 @@ class GPT2LoRAStep:
         self.dh = torch.empty(M, ff, **bf)
         self.dln = torch.empty(M, d, **bf)
         self.da = torch.empty(M, d, **bf)
-        self.dqkv = torch.empty(M, 3 * d, **bf)
         self.dU = torch.empty(M, R_PAD, **bf)
         self.attn_saved = [None] * L
 
@@ -210,16 +209,23 @@ class GPT2LoRAStep:
             a = a.contiguous()
         return a.view(self.M, self.dims.d_model)
 
-    def _attn_bwd(self, l: int, da: torch.Tensor) -> None:
+    def _attn_bwd(self, l: int, da: torch.Tensor):
+        """Returns (dq, dk, dv), each a [tokens, d_model] matrix.  The library hands them back as
+        three separate dense buffers; they are consumed as separate K segments downstream, so
+        nothing is copied into an interleaved [tokens, 3*d_model] layout."""
         B, T, H = self.B, self.T, self.dims.n_head
         dh = self.dims.d_model // H
         q, k, v, o = self.attn_saved[l]
         go = da.view(B, T, H, dh).permute(0, 2, 1, 3)
-        dq, dk, dv = torch.autograd.grad(o, (q, k, v), go)
-        d5 = self.dqkv.view(B, T, 3, H, dh)
-        for i, g in enumerate((dq, dk, dv)):
-            d5[:, :, i].permute(0, 2, 1, 3).copy_(g)
+        grads = torch.autograd.grad(o, (q, k, v), go)
         self.attn_saved[l] = None
+        out = []
+        for g in grads:
+            g = g.permute(0, 2, 1, 3)              # [B, T, H, dh]
+            if not g.is_contiguous():
+                g = g.contiguous()
+            out.append(g.view(self.M, self.dims.d_model))
+        return out
 
     # ------------------------------------------------------------------ the step
     @torch.no_grad()
@@ -264,12 +270,17 @@ class GPT2LoRAStep:
             ops.layernorm_bwd_dx(self.dln, self.x1[l], W["ln2.g"], *self.st2[l], dx1, dres=dx)
             # attention branch
             ops.gemm(dx1, W["attn_proj.w"], self.da)
-            self._attn_bwd(l, self.da)
-            # adapter gradients (dB = U^T dqkv, dU = s dqkv B^T, dA^T = dU^T h1) and d ln1
-            ops.lora_grad(self.U[l], self.dqkv, self.gB_all[rows], r=R_PAD, cols=3 * D.d_model)
-            ops.gemm(self.dqkv, self.B_sh[rows], self.dU, alpha=s)
-            ops.lora_grad(self.dU, self.h1[l], self.gAt_all[rows], r=R_PAD, cols=D.d_model)
-            ops.gemm(self.dqkv, W["c_attn.w"], self.dln, a2=self.dU, b2=self.A_sh[:, rows])
+            dq, dk, dv = self._attn_bwd(l, self.da)
+            # adapter gradients (dB = U^T dqkv, dU = s dqkv B^T, dA^T = dU^T h1) and d ln1, with
+            # dqkv = [dq | dk | dv] never materialised: each third is its own K segment / column block
+            d = D.d_model
+            gB, Bsh, Wqkv = self.gB_all[rows], self.B_sh[rows], W["c_attn.w"]
+            for i, g in enumerate((dq, dk, dv)):
+                ops.lora_grad(self.U[l], g, gB[:, i * d:(i + 1) * d], r=R_PAD, cols=d)
+            ops.gemm(dq, Bsh[:, :d], self.dU, a2=dk, b2=Bsh[:, d:2 * d], more=[(dv, Bsh[:, 2 * d:])], alpha=s)
+            ops.lora_grad(self.dU, self.h1[l], self.gAt_all[rows], r=R_PAD, cols=d)
+            ops.gemm(dq, Wqkv[:, :d], self.dln, a2=dk, b2=Wqkv[:, d:2 * d],
+                     more=[(dv, Wqkv[:, 2 * d:]), (self.dU, self.A_sh[:, rows])])
             ops.layernorm_bwd_dx(self.dln, self.x[l], W["ln1.g"], *self.st1[l], dx0, dres=dx1)
             dx, dx0 = dx0, dx
             if self.grad_sync is not None:

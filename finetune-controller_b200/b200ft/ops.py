@@ -54,10 +54,11 @@ def _need_cuda(*ts):
             raise _lib.B200FTError("b200ft ops take CUDA tensors only (no CPU path exists)")
 
 
-def gemm(a, b, out, *, a_mn=False, b_mn=False, a2=None, b2=None, bias=None, epilogue=EPI_NONE,
+def gemm(a, b, out, *, a_mn=False, b_mn=False, a2=None, b2=None, more=(), bias=None, epilogue=EPI_NONE,
          aux=None, out2=None, alpha=1.0, block_n=0, max_ctas=0, split_k=0, cta_group=0, m=None, n=None, k=None, k2=None):
-    """out[m,n] = epi(alpha * (A.B^T + A2.B2^T) + bias).  A: [M,K] (K-major) or [K,M] (a_mn);
-    B: [N,K] or [K,N] (b_mn); A2 [M,K2], B2 [N,K2].  Row pitch = stride(0)."""
+    """out[m,n] = epi(alpha * (A.B^T + A2.B2^T + ...) + bias).  A: [M,K] (K-major) or [K,M] (a_mn);
+    B: [N,K] or [K,N] (b_mn); A2 [M,K2], B2 [N,K2]; `more` = up to two further (A_i, B_i) pairs.
+    Row pitch = stride(0)."""
     global LAUNCHES
     _need_cuda(a, b, out, a2, b2, bias, aux, out2)
     assert a.dtype == b.dtype == torch.bfloat16
@@ -79,6 +80,14 @@ def gemm(a, b, out, *, a_mn=False, b_mn=False, a2=None, b2=None, bias=None, epil
         args.a2, args.lda2 = a2.data_ptr(), a2.stride(0)
         args.b2, args.ldb2 = b2.data_ptr(), b2.stride(0)
         args.k2 = k2 if k2 is not None else a2.shape[1]
+    kk_more = 0
+    for i, (ai, bi) in enumerate(more):
+        assert a2 is not None and i < 2 and ai.dtype == bi.dtype == torch.bfloat16
+        _need_cuda(ai, bi)
+        setattr(args, f"a{i + 3}", ai.data_ptr()); setattr(args, f"lda{i + 3}", ai.stride(0))
+        setattr(args, f"b{i + 3}", bi.data_ptr()); setattr(args, f"ldb{i + 3}", bi.stride(0))
+        setattr(args, f"k{i + 3}", ai.shape[1])
+        kk_more += ai.shape[1]
     args.layout = (A_MN_MAJOR if a_mn else 0) | (B_MN_MAJOR if b_mn else 0)
     args.epilogue = epilogue
     args.alpha = alpha
@@ -91,7 +100,7 @@ def gemm(a, b, out, *, a_mn=False, b_mn=False, a2=None, b2=None, bias=None, epil
     if out2 is not None:
         args.c2, args.ldc2 = out2.data_ptr(), out2.stride(0)
     args.block_n, args.max_ctas, args.split_k, args.cta_group = block_n, max_ctas, split_k, cta_group
-    kk = k + (args.k2 if a2 is not None else 0)
+    kk = k + (args.k2 if a2 is not None else 0) + kk_more
     with _timed("gemm", 2.0 * m * n * kk, (m, n, kk, int(a_mn), int(b_mn), epilogue)):
         check(lib().b200ft_gemm_bf16(ctypes.byref(args), _stream()), "gemm_bf16")
     LAUNCHES += 1

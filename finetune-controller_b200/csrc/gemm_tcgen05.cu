@@ -56,6 +56,7 @@ template <int CG> struct RingCfg {
   static_assert(kStages * (kAStageBytes + kBStageBytes) == kTileBytes, "ring size");
 };
 constexpr int kMaxStages = 6;
+constexpr int kMaxSeg = 4;
 constexpr uint32_t kPeerBitMask = 0xFEFFFFFFu;  // clears the CTA-rank bit of a shared::cluster address -> CTA 0
 constexpr int kEpiWarps = 8;                           // two per TMEM lane quarter
 constexpr int kEpiBufBytes = 32 * 32 * 2;              // one 32-row x 32-col bf16 staging tile (2 KB)
@@ -69,9 +70,16 @@ constexpr int kTmemCols = 512;
 constexpr int kAccStride = 256;  // TMEM columns per accumulator stage
 constexpr long long kWaitLimitCycles = 4000000000ll;  // ~2 s: deadlock guard, trap instead of hanging the GPU
 
+struct TmapPack {  // one __grid_constant__ block: TMA reads descriptors straight from param space
+  CUtensorMap a[kMaxSeg], b[kMaxSeg];
+  CUtensorMap c, c2, aux;
+};
+
 struct GemmParams {
   int M, N, BN;
-  int k1, k2, kblocks1, kblocks2;
+  int nseg;                    // K segments: acc = sum_s A_s . B_s^T
+  int k[kMaxSeg];              // reduction length of each
+  int kb_prefix[kMaxSeg + 1];  // first 64-wide K slab of each (prefix sums)
   int a_mn, b_mn;
   int tiles_m, tiles_n;
   int splits, kb_per_split;  // split-K: work item w -> (tile = w / splits, K slabs of split w % splits)
@@ -435,10 +443,7 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtenso
 // ---------------------------------------------------------------------------------------
 template <int CG>
 __global__ void __launch_bounds__(kThreads, 1)
-gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_constant__ CUtensorMap tmB1,
-                         const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmB2,
-                         const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmC2,
-                         const __grid_constant__ CUtensorMap tmAux, const GemmParams p) {
+gemm_bf16_tcgen05_kernel(const __grid_constant__ TmapPack maps, const GemmParams p) {
   constexpr int kStages = RingCfg<CG>::kStages;
   constexpr int kBStageBytes = RingCfg<CG>::kBStageBytes;
   extern __shared__ uint8_t smem_raw[];
@@ -466,10 +471,8 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
   const int w_stride = gridDim.x / CG;
 
   if (warp == 0 && lane == 0) {
-    tma_prefetch_desc(&tmA1);
-    tma_prefetch_desc(&tmB1);
-    if (p.kblocks2 > 0) { tma_prefetch_desc(&tmA2); tma_prefetch_desc(&tmB2); }
-    tma_prefetch_desc(&tmC);
+    for (int sgi = 0; sgi < p.nseg; ++sgi) { tma_prefetch_desc(&maps.a[sgi]); tma_prefetch_desc(&maps.b[sgi]); }
+    tma_prefetch_desc(&maps.c);
   }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < kStages; ++s) { mbar_init(full_bar(s), CG); mbar_init(empty_bar(s), 1); }
@@ -488,7 +491,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
   const uint32_t tmem_base = *tmem_slot_ptr;
 
   const int num_work = p.tiles_m * p.tiles_n * p.splits;
-  const int kb_total = p.kblocks1 + p.kblocks2;
+  const int kb_total = p.kb_prefix[p.nseg];
   const int BN = p.BN;
 
   if (warp == 0) {
@@ -508,10 +511,14 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
       const int n0 = (tile % p.tiles_n) * BN + cta_rank * (int)b_rows;
       const int kb_begin = (w % p.splits) * p.kb_per_split;
       const int kb_end = min(kb_total, kb_begin + p.kb_per_split);
+      int seg = 0;
       for (int kb = kb_begin; kb < kb_end; ++kb) {
         mbar_wait(empty_bar(stage), phase ^ 1u);
-        const bool seg2 = kb >= p.kblocks1;
-        const int kk = (seg2 ? kb - p.kblocks1 : kb) * kBlockK;
+        while (kb >= p.kb_prefix[seg + 1]) ++seg;
+        const bool seg2 = seg > 0;  // only segment 0 may be MN-major
+        const int kk = (kb - p.kb_prefix[seg]) * kBlockK;
+        const CUtensorMap* tma_a = &maps.a[seg];
+        const CUtensorMap* tma_b = &maps.b[seg];
         const uint32_t a_dst = sA + stage * kAStageBytes;
         const uint32_t b_dst = sB + stage * kBStageBytes;
         const uint32_t fb = full_bar(stage);
@@ -520,19 +527,19 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
           if constexpr (CG == 1) {
             mbar_expect_tx(fb, bytes);
             if (seg2) {
-              tma_load_2d(a_dst, &tmA2, kk, m0, fb);
-              tma_load_2d(b_dst, &tmB2, kk, n0, fb);
+              tma_load_2d(a_dst, tma_a, kk, m0, fb);
+              tma_load_2d(b_dst, tma_b, kk, n0, fb);
             } else {
               if (a_mn) {
-                tma_load_2d(a_dst, &tmA1, m0, kk, fb);
-                tma_load_2d(a_dst + 8192u, &tmA1, m0 + 64, kk, fb);
+                tma_load_2d(a_dst, tma_a, m0, kk, fb);
+                tma_load_2d(a_dst + 8192u, tma_a, m0 + 64, kk, fb);
               } else {
-                tma_load_2d(a_dst, &tmA1, kk, m0, fb);
+                tma_load_2d(a_dst, tma_a, kk, m0, fb);
               }
               if (b_mn) {
-                for (int j = 0; j * 64 < BN; ++j) tma_load_2d(b_dst + 8192u * j, &tmB1, n0 + 64 * j, kk, fb);
+                for (int j = 0; j * 64 < BN; ++j) tma_load_2d(b_dst + 8192u * j, tma_b, n0 + 64 * j, kk, fb);
               } else {
-                tma_load_2d(b_dst, &tmB1, kk, n0, fb);
+                tma_load_2d(b_dst, tma_b, kk, n0, fb);
               }
             }
           } else {
@@ -540,8 +547,8 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
             // the peer adds its (byte-less) arrival
             if (cta_rank == 0) mbar_expect_tx(fb, 2u * bytes);
             else mbar_arrive_cluster(fb, 0);
-            tma_load_2d_cg2(a_dst, seg2 ? &tmA2 : &tmA1, kk, m0, fb);
-            tma_load_2d_cg2(b_dst, seg2 ? &tmB2 : &tmB1, kk, n0, fb);
+            tma_load_2d_cg2(a_dst, tma_a, kk, m0, fb);
+            tma_load_2d_cg2(b_dst, tma_b, kk, n0, fb);
           }
         }
         __syncwarp();
@@ -573,11 +580,13 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
         const uint32_t d_tmem = tmem_base + (uint32_t)(acc * kAccStride);
         const int kb_begin = (w % p.splits) * p.kb_per_split;
         const int kb_end = min(kb_total, kb_begin + p.kb_per_split);
+        int seg = 0;
         for (int kb = kb_begin; kb < kb_end; ++kb) {
           mbar_wait(full_bar(stage), phase);
           tc_fence_after();
-          const bool seg2 = kb >= p.kblocks1;
-          const int kleft = seg2 ? p.k2 - (kb - p.kblocks1) * kBlockK : p.k1 - kb * kBlockK;
+          while (kb >= p.kb_prefix[seg + 1]) ++seg;
+          const bool seg2 = seg > 0;
+          const int kleft = p.k[seg] - (kb - p.kb_prefix[seg]) * kBlockK;
           const uint32_t a_lo = (seg2 ? a_lo2 : a_lo1) + (uint32_t)stage * (kAStageBytes >> 4);
           const uint32_t b_lo = (seg2 ? b_lo2 : b_lo1) + (uint32_t)stage * (kBStageBytes >> 4);
           const uint32_t a_step = seg2 ? 2u : a_step1, b_step = seg2 ? 2u : b_step1;
@@ -630,10 +639,10 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA1, const __grid_
     const int et = threadIdx.x - 128;
     const uint32_t eb = sEpi + ew * 2 * kEpiBufBytes;
     if (p.cw == 32)
-      epilogue_loop<32, CG>(p, &tmC, &tmC2, &tmAux, q, h, lane, et, tmem_base, eb, sBias, aux_bar(ew, 0), aux_bar(ew, 1),
+      epilogue_loop<32, CG>(p, &maps.c, &maps.c2, &maps.aux, q, h, lane, et, tmem_base, eb, sBias, aux_bar(ew, 0), aux_bar(ew, 1),
                             tfull_bar(0), tempty_bar(0), num_work, w_begin, w_stride, cta_rank);
     else
-      epilogue_loop<16, CG>(p, &tmC, &tmC2, &tmAux, q, h, lane, et, tmem_base, eb, sBias, aux_bar(ew, 0), aux_bar(ew, 1),
+      epilogue_loop<16, CG>(p, &maps.c, &maps.c2, &maps.aux, q, h, lane, et, tmem_base, eb, sBias, aux_bar(ew, 0), aux_bar(ew, 1),
                             tfull_bar(0), tempty_bar(0), num_work, w_begin, w_stride, cta_rank);
   }
 
@@ -736,12 +745,21 @@ extern "C" int b200ft_gemm_bf16(const b200ft_gemm_args* a, void* stream) {
   B200FT_CHECK_ARG(a->lda1 % 8 == 0 && a->ldb1 % 8 == 0, "gemm: lda1=%lld ldb1=%lld must be multiples of 8",
                    (long long)a->lda1, (long long)a->ldb1);
   B200FT_CHECK_ARG(((uintptr_t)a->a1 | (uintptr_t)a->b1 | (uintptr_t)a->c) % 16 == 0, "gemm: 16-byte alignment required");
-  const bool seg2 = a->a2 != nullptr;
-  if (seg2) {
-    B200FT_CHECK_ARG(a->b2 && a->k2 > 0 && a->lda2 % 8 == 0 && a->ldb2 % 8 == 0 &&
-                         ((uintptr_t)a->a2 | (uintptr_t)a->b2) % 16 == 0,
-                     "gemm: bad second segment (k2=%d lda2=%lld ldb2=%lld)", a->k2, (long long)a->lda2,
-                     (long long)a->ldb2);
+  // K segments 2..4 (all K-major): a NULL a_i ends the list
+  const void* seg_a[kMaxSeg] = {a->a1, a->a2, a->a3, a->a4};
+  const void* seg_b[kMaxSeg] = {a->b1, a->b2, a->b3, a->b4};
+  const int64_t seg_lda[kMaxSeg] = {a->lda1, a->lda2, a->lda3, a->lda4};
+  const int64_t seg_ldb[kMaxSeg] = {a->ldb1, a->ldb2, a->ldb3, a->ldb4};
+  const int seg_k[kMaxSeg] = {a->k1, a->k2, a->k3, a->k4};
+  int nseg = 1;
+  while (nseg < kMaxSeg && seg_a[nseg] != nullptr) ++nseg;
+  for (int i = nseg; i < kMaxSeg; ++i)
+    B200FT_CHECK_ARG(seg_a[i] == nullptr, "gemm: segment %d given after an empty segment", i + 1);
+  for (int i = 1; i < nseg; ++i) {
+    B200FT_CHECK_ARG(seg_b[i] && seg_k[i] > 0 && seg_lda[i] % 8 == 0 && seg_ldb[i] % 8 == 0 &&
+                         ((uintptr_t)seg_a[i] | (uintptr_t)seg_b[i]) % 16 == 0,
+                     "gemm: bad segment %d (k=%d lda=%lld ldb=%lld)", i + 1, seg_k[i], (long long)seg_lda[i],
+                     (long long)seg_ldb[i]);
   }
   B200FT_CHECK_ARG(a->epilogue >= 0 && a->epilogue <= 4, "gemm: epilogue=%d", a->epilogue);
   B200FT_CHECK_ARG(a->split_k >= 0 && (a->split_k <= 1 || atomic_t), "gemm: split_k=%d needs the ATOMIC_F32_T epilogue",
@@ -765,9 +783,12 @@ extern "C" int b200ft_gemm_bf16(const b200ft_gemm_args* a, void* stream) {
   GemmParams p;
   memset(&p, 0, sizeof(p));
   p.M = a->m; p.N = a->n; p.BN = BN;
-  p.k1 = a->k1; p.k2 = seg2 ? a->k2 : 0;
-  p.kblocks1 = (a->k1 + kBlockK - 1) / kBlockK;
-  p.kblocks2 = seg2 ? (a->k2 + kBlockK - 1) / kBlockK : 0;
+  p.nseg = nseg;
+  p.kb_prefix[0] = 0;
+  for (int i = 0; i < kMaxSeg; ++i) {
+    p.k[i] = i < nseg ? seg_k[i] : 0;
+    p.kb_prefix[i + 1] = p.kb_prefix[i] + (p.k[i] + kBlockK - 1) / kBlockK;
+  }
   p.a_mn = (a->layout & B200FT_A_MN_MAJOR) ? 1 : 0;
   p.b_mn = (a->layout & B200FT_B_MN_MAJOR) ? 1 : 0;
   p.tiles_m = (a->m + kBlockM * cg - 1) / (kBlockM * cg);
@@ -780,7 +801,7 @@ extern "C" int b200ft_gemm_bf16(const b200ft_gemm_args* a, void* stream) {
   p.c2 = (__nv_bfloat16*)a->c2; p.ldc2 = a->ldc2;
   p.cf = (float*)a->c;
   {
-    const int kb_total = p.kblocks1 + p.kblocks2;
+    const int kb_total = p.kb_prefix[nseg];
     int splits = a->split_k > 0 ? a->split_k : 1;
     if (atomic_t && a->split_k == 0) {  // fill the machine: tiles * splits ~ one wave of CTAs
       const int tiles = p.tiles_m * p.tiles_n;
@@ -794,38 +815,40 @@ extern "C" int b200ft_gemm_bf16(const b200ft_gemm_args* a, void* stream) {
 
   p.cw = (BN % 32 == 0) ? 32 : 16;
   const int esw = p.cw == 32 ? 1 : 0;  // staging tile swizzle: 64B for the 32-column tile, none for 16
-  CUtensorMap tA1, tB1, tA2, tB2, tC, tC2, tAux;
+  TmapPack maps;
   int rc;
+  if (p.a_mn) rc = get_tensor_map(a->a1, (uint64_t)a->m, (uint64_t)a->k1, (uint64_t)a->lda1, 64, 64, &maps.a[0]);
+  else        rc = get_tensor_map(a->a1, (uint64_t)a->k1, (uint64_t)a->m, (uint64_t)a->lda1, 64, kBlockM, &maps.a[0]);
+  if (rc) return rc;
+  if (p.b_mn) rc = get_tensor_map(a->b1, (uint64_t)a->n, (uint64_t)a->k1, (uint64_t)a->ldb1, 64, 64, &maps.b[0]);
+  else        rc = get_tensor_map(a->b1, (uint64_t)a->k1, (uint64_t)a->n, (uint64_t)a->ldb1, 64, (uint32_t)(BN / cg), &maps.b[0]);
+  if (rc) return rc;
+  for (int i = 1; i < kMaxSeg; ++i) {
+    if (i < nseg) {
+      rc = get_tensor_map(seg_a[i], (uint64_t)seg_k[i], (uint64_t)a->m, (uint64_t)seg_lda[i], 64, kBlockM, &maps.a[i]);
+      if (rc) return rc;
+      rc = get_tensor_map(seg_b[i], (uint64_t)seg_k[i], (uint64_t)a->n, (uint64_t)seg_ldb[i], 64, (uint32_t)(BN / cg), &maps.b[i]);
+      if (rc) return rc;
+    } else {
+      maps.a[i] = maps.a[0]; maps.b[i] = maps.b[0];  // never dereferenced; keep the block initialised
+    }
+  }
   // epilogue staging tiles: {cw columns, 32 rows}
-  if (!atomic_t) {
-    rc = get_tensor_map(a->c, (uint64_t)a->n, (uint64_t)a->m, (uint64_t)a->ldc, (uint32_t)p.cw, 32, &tC, esw);
+  if (atomic_t) {
+    maps.c = maps.a[0];  // unused by this epilogue; any valid descriptor
+  } else {
+    rc = get_tensor_map(a->c, (uint64_t)a->n, (uint64_t)a->m, (uint64_t)a->ldc, (uint32_t)p.cw, 32, &maps.c, esw);
     if (rc) return rc;
   }
+  maps.c2 = maps.c; maps.aux = maps.c;
   if (a->epilogue == B200FT_EPI_GELU) {
-    rc = get_tensor_map(a->c2, (uint64_t)a->n, (uint64_t)a->m, (uint64_t)a->ldc2, (uint32_t)p.cw, 32, &tC2, esw);
+    rc = get_tensor_map(a->c2, (uint64_t)a->n, (uint64_t)a->m, (uint64_t)a->ldc2, (uint32_t)p.cw, 32, &maps.c2, esw);
     if (rc) return rc;
   }
   if (a->epilogue == B200FT_EPI_RESIDUAL || a->epilogue == B200FT_EPI_DGELU) {
-    rc = get_tensor_map(a->aux, (uint64_t)a->n, (uint64_t)a->m, (uint64_t)a->ld_aux, (uint32_t)p.cw, 32, &tAux, esw);
+    rc = get_tensor_map(a->aux, (uint64_t)a->n, (uint64_t)a->m, (uint64_t)a->ld_aux, (uint32_t)p.cw, 32, &maps.aux, esw);
     if (rc) return rc;
   }
-  if (p.a_mn) rc = get_tensor_map(a->a1, (uint64_t)a->m, (uint64_t)a->k1, (uint64_t)a->lda1, 64, 64, &tA1);
-  else        rc = get_tensor_map(a->a1, (uint64_t)a->k1, (uint64_t)a->m, (uint64_t)a->lda1, 64, kBlockM, &tA1);
-  if (rc) return rc;
-  if (p.b_mn) rc = get_tensor_map(a->b1, (uint64_t)a->n, (uint64_t)a->k1, (uint64_t)a->ldb1, 64, 64, &tB1);
-  else        rc = get_tensor_map(a->b1, (uint64_t)a->k1, (uint64_t)a->n, (uint64_t)a->ldb1, 64, (uint32_t)(BN / cg), &tB1);
-  if (rc) return rc;
-  if (seg2) {
-    rc = get_tensor_map(a->a2, (uint64_t)a->k2, (uint64_t)a->m, (uint64_t)a->lda2, 64, kBlockM, &tA2);
-    if (rc) return rc;
-    rc = get_tensor_map(a->b2, (uint64_t)a->k2, (uint64_t)a->n, (uint64_t)a->ldb2, 64, (uint32_t)(BN / cg), &tB2);
-    if (rc) return rc;
-  } else {
-    tA2 = tA1; tB2 = tB1;
-  }
-  if (atomic_t) tC = tA1;  // unused by this epilogue; any valid descriptor
-  if (a->epilogue != B200FT_EPI_GELU) tC2 = tC;
-  if (!(a->epilogue == B200FT_EPI_RESIDUAL || a->epilogue == B200FT_EPI_DGELU)) tAux = tC;
 
   // the opt-in shared-memory size is a per-device function attribute
   static thread_local int attr_dev = -1;
@@ -839,7 +862,7 @@ extern "C" int b200ft_gemm_bf16(const b200ft_gemm_args* a, void* stream) {
   const int num_work = p.tiles_m * p.tiles_n * p.splits;
   if (cg == 1) {
     const int grid = num_work < ctas_max ? num_work : ctas_max;
-    gemm_bf16_tcgen05_kernel<1><<<grid, kThreads, kSmemBytes, (cudaStream_t)stream>>>(tA1, tB1, tA2, tB2, tC, tC2, tAux, p);
+    gemm_bf16_tcgen05_kernel<1><<<grid, kThreads, kSmemBytes, (cudaStream_t)stream>>>(maps, p);
     B200FT_LAUNCH_CHECK();
     return 0;
   }
@@ -856,6 +879,6 @@ extern "C" int b200ft_gemm_bf16(const b200ft_gemm_args* a, void* stream) {
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr; cfg.numAttrs = 1;
-  B200FT_CUDA(cudaLaunchKernelEx(&cfg, gemm_bf16_tcgen05_kernel<2>, tA1, tB1, tA2, tB2, tC, tC2, tAux, p));
+  B200FT_CUDA(cudaLaunchKernelEx(&cfg, gemm_bf16_tcgen05_kernel<2>, maps, p));
   return 0;
 }

@@ -46,7 +46,7 @@ const char* b200ft_last_error_string(void);
  * Projection / LoRA GEMM on tcgen05 tensor cores (SURVEY.md §8 a2.1, a2.2, a2.3, a2.5;
  * oracle/gpt2_lora_ref.py:_linear and its autograd transpose).
  *
- *   acc[m,n] = sum_{k<k1} A1[m,k]*B1[n,k]  +  sum_{k<k2} A2[m,k]*B2[n,k]      (fp32 in TMEM)
+ *   acc[m,n] = sum_s sum_{k<k_s} A_s[m,k]*B_s[n,k],  s = 1..4                 (fp32 in TMEM)
  *   v        = alpha*acc + bias[n]
  *   epilogue NONE     : C = v
  *            RESIDUAL : C = v + AUX[m,n]
@@ -56,11 +56,12 @@ const char* b200ft_last_error_string(void);
  *                       the reduction can be split over K slabs (split_k) across CTAs; no bias.
  *                       Used for the adapter-gradient contractions over tokens.
  *
- * The second K segment is how a LoRA branch is fused: with A2 = s*(X*A_lora) and
- * B2 = B_lora^T it adds the rank-r product into the same TMEM accumulator as the frozen
- * projection.  Operands are bf16.  "K-major" = the reduction index is contiguous
- * (A: [M, lda], B: [N, ldb]); "MN-major" = the M (resp. N) index is contiguous
- * (A: [K, lda], B: [K, ldb]).  Segment 2 is always K-major.
+ * Extra K segments are how a LoRA branch is fused: with A2 = s*(X*A_lora) and B2 = B_lora^T the
+ * rank-r product lands in the same TMEM accumulator as the frozen projection; backward of the
+ * fused qkv projection uses four (dq, dk, dv and the adapter term).  Operands are bf16.
+ * "K-major" = the reduction index is contiguous (A: [M, lda], B: [N, ldb]); "MN-major" = the M
+ * (resp. N) index is contiguous (A: [K, lda], B: [K, ldb]).  Segments 2..4 are always K-major;
+ * a NULL a_i ends the list.
  * ------------------------------------------------------------------------------------- */
 enum {
   B200FT_EPI_NONE = 0,
@@ -79,6 +80,12 @@ typedef struct b200ft_gemm_args {
   const void* a2; int64_t lda2;   /* NULL when there is no second segment */
   const void* b2; int64_t ldb2;
   int32_t k2;
+  const void* a3; int64_t lda3;
+  const void* b3; int64_t ldb3;
+  int32_t k3;
+  const void* a4; int64_t lda4;
+  const void* b4; int64_t ldb4;
+  int32_t k4;
   int32_t layout;                 /* B200FT_A_MN_MAJOR | B200FT_B_MN_MAJOR, segment 1 only */
   int32_t epilogue;               /* B200FT_EPI_* */
   float alpha;

@@ -283,6 +283,28 @@ def test_gemm_second_segment(ops, K2, cta_group):
 
 
 @pytest.mark.parametrize("cta_group", [1, 2])
+def test_gemm_four_segments_with_strided_views(ops, cta_group):
+    # backward of the fused qkv projection: dq.Wq^T + dk.Wk^T + dv.Wv^T + dU.A^T, the B operands
+    # being column blocks (views) of one [d, 3d] weight
+    g = torch.Generator().manual_seed(5)
+    M, d, r = 640, 256, 16
+    W = bf16_round(torch.randn(d, 3 * d, generator=g) * 0.1)
+    As = [bf16_round(torch.randn(M, d, generator=g)) for _ in range(3)]
+    dU = bf16_round(torch.randn(M, r, generator=g))
+    Ad = bf16_round(torch.randn(d, 48, generator=g))      # adapter block lives inside a wider matrix
+    exp = sum(As[i].double() @ W[:, i * d:(i + 1) * d].double().t() for i in range(3)) + dU.double() @ Ad[:, 16:32].double().t()
+    Wd = W.to(DEV, torch.bfloat16)
+    Add = Ad.to(DEV, torch.bfloat16)
+    Asd = [a.to(DEV, torch.bfloat16) for a in As]
+    out = torch.full((M, d), float("nan"), dtype=torch.bfloat16, device=DEV)
+    ops.gemm(Asd[0], Wd[:, :d], out, a2=Asd[1], b2=Wd[:, d:2 * d],
+             more=[(Asd[2], Wd[:, 2 * d:]), (dU.to(DEV, torch.bfloat16), Add[:, 16:32])], cta_group=cta_group)
+    got = out.cpu().double()
+    assert not torch.isnan(got).any()
+    assert (got - exp).abs().max().item() <= 1e-2 * math.sqrt(3 * d) + 2 ** -7 * exp.abs().max().item()
+
+
+@pytest.mark.parametrize("cta_group", [1, 2])
 @pytest.mark.parametrize("block_n", [16, 64, 128, 192, 256])
 def test_gemm_block_n(ops, block_n, cta_group):
     _gemm_case(ops, 640, 768, 320, block_n=block_n, cta_group=cta_group)
