@@ -122,4 +122,71 @@ __device__ __forceinline__ float gelu_new_grad_f(float x) {
   return 0.5f * (1.f + t) + 0.5f * x * dt;
 }
 
+// ----------------------------------------------------------------------------------
+// packed fp32 pairs (sm_100 FFMA2 / FMUL2 / FADD2): one instruction per two elements.  A pair
+// lives in a 64-bit register; pack/unpack are register-pair moves the assembler elides.
+// ----------------------------------------------------------------------------------
+typedef unsigned long long f32x2_t;
+__device__ __forceinline__ f32x2_t pk2(float lo, float hi) {
+  f32x2_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void upk2(f32x2_t v, float& lo, float& hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ f32x2_t fma2(f32x2_t a, f32x2_t b, f32x2_t c) {
+  f32x2_t d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+__device__ __forceinline__ f32x2_t mul2(f32x2_t a, f32x2_t b) {
+  f32x2_t d;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+__device__ __forceinline__ f32x2_t add2(f32x2_t a, f32x2_t b) {
+  f32x2_t d;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+__device__ __forceinline__ f32x2_t sub2(f32x2_t a, f32x2_t b) {
+  f32x2_t d;
+  asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+__device__ __forceinline__ f32x2_t tanh2(f32x2_t u) {
+  float a, b;
+  upk2(u, a, b);
+  return pk2(tanh_approx(a), tanh_approx(b));
+}
+// a bf16x2 word <-> a packed fp32 pair (.lo = low 16 bits)
+__device__ __forceinline__ f32x2_t bf16x2_to_f32x2(uint32_t w) { return pk2(bf16lo(w), bf16hi(w)); }
+__device__ __forceinline__ uint32_t f32x2_to_bf16x2(f32x2_t v) {
+  float lo, hi;
+  upk2(v, lo, hi);
+  return pack_bf16x2(lo, hi);
+}
+// gelu_new and its derivative on a pair; same formulas as the scalar versions above
+__device__ __forceinline__ f32x2_t gelu_new2(f32x2_t x) {
+  const f32x2_t k0 = pk2(0.7978845608028654f, 0.7978845608028654f);
+  const f32x2_t k0k1 = pk2(0.7978845608028654f * 0.044715f, 0.7978845608028654f * 0.044715f);
+  const f32x2_t half = pk2(0.5f, 0.5f);
+  const f32x2_t x2 = mul2(x, x);
+  const f32x2_t t = tanh2(mul2(x, fma2(x2, k0k1, k0)));
+  const f32x2_t hx = mul2(x, half);
+  return fma2(hx, t, hx);
+}
+__device__ __forceinline__ f32x2_t gelu_new_grad2(f32x2_t x) {
+  const f32x2_t k0 = pk2(0.7978845608028654f, 0.7978845608028654f);
+  const f32x2_t k0k1 = pk2(0.7978845608028654f * 0.044715f, 0.7978845608028654f * 0.044715f);
+  const f32x2_t k0k1x3 = pk2(3.f * 0.7978845608028654f * 0.044715f, 3.f * 0.7978845608028654f * 0.044715f);
+  const f32x2_t half = pk2(0.5f, 0.5f), one = pk2(1.f, 1.f);
+  const f32x2_t x2 = mul2(x, x);
+  const f32x2_t t = tanh2(mul2(x, fma2(x2, k0k1, k0)));
+  const f32x2_t sech2 = sub2(one, mul2(t, t));
+  const f32x2_t w = mul2(mul2(x, half), fma2(x2, k0k1x3, k0));   // 0.5 x k0 (1 + 3 k1 x^2)
+  return fma2(w, sech2, fma2(half, t, half));
+}
+
 #endif  // __CUDACC__

@@ -49,20 +49,21 @@ constexpr int kBlockM = 128;
 constexpr int kBlockK = 64;  // 64 bf16 = 128 B = one swizzle row
 constexpr int kMaxBN = 256;
 constexpr int kAStageBytes = kBlockM * kBlockK * 2;  // 16 KB
-constexpr int kTileBytes = 4 * (kAStageBytes + kMaxBN * kBlockK * 2);  // 192 KB of operand ring either way
+constexpr int kTileBytes = 160 * 1024;  // operand ring
 template <int CG> struct RingCfg {
-  static constexpr int kStages = CG == 1 ? 4 : 6;
+  static constexpr int kStages = CG == 1 ? 3 : 5;
   static constexpr int kBStageBytes = kMaxBN / CG * kBlockK * 2;  // 32 KB, or 16 KB (half of B per CTA)
-  static_assert(kStages * (kAStageBytes + kBStageBytes) == kTileBytes, "ring size");
+  static_assert(kStages * (kAStageBytes + kBStageBytes) <= kTileBytes, "ring size");
 };
-constexpr int kMaxStages = 6;
+constexpr int kMaxStages = 5;
 constexpr int kMaxSeg = 4;
 constexpr uint32_t kPeerBitMask = 0xFEFFFFFFu;  // clears the CTA-rank bit of a shared::cluster address -> CTA 0
 constexpr int kEpiWarps = 8;                           // two per TMEM lane quarter
 constexpr int kEpiBufBytes = 32 * 32 * 2;              // one 32-row x 32-col bf16 staging tile (2 KB)
-constexpr int kEpiBytes = kEpiWarps * 2 * kEpiBufBytes;  // 8 epilogue warps x 2 tiles = 32 KB
+constexpr int kEpiBufs = 4;                            // staging ring per epilogue warp
+constexpr int kEpiBytes = kEpiWarps * kEpiBufs * kEpiBufBytes;  // 8 warps x 4 tiles x 2 KB = 64 KB
 constexpr int kBiasBytes = kMaxBN * 4;                 // the tile's bias slice, fp32
-constexpr int kBarrierBytes = 384;
+constexpr int kBarrierBytes = 512;
 constexpr int kSmemBytes = kTileBytes + kEpiBytes + kBiasBytes + kBarrierBytes + 1024;  // + slack to align to 1024
 static_assert(kSmemBytes <= 227 * 1024, "shared memory budget");
 constexpr int kThreads = 128 + 32 * kEpiWarps;         // 4 control warps + 8 epilogue warps
@@ -288,22 +289,45 @@ __device__ __forceinline__ float4 lds_f4(uint32_t addr) {
 }
 
 // q = TMEM lane quarter, h = which of the quarter's two warps (takes chunks h, h+2, ...),
-// et = index among the 256 epilogue threads
+// et = index among the 256 epilogue threads.
+//
+// Staging ring: kEpiBufs 2 KB tiles per warp, used in sequence (n & 3).  For the epilogues with a
+// second operand (residual / gelu') chunk n's operand is TMA-loaded into buffer n & 3 THREE chunks
+// ahead of its use — across tile boundaries — so that every warp keeps 6 KB (48 KB per SM) of
+// that stream in flight; the result is written over it in place and leaves by TMA store.
 template <int CW, int CG>
 __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtensorMap* tmC, const CUtensorMap* tmC2,
                                               const CUtensorMap* tmAux, int q, int h, int lane, int et,
-                                              uint32_t tmem_base, uint32_t ebuf, uint32_t sbias, uint32_t abar0,
-                                              uint32_t abar1, uint32_t tfull0, uint32_t tempty0, int num_work,
-                                              int w_begin, int w_stride, int cta_rank) {
+                                              uint32_t tmem_base, uint32_t ebuf, uint32_t sbias, uint32_t abar,
+                                              uint32_t tfull0, uint32_t tempty0, int num_work, int w_begin,
+                                              int w_stride, int cta_rank) {
   const int BN = p.BN;
   const int nchunks = BN / CW;
+  const int cpw = nchunks > h ? (nchunks - h + 1) / 2 : 0;  // chunks of a tile this warp owns
   const bool has_aux = (p.epilogue == B200FT_EPI_RESIDUAL) || (p.epilogue == B200FT_EPI_DGELU);
   const bool atomic_t = (p.epilogue == B200FT_EPI_ATOMIC_F32_T);
   const bool has_bias = p.bias != nullptr;
   const bool scale = p.alpha != 1.0f;
   const uint32_t aux_bytes = 32u * CW * 2u;
-  uint32_t slot = 0;          // running count of staged tiles: buffer = slot & 1
-  uint32_t aux_phase = 0;     // bit b = parity to wait for on aux barrier b
+  constexpr uint32_t kDepth = kEpiBufs - 1;  // operand prefetch distance, in chunks
+
+  // operand load of this warp's chunk number n (counted across all its tiles); lane 0 only
+  auto issue_aux = [&](uint32_t n) {
+    const int ti = (int)n / cpw, ci = (int)n % cpw;
+    const int w2 = w_begin + ti * w_stride;
+    if (w2 >= num_work) return;
+    const int tile2 = w2 / p.splits;
+    const int r0 = (tile2 / p.tiles_n) * (kBlockM * CG) + cta_rank * kBlockM + q * 32;
+    const int c0 = (tile2 % p.tiles_n) * BN + (h + 2 * ci) * CW;
+    const uint32_t b = n & (kEpiBufs - 1);
+    mbar_expect_tx(abar + 8u * b, aux_bytes);
+    tma_load_2d(ebuf + b * kEpiBufBytes, tmAux, c0, r0, abar + 8u * b);
+  };
+  if (has_aux && cpw > 0 && lane == 0) {
+    for (uint32_t n = 0; n < kDepth; ++n) issue_aux(n);
+  }
+
+  uint32_t seq = 0;  // staged tiles so far: buffer = seq & 3 (== chunk number when has_aux)
   int acc = 0;
   uint32_t acc_phase = 0;
   for (int w = w_begin; w < num_work; w += w_stride) {
@@ -320,18 +344,11 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtenso
       }
       epi_bar_sync();
     }
-    if (has_aux && h < nchunks && lane == 0) {  // first chunk's operand, in flight during the tfull wait
-      const uint32_t b = slot & 1u;
-      tma_store_wait_read<1>();  // the store that last used this buffer has drained it
-      const uint32_t bar = b ? abar1 : abar0;
-      mbar_expect_tx(bar, aux_bytes);
-      tma_load_2d(ebuf + b * kEpiBufBytes, tmAux, n0 + h * CW, row0, bar);
-    }
     mbar_wait(tfull0 + 8u * acc, acc_phase);
     tc_fence_after();
     const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * kAccStride);
     for (int c = h; c < nchunks; c += 2) {
-      const uint32_t b = slot & 1u;
+      const uint32_t b = seq & (kEpiBufs - 1);
       const uint32_t buf = ebuf + b * kEpiBufBytes;
       uint32_t r[CW];
       if constexpr (CW == 32) tmem_ld32(t_row + c * CW, r);
@@ -352,41 +369,45 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtenso
         continue;
       }
       if (has_aux) {
-        mbar_wait(b ? abar1 : abar0, (aux_phase >> b) & 1u);
-        aux_phase ^= (1u << b);
+        mbar_wait(abar + 8u * b, (seq >> 2) & 1u);  // operand of this chunk has landed
       } else {
-        if (lane == 0) tma_store_wait_read<1>();
+        if (lane == 0) tma_store_wait_read<kEpiBufs - 1>();  // the store 4 tiles back has drained this buffer
         __syncwarp();
       }
       tmem_wait_ld();
-      if (scale) {
-#pragma unroll
-        for (int j = 0; j < CW; ++j) r[j] = __float_as_uint(__uint_as_float(r[j]) * p.alpha);
-      }
+      // the arithmetic below runs on packed fp32 pairs (FFMA2/FMUL2/FADD2): half the issue slots
+      const f32x2_t alpha2 = pk2(p.alpha, p.alpha);
 #pragma unroll
       for (int v = 0; v < CW / 8; ++v) {
-        float f[8];
+        f32x2_t f[4];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) f[j] = __uint_as_float(r[v * 8 + j]);
+        for (int i = 0; i < 4; ++i)
+          f[i] = pk2(__uint_as_float(r[v * 8 + 2 * i]), __uint_as_float(r[v * 8 + 2 * i + 1]));
+        if (scale) {
+#pragma unroll
+          for (int i = 0; i < 4; ++i) f[i] = mul2(f[i], alpha2);
+        }
         if (has_bias) {
           const float4 b0 = lds_f4(sbias + 4u * (c * CW + v * 8));
           const float4 b1 = lds_f4(sbias + 4u * (c * CW + v * 8 + 4));
-          f[0] += b0.x; f[1] += b0.y; f[2] += b0.z; f[3] += b0.w;
-          f[4] += b1.x; f[5] += b1.y; f[6] += b1.z; f[7] += b1.w;
+          f[0] = add2(f[0], pk2(b0.x, b0.y)); f[1] = add2(f[1], pk2(b0.z, b0.w));
+          f[2] = add2(f[2], pk2(b1.x, b1.y)); f[3] = add2(f[3], pk2(b1.z, b1.w));
         }
         const uint32_t addr = epi_vec_addr<CW>(buf, lane, v);
         if (has_aux) {
-          float a[8];
-          unpack8(lds16(addr), a);
+          const uint4 aw = lds16(addr);
+          const uint32_t a4[4] = {aw.x, aw.y, aw.z, aw.w};
           if (p.epilogue == B200FT_EPI_RESIDUAL) {
 #pragma unroll
-            for (int j = 0; j < 8; ++j) f[j] += a[j];
+            for (int i = 0; i < 4; ++i) f[i] = add2(f[i], bf16x2_to_f32x2(a4[i]));
           } else {
 #pragma unroll
-            for (int j = 0; j < 8; ++j) f[j] *= gelu_new_grad_f(a[j]);
+            for (int i = 0; i < 4; ++i) f[i] = mul2(f[i], gelu_new_grad2(bf16x2_to_f32x2(a4[i])));
           }
         }
-        const uint4 packed = pack8(f);
+        uint4 packed;
+        packed.x = f32x2_to_bf16x2(f[0]); packed.y = f32x2_to_bf16x2(f[1]);
+        packed.z = f32x2_to_bf16x2(f[2]); packed.w = f32x2_to_bf16x2(f[3]);
         sts16(addr, packed);
         if (p.epilogue == B200FT_EPI_GELU) {  // keep the bf16-rounded pre-activation for pass 2
           r[v * 8 + 0] = packed.x; r[v * 8 + 1] = packed.y; r[v * 8 + 2] = packed.z; r[v * 8 + 3] = packed.w;
@@ -395,34 +416,32 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtenso
       fence_proxy_async_smem();
       __syncwarp();
       if (lane == 0) tma_store_2d(tmC, buf, colbase, row0);
-      ++slot;
+      ++seq;
       if (p.epilogue == B200FT_EPI_GELU) {
         // second output: gelu of the bf16-ROUNDED pre-activation, so that backward (which only
         // has the stored bf16 value) differentiates exactly the function applied here
-        const uint32_t buf2 = ebuf + (slot & 1u) * kEpiBufBytes;
-        if (lane == 0) tma_store_wait_read<1>();
+        const uint32_t buf2 = ebuf + (seq & (kEpiBufs - 1)) * kEpiBufBytes;
+        if (lane == 0) tma_store_wait_read<kEpiBufs - 1>();
         __syncwarp();
 #pragma unroll
         for (int v = 0; v < CW / 8; ++v) {
-          uint4 pk;
-          pk.x = r[v * 8 + 0]; pk.y = r[v * 8 + 1]; pk.z = r[v * 8 + 2]; pk.w = r[v * 8 + 3];
-          float g[8];
-          unpack8(pk, g);
-#pragma unroll
-          for (int j = 0; j < 8; ++j) g[j] = gelu_new_f(g[j]);
-          sts16(epi_vec_addr<CW>(buf2, lane, v), pack8(g));
+          uint4 gq;
+          gq.x = f32x2_to_bf16x2(gelu_new2(bf16x2_to_f32x2(r[v * 8 + 0])));
+          gq.y = f32x2_to_bf16x2(gelu_new2(bf16x2_to_f32x2(r[v * 8 + 1])));
+          gq.z = f32x2_to_bf16x2(gelu_new2(bf16x2_to_f32x2(r[v * 8 + 2])));
+          gq.w = f32x2_to_bf16x2(gelu_new2(bf16x2_to_f32x2(r[v * 8 + 3])));
+          sts16(epi_vec_addr<CW>(buf2, lane, v), gq);
         }
         fence_proxy_async_smem();
         __syncwarp();
         if (lane == 0) tma_store_2d(tmC2, buf2, colbase, row0);
-        ++slot;
+        ++seq;
       }
-      if (has_aux && c + 2 < nchunks && lane == 0) {  // this warp's next chunk's operand
-        const uint32_t nb = slot & 1u;
+      if (has_aux && lane == 0) {
+        // chunk seq-1 was just stored; chunk seq+2 reuses the buffer of chunk seq-2, whose store
+        // is older than the one just issued: allow only that newest store to be unread
         tma_store_wait_read<1>();
-        const uint32_t bar = nb ? abar1 : abar0;
-        mbar_expect_tx(bar, aux_bytes);
-        tma_load_2d(ebuf + nb * kEpiBufBytes, tmAux, colbase + 2 * CW, row0, bar);
+        issue_aux(seq - 1 + kDepth);
       }
     }
     tc_fence_before();
@@ -458,11 +477,11 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ TmapPack maps, const GemmParams
   auto empty_bar = [&](int s) { return bars + 8u * (kMaxStages + s); };
   auto tfull_bar = [&](int a) { return bars + 8u * (2 * kMaxStages + a); };
   auto tempty_bar = [&](int a) { return bars + 8u * (2 * kMaxStages + 2 + a); };
-  auto aux_bar = [&](int ew, int b) { return bars + 8u * (2 * kMaxStages + 4 + 2 * ew + b); };
-  const uint32_t tmem_slot = bars + 8u * (2 * kMaxStages + 4 + 2 * kEpiWarps);
+  auto aux_bar = [&](int ew, int b) { return bars + 8u * (2 * kMaxStages + 4 + kEpiBufs * ew + b); };
+  const uint32_t tmem_slot = bars + 8u * (2 * kMaxStages + 4 + kEpiBufs * kEpiWarps);
   volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(
-      smem_raw + (base - raw) + kTileBytes + kEpiBytes + kBiasBytes + 8 * (2 * kMaxStages + 4 + 2 * kEpiWarps));
-  static_assert(8 * (2 * kMaxStages + 4 + 2 * kEpiWarps) + 4 <= kBarrierBytes, "barrier area");
+      smem_raw + (base - raw) + kTileBytes + kEpiBytes + kBiasBytes + 8 * (2 * kMaxStages + 4 + kEpiBufs * kEpiWarps));
+  static_assert(8 * (2 * kMaxStages + 4 + kEpiBufs * kEpiWarps) + 4 <= kBarrierBytes, "barrier area");
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -477,7 +496,8 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ TmapPack maps, const GemmParams
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < kStages; ++s) { mbar_init(full_bar(s), CG); mbar_init(empty_bar(s), 1); }
     for (int a = 0; a < 2; ++a) { mbar_init(tfull_bar(a), 1); mbar_init(tempty_bar(a), kEpiWarps * CG); }
-    for (int ew = 0; ew < kEpiWarps; ++ew) { mbar_init(aux_bar(ew, 0), 1); mbar_init(aux_bar(ew, 1), 1); }
+    for (int ew = 0; ew < kEpiWarps; ++ew)
+      for (int b = 0; b < kEpiBufs; ++b) mbar_init(aux_bar(ew, b), 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 2) {
@@ -637,12 +657,12 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ TmapPack maps, const GemmParams
     const int q = warp & 3;       // TMEM lane quarter this warp may touch (== warp % 4)
     const int h = ew >> 2;        // first or second warp of the quarter
     const int et = threadIdx.x - 128;
-    const uint32_t eb = sEpi + ew * 2 * kEpiBufBytes;
+    const uint32_t eb = sEpi + ew * kEpiBufs * kEpiBufBytes;
     if (p.cw == 32)
-      epilogue_loop<32, CG>(p, &maps.c, &maps.c2, &maps.aux, q, h, lane, et, tmem_base, eb, sBias, aux_bar(ew, 0), aux_bar(ew, 1),
+      epilogue_loop<32, CG>(p, &maps.c, &maps.c2, &maps.aux, q, h, lane, et, tmem_base, eb, sBias, aux_bar(ew, 0),
                             tfull_bar(0), tempty_bar(0), num_work, w_begin, w_stride, cta_rank);
     else
-      epilogue_loop<16, CG>(p, &maps.c, &maps.c2, &maps.aux, q, h, lane, et, tmem_base, eb, sBias, aux_bar(ew, 0), aux_bar(ew, 1),
+      epilogue_loop<16, CG>(p, &maps.c, &maps.c2, &maps.aux, q, h, lane, et, tmem_base, eb, sBias, aux_bar(ew, 0),
                             tfull_bar(0), tempty_bar(0), num_work, w_begin, w_stride, cta_rank);
   }
 
