@@ -1,6 +1,7 @@
-// LayerNorm forward and input-gradient backward over bf16 rows.  One warp per row: the row
-// is read once with 16-byte loads into registers, reduced with warp shuffles (no shared
-// memory, no block barrier), and written once.  HBM-bound: fwd 4*d bytes/row, bwd 8*d (+2*d
+// LayerNorm forward and input-gradient backward over bf16 rows.  One warp per PAIR of rows: the
+// rows are read once with 16-byte loads into registers (kept packed), reduced with warp shuffles
+// (no shared memory, no block barrier), and written once.  Two rows per warp because one was
+// latency-bound: 32 warps x 1.5 KB = 48 KB in flight per SM is ~3.3 TB/s by Little's law.  HBM-bound: fwd 4*d bytes/row, bwd 8*d (+2*d
 // with the fused residual-gradient add).
 #include "common.cuh"
 #include "../../include/b200ft.h"
@@ -8,47 +9,62 @@
 namespace {
 
 constexpr int kWarpsPerBlock = 8;
-constexpr int kMaxVecPerLane = 32;  // d <= 32 lanes * 32 vectors * 8 = 8192
+constexpr int kRowsPerWarp = 2;      // two rows in flight per warp: twice the bytes per SM in flight
+constexpr int kMaxVecPerLane = 32;   // d <= 32 lanes * 32 vectors * 8 = 8192
 
+// Rows are kept as the raw 16-byte bf16 vectors they were loaded as (4 registers per vector
+// instead of 8) and unpacked on the fly in each pass; all loads of both rows are issued before
+// the first reduction.
 template <int VPL>
-__global__ void __launch_bounds__(kWarpsPerBlock * 32)
+__global__ void __launch_bounds__(kWarpsPerBlock * 32, VPL <= 4 ? 4 : 1)
 layernorm_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ gamma,
                      const float* __restrict__ beta, __nv_bfloat16* __restrict__ y,
                      float* __restrict__ mean, float* __restrict__ rstd, int64_t rows, int d, float eps) {
   const int lane = threadIdx.x & 31;
-  const int64_t row = (int64_t)blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5);
-  if (row >= rows) return;
+  const int64_t row0 = ((int64_t)blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5)) * kRowsPerWarp;
+  if (row0 >= rows) return;
   const int nvec = d >> 3;
-  const __nv_bfloat16* xr = x + row * d;
-  float v[VPL][8];
-  float sum = 0.f;
+  uint4 q[kRowsPerWarp][VPL];
 #pragma unroll
-  for (int i = 0; i < VPL; ++i) {
-    int vi = lane + i * 32;
-    if (vi < nvec) {
-      unpack8(ld_stream16(xr + (vi << 3)), v[i]);
+  for (int r = 0; r < kRowsPerWarp; ++r) {
+    const bool live = row0 + r < rows;
 #pragma unroll
-      for (int j = 0; j < 8; ++j) sum += v[i][j];
+    for (int i = 0; i < VPL; ++i) {
+      const int vi = lane + i * 32;
+      q[r][i] = (live && vi < nvec) ? ld_stream16(x + (row0 + r) * d + (vi << 3)) : make_uint4(0u, 0u, 0u, 0u);
     }
   }
-  sum = warp_sum(sum);
-  const float mu = sum / (float)d;
-  float sq = 0.f;
+  float mu[kRowsPerWarp], rs[kRowsPerWarp];
 #pragma unroll
-  for (int i = 0; i < VPL; ++i) {
-    int vi = lane + i * 32;
-    if (vi < nvec) {
+  for (int r = 0; r < kRowsPerWarp; ++r) {
+    float sum = 0.f;
 #pragma unroll
-      for (int j = 0; j < 8; ++j) { float c = v[i][j] - mu; sq += c * c; }
+    for (int i = 0; i < VPL; ++i) {
+      float f[8];
+      unpack8(q[r][i], f);  // vectors beyond the row are zero and add nothing
+#pragma unroll
+      for (int j = 0; j < 8; ++j) sum += f[j];
     }
+    mu[r] = warp_sum(sum) / (float)d;
   }
-  sq = warp_sum(sq);
-  const float rs = rsqrtf(sq / (float)d + eps);
-  if (lane == 0) { mean[row] = mu; rstd[row] = rs; }
-  __nv_bfloat16* yr = y + row * d;
+#pragma unroll
+  for (int r = 0; r < kRowsPerWarp; ++r) {
+    float sq = 0.f;
+#pragma unroll
+    for (int i = 0; i < VPL; ++i) {
+      if (lane + i * 32 < nvec) {
+        float f[8];
+        unpack8(q[r][i], f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { const float c = f[j] - mu[r]; sq += c * c; }
+      }
+    }
+    rs[r] = rsqrtf(warp_sum(sq) / (float)d + eps);
+    if (lane == 0 && row0 + r < rows) { mean[row0 + r] = mu[r]; rstd[row0 + r] = rs[r]; }
+  }
 #pragma unroll
   for (int i = 0; i < VPL; ++i) {
-    int vi = lane + i * 32;
+    const int vi = lane + i * 32;
     if (vi < nvec) {
       const float4 g0 = __ldg(reinterpret_cast<const float4*>(gamma + (vi << 3)));
       const float4 g1 = __ldg(reinterpret_cast<const float4*>(gamma + (vi << 3) + 4));
@@ -56,63 +72,99 @@ layernorm_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restric
       const float4 b1 = __ldg(reinterpret_cast<const float4*>(beta + (vi << 3) + 4));
       const float gg[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
       const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
-      float o[8];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) o[j] = (v[i][j] - mu) * rs * gg[j] + bb[j];
-      st_stream16(yr + (vi << 3), pack8(o));
+      for (int r = 0; r < kRowsPerWarp; ++r) {
+        if (row0 + r < rows) {
+          float f[8], o[8];
+          unpack8(q[r][i], f);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) o[j] = (f[j] - mu[r]) * rs[r] * gg[j] + bb[j];
+          st_stream16(y + (row0 + r) * d + (vi << 3), pack8(o));
+        }
+      }
     }
   }
 }
 
 // dx = dres + rstd * (g*dy - mean(g*dy) - xhat * mean(g*dy*xhat))
 template <int VPL>
-__global__ void __launch_bounds__(kWarpsPerBlock * 32)
+__global__ void __launch_bounds__(kWarpsPerBlock * 32, VPL <= 4 ? 3 : 1)
 layernorm_bwd_dx_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
                         const float* __restrict__ gamma, const float* __restrict__ mean,
                         const float* __restrict__ rstd, const __nv_bfloat16* __restrict__ dres,
                         __nv_bfloat16* __restrict__ dx, int64_t rows, int d) {
   const int lane = threadIdx.x & 31;
-  const int64_t row = (int64_t)blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5);
-  if (row >= rows) return;
+  const int64_t row0 = ((int64_t)blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5)) * kRowsPerWarp;
+  if (row0 >= rows) return;
   const int nvec = d >> 3;
-  const float mu = mean[row], rs = rstd[row];
-  float gdy[VPL][8], xh[VPL][8];
-  float s1 = 0.f, s2 = 0.f;
+  uint4 qdy[kRowsPerWarp][VPL], qx[kRowsPerWarp][VPL];
+  float mu[kRowsPerWarp], rs[kRowsPerWarp];
+#pragma unroll
+  for (int r = 0; r < kRowsPerWarp; ++r) {
+    const bool live = row0 + r < rows;
+    mu[r] = live ? mean[row0 + r] : 0.f;
+    rs[r] = live ? rstd[row0 + r] : 0.f;
+#pragma unroll
+    for (int i = 0; i < VPL; ++i) {
+      const int vi = lane + i * 32;
+      const bool ok = live && vi < nvec;
+      qdy[r][i] = ok ? ld_stream16(dy + (row0 + r) * d + (vi << 3)) : make_uint4(0u, 0u, 0u, 0u);
+      qx[r][i] = ok ? ld_stream16(x + (row0 + r) * d + (vi << 3)) : make_uint4(0u, 0u, 0u, 0u);
+    }
+  }
+  float s1[kRowsPerWarp], s2[kRowsPerWarp];
+#pragma unroll
+  for (int r = 0; r < kRowsPerWarp; ++r) { s1[r] = 0.f; s2[r] = 0.f; }
 #pragma unroll
   for (int i = 0; i < VPL; ++i) {
-    int vi = lane + i * 32;
+    const int vi = lane + i * 32;
     if (vi < nvec) {
-      float a[8], b[8];
-      unpack8(ld_stream16(dy + row * d + (vi << 3)), a);
-      unpack8(ld_stream16(x + row * d + (vi << 3)), b);
       const float4 g0 = __ldg(reinterpret_cast<const float4*>(gamma + (vi << 3)));
       const float4 g1 = __ldg(reinterpret_cast<const float4*>(gamma + (vi << 3) + 4));
       const float gg[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        gdy[i][j] = a[j] * gg[j];
-        xh[i][j] = (b[j] - mu) * rs;
-        s1 += gdy[i][j];
-        s2 += gdy[i][j] * xh[i][j];
+      for (int r = 0; r < kRowsPerWarp; ++r) {
+        float a[8], b[8];
+        unpack8(qdy[r][i], a);
+        unpack8(qx[r][i], b);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float gdy = a[j] * gg[j];
+          s1[r] += gdy;
+          s2[r] += gdy * ((b[j] - mu[r]) * rs[r]);
+        }
       }
     }
   }
-  s1 = warp_sum(s1) / (float)d;
-  s2 = warp_sum(s2) / (float)d;
+#pragma unroll
+  for (int r = 0; r < kRowsPerWarp; ++r) {
+    s1[r] = warp_sum(s1[r]) / (float)d;
+    s2[r] = warp_sum(s2[r]) / (float)d;
+  }
 #pragma unroll
   for (int i = 0; i < VPL; ++i) {
-    int vi = lane + i * 32;
+    const int vi = lane + i * 32;
     if (vi < nvec) {
-      float o[8];
+      const float4 g0 = __ldg(reinterpret_cast<const float4*>(gamma + (vi << 3)));
+      const float4 g1 = __ldg(reinterpret_cast<const float4*>(gamma + (vi << 3) + 4));
+      const float gg[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
 #pragma unroll
-      for (int j = 0; j < 8; ++j) o[j] = rs * (gdy[i][j] - s1 - xh[i][j] * s2);
-      if (dres) {
-        float r[8];
-        unpack8(ld_stream16(dres + row * d + (vi << 3)), r);
+      for (int r = 0; r < kRowsPerWarp; ++r) {
+        if (row0 + r < rows) {
+          float a[8], b[8], o[8];
+          unpack8(qdy[r][i], a);
+          unpack8(qx[r][i], b);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) o[j] += r[j];
+          for (int j = 0; j < 8; ++j) o[j] = rs[r] * (a[j] * gg[j] - s1[r] - (b[j] - mu[r]) * rs[r] * s2[r]);
+          if (dres) {
+            float rr[8];
+            unpack8(ld_stream16(dres + (row0 + r) * d + (vi << 3)), rr);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) o[j] += rr[j];
+          }
+          st_stream16(dx + (row0 + r) * d + (vi << 3), pack8(o));
+        }
       }
-      st_stream16(dx + row * d + (vi << 3), pack8(o));
     }
   }
 }
@@ -137,7 +189,8 @@ extern "C" int b200ft_layernorm_fwd(const void* x, const float* gamma, const flo
   B200FT_CHECK_ARG(rows > 0 && d > 0 && d % 8 == 0 && d <= 8 * 32 * kMaxVecPerLane,
                    "layernorm_fwd: rows=%lld d=%d (d must be a multiple of 8, <= 8192)", (long long)rows, d);
   cudaStream_t st = (cudaStream_t)stream;
-  unsigned blocks = (unsigned)((rows + kWarpsPerBlock - 1) / kWarpsPerBlock);
+  const int64_t rows_per_block = (int64_t)kWarpsPerBlock * kRowsPerWarp;
+  unsigned blocks = (unsigned)((rows + rows_per_block - 1) / rows_per_block);
   int vpl = vpl_for(d);
 #define CALL(V)                                                                                     \
   layernorm_fwd_kernel<V><<<blocks, kWarpsPerBlock * 32, 0, st>>>(                                   \
@@ -155,7 +208,8 @@ extern "C" int b200ft_layernorm_bwd_dx(const void* dy, const void* x, const floa
   B200FT_CHECK_ARG(rows > 0 && d > 0 && d % 8 == 0 && d <= 8 * 32 * kMaxVecPerLane,
                    "layernorm_bwd_dx: rows=%lld d=%d (d must be a multiple of 8, <= 8192)", (long long)rows, d);
   cudaStream_t st = (cudaStream_t)stream;
-  unsigned blocks = (unsigned)((rows + kWarpsPerBlock - 1) / kWarpsPerBlock);
+  const int64_t rows_per_block = (int64_t)kWarpsPerBlock * kRowsPerWarp;
+  unsigned blocks = (unsigned)((rows + rows_per_block - 1) / rows_per_block);
   int vpl = vpl_for(d);
 #define CALL(V)                                                                                     \
   layernorm_bwd_dx_kernel<V><<<blocks, kWarpsPerBlock * 32, 0, st>>>(                                \
