@@ -39,6 +39,14 @@ for p in (ROOT, PKG):
 
 import torch  # noqa: E402
 
+# DRAM bytes (read + write) per launch of the dominant kernel, averaged over the 98 launches of
+# one step: ncu `dram__bytes_read.sum + dram__bytes_write.sum` (see GEMM_DRAM_SOURCE).  None until
+# the capture for the current kernel has been taken.
+GEMM_DRAM_BYTES_PER_LAUNCH = 342.6e6
+GEMM_DRAM_SOURCE = ("profiles/r01_step_launch_summary_final.txt: 33.57 GB over the 98 launches of one step "
+                    "(ncu dram__bytes_read.sum + dram__bytes_write.sum); algorithmic operand + output bytes of "
+                    "those launches: 32.5 GB")
+
 METRIC = "fine-tune tokens/sec"
 UNIT = "tokens/s"
 MODEL = "gpt2-124m"
@@ -237,13 +245,21 @@ def run_ours(args) -> None:
     for e in prof["gemm"]:
         rec = shapes.setdefault(e[3], [0, 0.0, 0.0])
         rec[0] += 1; rec[1] += e[0].elapsed_time(e[1]); rec[2] += e[2]
-    gemm_shapes = [{"m_n_k_amn_bmn_epi": list(k), "launches_per_step": v[0] / prof_steps,
+    gemm_shapes = [{"m_n_k_amn_bmn_epi_cg": list(k), "launches_per_step": v[0] / prof_steps,
                     "us_per_launch": 1e3 * v[1] / v[0], "tflops": v[2] / (v[1] * 1e-3) / 1e12}
                    for k, v in sorted(shapes.items(), key=lambda kv: -kv[1][1])]
-    gm = classes["gemm"]
+    # dominant kernel = the cta_group::2 instantiation (every large GEMM of the step); the N = 16
+    # adapter GEMMs and the split-K adapter-gradient contractions run the <1> instantiation
+    big = [e for e in prof["gemm"] if e[3][6] == 2]
+    gm = {"launches_per_step": len(big) / prof_steps,
+          "ms_per_step": sum(e[0].elapsed_time(e[1]) for e in big) / prof_steps,
+          "work_per_step": sum(e[2] for e in big) / prof_steps}
     tf = gm["work_per_step"] / (gm["ms_per_step"] * 1e-3) / 1e12
-    roofline = {"kernel": "gemm_bf16_tcgen05_kernel", "bound": "tensor", "achieved": tf, "peak": pk["tf_sustained"],
-                "unit": "TFLOP/s", "frac": tf / pk["tf_sustained"], "traffic": None,
+    roofline = {"kernel": "gemm_bf16_tcgen05_kernel<2>", "bound": "tensor", "achieved": tf, "peak": pk["tf_sustained"],
+                "unit": "TFLOP/s", "frac": tf / pk["tf_sustained"],
+                "flop_per_launch": gm["work_per_step"] / gm["launches_per_step"],
+                "us_per_launch": 1e3 * gm["ms_per_step"] / gm["launches_per_step"],
+                "traffic": GEMM_DRAM_BYTES_PER_LAUNCH, "traffic_source": GEMM_DRAM_SOURCE,
                 "peak_source": pk["source"] + ", sustained bf16 (kernel timed inside a long step)",
                 "launches_per_step": gm["launches_per_step"], "ms_per_step": gm["ms_per_step"],
                 "share_of_step": gm["ms_per_step"] / (ms / args.steps)}

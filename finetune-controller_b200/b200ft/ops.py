@@ -101,7 +101,9 @@ def gemm(a, b, out, *, a_mn=False, b_mn=False, a2=None, b2=None, more=(), bias=N
         args.c2, args.ldc2 = out2.data_ptr(), out2.stride(0)
     args.block_n, args.max_ctas, args.split_k, args.cta_group = block_n, max_ctas, split_k, cta_group
     kk = k + (args.k2 if a2 is not None else 0) + kk_more
-    with _timed("gemm", 2.0 * m * n * kk, (m, n, kk, int(a_mn), int(b_mn), epilogue)):
+    # which instantiation the library will pick (mirrors b200ft_gemm_bf16's rule for cta_group = 0)
+    cg = cta_group or (2 if (not a_mn and not b_mn and epilogue != EPI_ATOMIC_F32_T and m > 128 and n >= 128) else 1)
+    with _timed("gemm", 2.0 * m * n * kk, (m, n, kk, int(a_mn), int(b_mn), epilogue, cg)):
         check(lib().b200ft_gemm_bf16(ctypes.byref(args), _stream()), "gemm_bf16")
     LAUNCHES += 1
     return out
