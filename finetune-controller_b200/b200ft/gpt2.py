@@ -162,6 +162,21 @@ class GPT2LoRAStep:
             out[f"h{l}.c_attn.lora_B"] = self.gB_all[l * R_PAD: l * R_PAD + r].contiguous().cpu()
         return out
 
+    def state_dict(self) -> dict:
+        """Everything needed to continue training bit-for-bit: fp32 master adapters, Adam moments, step."""
+        return {"P": self.P.detach().cpu().clone(), "m": self.Mo.detach().cpu().clone(),
+                "v": self.Vo.detach().cpu().clone(), "step": self.step_count,
+                "r": self.lora.r, "alpha": self.lora.alpha, "n_layer": self.dims.n_layer, "d_model": self.dims.d_model}
+
+    def load_state_dict(self, st: dict) -> None:
+        want = (self.lora.r, self.dims.n_layer, self.dims.d_model)
+        got = (st["r"], st["n_layer"], st["d_model"])
+        if want != got or st["P"].numel() != self.P.numel():
+            raise ValueError(f"checkpoint is for (r, layers, d_model) = {got}, this job is {want}")
+        self.P.copy_(st["P"]); self.Mo.copy_(st["m"]); self.Vo.copy_(st["v"])
+        self.step_count = int(st["step"])
+        self._refresh_shadows(cast=True)
+
     def grad_views(self, lo: int, hi: int) -> list:
         """Contiguous gradient slices of layers [lo, hi) (what one all-reduce bucket covers)."""
         return [self.gAt_all[lo * R_PAD: hi * R_PAD], self.gB_all[lo * R_PAD: hi * R_PAD]]

@@ -48,6 +48,8 @@ def build_parser() -> argparse.ArgumentParser:
     ap.add_argument("--log_interval", type=int, default=10)
     ap.add_argument("--save_model", action="store_true")
     ap.add_argument("--synthetic", action="store_true")
+    ap.add_argument("--save_interval", type=int, default=0,
+                    help="steps between resume points (state.pt); 0 = only at the end of each epoch")
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--dataset_path", default="/data/dataset")
     ap.add_argument("--checkpoint_path", default="/data/artifacts")
@@ -55,16 +57,60 @@ def build_parser() -> argparse.ArgumentParser:
 
 
 def load_token_stream(dataset_path: str):
-    """tokens.pt (1-D int tensor) or tokens.bin (little-endian uint16/int32 ids) if present."""
+    """Pre-tokenised data from the dataset mount (the controller's init container copies the
+    uploaded object into it, reference PyTorchJobDeployer.py:70-91).  Accepted, first match wins:
+    tokens.pt (1-D integer tensor), tokens.bin (little-endian uint16 ids, the nanoGPT/llm.c
+    convention), any *.jsonl whose lines carry {"input_ids": [...]}.  None if nothing is there."""
+    import glob
     import numpy as np
     import torch
     pt, bn = os.path.join(dataset_path, "tokens.pt"), os.path.join(dataset_path, "tokens.bin")
     if os.path.exists(pt):
         return torch.load(pt).to(torch.int64).flatten()
     if os.path.exists(bn):
-        raw = np.fromfile(bn, dtype=np.uint16)
+        raw = np.fromfile(bn, dtype="<u2")
         return torch.from_numpy(raw.astype(np.int64))
-    return None
+    ids = []
+    for path in sorted(glob.glob(os.path.join(dataset_path, "*.jsonl"))):
+        with open(path) as f:
+            for line in f:
+                line = line.strip()
+                if line:
+                    ids.extend(json.loads(line)["input_ids"])
+    return torch.tensor(ids, dtype=torch.int64) if ids else None
+
+
+def batch_from_stream(stream, global_step: int, rank: int, world: int, batch: int, seq: int, vocab: int):
+    """Deterministic [batch, seq] window of the token stream for (step, rank): consecutive
+    batch*seq spans, ranks interleaved, wrapping around at the end of the stream."""
+    import torch
+    span = batch * seq
+    n_chunks = max(1, stream.numel() // span)
+    off = ((global_step * world + rank) % n_chunks) * span
+    chunk = stream[off: off + span]
+    if chunk.numel() < span:
+        reps = (span + stream.numel() - 1) // stream.numel()
+        chunk = torch.cat([chunk] + [stream] * reps)[:span]
+    return chunk.view(batch, seq).clamp(0, vocab - 1)
+
+
+STATE_FILE = "state.pt"
+
+
+def save_state(eng, checkpoint_path: str, epoch: int, it: int, gstep: int) -> None:
+    """Resume point (rank 0): written to a temp name and renamed so a kill never leaves half a file."""
+    import torch
+    st = eng.state_dict()
+    st.update(epoch=epoch, it=it, gstep=gstep)
+    tmp = os.path.join(checkpoint_path, STATE_FILE + ".tmp")
+    torch.save(st, tmp)
+    os.replace(tmp, os.path.join(checkpoint_path, STATE_FILE))
+
+
+def load_state(checkpoint_path: str):
+    import torch
+    path = os.path.join(checkpoint_path, STATE_FILE)
+    return torch.load(path) if os.path.exists(path) else None
 
 
 def worker(args, rank: int, world: int, local: int) -> None:
@@ -83,38 +129,44 @@ def worker(args, rank: int, world: int, local: int) -> None:
                             world_size=world, grad_sync=sync)
     del base
     stream = None if args.synthetic else load_token_stream(args.dataset_path)
-    gen = torch.Generator().manual_seed(1234 + args.seed + rank)
     B, T = args.batch_size, args.seq_len
     ids_host = torch.empty(B, T, dtype=torch.int64).pin_memory()
 
     def next_batch(global_step: int):
         if stream is None:
-            ids_host.copy_(torch.randint(0, dims.vocab, (B, T), generator=gen, dtype=torch.int64))
+            g = torch.Generator().manual_seed(1234 + args.seed + rank + 7919 * global_step)  # resumable
+            ids_host.copy_(torch.randint(0, dims.vocab, (B, T), generator=g, dtype=torch.int64))
         else:
-            span = B * T
-            n_chunks = max(1, (stream.numel() - 1) // span)
-            off = ((global_step * world + rank) % n_chunks) * span
-            chunk = stream[off: off + span]
-            if chunk.numel() < span:
-                chunk = torch.cat([chunk, stream[: span - chunk.numel()]])
-            ids_host.copy_(chunk.view(B, T).clamp_(0, dims.vocab - 1))
+            ids_host.copy_(batch_from_stream(stream, global_step, rank, world, B, T, dims.vocab))
         return ids_host
+
+    # resume: the artifacts volume outlives container restarts inside the pod (restartPolicy
+    # OnFailure, backoffLimit 2: reference PyTorchJobDeployer.py:179-189,196)
+    start_epoch, start_it, gstep0 = 1, 1, 0
+    st = load_state(args.checkpoint_path)
+    if st is not None:
+        eng.load_state_dict(st)
+        start_epoch, start_it, gstep0 = st["epoch"], st["it"] + 1, st["gstep"]
+        if start_it > args.steps_per_epoch:
+            start_epoch, start_it = start_epoch + 1, 1
 
     os.makedirs(args.checkpoint_path, exist_ok=True)
     metrics_path = os.path.join(args.checkpoint_path, "metrics.csv")
     writer = fh = None
     if rank == 0:
-        fh = open(metrics_path, "w", newline="")
+        resumed = st is not None and os.path.exists(metrics_path)
+        fh = open(metrics_path, "a" if resumed else "w", newline="")
         writer = csv.writer(fh)
-        writer.writerow(["epoch", "step", "loss", "lr", "tokens_per_sec", "elapsed_s"])
-        print(f"Epoch 0/{args.epochs} starting: model={args.model} lora_r={args.lora_r} world={world} "
-              f"batch/gpu={B} seq={T}", flush=True)
+        if not resumed:
+            writer.writerow(["epoch", "step", "loss", "lr", "tokens_per_sec", "elapsed_s"])
+        print(f"Epoch {start_epoch - 1}/{args.epochs} starting: model={args.model} lora_r={args.lora_r} world={world} "
+              f"batch/gpu={B} seq={T}" + (f" (resumed at step {gstep0})" if st is not None else ""), flush=True)
     t_start = time.time()
-    gstep = 0
-    for epoch in range(1, args.epochs + 1):
+    gstep = gstep0
+    for epoch in range(start_epoch, args.epochs + 1):
         t0, tok0 = time.time(), 0
         loss = float("nan")
-        for it in range(1, args.steps_per_epoch + 1):
+        for it in range(start_it if epoch == start_epoch else 1, args.steps_per_epoch + 1):
             batch = next_batch(gstep)
             loss = eng.step_host(batch, batch)
             gstep += 1
@@ -125,8 +177,10 @@ def worker(args, rank: int, world: int, local: int) -> None:
                       f"tokens/s {tps:.0f}", flush=True)
                 writer.writerow([epoch, gstep, f"{loss:.6f}", args.lr, f"{tps:.1f}", f"{time.time() - t_start:.2f}"])
                 fh.flush()
-        if loss != loss:
-            raise RuntimeError("loss is NaN")
+            if loss != loss:
+                raise RuntimeError("loss is NaN")
+            if rank == 0 and ((args.save_interval > 0 and it % args.save_interval == 0) or it == args.steps_per_epoch):
+                save_state(eng, args.checkpoint_path, epoch, it, gstep)
     if rank == 0:
         fh.close()
         if args.save_model:

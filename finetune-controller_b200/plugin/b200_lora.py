@@ -42,6 +42,7 @@ class B200LoRAConfig(TrainingArguments):
     max_grad_norm: float = Field(default=0.0, description="Global gradient-norm clip; 0 disables")
     seed: int = Field(default=0, description="Seed for weight init and synthetic data")
     log_interval: int = Field(default=10, description="Steps between metric rows / log lines")
+    save_interval: int = Field(default=0, description="Steps between resume points (state.pt); 0 = once per epoch")
     save_model: bool = Field(default=True, description="Write adapter.pt + adapter_config.json at the end")
     synthetic: bool = Field(default=True, description="Use synthetic token ids instead of the mounted dataset")
 
@@ -92,7 +93,7 @@ class B200LoRA(BaseFineTuneModel):
                 args.append(f"--{flag}")
         for key in ("model", "mode", "lora_r", "lora_alpha", "seq_len", "batch_size", "epochs",
                     "steps_per_epoch", "lr", "weight_decay", "beta1", "beta2", "eps", "max_grad_norm",
-                    "seed", "log_interval"):
+                    "seed", "log_interval", "save_interval"):
             args.append(f"--{key}={getattr(ta, key)}")
         args.append(f"--gpus={self.accelerator_count}")
         # the two mounts every payload must honour (reference mnist.py:93-95)
