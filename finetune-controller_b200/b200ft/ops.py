@@ -210,11 +210,70 @@ def layernorm_bwd_dx(dy, x, gamma, mean, rstd, dx, dres=None):
     return dx
 
 
+def rmsnorm_fwd(x, gamma, y, rstd, eps):
+    global LAUNCHES
+    _need_cuda(x, gamma, y, rstd)
+    rows, d = x.shape
+    assert x.is_contiguous() and y.is_contiguous()
+    with _timed("rmsnorm_fwd", 4.0 * rows * d):
+        check(lib().b200ft_rmsnorm_fwd(_p(x), _p(gamma), _p(y), _p(rstd), rows, d, eps, _stream()), "rmsnorm_fwd")
+    LAUNCHES += 1
+    return y
+
+
+def rmsnorm_bwd_dx(dy, x, gamma, rstd, dx, dres=None):
+    global LAUNCHES
+    _need_cuda(dy, x, gamma, rstd, dx, dres)
+    rows, d = x.shape
+    assert dy.is_contiguous() and x.is_contiguous() and dx.is_contiguous()
+    with _timed("rmsnorm_bwd", (8.0 if dres is not None else 6.0) * rows * d):
+        check(lib().b200ft_rmsnorm_bwd_dx(_p(dy), _p(x), _p(gamma), _p(rstd), _p(dres), _p(dx), rows, d, _stream()),
+              "rmsnorm_bwd_dx")
+    LAUNCHES += 1
+    return dx
+
+
+def rope_inplace(x, cos, sin, *, seq, n_heads, d_head, backward=False, rows=None):
+    """Rotate the first n_heads*d_head columns of each row of x (bf16, pitch x.stride(0)) in place."""
+    global LAUNCHES
+    _need_cuda(x, cos, sin)
+    assert x.dtype == torch.bfloat16 and cos.dtype == sin.dtype == torch.float32 and x.stride(-1) == 1
+    rows = x.shape[0] if rows is None else rows
+    with _timed("rope", 4.0 * rows * n_heads * d_head):
+        check(lib().b200ft_rope_inplace(_p(x), x.stride(0), rows, seq, n_heads, d_head, _p(cos), _p(sin),
+                                        int(backward), _stream()), "rope_inplace")
+    LAUNCHES += 1
+    return x
+
+
+def swiglu_fwd(gate_up, act):
+    global LAUNCHES
+    _need_cuda(gate_up, act)
+    rows, ff = act.shape
+    assert gate_up.shape == (rows, 2 * ff) and gate_up.is_contiguous() and act.is_contiguous()
+    with _timed("swiglu_fwd", 6.0 * rows * ff):
+        check(lib().b200ft_swiglu_fwd(_p(gate_up), _p(act), rows, ff, _stream()), "swiglu_fwd")
+    LAUNCHES += 1
+    return act
+
+
+def swiglu_bwd(dact, gate_up, dgate_up):
+    global LAUNCHES
+    _need_cuda(dact, gate_up, dgate_up)
+    rows, ff = dact.shape
+    assert gate_up.shape == (rows, 2 * ff) and dgate_up.shape == (rows, 2 * ff)
+    assert dact.is_contiguous() and gate_up.is_contiguous() and dgate_up.is_contiguous()
+    with _timed("swiglu_bwd", 10.0 * rows * ff):
+        check(lib().b200ft_swiglu_bwd(_p(dact), _p(gate_up), _p(dgate_up), rows, ff, _stream()), "swiglu_bwd")
+    LAUNCHES += 1
+    return dgate_up
+
+
 def embed_fwd(ids, wte, wpe, x, *, seq, vocab):
     global LAUNCHES
     _need_cuda(ids, wte, wpe, x)
     rows, d = x.shape
-    assert wte.stride(0) == d and wpe.stride(0) == d
+    assert wte.stride(0) == d and (wpe is None or wpe.stride(0) == d)
     check(lib().b200ft_embed_fwd(_p(ids), _p(wte), _p(wpe), _p(x), rows, seq, d, vocab, _stream()), "embed_fwd")
     LAUNCHES += 1
     return x

@@ -17,14 +17,19 @@ embed_fwd_kernel(const int64_t* __restrict__ ids, const __nv_bfloat16* __restric
   id = id < 0 ? 0 : (id >= vocab ? vocab - 1 : id);  // out-of-range ids are clamped, never read OOB
   const int pos = (int)(row % seq);
   const __nv_bfloat16* te = wte + id * d;
-  const __nv_bfloat16* pe = wpe + (int64_t)pos * d;
+  const __nv_bfloat16* pe = wpe ? wpe + (int64_t)pos * d : nullptr;
   for (int vi = lane; vi < (d >> 3); vi += 32) {
-    float a[8], b[8];
-    unpack8(__ldg(reinterpret_cast<const uint4*>(te + (vi << 3))), a);
-    unpack8(__ldg(reinterpret_cast<const uint4*>(pe + (vi << 3))), b);
+    const uint4 tv = __ldg(reinterpret_cast<const uint4*>(te + (vi << 3)));
+    if (pe) {
+      float a[8], b[8];
+      unpack8(tv, a);
+      unpack8(__ldg(reinterpret_cast<const uint4*>(pe + (vi << 3))), b);
 #pragma unroll
-    for (int j = 0; j < 8; ++j) a[j] += b[j];
-    st_stream16(x + row * d + (vi << 3), pack8(a));
+      for (int j = 0; j < 8; ++j) a[j] += b[j];
+      st_stream16(x + row * d + (vi << 3), pack8(a));
+    } else {
+      st_stream16(x + row * d + (vi << 3), tv);
+    }
   }
 }
 
@@ -66,7 +71,7 @@ cast_f32_bf16_kernel(const float* __restrict__ in, __nv_bfloat16* __restrict__ o
 
 extern "C" int b200ft_embed_fwd(const int64_t* ids, const void* wte, const void* wpe, void* x,
                                 int64_t rows, int seq, int d, int vocab, void* stream) {
-  B200FT_CHECK_ARG(ids && wte && wpe && x, "embed_fwd: null buffer");
+  B200FT_CHECK_ARG(ids && wte && x, "embed_fwd: null buffer");
   B200FT_CHECK_ARG(rows > 0 && seq > 0 && d > 0 && d % 8 == 0 && vocab > 0,
                    "embed_fwd: rows=%lld seq=%d d=%d vocab=%d", (long long)rows, seq, d, vocab);
   embed_fwd_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, (cudaStream_t)stream>>>(

@@ -1,0 +1,185 @@
+// RMSNorm forward and input-gradient backward over bf16 rows (Llama family):
+//   y = x * rstd * g,  rstd = rsqrt(mean(x^2) + eps)
+//   dx = dres + rstd * (g*dy - xhat * mean(g*dy*xhat)),  xhat = x * rstd
+// Same shape as layernorm.cu: one warp per pair of rows, rows kept as packed 16-byte vectors in
+// registers, warp-shuffle reductions, no shared memory.  HBM-bound: fwd 4*d bytes/row, bwd 6*d
+// (+2*d with the fused residual-gradient add).
+#include "common.cuh"
+#include "../../include/b200ft.h"
+
+namespace {
+
+constexpr int kWarpsPerBlock = 8;
+constexpr int kRowsPerWarp = 2;
+
+template <int VPL>
+__global__ void __launch_bounds__(kWarpsPerBlock * 32)
+rmsnorm_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ gamma,
+                   __nv_bfloat16* __restrict__ y, float* __restrict__ rstd, int64_t rows, int d, float eps) {
+  const int lane = threadIdx.x & 31;
+  const int64_t row0 = ((int64_t)blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5)) * kRowsPerWarp;
+  if (row0 >= rows) return;
+  const int nvec = d >> 3;
+  uint4 q[kRowsPerWarp][VPL];
+#pragma unroll
+  for (int r = 0; r < kRowsPerWarp; ++r) {
+    const bool live = row0 + r < rows;
+#pragma unroll
+    for (int i = 0; i < VPL; ++i) {
+      const int vi = lane + i * 32;
+      q[r][i] = (live && vi < nvec) ? ld_stream16(x + (row0 + r) * d + (vi << 3)) : make_uint4(0u, 0u, 0u, 0u);
+    }
+  }
+  float rs[kRowsPerWarp];
+#pragma unroll
+  for (int r = 0; r < kRowsPerWarp; ++r) {
+    float sq = 0.f;
+#pragma unroll
+    for (int i = 0; i < VPL; ++i) {
+      float f[8];
+      unpack8(q[r][i], f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) sq += f[j] * f[j];
+    }
+    rs[r] = rsqrtf(warp_sum(sq) / (float)d + eps);
+    if (lane == 0 && row0 + r < rows) rstd[row0 + r] = rs[r];
+  }
+#pragma unroll
+  for (int i = 0; i < VPL; ++i) {
+    const int vi = lane + i * 32;
+    if (vi < nvec) {
+      const float4 g0 = __ldg(reinterpret_cast<const float4*>(gamma + (vi << 3)));
+      const float4 g1 = __ldg(reinterpret_cast<const float4*>(gamma + (vi << 3) + 4));
+      const float gg[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+#pragma unroll
+      for (int r = 0; r < kRowsPerWarp; ++r) {
+        if (row0 + r < rows) {
+          float f[8], o[8];
+          unpack8(q[r][i], f);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) o[j] = f[j] * rs[r] * gg[j];
+          st_stream16(y + (row0 + r) * d + (vi << 3), pack8(o));
+        }
+      }
+    }
+  }
+}
+
+template <int VPL>
+__global__ void __launch_bounds__(kWarpsPerBlock * 32)
+rmsnorm_bwd_dx_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
+                      const float* __restrict__ gamma, const float* __restrict__ rstd,
+                      const __nv_bfloat16* __restrict__ dres, __nv_bfloat16* __restrict__ dx, int64_t rows, int d) {
+  const int lane = threadIdx.x & 31;
+  const int64_t row0 = ((int64_t)blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5)) * kRowsPerWarp;
+  if (row0 >= rows) return;
+  const int nvec = d >> 3;
+  uint4 qdy[kRowsPerWarp][VPL], qx[kRowsPerWarp][VPL];
+  float rs[kRowsPerWarp], s2[kRowsPerWarp];
+#pragma unroll
+  for (int r = 0; r < kRowsPerWarp; ++r) {
+    const bool live = row0 + r < rows;
+    rs[r] = live ? rstd[row0 + r] : 0.f;
+    s2[r] = 0.f;
+#pragma unroll
+    for (int i = 0; i < VPL; ++i) {
+      const int vi = lane + i * 32;
+      const bool ok = live && vi < nvec;
+      qdy[r][i] = ok ? ld_stream16(dy + (row0 + r) * d + (vi << 3)) : make_uint4(0u, 0u, 0u, 0u);
+      qx[r][i] = ok ? ld_stream16(x + (row0 + r) * d + (vi << 3)) : make_uint4(0u, 0u, 0u, 0u);
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < VPL; ++i) {
+    const int vi = lane + i * 32;
+    if (vi < nvec) {
+      const float4 g0 = __ldg(reinterpret_cast<const float4*>(gamma + (vi << 3)));
+      const float4 g1 = __ldg(reinterpret_cast<const float4*>(gamma + (vi << 3) + 4));
+      const float gg[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+#pragma unroll
+      for (int r = 0; r < kRowsPerWarp; ++r) {
+        float a[8], b[8];
+        unpack8(qdy[r][i], a);
+        unpack8(qx[r][i], b);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) s2[r] += a[j] * gg[j] * (b[j] * rs[r]);
+      }
+    }
+  }
+#pragma unroll
+  for (int r = 0; r < kRowsPerWarp; ++r) s2[r] = warp_sum(s2[r]) / (float)d;
+#pragma unroll
+  for (int i = 0; i < VPL; ++i) {
+    const int vi = lane + i * 32;
+    if (vi < nvec) {
+      const float4 g0 = __ldg(reinterpret_cast<const float4*>(gamma + (vi << 3)));
+      const float4 g1 = __ldg(reinterpret_cast<const float4*>(gamma + (vi << 3) + 4));
+      const float gg[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+#pragma unroll
+      for (int r = 0; r < kRowsPerWarp; ++r) {
+        if (row0 + r < rows) {
+          float a[8], b[8], o[8];
+          unpack8(qdy[r][i], a);
+          unpack8(qx[r][i], b);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) o[j] = rs[r] * (a[j] * gg[j] - b[j] * rs[r] * s2[r]);
+          if (dres) {
+            float rr[8];
+            unpack8(ld_stream16(dres + (row0 + r) * d + (vi << 3)), rr);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) o[j] += rr[j];
+          }
+          st_stream16(dx + (row0 + r) * d + (vi << 3), pack8(o));
+        }
+      }
+    }
+  }
+}
+
+inline int vpl_for(int d) { return ((d >> 3) + 31) / 32; }
+
+}  // namespace
+
+#define RMS_DISPATCH(VPL_RT, CALL)                      \
+  if ((VPL_RT) <= 1) { CALL(1); }                       \
+  else if ((VPL_RT) <= 2) { CALL(2); }                  \
+  else if ((VPL_RT) <= 4) { CALL(4); }                  \
+  else if ((VPL_RT) <= 8) { CALL(8); }                  \
+  else { CALL(16); }
+
+extern "C" int b200ft_rmsnorm_fwd(const void* x, const float* gamma, void* y, float* rstd, int64_t rows, int d,
+                                  float eps, void* stream) {
+  B200FT_CHECK_ARG(x && gamma && y && rstd, "rmsnorm_fwd: null buffer");
+  B200FT_CHECK_ARG(rows > 0 && d > 0 && d % 8 == 0 && d <= 4096,
+                   "rmsnorm_fwd: rows=%lld d=%d (d must be a multiple of 8, <= 4096)", (long long)rows, d);
+  cudaStream_t st = (cudaStream_t)stream;
+  const int64_t rpb = (int64_t)kWarpsPerBlock * kRowsPerWarp;
+  unsigned blocks = (unsigned)((rows + rpb - 1) / rpb);
+  int vpl = vpl_for(d);
+#define CALL(V)                                                                                   \
+  rmsnorm_fwd_kernel<V><<<blocks, kWarpsPerBlock * 32, 0, st>>>((const __nv_bfloat16*)x, gamma,    \
+                                                                (__nv_bfloat16*)y, rstd, rows, d, eps)
+  RMS_DISPATCH(vpl, CALL)
+#undef CALL
+  B200FT_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int b200ft_rmsnorm_bwd_dx(const void* dy, const void* x, const float* gamma, const float* rstd,
+                                     const void* dres, void* dx, int64_t rows, int d, void* stream) {
+  B200FT_CHECK_ARG(dy && x && gamma && rstd && dx, "rmsnorm_bwd_dx: null buffer");
+  B200FT_CHECK_ARG(rows > 0 && d > 0 && d % 8 == 0 && d <= 4096,
+                   "rmsnorm_bwd_dx: rows=%lld d=%d (d must be a multiple of 8, <= 4096)", (long long)rows, d);
+  cudaStream_t st = (cudaStream_t)stream;
+  const int64_t rpb = (int64_t)kWarpsPerBlock * kRowsPerWarp;
+  unsigned blocks = (unsigned)((rows + rpb - 1) / rpb);
+  int vpl = vpl_for(d);
+#define CALL(V)                                                                                       \
+  rmsnorm_bwd_dx_kernel<V><<<blocks, kWarpsPerBlock * 32, 0, st>>>(                                    \
+      (const __nv_bfloat16*)dy, (const __nv_bfloat16*)x, gamma, rstd, (const __nv_bfloat16*)dres,      \
+      (__nv_bfloat16*)dx, rows, d)
+  RMS_DISPATCH(vpl, CALL)
+#undef CALL
+  B200FT_LAUNCH_CHECK();
+  return 0;
+}

@@ -180,8 +180,28 @@ int b200ft_layernorm_bwd_dx(const void* dy, const void* x, const float* gamma, c
                             const float* rstd, const void* dres, void* dx, int64_t rows, int d,
                             void* stream);
 
+/* ---------------------------------------------------------------------------------------
+ * Llama-family pieces (BASELINE.json configs[2..4]; oracle/llama_lora_ref.py).
+ * RMSNorm: y = x * rstd * gamma, rstd = rsqrt(mean(x^2) + eps) saved per row; bwd_dx fuses the
+ * residual-gradient add like the LayerNorm one.  d %% 8 == 0, d <= 4096.
+ * RoPE: rotates, in place, the first n_heads * d_head columns of each row of a bf16 matrix with
+ * pitch ld (the q and k heads of a fused qkv buffer) by the angle table cos/sin [seq, d_head/2]
+ * (fp32), pairs (i, i + d_head/2) — HF's rotate_half; position = row %% seq; backward != 0 applies
+ * the inverse rotation (the gradient map).
+ * SwiGLU: gate_up [rows, 2*d_ff] (gate columns first) -> act = silu(gate) * up, and its backward.
+ * ------------------------------------------------------------------------------------- */
+int b200ft_rmsnorm_fwd(const void* x, const float* gamma, void* y, float* rstd, int64_t rows, int d, float eps,
+                       void* stream);
+int b200ft_rmsnorm_bwd_dx(const void* dy, const void* x, const float* gamma, const float* rstd, const void* dres,
+                          void* dx, int64_t rows, int d, void* stream);
+int b200ft_rope_inplace(void* x, int64_t ld, int64_t rows, int seq, int n_heads, int d_head,
+                        const float* cos_table, const float* sin_table, int backward, void* stream);
+int b200ft_swiglu_fwd(const void* gate_up, void* act, int64_t rows, int d_ff, void* stream);
+int b200ft_swiglu_bwd(const void* dact, const void* gate_up, void* dgate_up, int64_t rows, int d_ff, void* stream);
+
 /* Token + position embedding (oracle forward(): F.embedding(ids,wte)+F.embedding(pos,wpe)).
- * wte bf16 [vocab, d], wpe bf16 [ctx, d], x bf16 [rows, d], position = row % seq. */
+ * wte bf16 [vocab, d], wpe bf16 [ctx, d], x bf16 [rows, d], position = row % seq.  wpe may be NULL
+ * (Llama: rotary positions, no learned table). */
 int b200ft_embed_fwd(const int64_t* ids, const void* wte, const void* wpe, void* x, int64_t rows,
                      int seq, int d, int vocab, void* stream);
 
