@@ -51,6 +51,16 @@ METRIC = "fine-tune tokens/sec"
 UNIT = "tokens/s"
 MODEL = "gpt2-124m"
 BATCH, SEQ, LORA_R, LORA_ALPHA = 32, 1024, 8, 16.0
+# name -> (model, batch per GPU, seq, lora r, lora alpha, description).  The driver's runs use the
+# default (c2 = BASELINE.json configs[1]); c3 / c4 are the Llama configs, for our own measurements.
+WORKLOADS = {
+    "c2": ("gpt2-124m", 32, 1024, 8, 16.0, "GPT-2 124M LoRA r=8 bf16 fine-tune step (fwd+loss+bwd+AdamW), seq 1024, "
+                                          "batch 32/GPU (BASELINE.json configs[1])"),
+    "c3": ("llama-3.2-1b", 4, 2048, 16, 32.0, "Llama-3.2-1B LoRA r=16 (q_proj, v_proj) bf16 fine-tune step, seq 2048, "
+                                              "batch 4/GPU (BASELINE.json configs[2])"),
+    "c4": ("llama-3-8b", 1, 4096, 16, 32.0, "Llama-3-8B LoRA r=16 (q_proj, v_proj) bf16 fine-tune step, seq 4096, "
+                                            "batch 1/GPU (BASELINE.json configs[3])"),
+}
 
 
 def peaks():
@@ -167,20 +177,13 @@ def run_ours(args) -> None:
         raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
-    dims = params.MODELS[MODEL]
-    lora = gpt2.LoRASpec(LORA_R, LORA_ALPHA)
+    model, BATCH, SEQ, lora_r, lora_alpha, workload_desc = WORKLOADS[args.workload]
+    lora = gpt2.LoRASpec(lora_r, lora_alpha)
     opt = gpt2.OptSpec()
-    base = params.init_gpt2(dims, seed=0, device=dev)
-    # B drawn at random (not PEFT's zero) so that every gradient path carries non-trivial data
-    ad = params.init_lora(dims, lora, seed=1, device=dev)
-    gen = torch.Generator(device=dev).manual_seed(99)
-    for k in ad:
-        if k.endswith("lora_B"):
-            ad[k].normal_(0.0, 0.02, generator=gen)
-    sync = ddp.BucketedGradSync(dims.n_layer, n_buckets=2) if world > 1 else None
-    eng = gpt2.GPT2LoRAStep(dims, lora, opt, base, ad, batch=BATCH, seq=SEQ, device=dev, world_size=world,
-                            grad_sync=sync)
-    del base
+    sync = ddp.BucketedGradSync(params.MODELS[model].n_layer, n_buckets=2) if world > 1 else None
+    # random-init weights; B drawn at random (not PEFT's zero) so every gradient path carries data
+    eng, dims = params.build_engine(model, lora, opt, batch=BATCH, seq=SEQ, device=dev, seed=0, world_size=world,
+                                    grad_sync=sync, randomize_b=True)
     g = torch.Generator().manual_seed(1234 + rank)
     n_sets = 4
     host = [torch.randint(0, dims.vocab, (BATCH, SEQ), generator=g, dtype=torch.int64).pin_memory()
@@ -259,12 +262,14 @@ def run_ours(args) -> None:
                 "unit": "TFLOP/s", "frac": tf / pk["tf_sustained"],
                 "flop_per_launch": gm["work_per_step"] / gm["launches_per_step"],
                 "us_per_launch": 1e3 * gm["ms_per_step"] / gm["launches_per_step"],
-                "traffic": GEMM_DRAM_BYTES_PER_LAUNCH, "traffic_source": GEMM_DRAM_SOURCE,
+                "traffic": GEMM_DRAM_BYTES_PER_LAUNCH if args.workload == "c2" else None,
+                "traffic_source": GEMM_DRAM_SOURCE if args.workload == "c2" else None,
                 "peak_source": pk["source"] + ", sustained bf16 (kernel timed inside a long step)",
                 "launches_per_step": gm["launches_per_step"], "ms_per_step": gm["ms_per_step"],
                 "share_of_step": gm["ms_per_step"] / (ms / args.steps)}
     others = []
-    for name in ("softmax_xent", "adamw", "layernorm_fwd", "layernorm_bwd", "lora_grad"):
+    for name in ("softmax_xent", "adamw", "layernorm_fwd", "layernorm_bwd", "rmsnorm_fwd", "rmsnorm_bwd", "rope",
+                 "swiglu_fwd", "swiglu_bwd", "lora_grad"):
         if name in classes:
             c = classes[name]
             gbs = c["work_per_step"] / (c["ms_per_step"] * 1e-3) / 1e9
@@ -282,7 +287,7 @@ def run_ours(args) -> None:
     if world == 1:
         others.append(adamw_large_buffer(ops, dev, pk))
     cpu = None
-    if world == 1 and not args.no_cpu_baseline:
+    if world == 1 and not args.no_cpu_baseline and args.workload == "c2":
         tps, cores, per_step = cpu_oracle_tokens_per_s(8, 512, steps=2, warmup=1)
         cpu = {"value": tps, "unit": UNIT, "cores": cores, "kind": "port",
                "sample": "oracle/gpt2_lora_ref.py at BASELINE.json configs[0] (GPT-2 124M LoRA r=8 fp32, batch 8, "
@@ -291,10 +296,9 @@ def run_ours(args) -> None:
         "metric": METRIC, "value": tokens / (ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-        "config": {"workload": f"GPT-2 124M LoRA r={LORA_R} bf16 fine-tune step (fwd+loss+bwd+AdamW), seq {SEQ}, "
-                               f"batch {BATCH}/GPU (BASELINE.json configs[1])",
+        "config": {"workload": workload_desc,
                    "global_batch": BATCH * world, "seq_len": SEQ, "parallelism": f"dp{world}",
-                   "l2": "per-step working set (~11 GB of activations + 3.3 GB of logits) is far larger than the "
+                   "l2": "per-step working set (GBs of activations and logits) is far larger than the "
                          "126 MB L2; no explicit flush",
                    "attention": "torch SDPA (library) this round; every other op is this repo's CUDA"},
         "e2e": {"value": tokens / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e / args.steps,
@@ -335,6 +339,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
     ap.add_argument("--detail", default="", help="write per-shape GEMM timings of the instrumented pass to this JSON file")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup

@@ -60,7 +60,43 @@ class OptSpec:
     max_grad_norm: float = 0.0
 
 
-class GPT2LoRAStep:
+class StepHostMixin:
+    """What every step engine offers to the payload besides step(): the host-buffer call and the
+    resume state.  Engines provide B, T, dev, loss, step(), P / Mo / Vo, step_count, lora, dims,
+    _refresh_shadows()."""
+
+    def step_host(self, ids_host: torch.Tensor, labels_host: torch.Tensor) -> float:
+        """The call a user of the package makes: HOST int64 [batch, seq] tensors in (pinned
+        memory makes the copies asynchronous), python float loss out.  Copies the inputs to
+        the device, runs one full step, reads the loss back."""
+        if not hasattr(self, "_ids_dev"):
+            self._ids_dev = torch.empty(self.B, self.T, dtype=torch.int64, device=self.dev)
+            self._labels_dev = torch.empty(self.B, self.T, dtype=torch.int64, device=self.dev)
+            self._loss_host = torch.empty(1, dtype=torch.float32).pin_memory()
+        self._ids_dev.copy_(ids_host, non_blocking=True)
+        self._labels_dev.copy_(labels_host, non_blocking=True)
+        self.step(self._ids_dev, self._labels_dev)
+        self._loss_host.copy_(self.loss, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        return float(self._loss_host[0])
+
+    def state_dict(self) -> dict:
+        """Everything needed to continue training: fp32 master adapters, Adam moments, step."""
+        return {"P": self.P.detach().cpu().clone(), "m": self.Mo.detach().cpu().clone(),
+                "v": self.Vo.detach().cpu().clone(), "step": self.step_count,
+                "r": self.lora.r, "alpha": self.lora.alpha, "n_layer": self.dims.n_layer, "d_model": self.dims.d_model}
+
+    def load_state_dict(self, st: dict) -> None:
+        want = (self.lora.r, self.dims.n_layer, self.dims.d_model)
+        got = (st["r"], st["n_layer"], st["d_model"])
+        if want != got or st["P"].numel() != self.P.numel():
+            raise ValueError(f"checkpoint is for (r, layers, d_model) = {got}, this job is {want}")
+        self.P.copy_(st["P"]); self.Mo.copy_(st["m"]); self.Vo.copy_(st["v"])
+        self.step_count = int(st["step"])
+        self._refresh_shadows(cast=True)
+
+
+class GPT2LoRAStep(StepHostMixin):
     """Holds device state for one rank and runs fwd + loss + bwd + AdamW per `step()`."""
 
     def __init__(self, dims: GPT2Dims, lora: LoRASpec, opt: OptSpec, base: dict, adapters: dict, *,
@@ -161,21 +197,6 @@ class GPT2LoRAStep:
             out[f"h{l}.c_attn.lora_A"] = self.gAt_all[l * R_PAD: l * R_PAD + r].t().contiguous().cpu()
             out[f"h{l}.c_attn.lora_B"] = self.gB_all[l * R_PAD: l * R_PAD + r].contiguous().cpu()
         return out
-
-    def state_dict(self) -> dict:
-        """Everything needed to continue training bit-for-bit: fp32 master adapters, Adam moments, step."""
-        return {"P": self.P.detach().cpu().clone(), "m": self.Mo.detach().cpu().clone(),
-                "v": self.Vo.detach().cpu().clone(), "step": self.step_count,
-                "r": self.lora.r, "alpha": self.lora.alpha, "n_layer": self.dims.n_layer, "d_model": self.dims.d_model}
-
-    def load_state_dict(self, st: dict) -> None:
-        want = (self.lora.r, self.dims.n_layer, self.dims.d_model)
-        got = (st["r"], st["n_layer"], st["d_model"])
-        if want != got or st["P"].numel() != self.P.numel():
-            raise ValueError(f"checkpoint is for (r, layers, d_model) = {got}, this job is {want}")
-        self.P.copy_(st["P"]); self.Mo.copy_(st["m"]); self.Vo.copy_(st["v"])
-        self.step_count = int(st["step"])
-        self._refresh_shadows(cast=True)
 
     def grad_views(self, lo: int, hi: int) -> list:
         """Contiguous gradient slices of layers [lo, hi) (what one all-reduce bucket covers)."""
@@ -315,21 +336,6 @@ class GPT2LoRAStep:
                        beta2=o.beta2, eps=o.eps, weight_decay=o.weight_decay, shadow=self.S, grad_scale=gs,
                        grad_scale_dev=coef)
         self._refresh_shadows(cast=False)
-
-    def step_host(self, ids_host: torch.Tensor, labels_host: torch.Tensor) -> float:
-        """The call a user of the package makes: HOST int64 [batch, seq] tensors in (pinned
-        memory makes the copies asynchronous), python float loss out.  Copies the inputs to
-        the device, runs one full step, reads the loss back."""
-        if not hasattr(self, "_ids_dev"):
-            self._ids_dev = torch.empty(self.B, self.T, dtype=torch.int64, device=self.dev)
-            self._labels_dev = torch.empty(self.B, self.T, dtype=torch.int64, device=self.dev)
-            self._loss_host = torch.empty(1, dtype=torch.float32).pin_memory()
-        self._ids_dev.copy_(ids_host, non_blocking=True)
-        self._labels_dev.copy_(labels_host, non_blocking=True)
-        self.step(self._ids_dev, self._labels_dev)
-        self._loss_host.copy_(self.loss, non_blocking=True)
-        torch.cuda.current_stream().synchronize()
-        return float(self._loss_host[0])
 
     def step(self, ids: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:
         """ids, labels: int64 [batch, seq] on the device.  Returns the (device) loss scalar."""

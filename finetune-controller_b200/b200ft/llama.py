@@ -18,7 +18,7 @@ import torch.nn.functional as F
 
 from . import ops
 from ._lib import EPI_NONE, EPI_RESIDUAL
-from .gpt2 import LoRASpec, OptSpec, R_PAD
+from .gpt2 import LoRASpec, OptSpec, R_PAD, StepHostMixin
 
 A_BLK = 2 * R_PAD  # adapter rows per layer in the flat buffers: q adapter 0..15, v adapter 16..31
 
@@ -72,7 +72,7 @@ def rope_tables(dims: LlamaDims, seq: int, device) -> tuple[torch.Tensor, torch.
     return ang.cos().contiguous().to(device), ang.sin().contiguous().to(device)
 
 
-class LlamaLoRAStep:
+class LlamaLoRAStep(StepHostMixin):
     """Device state of one rank; `step()` = fwd + loss + bwd + AdamW on the q/v adapters."""
 
     def __init__(self, dims: LlamaDims, lora: LoRASpec, opt: OptSpec, base: dict, adapters: dict, *,

@@ -119,15 +119,14 @@ def worker(args, rank: int, world: int, local: int) -> None:
 
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
-    dims = params.MODELS[args.model]
     lora = gpt2.LoRASpec(args.lora_r, args.lora_alpha)
     opt = gpt2.OptSpec(args.lr, args.beta1, args.beta2, args.eps, args.weight_decay, args.max_grad_norm)
-    base = params.init_gpt2(dims, args.seed, device=dev)          # identical on every rank (same seed)
-    ad = params.init_lora(dims, lora, args.seed + 1, device=dev)
-    sync = ddp.BucketedGradSync(dims.n_layer, n_buckets=2) if world > 1 else None
-    eng = gpt2.GPT2LoRAStep(dims, lora, opt, base, ad, batch=args.batch_size, seq=args.seq_len, device=dev,
-                            world_size=world, grad_sync=sync)
-    del base
+    n_layer = params.MODELS[args.model].n_layer
+    sync = ddp.BucketedGradSync(n_layer, n_buckets=2) if world > 1 else None
+    # random init, identical on every rank (same seed): the image has no network for checkpoints
+    eng, dims = params.build_engine(args.model, lora, opt, batch=args.batch_size, seq=args.seq_len, device=dev,
+                                    seed=args.seed, world_size=world, grad_sync=sync)
+    targets = ["q_proj", "v_proj"] if params.is_llama(dims) else ["c_attn"]
     stream = None if args.synthetic else load_token_stream(args.dataset_path)
     B, T = args.batch_size, args.seq_len
     ids_host = torch.empty(B, T, dtype=torch.int64).pin_memory()
@@ -187,7 +186,8 @@ def worker(args, rank: int, world: int, local: int) -> None:
             torch.save({k: v for k, v in eng.adapters_state().items()}, os.path.join(args.checkpoint_path, "adapter.pt"))
             with open(os.path.join(args.checkpoint_path, "adapter_config.json"), "w") as f:
                 json.dump({"peft_type": "LORA", "base_model": args.model, "r": args.lora_r,
-                           "lora_alpha": args.lora_alpha, "target_modules": ["c_attn"], "fan_in_fan_out": True,
+                           "lora_alpha": args.lora_alpha, "target_modules": targets,
+                           "fan_in_fan_out": not params.is_llama(dims),
                            "lora_dropout": 0.0, "steps": gstep}, f, indent=1)
         print(f"Epoch {args.epochs}/{args.epochs} done: {gstep} steps in {time.time() - t_start:.1f}s", flush=True)
 

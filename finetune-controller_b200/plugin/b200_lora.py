@@ -26,8 +26,8 @@ from app.models.base.finetuning import (
 class B200LoRAConfig(TrainingArguments):
     """Hyper-parameters of the B200-native LoRA fine-tune job (one type + default each)."""
 
-    model: str = Field(default="gpt2-124m", description="Architecture: gpt2-124m | gpt2-tiny")
-    mode: str = Field(default="lora", description="lora (adapters on c_attn) — full fine-tune is not in this build")
+    model: str = Field(default="gpt2-124m", description="Architecture: gpt2-124m | llama-3.2-1b | llama-3-8b (gpt2-tiny, llama-tiny for smoke runs)")
+    mode: str = Field(default="lora", description="lora: adapters on c_attn (GPT-2) or q_proj + v_proj (Llama); full fine-tune is not in this build")
     lora_r: int = Field(default=8, description="LoRA rank (<= 16)")
     lora_alpha: float = Field(default=16.0, description="LoRA alpha; the branch is scaled by alpha / r")
     seq_len: int = Field(default=1024, description="Tokens per sequence")
