@@ -739,11 +739,17 @@ int choose_block_n(int M, int N, int units, int tile_m) {
   const int tiles_m = (M + tile_m - 1) / tile_m;
   const int ctas = units < 1 ? 1 : units;
   int best = 256;
-  long best_cost = -1;
-  for (int bn : {256, 192, 128}) {
+  double best_cost = -1.0;
+  // time ~ waves x per-tile time; per FLOP a narrower tile re-reads more of A from L2 and keeps the
+  // tensor pipe less busy (measured on the step's shapes, profiles/README.md): relative efficiency
+  // 1.0 / 0.90 / 0.75 for BN = 256 / 192 / 128.  A narrower tile only wins when it saves a whole wave.
+  const int bns[3] = {256, 192, 128};
+  const double eff[3] = {1.0, 0.90, 0.75};
+  for (int i = 0; i < 3; ++i) {
+    const int bn = bns[i];
     long tiles = (long)tiles_m * ((N + bn - 1) / bn);
     long waves = (tiles + ctas - 1) / ctas;
-    long cost = waves * (bn + 24);  // + fixed per-tile overhead (pipeline fill, epilogue tail)
+    double cost = (double)waves * (bn / eff[i] + 16.0);  // + fixed per-tile overhead (pipeline fill, epilogue tail)
     if (best_cost < 0 || cost < best_cost) { best_cost = cost; best = bn; }
   }
   return best;
