@@ -269,6 +269,19 @@ def swiglu_bwd(dact, gate_up, dgate_up):
     return dgate_up
 
 
+def attn_fwd(qkv, out, lse2, *, batch, seq, n_head, n_kv_head, d_head, q_off, k_off, v_off, scale):
+    """Causal attention forward over the fused projection buffer (see include/b200ft.h)."""
+    global LAUNCHES
+    _need_cuda(qkv, out, lse2)
+    assert qkv.dtype == out.dtype == torch.bfloat16 and lse2.dtype == torch.float32
+    flops = 4.0 * batch * n_head * d_head * seq * (seq + 128) / 2  # causal, counted in whole 128-key tiles
+    with _timed("attn_fwd", flops):
+        check(lib().b200ft_attn_fwd(_p(qkv), qkv.stride(0), q_off, k_off, v_off, _p(out), out.stride(0), _p(lse2),
+                                    batch, seq, n_head, n_kv_head, d_head, scale, _stream()), "attn_fwd")
+    LAUNCHES += 1
+    return out
+
+
 def embed_fwd(ids, wte, wpe, x, *, seq, vocab):
     global LAUNCHES
     _need_cuda(ids, wte, wpe, x)

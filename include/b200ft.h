@@ -199,6 +199,19 @@ int b200ft_rope_inplace(void* x, int64_t ld, int64_t rows, int seq, int n_heads,
 int b200ft_swiglu_fwd(const void* gate_up, void* act, int64_t rows, int d_ff, void* stream);
 int b200ft_swiglu_bwd(const void* dact, const void* gate_up, void* dgate_up, int64_t rows, int d_ff, void* stream);
 
+/* ---------------------------------------------------------------------------------------
+ * Causal flash-attention forward on tcgen05 (oracle causal_attention()).
+ * q, k, v are read in place from the fused projection buffer qkv [batch*seq, ld] (bf16): head h of
+ * q starts at column q_off + h*d_head, kv head g at k_off + g*d_head / v_off + g*d_head, with
+ * g = h / (n_head / n_kv_head) (grouped-query attention).  out [batch*seq, ld_out] receives head h
+ * at column h*d_head; lse2 [batch*n_head, seq] receives max + log2(sum) of the scaled scores in
+ * the log2 domain (what the backward needs).  d_head = 64 only; other sizes return
+ * B200FT_ERR_UNSUPPORTED.  seq may be ragged (not a multiple of the 128-row tile).
+ * ------------------------------------------------------------------------------------- */
+int b200ft_attn_fwd(const void* qkv, int64_t ld, int q_off, int k_off, int v_off, void* out, int64_t ld_out,
+                    float* lse2, int batch, int seq, int n_head, int n_kv_head, int d_head, float scale,
+                    void* stream);
+
 /* Token + position embedding (oracle forward(): F.embedding(ids,wte)+F.embedding(pos,wpe)).
  * wte bf16 [vocab, d], wpe bf16 [ctx, d], x bf16 [rows, d], position = row % seq.  wpe may be NULL
  * (Llama: rotary positions, no learned table). */

@@ -1,0 +1,59 @@
+"""Own causal flash-attention (tcgen05) against the oracle's explicit masked-softmax attention."""
+import math
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+DEV = "cuda:0"
+
+
+def ref_attention(qkv, B, T, H, KV, dh, q_off, k_off, v_off):
+    """fp32, explicit: what oracle/gpt2_lora_ref.py:causal_attention and llama forward() compute."""
+    x = qkv.float().view(B, T, -1)
+    q = x[..., q_off:q_off + H * dh].view(B, T, H, dh).transpose(1, 2)
+    k = x[..., k_off:k_off + KV * dh].view(B, T, KV, dh).transpose(1, 2).repeat_interleave(H // KV, dim=1)
+    v = x[..., v_off:v_off + KV * dh].view(B, T, KV, dh).transpose(1, 2).repeat_interleave(H // KV, dim=1)
+    s = (q @ k.transpose(-1, -2)) / math.sqrt(dh)
+    mask = torch.ones(T, T, dtype=torch.bool).tril()
+    s = s.masked_fill(~mask, float("-inf"))
+    lse = torch.logsumexp(s, dim=-1)                                  # [B, H, T]
+    o = torch.softmax(s, dim=-1) @ v
+    return o.transpose(1, 2).reshape(B * T, H * dh), lse
+
+
+@pytest.mark.parametrize("B,T,H,KV", [(1, 128, 1, 1), (2, 256, 3, 3), (1, 1024, 2, 2), (2, 384, 8, 2), (3, 200, 4, 1),
+                                      (1, 40, 2, 2)])
+def test_attn_fwd_matches_oracle(B, T, H, KV):
+    from b200ft import ops
+    from oracle import gpt2_lora_ref as ref
+    dh = 64
+    g = torch.Generator().manual_seed(T + H)
+    ld = (H + 2 * KV) * dh
+    qkv = (torch.randn(B * T, ld, generator=g) * 1.5).to(torch.bfloat16)
+    q_off, k_off, v_off = 0, H * dh, (H + KV) * dh
+    o_ref, lse_ref = ref_attention(qkv, B, T, H, KV, dh, q_off, k_off, v_off)
+    if H == KV:  # the GPT-2 oracle's own function on the same buffer
+        o2 = ref.causal_attention(qkv.float().view(B, T, ld), H).reshape(B * T, H * dh)
+        torch.testing.assert_close(o2, o_ref, rtol=1e-5, atol=1e-5)
+    qd = qkv.to(DEV)
+    out = torch.full((B * T, H * dh), float("nan"), dtype=torch.bfloat16, device=DEV)
+    lse2 = torch.full((B * H, T), float("nan"), device=DEV)
+    ops.attn_fwd(qd, out, lse2, batch=B, seq=T, n_head=H, n_kv_head=KV, d_head=dh, q_off=q_off, k_off=k_off,
+                 v_off=v_off, scale=1.0 / math.sqrt(dh))
+    torch.cuda.synchronize()
+    got = out.cpu().float()
+    assert not torch.isnan(got).any()
+    torch.testing.assert_close(got, o_ref, rtol=2e-2, atol=2e-2)          # bf16 P and bf16 output
+    lse_got = lse2.cpu().view(B, H, T) * math.log(2.0)                    # log2 domain -> natural log
+    torch.testing.assert_close(lse_got, lse_ref, rtol=1e-3, atol=2e-3)
+
+
+def test_attn_fwd_rejects_other_head_sizes():
+    from b200ft import ops
+    from b200ft._lib import B200FTError
+    x = torch.zeros(128, 3 * 128, dtype=torch.bfloat16, device=DEV)
+    with pytest.raises(B200FTError):
+        ops.attn_fwd(x, torch.zeros(128, 128, dtype=torch.bfloat16, device=DEV), torch.zeros(1, 128, device=DEV),
+                     batch=1, seq=128, n_head=1, n_kv_head=1, d_head=128, q_off=0, k_off=128, v_off=256, scale=0.1)

@@ -1,37 +1,31 @@
+"""Own attention forward (tcgen05) vs torch SDPA (cuDNN) forward, CUDA-event timed."""
+import math, os, sys
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "finetune-controller_b200"))
 import torch, torch.nn.functional as F
-from torch.profiler import profile, ProfilerActivity
-B,T,H,dh=32,1024,12,64
-d=H*dh
-qkv=torch.randn(B*T,3*d,device='cuda',dtype=torch.bfloat16)
-v5=qkv.view(B,T,3,H,dh)
-q,k,v=(v5[:,:,i].permute(0,2,1,3).detach().requires_grad_(True) for i in range(3))
-print('q strides',q.stride(), q.is_contiguous())
-with torch.enable_grad():
-    o=F.scaled_dot_product_attention(q,k,v,is_causal=True)
-print('o shape',o.shape,'strides',o.stride())
-a=o.detach().permute(0,2,1,3); print('a contiguous',a.is_contiguous())
-da=torch.randn(B*T,d,device='cuda',dtype=torch.bfloat16)
-go=da.view(B,T,H,dh).permute(0,2,1,3)
-dq,dk,dv=torch.autograd.grad(o,(q,k,v),go,retain_graph=True)
-print('dq strides',dq.stride(),'dk',dk.stride(),'dv',dv.stride())
-torch.cuda.synchronize()
-with profile(activities=[ProfilerActivity.CUDA]) as prof:
-    with torch.enable_grad():
-        o=F.scaled_dot_product_attention(q,k,v,is_causal=True)
-    torch.cuda.synchronize()
-    dq,dk,dv=torch.autograd.grad(o,(q,k,v),go)
-    torch.cuda.synchronize()
-print(prof.key_averages().table(sort_by="cuda_time_total", row_limit=12, max_name_column_width=70))
-# separate q,k,v contiguous [B,T,H,dh]
-qs,ks,vs=(torch.randn(B,T,H,dh,device='cuda',dtype=torch.bfloat16).transpose(1,2).requires_grad_(True) for _ in range(3))
-with torch.enable_grad():
-    o2=F.scaled_dot_product_attention(qs,ks,vs,is_causal=True)
-print('o2 strides',o2.stride())
-g=torch.autograd.grad(o2,(qs,ks,vs),go)
-print('sep dq strides',g[0].stride())
-with profile(activities=[ProfilerActivity.CUDA]) as prof:
-    with torch.enable_grad():
-        o2=F.scaled_dot_product_attention(qs,ks,vs,is_causal=True)
-    g=torch.autograd.grad(o2,(qs,ks,vs),go)
-    torch.cuda.synchronize()
-print(prof.key_averages().table(sort_by="cuda_time_total", row_limit=12, max_name_column_width=70))
+from b200ft import ops
+dev = "cuda:0"
+def timeit(fn, n=20):
+    for _ in range(3): fn()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize(); e0.record()
+    for _ in range(n): fn()
+    e1.record(); torch.cuda.synchronize()
+    return e0.elapsed_time(e1) * 1e3 / n
+for (B, T, H, KV) in [(32, 1024, 12, 12), (4, 2048, 32, 8), (8, 4096, 12, 12)]:
+    dh = 64
+    ld = (H + 2 * KV) * dh
+    qkv = torch.randn(B * T, ld, device=dev).to(torch.bfloat16)
+    out = torch.empty(B * T, H * dh, dtype=torch.bfloat16, device=dev)
+    lse = torch.empty(B * H, T, device=dev)
+    flops = 4.0 * B * H * dh * T * T / 2
+    us = timeit(lambda: ops.attn_fwd(qkv, out, lse, batch=B, seq=T, n_head=H, n_kv_head=KV, d_head=dh, q_off=0,
+                                     k_off=H * dh, v_off=(H + KV) * dh, scale=1 / math.sqrt(dh)))
+    v5 = qkv.view(B, T, ld)
+    q = v5[..., : H * dh].view(B, T, H, dh).permute(0, 2, 1, 3)
+    k = v5[..., H * dh: (H + KV) * dh].view(B, T, KV, dh).permute(0, 2, 1, 3)
+    v = v5[..., (H + KV) * dh:].view(B, T, KV, dh).permute(0, 2, 1, 3)
+    us_lib = timeit(lambda: F.scaled_dot_product_attention(q, k, v, is_causal=True, enable_gqa=(H != KV)))
+    o_lib = F.scaled_dot_product_attention(q, k, v, is_causal=True, enable_gqa=(H != KV)).permute(0, 2, 1, 3).reshape(B * T, H * dh)
+    err = (out.float() - o_lib.float()).abs().max().item()
+    print(f"B={B} T={T} H={H} KV={KV}: own {us:8.1f} us ({flops/us/1e6:6.0f} TF)   SDPA {us_lib:8.1f} us ({flops/us_lib/1e6:6.0f} TF)   max|diff| {err:.4f}")
