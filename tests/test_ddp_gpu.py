@@ -14,6 +14,44 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 PKG = os.path.join(ROOT, "finetune-controller_b200")
 
 
+def _rank_llama(rank, world, port, out_dir):
+    for p in (ROOT, PKG):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    os.environ.update(RANK=str(rank), WORLD_SIZE=str(world), LOCAL_RANK=str(rank), MASTER_ADDR="127.0.0.1",
+                      MASTER_PORT=str(port))
+    import torch.distributed as dist
+    from b200ft import ddp, gpt2, llama
+    from oracle import llama_lora_ref as ref
+    from oracle.gpt2_lora_ref import AdamWConfig
+    ddp.init_process_group_from_env("nccl")
+    cfg, lora, opt = ref.LLAMA_TINY, ref.LoRAConfig(r=16, alpha=32.0), AdamWConfig(lr=1e-3)
+    base = ref.init_base_params(cfg, seed=0, randomize_all=True)
+    ad = ref.init_lora_params(cfg, lora, seed=1, b_init="normal")
+    dims = llama.LlamaDims(cfg.n_layer, cfg.d_model, cfg.n_head, cfg.n_kv_head, cfg.d_ff, cfg.vocab, cfg.ctx,
+                           cfg.rms_eps, cfg.rope_theta, cfg.rope_llama3, tie_embeddings=cfg.tie_embeddings)
+    eng = llama.LlamaLoRAStep(dims, gpt2.LoRASpec(lora.r, lora.alpha),
+                              gpt2.OptSpec(opt.lr, opt.beta1, opt.beta2, opt.eps, opt.weight_decay), base, ad,
+                              batch=2, seq=32, device=f"cuda:{rank}", world_size=world,
+                              grad_sync=ddp.BucketedGradSync(cfg.n_layer, n_buckets=2))
+    ids, labels = ref.synthetic_batch(cfg, 2, 32, seed=77, rank=rank)
+    loss = float(eng.step(ids.cuda(rank), labels.cuda(rank)).cpu())
+    torch.save({"loss": loss, "adapters": eng.adapters_state()}, os.path.join(out_dir, f"l{rank}.pt"))
+    dist.destroy_process_group()
+
+
+def test_llama_two_ranks_stay_identical(tmp_path):
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    import torch.multiprocessing as mp
+    from b200ft import ddp
+    mp.spawn(_rank_llama, args=(2, ddp.free_port(), str(tmp_path)), nprocs=2, join=True)
+    a, b = torch.load(tmp_path / "l0.pt"), torch.load(tmp_path / "l1.pt")
+    assert a["loss"] != b["loss"]                      # different micro-batches
+    for k in a["adapters"]:
+        assert torch.equal(a["adapters"][k], b["adapters"][k]), k
+
+
 def _rank(rank, world, port, out_dir):
     for p in (ROOT, PKG):
         if p not in sys.path:

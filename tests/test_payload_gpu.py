@@ -56,3 +56,17 @@ def test_entrypoint_synthetic_and_clipping(tmp_path):
     assert cfg["r"] == 16 and cfg["target_modules"] == ["c_attn"]
     w = torch.load(c / "adapter.pt")
     assert w["h0.c_attn.lora_A"].shape == (64, 16) and w["h1.c_attn.lora_B"].shape == (16, 192)
+
+
+def test_entrypoint_llama_tiny(tmp_path):
+    from b200ft import train
+    d = tmp_path / "l"
+    args = ["--model=llama-tiny", "--seq_len=32", "--batch_size=2", "--epochs=1", "--steps_per_epoch=3", "--lr=0.001",
+            "--log_interval=1", "--save_model", "--synthetic", "--lora_r=16", "--lora_alpha=32",
+            f"--dataset_path={tmp_path}", f"--checkpoint_path={d}"]
+    assert train.main(args) == 0
+    cfg = __import__("json").load(open(d / "adapter_config.json"))
+    assert cfg["target_modules"] == ["q_proj", "v_proj"] and cfg["fan_in_fan_out"] is False
+    w = torch.load(d / "adapter.pt")
+    assert w["l0.q_proj.lora_A"].shape == (16, 64) and w["l1.v_proj.lora_B"].shape == (32, 16)
+    assert float(w["l0.v_proj.lora_B"].abs().max()) > 0.0       # PEFT's zero B has moved after 3 steps

@@ -93,6 +93,13 @@ def test_medium_model_real_width():
     _run_parity(cfg, batch=2, seq=128, r=8, steps=2)
 
 
+def test_full_gpt2_124m_at_config_c1_one_step():
+    """BASELINE.json configs[0] exactly — GPT-2 124M, LoRA r=8, batch 8 x seq 512 — one step on the
+    GPU against the oracle on the host cores (the configuration the CPU baseline is timed at)."""
+    eng, oracle = _run_parity(ref.GPT2_124M, batch=8, seq=512, r=8, steps=1)
+    assert eng.M == 4096
+
+
 def test_golden_fixture():
     """The committed fixture was produced by the oracle in the build container
     (tests/golden/make_golden.py); the GPU step must land on it within the same tolerances."""
