@@ -2,19 +2,23 @@
 // straight out of the fused [tokens, q|k|v] projection buffer (grouped-query attention = several
 // q heads sharing one kv head) and writing o [tokens, heads*64] plus the per-row log-sum-exp.
 //
-// One CTA per (batch, head, 128-row query tile), heaviest tiles first; 192 threads:
-//   warp 0   TMA producer: Q once, then K_j / V_j into a 2-stage ring (and TMEM alloc/dealloc)
-//   warp 1   MMA issuer:   S = Q K_j^T (128x128x64, 4 UMMAs) into TMEM columns [0,128);
-//                          PV = P V_j (128x64x128, 8 UMMAs) into TMEM columns [128,192)
-//   warps 2-5 softmax, one thread per query row: two sweeps over S in TMEM (row max; then
-//            exp2, row sum, bf16 P into 128B-swizzled smem = the A operand of the PV UMMA), and the
-//            running output O kept in registers: O = O*alpha + PV_{j-1} folded in one tile later.
-// V_j is consumed as an MN-major B operand ([keys, d_head] rows as TMA delivers them), so nothing
-// is transposed.  Shared memory 113 KB and 256 TMEM columns per CTA: two CTAs share an SM, and one
-// CTA's softmax (MUFU-bound: 128x128 exp2 per tile) overlaps the other's UMMAs.
+// One CTA per (batch, head, PAIR of 128-row query tiles A and B), heaviest pairs first; 384 threads:
+//   warp 0    TMA producer: Q_A, Q_B once, then K_j / V_j into 2-stage rings — loaded once, used by both tiles
+//   warp 1    MMA issuer:   S_g = Q_g K_j^T (128x128x64, 4 UMMAs) and PV_g = P_g V_j (128x64x128, 8 UMMAs),
+//             software-pipelined  PV_A(j), S_A(j+1), PV_B(j), S_B(j+1)  so that while one tile's
+//             softmax runs the tensor core works for the other (ping-pong)
+//   warp 2    TMEM allocator (512 columns: S_A, S_B 128 each; PV_A, PV_B 64 each; P_A, P_B 64 each)
+//   warps 4-7 / 8-11  softmax of tile A / B, one thread per query row: ONE sweep over S in TMEM —
+//             p = exp2(s*scale - m_ref) against the running reference max, row sum, bf16 P written back to
+//             TMEM with tcgen05.st (the PV UMMA takes its A operand from TMEM: no smem round trip for P,
+//             whose 6 KB of reads per 32-cycle UMMA would exceed the shared-memory port) — repeated only if
+//             some row's max grew by more than 2^8 over its reference (lazy rescaling; exact after the final
+//             normalisation).  The running output O stays in registers: PV_{j-1} is folded in one tile later.
+// V_j is consumed as an MN-major B operand ([keys, d_head] rows as TMA delivers them): nothing is
+// transposed.  Registers are the per-scheduler resource that decides the shape: 12 warps x 168.
 //
-// Work per (batch, head): T^2/2 * 64 * 4 FLOP (causal); tensor-pipe time 512 cycles per 128x128
-// tile vs 1024 cycles of exp2 at 16/clk/SM: the kernel is bound by the special-function unit.
+// Work per (batch, head): T^2/2 * 64 * 4 FLOP (causal); per 128x128 tile the tensor pipe needs 512
+// cycles, the special-function unit 1024 (exp2 at 16/clk/SM): the kernel is bound by MUFU.
 #include <cuda.h>
 #include <mutex>
 #include <stdlib.h>
@@ -25,24 +29,24 @@ namespace {
 
 constexpr int kDH = 64;
 constexpr int kBQ = 128, kBK = 128;
-constexpr int kThreads = 192;
-constexpr int kQBytes = kBQ * kDH * 2;          // 16 KB
-constexpr int kKVBytes = kBK * kDH * 2;         // 16 KB each
-constexpr int kPBytes = kBQ * kBK * 2;          // 32 KB: two 64-key slabs of [128 rows x 128 B]
-constexpr int kKStages = 2;                     // K_j double-buffered; V_j single (it is needed a whole softmax later)
-constexpr int kTiles = kQBytes + (kKStages + 1) * kKVBytes + kPBytes;  // 96 KB: two CTAs per SM
+constexpr int kThreads = 384;
+constexpr int kQBytes = kBQ * kDH * 2;          // 16 KB per query tile
+constexpr int kKVBytes = kBK * kDH * 2;         // 16 KB
+constexpr int kStages = 2;
+constexpr int kTiles = 2 * kQBytes + 2 * kStages * kKVBytes;  // 96 KB
 constexpr int kSmemBytes = kTiles + 256;        // + barriers; no alignment slack (the kernel checks the base)
-constexpr int kTmemCols = 256;
-constexpr uint32_t kColS = 0, kColPV = 128;
+constexpr int kTmemCols = 512;
+constexpr uint32_t kColS = 0, kColPV = 256, kColP = 384;  // + 128*g, + 64*g, + 64*g (P: bf16 pairs, 64 columns)
+constexpr float kRescaleThreshold = 8.0f;       // log2 units: p stays below 2^8
 constexpr long long kWaitLimit = 4000000000ll;
 
 struct AttnParams {
   int batch, seq, n_head, n_kv_head;
   int q_off, k_off, v_off;  // column offsets of head 0 of q / k / v in the fused buffer
-  int nq_tiles;
+  int nq_tiles, nq_pairs;
   float scale_log2;         // softmax scale * log2(e)
   __nv_bfloat16* out; int64_t ld_out;
-  float* lse2;              // [batch*n_head, seq]: row max + log2(row sum), log2 domain incl. scale
+  float* lse2;              // [batch*n_head, seq]: reference max + log2(row sum), log2 domain incl. scale
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -96,6 +100,21 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* r) {
         "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
       : "r"(taddr) : "memory");
 }
+__device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t* w) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
+      "{%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16};"
+      ::"r"(taddr), "r"(w[0]), "r"(w[1]), "r"(w[2]), "r"(w[3]), "r"(w[4]), "r"(w[5]), "r"(w[6]), "r"(w[7]),
+        "r"(w[8]), "r"(w[9]), "r"(w[10]), "r"(w[11]), "r"(w[12]), "r"(w[13]), "r"(w[14]), "r"(w[15]) : "memory");
+}
+__device__ __forceinline__ void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+// D[tmem] (+)= A[tmem] * B[smem descriptor]
+__device__ __forceinline__ void umma_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+      ::"r"(d_tmem), "r"(a_tmem), "l"(bdesc), "r"(idesc), "r"(acc) : "memory");
+}
 __device__ __forceinline__ void tmem_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ float ex2(float x) {
   float y;
@@ -118,40 +137,98 @@ __device__ __forceinline__ uint32_t idesc(int n, int b_mn) {
   return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)b_mn << 16) | ((uint32_t)(n >> 3) << 17) | (8u << 24);
 }
 
-// 160 registers: 6 warps x 160 x 32 = 30720 per CTA, two CTAs per SM (168 rounds up past the file)
-__global__ void __maxnreg__(160)
+
+// One sweep over a 128-key score tile of this thread's query row: p = exp2(s*scale - m_ref) -> bf16 P in
+// TMEM, row sum and raw row max returned.  DIAG tiles mask keys beyond the query position; the other
+// tiles carry no masking code at all.  Before the first store into P the previous tile's P V UMMA must
+// have finished reading it (pv_bar / pv_parity; skipped when wait_pv is false).
+template <bool DIAG>
+__device__ __forceinline__ void softmax_sweep(uint32_t t_s, uint32_t t_p, float scale_log2, float m_ref, int kbase,
+                                              int qrow, bool wait_pv, uint32_t pv_bar, uint32_t pv_parity,
+                                              float& sum_out, float& max_out) {
+  const f32x2_t sc2 = pk2(scale_log2, scale_log2);
+  const f32x2_t nm2 = pk2(-m_ref, -m_ref);
+  // four independent accumulator chains each for the row sum and the row max: with two warps per
+  // scheduler a single 64-deep dependent chain cannot be hidden
+  f32x2_t sa[4] = {pk2(0.f, 0.f), pk2(0.f, 0.f), pk2(0.f, 0.f), pk2(0.f, 0.f)};
+  float ma[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+#pragma unroll
+  for (int c = 0; c < kBK / 32; ++c) {
+    uint32_t r[32];
+    tmem_ld32(t_s + 32 * c, r);
+    tmem_wait_ld();
+    uint32_t w[16];
+#pragma unroll
+    for (int i = 0; i < 32; i += 2) {
+      float s0 = __uint_as_float(r[i]), s1 = __uint_as_float(r[i + 1]);
+      if (DIAG) {
+        if (kbase + 32 * c + i > qrow) s0 = -INFINITY;
+        if (kbase + 32 * c + i + 1 > qrow) s1 = -INFINITY;
+      }
+      const int a = (i >> 1) & 3;
+      ma[a] = fmaxf(ma[a], fmaxf(s0, s1));
+      float e0, e1;
+      upk2(fma2(pk2(s0, s1), sc2, nm2), e0, e1);
+      const float p0 = ex2(e0), p1 = ex2(e1);  // exp2(-inf) = 0 for masked keys
+      sa[a] = add2(sa[a], pk2(p0, p1));
+      w[i >> 1] = pack_bf16x2(p0, p1);
+    }
+    if (c == 0 && wait_pv) {
+      mbar_wait(pv_bar, pv_parity);
+      tc_fence_after();
+    }
+    tmem_st16(t_p + 16 * c, w);  // keys 32c .. 32c+31 of this row = 16 packed columns of P
+  }
+  max_out = fmaxf(fmaxf(ma[0], ma[1]), fmaxf(ma[2], ma[3]));
+  float s_lo, s_hi;
+  upk2(add2(add2(sa[0], sa[1]), add2(sa[2], sa[3])), s_lo, s_hi);
+  sum_out = s_lo + s_hi;
+}
+
+__global__ void __launch_bounds__(kThreads, 1)
 attn_fwd_kernel(const __grid_constant__ CUtensorMap tm, const AttnParams p) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
   if (raw & 1023u) __trap();  // dynamic shared memory starts 1024-aligned (no static smem in this kernel)
-  const uint32_t base = raw;
-  const uint32_t sQ = base;
-  const uint32_t sK = sQ + kQBytes;
-  const uint32_t sV = sK + kKStages * kKVBytes;
-  const uint32_t sP = sV + kKVBytes;
-  const uint32_t bars = base + kTiles;
-  const uint32_t q_full = bars, k_full = bars + 8, k_empty = bars + 24, s_full = bars + 40, s_free = bars + 48,
-                 p_full = bars + 56, pv_full = bars + 64, v_full = bars + 72, v_empty = bars + 80, tmem_slot = bars + 88;
+  const uint32_t sQ = raw;                               // Q_A, Q_B
+  const uint32_t sK = sQ + 2 * kQBytes;                  // K ring
+  const uint32_t sV = sK + kStages * kKVBytes;           // V ring
+  const uint32_t bars = raw + kTiles;
+  const uint32_t q_full = bars;
+  auto k_full = [&](int s) { return bars + 8u * (1 + s); };
+  auto k_empty = [&](int s) { return bars + 8u * (3 + s); };
+  auto v_full = [&](int s) { return bars + 8u * (5 + s); };
+  auto v_empty = [&](int s) { return bars + 8u * (7 + s); };
+  auto s_full = [&](int g) { return bars + 8u * (9 + g); };
+  auto s_free = [&](int g) { return bars + 8u * (11 + g); };
+  auto p_full = [&](int g) { return bars + 8u * (13 + g); };
+  auto pv_full = [&](int g) { return bars + 8u * (15 + g); };
+  const uint32_t tmem_slot = bars + 8u * 17;
   volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - raw));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  // heaviest query tiles (most kv tiles) first
+  // heaviest pairs of query tiles (most kv tiles) first
   const int bh_count = p.batch * p.n_head;
-  const int qt = p.nq_tiles - 1 - (int)(blockIdx.x / bh_count);
+  const int pair = p.nq_pairs - 1 - (int)(blockIdx.x / bh_count);
   const int bh = (int)(blockIdx.x % bh_count);
   const int b = bh / p.n_head, h = bh % p.n_head;
   const int hk = h / (p.n_head / p.n_kv_head);
-  const int q0 = qt * kBQ;
-  const int n_kv = qt + 1;  // causal: kv tiles 0..qt
+  const int qtA = 2 * pair, qtB = 2 * pair + 1;
+  const bool hasB = qtB < p.nq_tiles;
+  const int nA = qtA + 1, nB = hasB ? qtB + 1 : 0;  // causal: tile g attends kv tiles 0 .. qt_g
+  const int n_kv = nA > nB ? nA : nB;
 
   if (warp == 1 && lane == 0) {
     mbar_init(q_full, 1);
-    for (int s = 0; s < kKStages; ++s) { mbar_init(k_full + 8 * s, 1); mbar_init(k_empty + 8 * s, 1); }
-    mbar_init(v_full, 1); mbar_init(v_empty, 1);
-    mbar_init(s_full, 1); mbar_init(s_free, 4); mbar_init(p_full, 4); mbar_init(pv_full, 1);
+    for (int s = 0; s < kStages; ++s) {
+      mbar_init(k_full(s), 1); mbar_init(k_empty(s), 1); mbar_init(v_full(s), 1); mbar_init(v_empty(s), 1);
+    }
+    for (int g = 0; g < 2; ++g) {
+      mbar_init(s_full(g), 1); mbar_init(s_free(g), 4); mbar_init(p_full(g), 4); mbar_init(pv_full(g), 1);
+    }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (warp == 0) {
+  if (warp == 2) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(kTmemCols) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
@@ -164,162 +241,188 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm, const AttnParams p) {
     // ================================ TMA producer ================================
     const bool issuer = elect_one();
     if (issuer) {
-      mbar_expect_tx(q_full, kQBytes);
-      tma_load_3d(sQ, &tm, p.q_off + h * kDH, q0, b, q_full);
+      mbar_expect_tx(q_full, hasB ? 2 * kQBytes : kQBytes);
+      tma_load_3d(sQ, &tm, p.q_off + h * kDH, qtA * kBQ, b, q_full);
+      if (hasB) tma_load_3d(sQ + kQBytes, &tm, p.q_off + h * kDH, qtB * kBQ, b, q_full);
     }
-    int stage = 0;
-    uint32_t phase = 0;
     for (int j = 0; j < n_kv; ++j) {
-      mbar_wait(k_empty + 8 * stage, phase ^ 1u);
+      const int st = j & 1;
+      const uint32_t ph = (uint32_t)(j >> 1) & 1u;
+      mbar_wait(k_empty(st), ph ^ 1u);
       if (issuer) {
-        mbar_expect_tx(k_full + 8 * stage, kKVBytes);
-        tma_load_3d(sK + stage * kKVBytes, &tm, p.k_off + hk * kDH, j * kBK, b, k_full + 8 * stage);
+        mbar_expect_tx(k_full(st), kKVBytes);
+        tma_load_3d(sK + st * kKVBytes, &tm, p.k_off + hk * kDH, j * kBK, b, k_full(st));
       }
       __syncwarp();
-      mbar_wait(v_empty, (uint32_t)(j & 1) ^ 1u);  // P V_{j-1} has consumed the V buffer
+      mbar_wait(v_empty(st), ph ^ 1u);
       if (issuer) {
-        mbar_expect_tx(v_full, kKVBytes);
-        tma_load_3d(sV, &tm, p.v_off + hk * kDH, j * kBK, b, v_full);
+        mbar_expect_tx(v_full(st), kKVBytes);
+        tma_load_3d(sV + st * kKVBytes, &tm, p.v_off + hk * kDH, j * kBK, b, v_full(st));
       }
       __syncwarp();
-      if (++stage == kKStages) { stage = 0; phase ^= 1u; }
     }
   } else if (warp == 1) {
     // ================================ MMA issuer ================================
     const bool issuer = elect_one();
     const uint32_t id_s = idesc(kBK, 0);   // S: N = 128 keys, K-major B (K_j rows = keys, d_head contiguous)
     const uint32_t id_pv = idesc(kDH, 1);  // PV: N = 64, MN-major B (V_j rows = keys = reduction index)
-    mbar_wait(q_full, 0);
-    int stage = 0;
-    uint32_t phase = 0;
-    for (int j = 0; j < n_kv; ++j) {
-      mbar_wait(k_full + 8 * stage, phase);
-      mbar_wait(s_free, (uint32_t)(j & 1) ^ 1u);  // softmax has drained S_{j-1}
-      tc_fence_after();
+    auto issue_s = [&](int g, int st) {    // S_g = Q_g K^T
       if (issuer) {
 #pragma unroll
         for (int k = 0; k < kDH / 16; ++k)
-          umma(tmem + kColS, sdesc(sQ + 32 * k, 16, 1024), sdesc(sK + stage * kKVBytes + 32 * k, 16, 1024), id_s, k > 0);
-        umma_commit(s_full);
-        umma_commit(k_empty + 8 * stage);
+          umma(tmem + kColS + 128u * g, sdesc(sQ + g * kQBytes + 32 * k, 16, 1024),
+               sdesc(sK + st * kKVBytes + 32 * k, 16, 1024), id_s, k > 0);
+        umma_commit(s_full(g));
       }
       __syncwarp();
-      mbar_wait(v_full, (uint32_t)(j & 1));
-      mbar_wait(p_full, (uint32_t)(j & 1));  // P_j is in smem and PV_{j-1} has been read out of TMEM
-      tc_fence_after();
+    };
+    auto issue_pv = [&](int g, int st) {   // PV_g = P_g V: reduction over keys; P from TMEM (8 columns = 16 keys per step), V rows 16 per step
       if (issuer) {
 #pragma unroll
-        for (int k = 0; k < kBK / 16; ++k)  // reduction over keys: P slab k/4, 32 B per step; V rows 16 per step
-          umma(tmem + kColPV, sdesc(sP + (k >> 2) * (kBQ * 128) + 32 * (k & 3), 16, 1024),
-               sdesc(sV + 2048 * k, 8192, 1024), id_pv, k > 0);
-        umma_commit(pv_full);
-        umma_commit(v_empty);
+        for (int k = 0; k < kBK / 16; ++k)
+          umma_ts(tmem + kColPV + 64u * g, tmem + kColP + 64u * g + 8u * k,
+                  sdesc(sV + st * kKVBytes + 2048 * k, 8192, 1024), id_pv, k > 0);
+        umma_commit(pv_full(g));
       }
       __syncwarp();
-      if (++stage == kKStages) { stage = 0; phase ^= 1u; }
+    };
+    mbar_wait(q_full, 0);
+    mbar_wait(k_full(0), 0);
+    tc_fence_after();
+    issue_s(0, 0);
+    if (hasB) issue_s(1, 0);
+    if (issuer) umma_commit(k_empty(0));
+    __syncwarp();
+    for (int j = 0; j < n_kv; ++j) {
+      const int st = j & 1, nst = st ^ 1;
+      const uint32_t ph = (uint32_t)(j >> 1) & 1u, nph = (uint32_t)((j + 1) >> 1) & 1u;
+      const uint32_t par = (uint32_t)(j & 1);
+      bool k_next_ready = false;
+      mbar_wait(v_full(st), ph);
+      // per tile g: the next scores S_g(j+1) first (the softmax is waiting for them), then P_g V(j)
+      if (j + 1 < nA) {
+        mbar_wait(k_full(nst), nph); k_next_ready = true;
+        mbar_wait(s_free(0), par);       // softmax A has drained S_A(j)
+        tc_fence_after();
+        issue_s(0, nst);
+      }
+      if (j < nA) {
+        mbar_wait(p_full(0), par);       // P_A(j) is in TMEM and PV_A(j-1) has been read out
+        tc_fence_after();
+        issue_pv(0, st);
+      }
+      if (j + 1 < nB) {
+        if (!k_next_ready) mbar_wait(k_full(nst), nph);
+        mbar_wait(s_free(1), par);
+        tc_fence_after();
+        issue_s(1, nst);
+      }
+      if (j < nB) {
+        mbar_wait(p_full(1), par);
+        tc_fence_after();
+        issue_pv(1, st);
+      }
+      if (issuer) umma_commit(v_empty(st));
+      __syncwarp();
+      if (j + 1 < n_kv) {
+        if (issuer) umma_commit(k_empty(nst));
+        __syncwarp();
+      }
     }
-  } else {
+  } else if (warp >= 4) {
     // ================================ softmax, one thread per query row ================================
+    const int g = (warp - 4) >> 2;                // 0 = tile A, 1 = tile B
     const int quarter = warp & 3;                 // TMEM lanes this warp may touch
     const int row = quarter * 32 + lane;          // row within the query tile
-    const uint32_t t_lane = tmem + ((uint32_t)(quarter * 32) << 16);
-    const int qrow = q0 + row;                    // position in the sequence
+    const int qt = g ? qtB : qtA;
+    const int n_mine = g ? nB : nA;
+    const uint32_t t_s = tmem + ((uint32_t)(quarter * 32) << 16) + kColS + 128u * g;
+    const uint32_t t_pv = tmem + ((uint32_t)(quarter * 32) << 16) + kColPV + 64u * g;
+    const uint32_t t_p = tmem + ((uint32_t)(quarter * 32) << 16) + kColP + 64u * g;
+    const int qrow = qt * kBQ + row;              // position in the sequence
     float o[kDH];
 #pragma unroll
     for (int i = 0; i < kDH; ++i) o[i] = 0.f;
-    float m = -INFINITY, l = 0.f;
-    for (int j = 0; j < n_kv; ++j) {
-      mbar_wait(s_full, (uint32_t)(j & 1));
+    float m_ref = -INFINITY, l = 0.f;
+    for (int j = 0; j < n_mine; ++j) {
+      const uint32_t par = (uint32_t)(j & 1);
+      mbar_wait(s_full(g), par);
       tc_fence_after();
       const bool diag = (j == qt);
       const int kbase = j * kBK;
-      // ---- sweep 1: row max of the raw scores ----
-      float mx = -INFINITY;
+      if (j == 0) {  // the first tile has no reference yet: one extra sweep for the row max
+        float mx0 = -INFINITY;
 #pragma unroll
-      for (int c = 0; c < kBK / 32; ++c) {
-        uint32_t r[32];
-        tmem_ld32(t_lane + kColS + 32 * c, r);
-        tmem_wait_ld();
-#pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          const float s = __uint_as_float(r[i]);
-          mx = fmaxf(mx, (diag && kbase + 32 * c + i > qrow) ? -INFINITY : s);
-        }
-      }
-      const float m_new = fmaxf(m, mx * p.scale_log2);
-      const float alpha = ex2(m - m_new);  // exp2(-inf) = 0 on the first tile
-      // ---- fold the previous tile's P V into O (it was computed against the old max), then rescale ----
-      if (j > 0) {
-        mbar_wait(pv_full, (uint32_t)((j - 1) & 1));
-        tc_fence_after();
-#pragma unroll
-        for (int c = 0; c < kDH / 32; ++c) {
+        for (int c = 0; c < kBK / 32; ++c) {
           uint32_t r[32];
-          tmem_ld32(t_lane + kColPV + 32 * c, r);
+          tmem_ld32(t_s + 32 * c, r);
           tmem_wait_ld();
 #pragma unroll
-          for (int i = 0; i < 32; ++i) o[32 * c + i] = (o[32 * c + i] + __uint_as_float(r[i])) * alpha;
+          for (int i = 0; i < 32; ++i)
+            mx0 = fmaxf(mx0, (diag && kbase + 32 * c + i > qrow) ? -INFINITY : __uint_as_float(r[i]));
         }
+        m_ref = mx0 * p.scale_log2;
       }
-      l *= alpha;
-      m = m_new;
-      // ---- sweep 2: p = exp2(s*scale - m), row sum, bf16 P into the swizzled A-operand tile ----
-      float sum = 0.f;
+      float sum, mx;
+      bool first_pass = true;
+      while (true) {
+        const bool wait_pv = first_pass && j > 0;
+        if (diag) softmax_sweep<true>(t_s, t_p, p.scale_log2, m_ref, kbase, qrow, wait_pv, pv_full(g), par ^ 1u, sum, mx);
+        else      softmax_sweep<false>(t_s, t_p, p.scale_log2, m_ref, kbase, qrow, wait_pv, pv_full(g), par ^ 1u, sum, mx);
+        if (wait_pv) {  // fold the previous tile's P V into O (it was taken against the same reference max)
 #pragma unroll
-      for (int c = 0; c < kBK / 32; ++c) {
-        uint32_t r[32];
-        tmem_ld32(t_lane + kColS + 32 * c, r);
-        tmem_wait_ld();
-        uint32_t w[16];
+          for (int c = 0; c < kDH / 32; ++c) {
+            uint32_t r[32];
+            tmem_ld32(t_pv + 32 * c, r);
+            tmem_wait_ld();
 #pragma unroll
-        for (int i = 0; i < 32; i += 2) {
-          float p0 = ex2(fmaf(__uint_as_float(r[i]), p.scale_log2, -m));
-          float p1 = ex2(fmaf(__uint_as_float(r[i + 1]), p.scale_log2, -m));
-          if (diag) {
-            if (kbase + 32 * c + i > qrow) p0 = 0.f;
-            if (kbase + 32 * c + i + 1 > qrow) p1 = 0.f;
+            for (int i = 0; i < 32; ++i) o[32 * c + i] += __uint_as_float(r[i]);
           }
-          sum += p0 + p1;
-          w[i >> 1] = pack_bf16x2(p0, p1);
         }
-        // keys 32c..32c+31 of this row: slab = c/2, 16-byte chunks 4*(c&1) .. +3 of the 128-byte row
-        const uint32_t rowaddr = sP + (uint32_t)(c >> 1) * (kBQ * 128) + (uint32_t)row * 128;
+        first_pass = false;
+        // lazy rescaling: keep the old reference unless this row's max outgrew it by 2^8
+        const bool grow = mx * p.scale_log2 > m_ref + kRescaleThreshold;
+        if (!__any_sync(0xffffffffu, grow)) break;
+        if (grow) {
+          const float m_new = mx * p.scale_log2;
+          const float alpha = ex2(m_ref - m_new);
+          l *= alpha;
 #pragma unroll
-        for (int v = 0; v < 4; ++v) {
-          const uint32_t chunk = (uint32_t)(4 * (c & 1) + v);
-          asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(rowaddr + ((chunk ^ (uint32_t)(row & 7)) << 4)),
-                       "r"(w[4 * v]), "r"(w[4 * v + 1]), "r"(w[4 * v + 2]), "r"(w[4 * v + 3]) : "memory");
+          for (int i = 0; i < kDH; ++i) o[i] *= alpha;
+          m_ref = m_new;
         }
       }
       l += sum;
+      tmem_wait_st();
       tc_fence_before();
-      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
       __syncwarp();
-      if (lane == 0) { mbar_arrive(s_free); mbar_arrive(p_full); }
+      if (lane == 0) { mbar_arrive(s_free(g)); mbar_arrive(p_full(g)); }
     }
-    // ---- last tile's P V, normalise, write o and the log-sum-exp ----
-    mbar_wait(pv_full, (uint32_t)((n_kv - 1) & 1));
-    tc_fence_after();
-    const float inv_l = 1.f / l;
+    if (n_mine > 0) {
+      // ---- last tile's P V, normalise, write o and the log-sum-exp ----
+      mbar_wait(pv_full(g), (uint32_t)((n_mine - 1) & 1));
+      tc_fence_after();
+      const float inv_l = 1.f / l;
 #pragma unroll
-    for (int c = 0; c < kDH / 32; ++c) {
-      uint32_t r[32];
-      tmem_ld32(t_lane + kColPV + 32 * c, r);
-      tmem_wait_ld();
+      for (int c = 0; c < kDH / 32; ++c) {
+        uint32_t r[32];
+        tmem_ld32(t_pv + 32 * c, r);
+        tmem_wait_ld();
 #pragma unroll
-      for (int i = 0; i < 32; ++i) o[32 * c + i] = (o[32 * c + i] + __uint_as_float(r[i])) * inv_l;
-    }
-    if (qrow < p.seq) {
-      __nv_bfloat16* dst = p.out + ((int64_t)b * p.seq + qrow) * p.ld_out + h * kDH;
+        for (int i = 0; i < 32; ++i) o[32 * c + i] = (o[32 * c + i] + __uint_as_float(r[i])) * inv_l;
+      }
+      if (qrow < p.seq) {
+        __nv_bfloat16* dst = p.out + ((int64_t)b * p.seq + qrow) * p.ld_out + h * kDH;
 #pragma unroll
-      for (int v = 0; v < kDH / 8; ++v) *reinterpret_cast<uint4*>(dst + 8 * v) = pack8(o + 8 * v);
-      p.lse2[(int64_t)bh * p.seq + qrow] = m + log2f(l);
+        for (int v = 0; v < kDH / 8; ++v) *reinterpret_cast<uint4*>(dst + 8 * v) = pack8(o + 8 * v);
+        p.lse2[(int64_t)bh * p.seq + qrow] = m_ref + log2f(l);
+      }
     }
     tc_fence_before();
   }
 
   __syncthreads();
-  if (warp == 0) {
+  if (warp == 2) {
     tc_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(kTmemCols) : "memory");
   }
@@ -373,6 +476,7 @@ extern "C" int b200ft_attn_fwd(const void* qkv, int64_t ld, int q_off, int k_off
   p.batch = batch; p.seq = seq; p.n_head = n_head; p.n_kv_head = n_kv_head;
   p.q_off = q_off; p.k_off = k_off; p.v_off = v_off;
   p.nq_tiles = (seq + kBQ - 1) / kBQ;
+  p.nq_pairs = (p.nq_tiles + 1) / 2;
   p.scale_log2 = scale * 1.4426950408889634f;
   p.out = (__nv_bfloat16*)out; p.ld_out = ld_out; p.lse2 = lse2;
   static thread_local int attr_dev = -1;
@@ -389,7 +493,7 @@ extern "C" int b200ft_attn_fwd(const void* qkv, int64_t ld, int q_off, int k_off
     fprintf(stderr, "[b200ft] attn_fwd_kernel: %d CTAs/SM (smem %d B)\n", nb, kSmemBytes);
     occ_reported = 1;
   }
-  const unsigned grid = (unsigned)(p.nq_tiles * batch * n_head);
+  const unsigned grid = (unsigned)(p.nq_pairs * batch * n_head);
   attn_fwd_kernel<<<grid, kThreads, kSmemBytes, (cudaStream_t)stream>>>(tm, p);
   B200FT_LAUNCH_CHECK();
   return 0;
