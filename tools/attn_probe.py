@@ -12,7 +12,9 @@ def timeit(fn, n=20):
     for _ in range(n): fn()
     e1.record(); torch.cuda.synchronize()
     return e0.elapsed_time(e1) * 1e3 / n
-for (B, T, H, KV) in [(32, 1024, 12, 12), (4, 2048, 32, 8), (8, 4096, 12, 12)]:
+import ast
+SHAPES = ast.literal_eval(sys.argv[1]) if len(sys.argv) > 1 else [(32, 1024, 12, 12), (4, 2048, 32, 8), (8, 4096, 12, 12)]
+for (B, T, H, KV) in SHAPES:
     dh = 64
     ld = (H + 2 * KV) * dh
     qkv = torch.randn(B * T, ld, device=dev).to(torch.bfloat16)
