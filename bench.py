@@ -60,6 +60,11 @@ WORKLOADS = {
                                               "batch 4/GPU (BASELINE.json configs[2])"),
     "c4": ("llama-3-8b", 1, 4096, 16, 32.0, "Llama-3-8B LoRA r=16 (q_proj, v_proj) bf16 fine-tune step, seq 4096, "
                                             "batch 1/GPU (BASELINE.json configs[3])"),
+    "c5": ("llama-3-8b", 1, 4096, 0, 0.0, "Llama-3-8B FULL-parameter bf16 fine-tune step (fp32 master + Adam moments, "
+                                          "fused AdamW over 8.03 B parameters), seq 4096, batch 1/GPU "
+                                          "(BASELINE.json configs[4])"),
+    "c5s": ("llama-3.2-1b", 2, 2048, 0, 0.0, "Llama-3.2-1B FULL-parameter bf16 fine-tune step, seq 2048, batch 2/GPU "
+                                             "(small sibling of BASELINE.json configs[4])"),
 }
 
 
@@ -178,12 +183,16 @@ def run_ours(args) -> None:
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     model, BATCH, SEQ, lora_r, lora_alpha, workload_desc = WORKLOADS[args.workload]
-    lora = gpt2.LoRASpec(lora_r, lora_alpha)
+    full = lora_r == 0
+    lora = gpt2.LoRASpec(lora_r or 8, lora_alpha or 16.0)
     opt = gpt2.OptSpec()
-    sync = ddp.BucketedGradSync(params.MODELS[model].n_layer, n_buckets=2) if world > 1 else None
+    n_layer = params.MODELS[model].n_layer
+    # LoRA gradients are a few MB: two buckets.  Full-parameter gradients are hundreds of MB per layer:
+    # one bucket per layer, each reduced while the layers below it are still in backward
+    sync = ddp.BucketedGradSync(n_layer, n_buckets=n_layer if full else 2) if world > 1 else None
     # random-init weights; B drawn at random (not PEFT's zero) so every gradient path carries data
     eng, dims = params.build_engine(model, lora, opt, batch=BATCH, seq=SEQ, device=dev, seed=0, world_size=world,
-                                    grad_sync=sync, randomize_b=True)
+                                    grad_sync=sync, randomize_b=True, mode="full" if full else "lora")
     g = torch.Generator().manual_seed(1234 + rank)
     n_sets = 4
     host = [torch.randint(0, dims.vocab, (BATCH, SEQ), generator=g, dtype=torch.int64).pin_memory()
@@ -269,7 +278,7 @@ def run_ours(args) -> None:
                 "share_of_step": gm["ms_per_step"] / (ms / args.steps)}
     others = []
     for name in ("softmax_xent", "adamw", "layernorm_fwd", "layernorm_bwd", "rmsnorm_fwd", "rmsnorm_bwd", "rope",
-                 "swiglu_fwd", "swiglu_bwd", "lora_grad"):
+                 "swiglu_fwd", "swiglu_bwd", "lora_grad", "rmsnorm_dgamma", "embed_bwd"):
         if name in classes:
             c = classes[name]
             gbs = c["work_per_step"] / (c["ms_per_step"] * 1e-3) / 1e9
@@ -284,7 +293,7 @@ def run_ours(args) -> None:
             json.dump({"gemm_shapes": gemm_shapes, "classes": classes}, f, indent=1)
     # north_star asks for the fused AdamW's HBM fraction; the LoRA parameter set (1.2 M) is
     # launch-latency-bound, so it is also timed on a 256 Mi-element buffer
-    if world == 1:
+    if world == 1 and not full:
         others.append(adamw_large_buffer(ops, dev, pk))
     cpu = None
     if world == 1 and not args.no_cpu_baseline and args.workload == "c2":

@@ -102,7 +102,7 @@ def gemm(a, b, out, *, a_mn=False, b_mn=False, a2=None, b2=None, more=(), bias=N
     args.block_n, args.max_ctas, args.split_k, args.cta_group = block_n, max_ctas, split_k, cta_group
     kk = k + (args.k2 if a2 is not None else 0) + kk_more
     # which instantiation the library will pick (mirrors b200ft_gemm_bf16's rule for cta_group = 0)
-    cg = cta_group or (2 if (not a_mn and not b_mn and epilogue != EPI_ATOMIC_F32_T and m > 128 and n >= 128) else 1)
+    cg = cta_group or (2 if (epilogue != EPI_ATOMIC_F32_T and m > 128 and n >= 128) else 1)
     with _timed("gemm", 2.0 * m * n * kk, (m, n, kk, int(a_mn), int(b_mn), epilogue, cg)):
         check(lib().b200ft_gemm_bf16(ctypes.byref(args), _stream()), "gemm_bf16")
     LAUNCHES += 1
@@ -290,6 +290,29 @@ def embed_fwd(ids, wte, wpe, x, *, seq, vocab):
     check(lib().b200ft_embed_fwd(_p(ids), _p(wte), _p(wpe), _p(x), rows, seq, d, vocab, _stream()), "embed_fwd")
     LAUNCHES += 1
     return x
+
+
+def rmsnorm_bwd_dgamma(dy, x, rstd, dgamma):
+    """dgamma (fp32, accumulated) += column sums of dy * x * rstd."""
+    global LAUNCHES
+    _need_cuda(dy, x, rstd, dgamma)
+    rows, d = x.shape
+    assert dy.is_contiguous() and x.is_contiguous() and dgamma.dtype == torch.float32 and dgamma.numel() == d
+    with _timed("rmsnorm_dgamma", 4.0 * rows * d):
+        check(lib().b200ft_rmsnorm_bwd_dgamma(_p(dy), _p(x), _p(rstd), _p(dgamma), rows, d, _stream()),
+              "rmsnorm_bwd_dgamma")
+    LAUNCHES += 1
+
+
+def embed_bwd(ids, dx, dwte, *, vocab):
+    """dwte[ids] += dx (bf16 atomics)."""
+    global LAUNCHES
+    _need_cuda(ids, dx, dwte)
+    rows, d = dx.shape
+    assert ids.dtype == torch.int64 and ids.numel() == rows and dx.is_contiguous() and dwte.stride(0) == d
+    with _timed("embed_bwd", 6.0 * rows * d):
+        check(lib().b200ft_embed_bwd(_p(ids), _p(dx), _p(dwte), rows, d, vocab, _stream()), "embed_bwd")
+    LAUNCHES += 1
 
 
 def transpose(inp, out, rows=None, cols=None):

@@ -1,0 +1,85 @@
+// Kernels only the full-parameter fine-tune needs (BASELINE.json configs[4]; SURVEY.md §8 a2.5
+// "full-FT adds dW" and a2.9): the RMSNorm gain gradient and the embedding-table gradient.
+// Both are HBM-bound column/row reductions; the weight gradients proper are tcgen05 GEMMs.
+#include "common.cuh"
+#include "../../include/b200ft.h"
+
+namespace {
+
+// dgamma[c] += sum_r dy[r,c] * x[r,c] * rstd[r].  A block owns 64 columns x one row chunk: lanes walk
+// the columns in bf16 pairs (one 128-byte line per warp and row), the 8 warps stride the rows, partial
+// sums meet in shared memory and leave as one fp32 atomic per column and block.
+__global__ void __launch_bounds__(256)
+rmsnorm_dgamma_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
+                      const float* __restrict__ rstd, float* __restrict__ dgamma, int64_t rows, int d,
+                      int64_t rows_per_block) {
+  __shared__ float2 part[8][32];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int c = blockIdx.x * 64 + 2 * lane;
+  const int64_t r0 = (int64_t)blockIdx.y * rows_per_block;
+  const int64_t r1 = min(rows, r0 + rows_per_block);
+  float2 acc = make_float2(0.f, 0.f);
+  if (c < d) {
+#pragma unroll 4
+    for (int64_t r = r0 + warp; r < r1; r += 8) {
+      const float rs = __ldg(rstd + r);
+      const __nv_bfloat162 a = *reinterpret_cast<const __nv_bfloat162*>(dy + r * d + c);
+      const __nv_bfloat162 b = *reinterpret_cast<const __nv_bfloat162*>(x + r * d + c);
+      const float2 fa = __bfloat1622float2(a), fb = __bfloat1622float2(b);
+      acc.x = fmaf(fa.x * fb.x, rs, acc.x);
+      acc.y = fmaf(fa.y * fb.y, rs, acc.y);
+    }
+  }
+  part[warp][lane] = acc;
+  __syncthreads();
+  if (warp == 0 && c < d) {
+    float2 s = part[0][lane];
+#pragma unroll
+    for (int w = 1; w < 8; ++w) { s.x += part[w][lane].x; s.y += part[w][lane].y; }
+    atomicAdd(dgamma + c, s.x);
+    atomicAdd(dgamma + c + 1, s.y);
+  }
+}
+
+// dwte[ids[r], :] += dx[r, :]; one warp per token row, bf16x2 atomics (rows of the same token collide)
+__global__ void __launch_bounds__(256)
+embed_bwd_kernel(const int64_t* __restrict__ ids, const __nv_bfloat16* __restrict__ dx,
+                 __nv_bfloat16* __restrict__ dwte, int64_t rows, int d, int vocab) {
+  const int64_t row = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const int lane = threadIdx.x & 31;
+  int64_t id = ids[row];
+  id = id < 0 ? 0 : (id >= vocab ? vocab - 1 : id);  // same clamp as the forward gather
+  const __nv_bfloat162* src = reinterpret_cast<const __nv_bfloat162*>(dx + row * d);
+  __nv_bfloat162* dst = reinterpret_cast<__nv_bfloat162*>(dwte + id * d);
+  for (int i = lane; i < (d >> 1); i += 32) atomicAdd(dst + i, src[i]);
+}
+
+}  // namespace
+
+extern "C" int b200ft_rmsnorm_bwd_dgamma(const void* dy, const void* x, const float* rstd, float* dgamma,
+                                         int64_t rows, int d, void* stream) {
+  B200FT_CHECK_ARG(dy && x && rstd && dgamma && rows > 0 && d > 0 && d % 2 == 0, "rmsnorm_bwd_dgamma: bad arguments");
+  const int col_blocks = (d + 63) / 64;
+  // ~4 blocks per SM in total; at least 64 rows per block so the atomics stay negligible
+  int64_t chunks = (4LL * B200FT_NUM_SMS + col_blocks - 1) / col_blocks;
+  const int64_t max_chunks = (rows + 63) / 64;
+  if (chunks > max_chunks) chunks = max_chunks;
+  if (chunks < 1) chunks = 1;
+  if (chunks > 65535) chunks = 65535;
+  const int64_t rpb = (rows + chunks - 1) / chunks;
+  dim3 grid(col_blocks, (unsigned)((rows + rpb - 1) / rpb));
+  rmsnorm_dgamma_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(
+      (const __nv_bfloat16*)dy, (const __nv_bfloat16*)x, rstd, dgamma, rows, d, rpb);
+  B200FT_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int b200ft_embed_bwd(const int64_t* ids, const void* dx, void* dwte, int64_t rows, int d, int vocab,
+                                void* stream) {
+  B200FT_CHECK_ARG(ids && dx && dwte && rows > 0 && d > 0 && d % 2 == 0 && vocab > 0, "embed_bwd: bad arguments");
+  embed_bwd_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, (cudaStream_t)stream>>>(
+      ids, (const __nv_bfloat16*)dx, (__nv_bfloat16*)dwte, rows, d, vocab);
+  B200FT_LAUNCH_CHECK();
+  return 0;
+}

@@ -520,9 +520,10 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ TmapPack maps, const GemmParams
     // uniform registers); one elected lane arms the barrier and issues the copies.
     const bool issuer = elect_one();
     const uint32_t b_rows = (uint32_t)BN / CG;  // CG == 2: this CTA stages half of the B tile
-    const uint32_t b_bytes = (CG == 1 && p.b_mn) ? (uint32_t)((BN + 63) / 64) * 8192u : b_rows * 128u;
+    // MN-major B is staged in 64-column boxes of 8 KB (CG == 2: BN / 2 is a multiple of 64, host-checked)
+    const uint32_t b_bytes = p.b_mn ? (uint32_t)((b_rows + 63) / 64) * 8192u : b_rows * 128u;
     const uint32_t b2_bytes = b_rows * 128u;
-    const bool a_mn = CG == 1 && p.a_mn, b_mn = CG == 1 && p.b_mn;
+    const bool a_mn = p.a_mn, b_mn = p.b_mn;
     int stage = 0;
     uint32_t phase = 0;
     for (int w = w_begin; w < num_work; w += w_stride) {
@@ -567,8 +568,17 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ TmapPack maps, const GemmParams
             // the peer adds its (byte-less) arrival
             if (cta_rank == 0) mbar_expect_tx(fb, 2u * bytes);
             else mbar_arrive_cluster(fb, 0);
-            tma_load_2d_cg2(a_dst, tma_a, kk, m0, fb);
-            tma_load_2d_cg2(b_dst, tma_b, kk, n0, fb);
+            if (a_mn && !seg2) {
+              tma_load_2d_cg2(a_dst, tma_a, m0, kk, fb);
+              tma_load_2d_cg2(a_dst + 8192u, tma_a, m0 + 64, kk, fb);
+            } else {
+              tma_load_2d_cg2(a_dst, tma_a, kk, m0, fb);
+            }
+            if (b_mn && !seg2) {
+              for (int j = 0; j * 64 < (int)b_rows; ++j) tma_load_2d_cg2(b_dst + 8192u * j, tma_b, n0 + 64 * j, kk, fb);
+            } else {
+              tma_load_2d_cg2(b_dst, tma_b, kk, n0, fb);
+            }
           }
         }
         __syncwarp();
@@ -581,7 +591,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ TmapPack maps, const GemmParams
     // tracks the MMAs of the thread that executes it).
     if (cta_rank == 0) {
       const bool issuer = elect_one();
-      const bool a_mn = CG == 1 && p.a_mn, b_mn = CG == 1 && p.b_mn;
+      const bool a_mn = p.a_mn, b_mn = p.b_mn;
       const uint32_t idesc1 = make_idesc(kBlockM * CG, BN, a_mn, b_mn);
       const uint32_t idesc2 = make_idesc(kBlockM * CG, BN, 0, 0);
       // descriptor words: K-major SW128 (LBO 16, SBO 1024, +32 B per K step) or MN-major SW128
@@ -800,11 +810,16 @@ extern "C" int b200ft_gemm_bf16(const b200ft_gemm_args* a, void* stream) {
   const bool kmajor = (a->layout & (B200FT_A_MN_MAJOR | B200FT_B_MN_MAJOR)) == 0;
   B200FT_CHECK_ARG(a->cta_group >= 0 && a->cta_group <= 2, "gemm: cta_group=%d", a->cta_group);
   int cg = a->cta_group;
-  if (cg == 0) cg = (kmajor && !atomic_t && a->m > kBlockM && a->n >= 128 && ctas_max >= 2) ? 2 : 1;
-  B200FT_CHECK_ARG(cg == 1 || (kmajor && !atomic_t && ctas_max >= 2),
-                   "gemm: cta_group=2 needs K-major operands, a non-atomic epilogue and >= 2 CTAs");
+  const bool b_mn_flag = (a->layout & B200FT_B_MN_MAJOR) != 0;
+  (void)kmajor;
+  if (cg == 0) cg = (!atomic_t && a->m > kBlockM && a->n >= 128 && ctas_max >= 2) ? 2 : 1;
+  B200FT_CHECK_ARG(cg == 1 || (!atomic_t && ctas_max >= 2),
+                   "gemm: cta_group=2 needs a non-atomic epilogue and >= 2 CTAs");
   int BN = a->block_n > 0 ? a->block_n : choose_block_n(a->m, a->n, ctas_max / cg, kBlockM * cg);
+  // an MN-major B operand of a CTA pair is staged in 64-column boxes per CTA: BN / 2 must be a multiple of 64
+  if (cg == 2 && b_mn_flag && BN % 128 != 0) BN = a->block_n > 0 ? BN : (a->n > 128 ? 256 : 128);
   B200FT_CHECK_ARG(BN % 16 == 0 && BN >= 16 && BN <= kMaxBN, "gemm: block_n=%d", BN);
+  B200FT_CHECK_ARG(!(cg == 2 && b_mn_flag) || BN % 128 == 0, "gemm: cta_group=2 with MN-major B needs block_n 128 or 256 (got %d)", BN);
 
   GemmParams p;
   memset(&p, 0, sizeof(p));

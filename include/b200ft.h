@@ -218,6 +218,20 @@ int b200ft_attn_fwd(const void* qkv, int64_t ld, int q_off, int k_off, int v_off
 int b200ft_embed_fwd(const int64_t* ids, const void* wte, const void* wpe, void* x, int64_t rows,
                      int seq, int d, int vocab, void* stream);
 
+/* ---------------------------------------------------------------------------------------
+ * Full-parameter fine-tune only (BASELINE.json configs[4]; SURVEY.md §8 a2.5 "full-FT adds dW",
+ * a2.9).  The weight gradients themselves are b200ft_gemm_bf16 calls with MN-major operands;
+ * these two cover what is not a GEMM.  Oracle: autograd of oracle/llama_lora_ref.py rmsnorm() /
+ * F.embedding under FullOracleTrainer.
+ *   rmsnorm_bwd_dgamma: dgamma[c] += sum_r dy[r,c] * x[r,c] * rstd[r]   (fp32 atomics: zero it first)
+ *   embed_bwd:          dwte[ids[r], :] += dx[r, :]                      (bf16x2 atomics into the
+ *                       bf16 gradient table; ids clamped to [0, vocab) like b200ft_embed_fwd)
+ * --------------------------------------------------------------------------------------- */
+int b200ft_rmsnorm_bwd_dgamma(const void* dy, const void* x, const float* rstd, float* dgamma,
+                              int64_t rows, int d, void* stream);
+int b200ft_embed_bwd(const int64_t* ids, const void* dx, void* dwte, int64_t rows, int d, int vocab,
+                     void* stream);
+
 /* out[c, r] = in[r, c] for bf16 matrices (weight re-layout at load; adapter shadows). */
 int b200ft_transpose_bf16(const void* in, int64_t ld_in, void* out, int64_t ld_out, int rows,
                           int cols, void* stream);

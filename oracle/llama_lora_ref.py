@@ -209,6 +209,38 @@ class OracleTrainer:
         return float(loss.detach())
 
 
+class FullOracleTrainer:
+    """Full-parameter fine-tune (BASELINE.json configs[4]): every tensor of `base` is trainable, no
+    adapters; fwd + shifted CE + autograd bwd + torch.optim.AdamW(foreach=False, fused=False) with one
+    uniform weight decay over all tensors.  `world_grads` averages externally supplied per-rank
+    gradients in (data-parallel emulation, as in OracleTrainer of gpt2_lora_ref)."""
+
+    def __init__(self, cfg: LlamaConfig, opt: AdamWConfig, base: dict):
+        self.cfg, self.opt_cfg = cfg, opt
+        self.trainable = {k: v.clone().float().requires_grad_(True) for k, v in base.items()}
+        self.optim = torch.optim.AdamW(list(self.trainable.values()), lr=opt.lr, betas=(opt.beta1, opt.beta2),
+                                       eps=opt.eps, weight_decay=opt.weight_decay, foreach=False, fused=False)
+        self.last_grads: dict = {}
+
+    def grads(self, ids, labels):
+        for t in self.trainable.values():
+            t.grad = None
+        loss = causal_lm_loss(forward(self.trainable, None, ids, self.cfg, None), labels)
+        loss.backward()
+        return float(loss.detach()), {k: t.grad.detach().clone() for k, t in self.trainable.items()}
+
+    def step(self, ids, labels, world_grads: list | None = None) -> float:
+        loss, g = self.grads(ids, labels)
+        if world_grads is not None:
+            for k, t in self.trainable.items():
+                t.grad = sum(wg[k] for wg in world_grads) / len(world_grads)
+        if self.opt_cfg.max_grad_norm > 0:
+            torch.nn.utils.clip_grad_norm_(list(self.trainable.values()), self.opt_cfg.max_grad_norm)
+        self.last_grads = {k: t.grad.detach().clone() for k, t in self.trainable.items()}
+        self.optim.step()
+        return loss
+
+
 def hf_crosscheck(cfg: LlamaConfig = LLAMA_TINY, batch: int = 2, seq: int = 24, seed: int = 0) -> dict:
     """transformers' LlamaForCausalLM from config with this module's weights: logits / loss / grads."""
     from transformers import LlamaConfig as HFConfig, LlamaForCausalLM

@@ -262,6 +262,22 @@ def test_gemm_mn_major(ops, M, N, K, a_mn, b_mn):
 
 
 @pytest.mark.parametrize("cta_group", [1, 2])
+@pytest.mark.parametrize("a_mn,b_mn", [(False, True), (True, False), (True, True)])
+@pytest.mark.parametrize("M,N,K", [(256, 256, 64), (512, 384, 520), (304, 200, 136), (2304, 768, 1000),
+                                   (1024, 3072, 4096), (136, 128, 72)])
+def test_gemm_mn_major_cta_groups(ops, M, N, K, a_mn, b_mn, cta_group):
+    """The weight-gradient (both operands MN-major) and dX-without-transposed-copy (B MN-major) forms
+    of the full-parameter step, on the single-CTA and the CTA-pair instantiation."""
+    _gemm_case(ops, M, N, K, a_mn=a_mn, b_mn=b_mn, cta_group=cta_group)
+
+
+@pytest.mark.parametrize("block_n", [128, 256])
+def test_gemm_mn_major_pair_block_n_and_epilogue(ops, block_n):
+    _gemm_case(ops, 512, 512, 256, a_mn=True, b_mn=True, cta_group=2, block_n=block_n)
+    _gemm_case(ops, 512, 512, 256, b_mn=True, cta_group=2, block_n=block_n, epilogue=1)
+
+
+@pytest.mark.parametrize("cta_group", [1, 2])
 @pytest.mark.parametrize("M,N,K", [(256, 256, 64), (256, 256, 768), (512, 512, 128), (300, 200, 136), (129, 256, 768),
                                    (1000, 768, 3072), (2048, 2304, 768), (4096, 768, 256), (200, 128, 72)])
 def test_gemm_cta_groups(ops, M, N, K, cta_group):
