@@ -272,11 +272,10 @@ class LlamaFullStep(StepHostMixin):
         for l in range(L - 1, -1, -1):
             g_attn, g_mlp = self.gain[l]
             dg_attn, dg_mlp = self.dgain[l]
-            # MLP branch (act and h2 recomputed)
-            ops.swiglu_fwd(self.gu[l], self.act)
-            ops.gemm(dx, self.act, dW[f"l{l}.down"], a_mn=True, b_mn=True)
+            # MLP branch (the SwiGLU product and h2 are recomputed, the former inside swiglu_bwd)
             ops.gemm(dx, W[f"l{l}.down"], self.dact, b_mn=True)
-            ops.swiglu_bwd(self.dact, self.gu[l], self.dgu)
+            ops.swiglu_bwd(self.dact, self.gu[l], self.dgu, act=self.act)
+            ops.gemm(dx, self.act, dW[f"l{l}.down"], a_mn=True, b_mn=True)
             ops.rmsnorm_fwd(self.x1[l], g_mlp, self.h, self.rs_tmp, D.rms_eps)
             ops.gemm(self.dgu, self.h, dW[f"l{l}.gu"], a_mn=True, b_mn=True)
             ops.gemm(self.dgu, W[f"l{l}.gu"], self.dln, b_mn=True)

@@ -257,14 +257,17 @@ def swiglu_fwd(gate_up, act):
     return act
 
 
-def swiglu_bwd(dact, gate_up, dgate_up):
+def swiglu_bwd(dact, gate_up, dgate_up, act=None):
+    """dgate_up from (dact, gate_up); with `act` given, also rewrites the forward product into it."""
     global LAUNCHES
-    _need_cuda(dact, gate_up, dgate_up)
+    _need_cuda(dact, gate_up, dgate_up, act)
     rows, ff = dact.shape
     assert gate_up.shape == (rows, 2 * ff) and dgate_up.shape == (rows, 2 * ff)
     assert dact.is_contiguous() and gate_up.is_contiguous() and dgate_up.is_contiguous()
-    with _timed("swiglu_bwd", 10.0 * rows * ff):
-        check(lib().b200ft_swiglu_bwd(_p(dact), _p(gate_up), _p(dgate_up), rows, ff, _stream()), "swiglu_bwd")
+    assert act is None or (act.shape == (rows, ff) and act.is_contiguous())
+    with _timed("swiglu_bwd", (12.0 if act is not None else 10.0) * rows * ff):
+        check(lib().b200ft_swiglu_bwd_act(_p(dact), _p(gate_up), _p(dgate_up), _p(act), rows, ff, _stream()),
+              "swiglu_bwd")
     LAUNCHES += 1
     return dgate_up
 

@@ -31,7 +31,8 @@ import time
 def build_parser() -> argparse.ArgumentParser:
     ap = argparse.ArgumentParser(prog="b200ft.train")
     ap.add_argument("--model", default="gpt2-124m")
-    ap.add_argument("--mode", default="lora", choices=["lora"])
+    ap.add_argument("--mode", default="lora", choices=["lora", "full"],
+                    help="lora: adapters on a frozen base; full: every tensor trainable (Llama family)")
     ap.add_argument("--lora_r", type=int, default=8)
     ap.add_argument("--lora_alpha", type=float, default=16.0)
     ap.add_argument("--seq_len", type=int, default=1024)
@@ -122,10 +123,12 @@ def worker(args, rank: int, world: int, local: int) -> None:
     lora = gpt2.LoRASpec(args.lora_r, args.lora_alpha)
     opt = gpt2.OptSpec(args.lr, args.beta1, args.beta2, args.eps, args.weight_decay, args.max_grad_norm)
     n_layer = params.MODELS[args.model].n_layer
-    sync = ddp.BucketedGradSync(n_layer, n_buckets=2) if world > 1 else None
+    full = args.mode == "full"
+    # full-parameter gradients are hundreds of MB per layer: one all-reduce bucket per layer
+    sync = ddp.BucketedGradSync(n_layer, n_buckets=n_layer if full else 2) if world > 1 else None
     # random init, identical on every rank (same seed): the image has no network for checkpoints
     eng, dims = params.build_engine(args.model, lora, opt, batch=args.batch_size, seq=args.seq_len, device=dev,
-                                    seed=args.seed, world_size=world, grad_sync=sync)
+                                    seed=args.seed, world_size=world, grad_sync=sync, mode=args.mode)
     targets = ["q_proj", "v_proj"] if params.is_llama(dims) else ["c_attn"]
     stream = None if args.synthetic else load_token_stream(args.dataset_path)
     B, T = args.batch_size, args.seq_len
@@ -158,7 +161,8 @@ def worker(args, rank: int, world: int, local: int) -> None:
         writer = csv.writer(fh)
         if not resumed:
             writer.writerow(["epoch", "step", "loss", "lr", "tokens_per_sec", "elapsed_s"])
-        print(f"Epoch {start_epoch - 1}/{args.epochs} starting: model={args.model} lora_r={args.lora_r} world={world} "
+        print(f"Epoch {start_epoch - 1}/{args.epochs} starting: model={args.model} mode={args.mode} "
+              f"lora_r={args.lora_r} world={world} "
               f"batch/gpu={B} seq={T}" + (f" (resumed at step {gstep0})" if st is not None else ""), flush=True)
     t_start = time.time()
     gstep = gstep0
@@ -182,7 +186,16 @@ def worker(args, rank: int, world: int, local: int) -> None:
                 save_state(eng, args.checkpoint_path, epoch, it, gstep)
     if rank == 0:
         fh.close()
-        if args.save_model:
+        if args.save_model and full:
+            # bf16 weights in the oracle's tensor naming (HF names minus the "model.layers." prefix)
+            torch.save({k: v.to(torch.bfloat16) for k, v in eng.params_state().items()},
+                       os.path.join(args.checkpoint_path, "model.pt"))
+            with open(os.path.join(args.checkpoint_path, "config.json"), "w") as f:
+                json.dump({"base_model": args.model, "mode": "full", "dtype": "bfloat16", "steps": gstep,
+                           **{k: getattr(dims, k) for k in ("n_layer", "d_model", "n_head", "n_kv_head", "d_ff",
+                                                            "vocab", "rms_eps", "rope_theta", "tie_embeddings")}},
+                          f, indent=1)
+        elif args.save_model:
             torch.save({k: v for k, v in eng.adapters_state().items()}, os.path.join(args.checkpoint_path, "adapter.pt"))
             with open(os.path.join(args.checkpoint_path, "adapter_config.json"), "w") as f:
                 json.dump({"peft_type": "LORA", "base_model": args.model, "r": args.lora_r,

@@ -6,38 +6,41 @@
 
 namespace {
 
-// dgamma[c] += sum_r dy[r,c] * x[r,c] * rstd[r].  A block owns 64 columns x one row chunk: lanes walk
-// the columns in bf16 pairs (one 128-byte line per warp and row), the 8 warps stride the rows, partial
-// sums meet in shared memory and leave as one fp32 atomic per column and block.
+// dgamma[c] += sum_r dy[r,c] * x[r,c] * rstd[r].  A block owns 256 columns x one row chunk: a lane
+// carries 8 columns (one 16-byte load per operand and row, 512 contiguous bytes per warp), the 8 warps
+// stride the rows, partial sums meet in shared memory and leave as one fp32 atomic per column and block.
 __global__ void __launch_bounds__(256)
 rmsnorm_dgamma_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
                       const float* __restrict__ rstd, float* __restrict__ dgamma, int64_t rows, int d,
                       int64_t rows_per_block) {
-  __shared__ float2 part[8][32];
+  __shared__ float part[8][256 + 8];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int c = blockIdx.x * 64 + 2 * lane;
+  const int c = blockIdx.x * 256 + 8 * lane;
   const int64_t r0 = (int64_t)blockIdx.y * rows_per_block;
   const int64_t r1 = min(rows, r0 + rows_per_block);
-  float2 acc = make_float2(0.f, 0.f);
+  float acc[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) acc[j] = 0.f;
   if (c < d) {
 #pragma unroll 4
     for (int64_t r = r0 + warp; r < r1; r += 8) {
       const float rs = __ldg(rstd + r);
-      const __nv_bfloat162 a = *reinterpret_cast<const __nv_bfloat162*>(dy + r * d + c);
-      const __nv_bfloat162 b = *reinterpret_cast<const __nv_bfloat162*>(x + r * d + c);
-      const float2 fa = __bfloat1622float2(a), fb = __bfloat1622float2(b);
-      acc.x = fmaf(fa.x * fb.x, rs, acc.x);
-      acc.y = fmaf(fa.y * fb.y, rs, acc.y);
+      float a[8], b[8];
+      unpack8(ld_stream16(dy + r * d + c), a);
+      unpack8(ld_stream16(x + r * d + c), b);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j] = fmaf(a[j] * b[j], rs, acc[j]);
     }
   }
-  part[warp][lane] = acc;
-  __syncthreads();
-  if (warp == 0 && c < d) {
-    float2 s = part[0][lane];
 #pragma unroll
-    for (int w = 1; w < 8; ++w) { s.x += part[w][lane].x; s.y += part[w][lane].y; }
-    atomicAdd(dgamma + c, s.x);
-    atomicAdd(dgamma + c + 1, s.y);
+  for (int j = 0; j < 8; ++j) part[warp][8 * lane + j] = acc[j];
+  __syncthreads();
+  const int cc = blockIdx.x * 256 + threadIdx.x;
+  if (cc < d) {
+    float s_ = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) s_ += part[w][threadIdx.x];
+    atomicAdd(dgamma + cc, s_);
   }
 }
 
@@ -59,8 +62,11 @@ embed_bwd_kernel(const int64_t* __restrict__ ids, const __nv_bfloat16* __restric
 
 extern "C" int b200ft_rmsnorm_bwd_dgamma(const void* dy, const void* x, const float* rstd, float* dgamma,
                                          int64_t rows, int d, void* stream) {
-  B200FT_CHECK_ARG(dy && x && rstd && dgamma && rows > 0 && d > 0 && d % 2 == 0, "rmsnorm_bwd_dgamma: bad arguments");
-  const int col_blocks = (d + 63) / 64;
+  B200FT_CHECK_ARG(dy && x && rstd && dgamma && rows > 0 && d > 0 && d % 8 == 0 &&
+                       ((uintptr_t)dy | (uintptr_t)x) % 16 == 0,
+                   "rmsnorm_bwd_dgamma: rows=%lld d=%d (d must be a multiple of 8, buffers 16-byte aligned)",
+                   (long long)rows, d);
+  const int col_blocks = (d + 255) / 256;
   // ~4 blocks per SM in total; at least 64 rows per block so the atomics stay negligible
   int64_t chunks = (4LL * B200FT_NUM_SMS + col_blocks - 1) / col_blocks;
   const int64_t max_chunks = (rows + 63) / 64;

@@ -65,14 +65,14 @@ swiglu_fwd_kernel(const __nv_bfloat16* __restrict__ gu, __nv_bfloat16* __restric
 // d gate = dact * up * sig(g) * (1 + g * (1 - sig(g))),  d up = dact * silu(g)
 __global__ void __launch_bounds__(256)
 swiglu_bwd_kernel(const __nv_bfloat16* __restrict__ dact, const __nv_bfloat16* __restrict__ gu,
-                  __nv_bfloat16* __restrict__ dgu, int64_t rows, int ff) {
+                  __nv_bfloat16* __restrict__ dgu, __nv_bfloat16* __restrict__ act, int64_t rows, int ff) {
   const int vpr = ff >> 3;
   const int64_t total = rows * vpr;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
     const int64_t row = i / vpr;
     const int v = (int)(i % vpr);
-    float g[8], u[8], d[8], dg[8], du[8];
+    float g[8], u[8], d[8], dg[8], du[8], a[8];
     unpack8(ld_stream16(gu + row * 2 * ff + (v << 3)), g);
     unpack8(ld_stream16(gu + row * 2 * ff + ff + (v << 3)), u);
     unpack8(ld_stream16(dact + row * ff + (v << 3)), d);
@@ -81,9 +81,11 @@ swiglu_bwd_kernel(const __nv_bfloat16* __restrict__ dact, const __nv_bfloat16* _
       const float sg = sigmoid_f(g[j]);
       dg[j] = d[j] * u[j] * sg * (1.f + g[j] * (1.f - sg));
       du[j] = d[j] * g[j] * sg;
+      a[j] = g[j] * sg * u[j];
     }
     st_stream16(dgu + row * 2 * ff + (v << 3), pack8(dg));
     st_stream16(dgu + row * 2 * ff + ff + (v << 3), pack8(du));
+    if (act) st_stream16(act + row * ff + (v << 3), pack8(a));  // the forward product, recomputed for dW_down
   }
 }
 
@@ -116,13 +118,18 @@ extern "C" int b200ft_swiglu_fwd(const void* gate_up, void* act, int64_t rows, i
 
 extern "C" int b200ft_swiglu_bwd(const void* dact, const void* gate_up, void* dgate_up, int64_t rows, int d_ff,
                                  void* stream) {
+  return b200ft_swiglu_bwd_act(dact, gate_up, dgate_up, nullptr, rows, d_ff, stream);
+}
+
+extern "C" int b200ft_swiglu_bwd_act(const void* dact, const void* gate_up, void* dgate_up, void* act, int64_t rows,
+                                     int d_ff, void* stream) {
   B200FT_CHECK_ARG(dact && gate_up && dgate_up && rows > 0 && d_ff > 0 && d_ff % 8 == 0,
                    "swiglu_bwd: rows=%lld d_ff=%d", (long long)rows, d_ff);
   const int64_t total = rows * (d_ff / 8);
   int64_t want = (total + 255) / 256;
   int blocks = (int)(want > B200FT_NUM_SMS * 16 ? B200FT_NUM_SMS * 16 : want);
   swiglu_bwd_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)dact, (const __nv_bfloat16*)gate_up,
-                                                               (__nv_bfloat16*)dgate_up, rows, d_ff);
+                                                               (__nv_bfloat16*)dgate_up, (__nv_bfloat16*)act, rows, d_ff);
   B200FT_LAUNCH_CHECK();
   return 0;
 }

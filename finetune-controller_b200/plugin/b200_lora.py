@@ -27,7 +27,7 @@ class B200LoRAConfig(TrainingArguments):
     """Hyper-parameters of the B200-native LoRA fine-tune job (one type + default each)."""
 
     model: str = Field(default="gpt2-124m", description="Architecture: gpt2-124m | llama-3.2-1b | llama-3-8b (gpt2-tiny, llama-tiny for smoke runs)")
-    mode: str = Field(default="lora", description="lora: adapters on c_attn (GPT-2) or q_proj + v_proj (Llama); full fine-tune is not in this build")
+    mode: str = Field(default="lora", description="lora: adapters on c_attn (GPT-2) or q_proj + v_proj (Llama); full: every tensor trainable (Llama family; fp32 master + Adam moments, 8B fits one 180 GB B200)")
     lora_r: int = Field(default=8, description="LoRA rank (<= 16)")
     lora_alpha: float = Field(default=16.0, description="LoRA alpha; the branch is scaled by alpha / r")
     seq_len: int = Field(default=1024, description="Tokens per sequence")
@@ -43,7 +43,7 @@ class B200LoRAConfig(TrainingArguments):
     seed: int = Field(default=0, description="Seed for weight init and synthetic data")
     log_interval: int = Field(default=10, description="Steps between metric rows / log lines")
     save_interval: int = Field(default=0, description="Steps between resume points (state.pt); 0 = once per epoch")
-    save_model: bool = Field(default=True, description="Write adapter.pt + adapter_config.json at the end")
+    save_model: bool = Field(default=True, description="Write adapter.pt + adapter_config.json (lora) or model.pt + config.json (full) at the end")
     synthetic: bool = Field(default=True, description="Use synthetic token ids instead of the mounted dataset")
 
 

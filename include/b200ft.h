@@ -198,6 +198,10 @@ int b200ft_rope_inplace(void* x, int64_t ld, int64_t rows, int seq, int n_heads,
                         const float* cos_table, const float* sin_table, int backward, void* stream);
 int b200ft_swiglu_fwd(const void* gate_up, void* act, int64_t rows, int d_ff, void* stream);
 int b200ft_swiglu_bwd(const void* dact, const void* gate_up, void* dgate_up, int64_t rows, int d_ff, void* stream);
+/* same, and also rewrites act = silu(gate) * up [rows, d_ff] from gate_up (may be NULL): the full-parameter
+ * step does not keep the forward product and needs it again for the down-projection's weight gradient */
+int b200ft_swiglu_bwd_act(const void* dact, const void* gate_up, void* dgate_up, void* act, int64_t rows,
+                          int d_ff, void* stream);
 
 /* ---------------------------------------------------------------------------------------
  * Causal flash-attention forward on tcgen05 (oracle causal_attention()).

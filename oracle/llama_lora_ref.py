@@ -212,8 +212,7 @@ class OracleTrainer:
 class FullOracleTrainer:
     """Full-parameter fine-tune (BASELINE.json configs[4]): every tensor of `base` is trainable, no
     adapters; fwd + shifted CE + autograd bwd + torch.optim.AdamW(foreach=False, fused=False) with one
-    uniform weight decay over all tensors.  `world_grads` averages externally supplied per-rank
-    gradients in (data-parallel emulation, as in OracleTrainer of gpt2_lora_ref)."""
+    uniform weight decay over all tensors."""
 
     def __init__(self, cfg: LlamaConfig, opt: AdamWConfig, base: dict):
         self.cfg, self.opt_cfg = cfg, opt
@@ -230,15 +229,21 @@ class FullOracleTrainer:
         return float(loss.detach()), {k: t.grad.detach().clone() for k, t in self.trainable.items()}
 
     def step(self, ids, labels, world_grads: list | None = None) -> float:
-        loss, g = self.grads(ids, labels)
-        if world_grads is not None:
-            for k, t in self.trainable.items():
-                t.grad = sum(wg[k] for wg in world_grads) / len(world_grads)
+        """One optimizer step.  `world_grads` = [(ids, labels) per rank] emulates data parallelism: the
+        gradient is the mean of the per-rank gradients and the returned loss the mean of the per-rank
+        losses (same convention as gpt2_lora_ref.OracleTrainer.step)."""
+        batches = world_grads if world_grads is not None else [(ids, labels)]
+        losses, per_rank = [], []
+        for b_ids, b_labels in batches:
+            loss, g = self.grads(b_ids, b_labels)
+            losses.append(loss); per_rank.append(g)
+        for k, t in self.trainable.items():
+            t.grad = sum(g[k] for g in per_rank) / len(per_rank)
         if self.opt_cfg.max_grad_norm > 0:
             torch.nn.utils.clip_grad_norm_(list(self.trainable.values()), self.opt_cfg.max_grad_norm)
         self.last_grads = {k: t.grad.detach().clone() for k, t in self.trainable.items()}
         self.optim.step()
-        return loss
+        return sum(losses) / len(losses)
 
 
 def hf_crosscheck(cfg: LlamaConfig = LLAMA_TINY, batch: int = 2, seq: int = 24, seed: int = 0) -> dict:

@@ -76,6 +76,10 @@ def test_swiglu_fwd_bwd(ops, rows, ff):
     dgu = torch.empty_like(gud)
     ops.swiglu_bwd(dact.to(DEV, torch.bfloat16), gud, dgu)
     torch.testing.assert_close(dgu.cpu().float(), gur.grad, rtol=2 ** -6, atol=2e-3)
+    # the recompute form used by the full-parameter step: same gradient, plus the forward product again
+    dgu2, act2 = torch.empty_like(gud), torch.empty_like(act)
+    ops.swiglu_bwd(dact.to(DEV, torch.bfloat16), gud, dgu2, act=act2)
+    assert torch.equal(dgu2, dgu) and torch.equal(act2, act)
 
 
 def _engine(cfg, lora, opt, base, ad, batch, seq):

@@ -70,3 +70,31 @@ def test_entrypoint_llama_tiny(tmp_path):
     w = torch.load(d / "adapter.pt")
     assert w["l0.q_proj.lora_A"].shape == (16, 64) and w["l1.v_proj.lora_B"].shape == (32, 16)
     assert float(w["l0.v_proj.lora_B"].abs().max()) > 0.0       # PEFT's zero B has moved after 3 steps
+
+
+def test_entrypoint_full_parameter_mode_and_resume(tmp_path, capsys):
+    """--mode=full (BASELINE.json configs[4] on the tiny Llama): model.pt + config.json instead of adapter
+    files, loss goes down on a repeated batch schedule, and a restart resumes master weights + moments."""
+    from b200ft import train
+
+    def args(ckpt, steps):
+        return ["--model=llama-tiny", "--mode=full", "--seq_len=32", "--batch_size=2", "--epochs=1",
+                f"--steps_per_epoch={steps}", "--lr=0.003", "--log_interval=1", "--save_model", "--synthetic",
+                f"--dataset_path={tmp_path}", f"--checkpoint_path={ckpt}"]
+
+    a, b = tmp_path / "fa", tmp_path / "fb"
+    assert train.main(args(a, 6)) == 0
+    assert "mode=full" in capsys.readouterr().out.splitlines()[0]
+    for f in ("metrics.csv", "model.pt", "config.json", "state.pt"):
+        assert (a / f).exists(), f
+    assert not (a / "adapter.pt").exists()
+    cfg = __import__("json").load(open(a / "config.json"))
+    assert cfg["mode"] == "full" and cfg["n_layer"] == 2 and cfg["tie_embeddings"] is True
+    w = torch.load(a / "model.pt")
+    assert w["l1.down_proj.w"].shape == (64, 128) and w["embed"].shape == (503, 64) and w["norm.g"].dtype == torch.bfloat16
+    assert train.main(args(b, 3)) == 0
+    assert train.main(args(b, 6)) == 0
+    assert "resumed at step 3" in capsys.readouterr().out
+    wb = torch.load(b / "model.pt")
+    for k in w:
+        torch.testing.assert_close(wb[k].float(), w[k].float(), rtol=0, atol=2 ** -7 * 0.1)
