@@ -189,7 +189,13 @@ def run_ours(args) -> None:
     n_layer = params.MODELS[model].n_layer
     # LoRA gradients are a few MB: two buckets.  Full-parameter gradients are hundreds of MB per layer:
     # one bucket per layer, each reduced while the layers below it are still in backward
-    sync = ddp.BucketedGradSync(n_layer, n_buckets=n_layer if full else 2) if world > 1 else None
+    sync = None
+    if world > 1 and full:
+        k = args.nccl_ctas
+        sync = ddp.BucketedGradSync(n_layer, n_buckets=n_layer, group=ddp.overlap_group(k) if k > 0 else None,
+                                    reserve_ctas=k, use_tail_group=True)
+    elif world > 1:
+        sync = ddp.BucketedGradSync(n_layer, n_buckets=2)
     # random-init weights; B drawn at random (not PEFT's zero) so every gradient path carries data
     eng, dims = params.build_engine(model, lora, opt, batch=BATCH, seq=SEQ, device=dev, seed=0, world_size=world,
                                     grad_sync=sync, randomize_b=True, mode="full" if full else "lora")
@@ -349,6 +355,9 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--nccl-ctas", type=int, default=8,
+                    help="full-parameter workloads: CTAs of the overlapped all-reduce (and SMs x2 left free by the "
+                         "backward GEMMs); 0 = default communicator, no reservation")
     ap.add_argument("--detail", default="", help="write per-shape GEMM timings of the instrumented pass to this JSON file")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup

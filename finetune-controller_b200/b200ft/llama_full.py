@@ -47,6 +47,10 @@ class LlamaFullStep(StepHostMixin):
         self.B, self.T, self.M = batch, seq, batch * seq
         self.dev = torch.device(device)
         self.world, self.grad_sync, self.step_count = world_size, grad_sync, 0
+        # SMs left to the overlapped all-reduce in backward (ddp.overlap_group): the GEMM works on CTA
+        # pairs, so each reserved collective CTA may cost a whole TPC
+        reserve = getattr(grad_sync, "reserve_ctas", 0) if grad_sync is not None else 0
+        self.bwd_ctas = 0 if reserve <= 0 else max(2, ops.NUM_SMS - 2 * reserve)
         self.Nq, self.Nkv = dims.n_head * dims.d_head, dims.n_kv_head * dims.d_head
         self.Nqkv = self.Nq + 2 * self.Nkv
         self._layout()
@@ -261,36 +265,36 @@ class LlamaFullStep(StepHostMixin):
     @torch.no_grad()
     def backward(self) -> None:
         D, W, dW = self.dims, self.W, self.dW
-        L = D.n_layer
+        L, mc = D.n_layer, self.bwd_ctas
         self.Gn.zero_()
         dx, dx1, dx0 = self.dxs
         # lm_head: dW = dlogits^T . hf (both MN-major), dhf = dlogits . W_head (B MN-major)
-        ops.gemm(self.logits, self.hf, dW["head"], a_mn=True, b_mn=True)
-        ops.gemm(self.logits, W["head"], self.dln, b_mn=True)
+        ops.gemm(self.logits, self.hf, dW["head"], a_mn=True, b_mn=True, max_ctas=mc)
+        ops.gemm(self.logits, W["head"], self.dln, b_mn=True, max_ctas=mc)
         ops.rmsnorm_bwd_dgamma(self.dln, self.x[L], self.rsf, self.dgain_f)
         ops.rmsnorm_bwd_dx(self.dln, self.x[L], self.gain_f, self.rsf, dx)
         for l in range(L - 1, -1, -1):
             g_attn, g_mlp = self.gain[l]
             dg_attn, dg_mlp = self.dgain[l]
             # MLP branch (the SwiGLU product and h2 are recomputed, the former inside swiglu_bwd)
-            ops.gemm(dx, W[f"l{l}.down"], self.dact, b_mn=True)
+            ops.gemm(dx, W[f"l{l}.down"], self.dact, b_mn=True, max_ctas=mc)
             ops.swiglu_bwd(self.dact, self.gu[l], self.dgu, act=self.act)
-            ops.gemm(dx, self.act, dW[f"l{l}.down"], a_mn=True, b_mn=True)
+            ops.gemm(dx, self.act, dW[f"l{l}.down"], a_mn=True, b_mn=True, max_ctas=mc)
             ops.rmsnorm_fwd(self.x1[l], g_mlp, self.h, self.rs_tmp, D.rms_eps)
-            ops.gemm(self.dgu, self.h, dW[f"l{l}.gu"], a_mn=True, b_mn=True)
-            ops.gemm(self.dgu, W[f"l{l}.gu"], self.dln, b_mn=True)
+            ops.gemm(self.dgu, self.h, dW[f"l{l}.gu"], a_mn=True, b_mn=True, max_ctas=mc)
+            ops.gemm(self.dgu, W[f"l{l}.gu"], self.dln, b_mn=True, max_ctas=mc)
             ops.rmsnorm_bwd_dgamma(self.dln, self.x1[l], self.rs2[l], dg_mlp)
             ops.rmsnorm_bwd_dx(self.dln, self.x1[l], g_mlp, self.rs2[l], dx1, dres=dx)
             # attention branch
             a = self._attn_out(self.attn_saved[l][3])
-            ops.gemm(dx1, a, dW[f"l{l}.o"], a_mn=True, b_mn=True)
-            ops.gemm(dx1, W[f"l{l}.o"], self.da, b_mn=True)
+            ops.gemm(dx1, a, dW[f"l{l}.o"], a_mn=True, b_mn=True, max_ctas=mc)
+            ops.gemm(dx1, W[f"l{l}.o"], self.da, b_mn=True, max_ctas=mc)
             self._attn_bwd(l, self.da)
             ops.rope_inplace(self.dqkv, self.cos, self.sin, seq=self.T, n_heads=D.n_head + D.n_kv_head,
                              d_head=D.d_head, backward=True)
             ops.rmsnorm_fwd(self.x[l], g_attn, self.h, self.rs_tmp, D.rms_eps)
-            ops.gemm(self.dqkv, self.h, dW[f"l{l}.qkv"], a_mn=True, b_mn=True)
-            ops.gemm(self.dqkv, W[f"l{l}.qkv"], self.dln, b_mn=True)
+            ops.gemm(self.dqkv, self.h, dW[f"l{l}.qkv"], a_mn=True, b_mn=True, max_ctas=mc)
+            ops.gemm(self.dqkv, W[f"l{l}.qkv"], self.dln, b_mn=True, max_ctas=mc)
             ops.rmsnorm_bwd_dgamma(self.dln, self.x[l], self.rs1[l], dg_attn)
             ops.rmsnorm_bwd_dx(self.dln, self.x[l], g_attn, self.rs1[l], dx0, dres=dx1)
             dx, dx0 = dx0, dx

@@ -20,6 +20,7 @@ LAUNCHES = 0
 # every wrapper brackets its launch with CUDA events on the launching stream and appends
 # (start, end, algorithmic_work) under its class name.  Off (None) in normal operation.
 PROFILE = None
+NUM_SMS = 148  # B200; mirrors B200FT_NUM_SMS of the library
 
 
 class _timed:

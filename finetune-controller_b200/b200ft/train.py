@@ -125,7 +125,12 @@ def worker(args, rank: int, world: int, local: int) -> None:
     n_layer = params.MODELS[args.model].n_layer
     full = args.mode == "full"
     # full-parameter gradients are hundreds of MB per layer: one all-reduce bucket per layer
-    sync = ddp.BucketedGradSync(n_layer, n_buckets=n_layer if full else 2) if world > 1 else None
+    sync = None
+    if world > 1 and full:
+        sync = ddp.BucketedGradSync(n_layer, n_buckets=n_layer, group=ddp.overlap_group(8), reserve_ctas=8,
+                                    use_tail_group=True)
+    elif world > 1:
+        sync = ddp.BucketedGradSync(n_layer, n_buckets=2)
     # random init, identical on every rank (same seed): the image has no network for checkpoints
     eng, dims = params.build_engine(args.model, lora, opt, batch=args.batch_size, seq=args.seq_len, device=dev,
                                     seed=args.seed, world_size=world, grad_sync=sync, mode=args.mode)
