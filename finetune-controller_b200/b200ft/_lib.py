@@ -80,6 +80,8 @@ SIGNATURES = {
     "b200ft_swiglu_bwd_act": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_void_p]),
     "b200ft_attn_fwd": (c_int, [c_void_p, c_int64, c_int, c_int, c_int, c_void_p, c_int64, c_void_p, c_int, c_int,
                                 c_int, c_int, c_int, c_float, c_void_p]),
+    "b200ft_attn_bwd": (c_int, [c_void_p, c_int64, c_int, c_int, c_int, c_void_p, c_int64, c_void_p, c_int64, c_void_p,
+                                c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_int, c_int, c_float, c_void_p]),
     "b200ft_embed_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_void_p]),
     "b200ft_rmsnorm_bwd_dgamma": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_void_p]),
     "b200ft_embed_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p]),

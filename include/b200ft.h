@@ -216,6 +216,19 @@ int b200ft_attn_fwd(const void* qkv, int64_t ld, int q_off, int k_off, int v_off
                     float* lse2, int batch, int seq, int n_head, int n_kv_head, int d_head, float scale,
                     void* stream);
 
+/* Causal flash-attention backward on tcgen05, the counterpart of b200ft_attn_fwd (same layout
+ * conventions; oracle: autograd of causal_attention()).  out / dout [batch*seq, ld_*] carry head h at
+ * column h*d_head; lse2 is the forward's output; delta [batch*n_head, seq] is scratch the call fills
+ * (row sums of dout*out).  dqkv [batch*seq, ld_dqkv] receives dq of head h at q_off + h*d_head and
+ * dk / dv of kv head g at k_off / v_off + g*d_head (summed over the q heads of the group), i.e. the
+ * column layout of the fused projection output itself; every element of those column ranges is
+ * written.  d_head must be 64; other sizes return B200FT_ERR_UNSUPPORTED.  Three launches (delta,
+ * dk|dv, dq); no atomics, bit-reproducible. */
+int b200ft_attn_bwd(const void* qkv, int64_t ld, int q_off, int k_off, int v_off, const void* out,
+                    int64_t ld_out, const void* dout, int64_t ld_dout, const float* lse2, float* delta,
+                    void* dqkv, int64_t ld_dqkv, int batch, int seq, int n_head, int n_kv_head, int d_head,
+                    float scale, void* stream);
+
 /* Token + position embedding (oracle forward(): F.embedding(ids,wte)+F.embedding(pos,wpe)).
  * wte bf16 [vocab, d], wpe bf16 [ctx, d], x bf16 [rows, d], position = row % seq.  wpe may be NULL
  * (Llama: rotary positions, no learned table). */
