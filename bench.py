@@ -198,7 +198,8 @@ def run_ours(args) -> None:
         sync = ddp.BucketedGradSync(n_layer, n_buckets=2)
     # random-init weights; B drawn at random (not PEFT's zero) so every gradient path carries data
     eng, dims = params.build_engine(model, lora, opt, batch=BATCH, seq=SEQ, device=dev, seed=0, world_size=world,
-                                    grad_sync=sync, randomize_b=True, mode="full" if full else "lora")
+                                    grad_sync=sync, randomize_b=True, mode="full" if full else "lora",
+                                    attention=args.attention)
     g = torch.Generator().manual_seed(1234 + rank)
     n_sets = 4
     host = [torch.randint(0, dims.vocab, (BATCH, SEQ), generator=g, dtype=torch.int64).pin_memory()
@@ -315,7 +316,8 @@ def run_ours(args) -> None:
                    "global_batch": BATCH * world, "seq_len": SEQ, "parallelism": f"dp{world}",
                    "l2": "per-step working set (GBs of activations and logits) is far larger than the "
                          "126 MB L2; no explicit flush",
-                   "attention": "torch SDPA (library) this round; every other op is this repo's CUDA"},
+                   "attention": ("torch SDPA (library); every other op is this repo's CUDA" if args.attention == "sdpa"
+                                 else "this repo's tcgen05 flash-attention forward + backward (no library kernel in the step)")},
         "e2e": {"value": tokens / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e / args.steps,
                 "h2d_bytes_per_step": 2 * BATCH * SEQ * 8, "d2h_bytes_per_step": 4, "last_loss": losses[-1]},
         "gpu_launches": launches,
@@ -358,6 +360,9 @@ def main():
     ap.add_argument("--nccl-ctas", type=int, default=8,
                     help="full-parameter workloads: CTAs of the overlapped all-reduce (and SMs x2 left free by the "
                          "backward GEMMs); 0 = default communicator, no reservation")
+    ap.add_argument("--attention", default="sdpa", choices=["sdpa", "own"],
+                    help="sdpa: torch SDPA (cuDNN, library; faster today); own: this repo's tcgen05 attention kernels "
+                         "(d_head 64 models), i.e. a step with no library kernel in it")
     ap.add_argument("--detail", default="", help="write per-shape GEMM timings of the instrumented pass to this JSON file")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup

@@ -20,6 +20,7 @@ import torch
 import torch.nn.functional as F
 
 from . import ops
+from .attention import OwnAttentionMixin
 from ._lib import EPI_DGELU, EPI_GELU, EPI_NONE, EPI_RESIDUAL
 
 R_PAD = 16  # adapter rank padded to one UMMA K step (16 bf16)
@@ -96,13 +97,15 @@ class StepHostMixin:
         self._refresh_shadows(cast=True)
 
 
-class GPT2LoRAStep(StepHostMixin):
+class GPT2LoRAStep(StepHostMixin, OwnAttentionMixin):
     """Holds device state for one rank and runs fwd + loss + bwd + AdamW per `step()`."""
 
     def __init__(self, dims: GPT2Dims, lora: LoRASpec, opt: OptSpec, base: dict, adapters: dict, *,
-                 batch: int, seq: int, device="cuda:0", world_size: int = 1, grad_sync=None):
+                 batch: int, seq: int, device="cuda:0", world_size: int = 1, grad_sync=None, attention: str = "sdpa"):
         if not torch.cuda.is_available():
             raise RuntimeError("GPT2LoRAStep needs a CUDA device: there is no CPU path")
+        assert attention in ("sdpa", "own")
+        self.attention = attention
         assert lora.r <= R_PAD and seq <= dims.ctx
         assert dims.d_model % 8 == 0 and dims.d_ff % 8 == 0
         self.dims, self.lora, self.opt = dims, lora, opt
@@ -230,9 +233,13 @@ class GPT2LoRAStep(StepHostMixin):
         self.da = torch.empty(M, d, **bf)
         self.dU = torch.empty(M, R_PAD, **bf)
         self.attn_saved = [None] * L
+        if self.attention == "own":
+            self._own_attn_setup(D.n_head, D.n_head, d // D.n_head, L)
 
-    # ------------------------------------------------------------------ attention (library, this round)
+    # ------------------------------------------------------------------ attention: torch SDPA (library) or own kernels
     def _attn_fwd(self, l: int) -> torch.Tensor:
+        if self.attention == "own":
+            return self._own_attn_fwd(l)
         B, T, H = self.B, self.T, self.dims.n_head
         dh = self.dims.d_model // H
         v5 = self.qkv[l].view(B, T, 3, H, dh)
@@ -248,7 +255,10 @@ class GPT2LoRAStep(StepHostMixin):
     def _attn_bwd(self, l: int, da: torch.Tensor):
         """Returns (dq, dk, dv), each a [tokens, d_model] matrix.  The library hands them back as
         three separate dense buffers; they are consumed as separate K segments downstream, so
-        nothing is copied into an interleaved [tokens, 3*d_model] layout."""
+        nothing is copied into an interleaved [tokens, 3*d_model] layout.  (The own kernels write one
+        [tokens, 3*d_model] buffer; its column blocks are returned.)"""
+        if self.attention == "own":
+            return self._own_attn_bwd(l, da)
         B, T, H = self.B, self.T, self.dims.n_head
         dh = self.dims.d_model // H
         q, k, v, o = self.attn_saved[l]

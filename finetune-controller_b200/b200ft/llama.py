@@ -18,6 +18,7 @@ import torch.nn.functional as F
 
 from . import ops
 from ._lib import EPI_NONE, EPI_RESIDUAL
+from .attention import OwnAttentionMixin
 from .gpt2 import LoRASpec, OptSpec, R_PAD, StepHostMixin
 
 A_BLK = 2 * R_PAD  # adapter rows per layer in the flat buffers: q adapter 0..15, v adapter 16..31
@@ -72,13 +73,15 @@ def rope_tables(dims: LlamaDims, seq: int, device) -> tuple[torch.Tensor, torch.
     return ang.cos().contiguous().to(device), ang.sin().contiguous().to(device)
 
 
-class LlamaLoRAStep(StepHostMixin):
+class LlamaLoRAStep(StepHostMixin, OwnAttentionMixin):
     """Device state of one rank; `step()` = fwd + loss + bwd + AdamW on the q/v adapters."""
 
     def __init__(self, dims: LlamaDims, lora: LoRASpec, opt: OptSpec, base: dict, adapters: dict, *,
-                 batch: int, seq: int, device="cuda:0", world_size: int = 1, grad_sync=None):
+                 batch: int, seq: int, device="cuda:0", world_size: int = 1, grad_sync=None, attention: str = "sdpa"):
         if not torch.cuda.is_available():
             raise RuntimeError("LlamaLoRAStep needs a CUDA device: there is no CPU path")
+        assert attention in ("sdpa", "own")
+        self.attention = attention
         assert lora.r <= R_PAD and dims.d_head % 16 == 0 and dims.d_model % 8 == 0 and dims.d_ff % 8 == 0
         self.dims, self.lora, self.opt = dims, lora, opt
         self.B, self.T, self.M = batch, seq, batch * seq
@@ -216,9 +219,13 @@ class LlamaLoRAStep(StepHostMixin):
         self.dln, self.da = torch.empty(M, d, **bf), torch.empty(M, self.Nq, **bf)
         self.dU = torch.empty(M, A_BLK, **bf)
         self.attn_saved = [None] * L
+        if self.attention == "own":
+            self._own_attn_setup(D.n_head, D.n_kv_head, D.d_head, L)
 
-    # ------------------------------------------------------------------ attention (library, this round)
+    # ------------------------------------------------------------------ attention: torch SDPA (library) or own kernels
     def _attn_fwd(self, l: int) -> torch.Tensor:
+        if self.attention == "own":
+            return self._own_attn_fwd(l)
         B, T, D = self.B, self.T, self.dims
         H, KV, dh = D.n_head, D.n_kv_head, D.d_head
         buf = self.qkv[l]
@@ -234,6 +241,8 @@ class LlamaLoRAStep(StepHostMixin):
         return a.view(self.M, self.Nq)
 
     def _attn_bwd(self, l: int, da: torch.Tensor):
+        if self.attention == "own":
+            return self._own_attn_bwd(l, da)
         B, T, D = self.B, self.T, self.dims
         q, k, v, o = self.attn_saved[l]
         go = da.view(B, T, D.n_head, D.d_head).permute(0, 2, 1, 3)

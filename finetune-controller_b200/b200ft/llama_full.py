@@ -24,6 +24,7 @@ import torch
 import torch.nn.functional as F
 
 from . import ops
+from .attention import OwnAttentionMixin
 from ._lib import EPI_RESIDUAL
 from .gpt2 import OptSpec, StepHostMixin
 from .llama import LlamaDims, rope_tables
@@ -31,7 +32,7 @@ from .llama import LlamaDims, rope_tables
 _MATS = ("qkv", "o", "gu", "down")
 
 
-class LlamaFullStep(StepHostMixin):
+class LlamaFullStep(StepHostMixin, OwnAttentionMixin):
     """Device state of one rank; `step()` = fwd + loss + bwd (dX and dW) + AdamW on every tensor.
 
     `base` is a dict in the oracle's naming (oracle/llama_lora_ref.py init_base_params) or None, in
@@ -39,9 +40,12 @@ class LlamaFullStep(StepHostMixin):
     an 8B model never exists twice in memory."""
 
     def __init__(self, dims: LlamaDims, opt: OptSpec, base: dict | None, *, batch: int, seq: int,
-                 device="cuda:0", world_size: int = 1, grad_sync=None, seed: int = 0, init_std: float = 0.02):
+                 device="cuda:0", world_size: int = 1, grad_sync=None, seed: int = 0, init_std: float = 0.02,
+                 attention: str = "sdpa"):
         if not torch.cuda.is_available():
             raise RuntimeError("LlamaFullStep needs a CUDA device: there is no CPU path")
+        assert attention in ("sdpa", "own")
+        self.attention = attention
         assert dims.d_head % 16 == 0 and dims.d_model % 8 == 0 and dims.d_ff % 8 == 0
         self.dims, self.opt, self.lora = dims, opt, None
         self.B, self.T, self.M = batch, seq, batch * seq
@@ -206,9 +210,13 @@ class LlamaFullStep(StepHostMixin):
         self.dln, self.da = torch.empty(M, d, **bf), torch.empty(M, self.Nq, **bf)
         self.dqkv = torch.empty(M, self.Nqkv, **bf)
         self.attn_saved = [None] * L
+        if self.attention == "own":
+            self._own_attn_setup(D.n_head, D.n_kv_head, D.d_head, L)
 
-    # ------------------------------------------------------------------ attention (library, this round)
+    # ------------------------------------------------------------------ attention: torch SDPA (library) or own kernels
     def _attn_fwd(self, l: int) -> torch.Tensor:
+        if self.attention == "own":
+            return self._own_attn_fwd(l)
         B, T, D = self.B, self.T, self.dims
         H, KV, dh = D.n_head, D.n_kv_head, D.d_head
         buf = self.qkv[l]
@@ -228,6 +236,9 @@ class LlamaFullStep(StepHostMixin):
 
     def _attn_bwd(self, l: int, da: torch.Tensor) -> None:
         """dq | dk | dv land side by side in self.dqkv (the layout of the fused projection's output)."""
+        if self.attention == "own":
+            self._own_attn_bwd(l, da)
+            return
         B, T, D = self.B, self.T, self.dims
         q, k, v, o = self.attn_saved[l]
         go = da.view(B, T, D.n_head, D.d_head).permute(0, 2, 1, 3)
@@ -286,7 +297,7 @@ class LlamaFullStep(StepHostMixin):
             ops.rmsnorm_bwd_dgamma(self.dln, self.x1[l], self.rs2[l], dg_mlp)
             ops.rmsnorm_bwd_dx(self.dln, self.x1[l], g_mlp, self.rs2[l], dx1, dres=dx)
             # attention branch
-            a = self._attn_out(self.attn_saved[l][3])
+            a = self.att_out[l] if self.attention == "own" else self._attn_out(self.attn_saved[l][3])
             ops.gemm(dx1, a, dW[f"l{l}.o"], a_mn=True, b_mn=True, max_ctas=mc)
             ops.gemm(dx1, W[f"l{l}.o"], self.da, b_mn=True, max_ctas=mc)
             self._attn_bwd(l, self.da)

@@ -96,7 +96,7 @@ def init_lora_llama(dims: LlamaDims, lora: LoRASpec, seed: int, device="cpu") ->
 
 
 def build_engine(model: str, lora: LoRASpec, opt, *, batch: int, seq: int, device, seed: int = 0, world_size: int = 1,
-                 grad_sync=None, randomize_b: bool = False, mode: str = "lora"):
+                 grad_sync=None, randomize_b: bool = False, mode: str = "lora", attention: str = "sdpa"):
     """Random-init model (+ adapters) of the named architecture on `device`, wrapped in its step engine.
     mode "lora" trains adapters on a frozen base; mode "full" (Llama family) trains every tensor."""
     from . import gpt2, llama
@@ -106,7 +106,7 @@ def build_engine(model: str, lora: LoRASpec, opt, *, batch: int, seq: int, devic
             raise ValueError("mode=full is implemented for the Llama family (BASELINE.json configs[4])")
         from . import llama_full
         return llama_full.LlamaFullStep(dims, opt, None, batch=batch, seq=seq, device=device, world_size=world_size,
-                                        grad_sync=grad_sync, seed=seed), dims
+                                        grad_sync=grad_sync, seed=seed, attention=attention), dims
     if mode != "lora":
         raise ValueError(f"unknown mode {mode!r}")
     if is_llama(dims):
@@ -121,4 +121,4 @@ def build_engine(model: str, lora: LoRASpec, opt, *, batch: int, seq: int, devic
             if k.endswith("lora_B"):
                 ad[k].normal_(0.0, 0.02, generator=gen)
     return cls(dims, lora, opt, base, ad, batch=batch, seq=seq, device=device, world_size=world_size,
-               grad_sync=grad_sync), dims
+               grad_sync=grad_sync, attention=attention), dims

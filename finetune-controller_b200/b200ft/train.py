@@ -33,6 +33,8 @@ def build_parser() -> argparse.ArgumentParser:
     ap.add_argument("--model", default="gpt2-124m")
     ap.add_argument("--mode", default="lora", choices=["lora", "full"],
                     help="lora: adapters on a frozen base; full: every tensor trainable (Llama family)")
+    ap.add_argument("--attention", default="sdpa", choices=["sdpa", "own"],
+                    help="sdpa: torch SDPA / cuDNN; own: this library's tcgen05 attention (d_head 64 models)")
     ap.add_argument("--lora_r", type=int, default=8)
     ap.add_argument("--lora_alpha", type=float, default=16.0)
     ap.add_argument("--seq_len", type=int, default=1024)
@@ -133,7 +135,8 @@ def worker(args, rank: int, world: int, local: int) -> None:
         sync = ddp.BucketedGradSync(n_layer, n_buckets=2)
     # random init, identical on every rank (same seed): the image has no network for checkpoints
     eng, dims = params.build_engine(args.model, lora, opt, batch=args.batch_size, seq=args.seq_len, device=dev,
-                                    seed=args.seed, world_size=world, grad_sync=sync, mode=args.mode)
+                                    seed=args.seed, world_size=world, grad_sync=sync, mode=args.mode,
+                                    attention=args.attention)
     targets = ["q_proj", "v_proj"] if params.is_llama(dims) else ["c_attn"]
     stream = None if args.synthetic else load_token_stream(args.dataset_path)
     B, T = args.batch_size, args.seq_len

@@ -73,11 +73,11 @@ def _engine(cfg, opt, base, batch, seq, **kw):
                                                        opt.max_grad_norm), base, batch=batch, seq=seq, device=DEV, **kw)
 
 
-def _run_parity(cfg, batch, seq, steps, max_grad_norm=0.0):
+def _run_parity(cfg, batch, seq, steps, max_grad_norm=0.0, **engine_kw):
     opt = AdamWConfig(lr=1e-3, max_grad_norm=max_grad_norm)
     base = ref.init_base_params(cfg, seed=0, randomize_all=True)
     oracle = ref.FullOracleTrainer(cfg, opt, base)
-    eng = _engine(cfg, opt, base, batch, seq)
+    eng = _engine(cfg, opt, base, batch, seq, **engine_kw)
     for s in range(steps):
         ids, labels = ref.synthetic_batch(cfg, batch, seq, seed=1234 + s)
         l_ref = oracle.step(ids, labels)
@@ -119,6 +119,12 @@ def test_full_ft_real_width_pair_kernels():
     cfg = ref.LlamaConfig(n_layer=2, d_model=1024, n_head=16, n_kv_head=4, d_ff=2816, vocab=4000, ctx=512,
                           rope_theta=500000.0, rope_llama3=True, tie_embeddings=False)
     _run_parity(cfg, batch=2, seq=512, steps=1)
+
+
+def test_full_ft_with_own_attention_kernels():
+    cfg = ref.LlamaConfig(n_layer=2, d_model=256, n_head=4, n_kv_head=2, d_ff=512, vocab=1000, ctx=512,
+                          rope_theta=10000.0, rope_llama3=False, tie_embeddings=True)
+    _run_parity(cfg, batch=2, seq=160, steps=2, attention="own")
 
 
 def test_full_ft_in_place_init_and_state_roundtrip():

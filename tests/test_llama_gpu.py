@@ -82,14 +82,14 @@ def test_swiglu_fwd_bwd(ops, rows, ff):
     assert torch.equal(dgu2, dgu) and torch.equal(act2, act)
 
 
-def _engine(cfg, lora, opt, base, ad, batch, seq):
+def _engine(cfg, lora, opt, base, ad, batch, seq, **kw):
     from b200ft import gpt2, llama
     dims = llama.LlamaDims(cfg.n_layer, cfg.d_model, cfg.n_head, cfg.n_kv_head, cfg.d_ff, cfg.vocab, cfg.ctx,
                            cfg.rms_eps, cfg.rope_theta, cfg.rope_llama3, cfg.rope_factor, cfg.rope_low_freq_factor,
                            cfg.rope_high_freq_factor, cfg.rope_original_ctx, cfg.tie_embeddings, cfg.d_head_override)
     return llama.LlamaLoRAStep(dims, gpt2.LoRASpec(lora.r, lora.alpha),
                                gpt2.OptSpec(opt.lr, opt.beta1, opt.beta2, opt.eps, opt.weight_decay, opt.max_grad_norm),
-                               base, ad, batch=batch, seq=seq, device=DEV)
+                               base, ad, batch=batch, seq=seq, device=DEV, **kw)
 
 
 def _cos(a, b):
@@ -97,13 +97,13 @@ def _cos(a, b):
     return float((a @ b) / (a.norm() * b.norm() + 1e-30))
 
 
-def _parity(cfg, batch, seq, r, steps):
+def _parity(cfg, batch, seq, r, steps, **kw):
     lora = ref.LoRAConfig(r=r, alpha=2.0 * r)
     opt = AdamWConfig(lr=1e-3)
     base = ref.init_base_params(cfg, seed=0, randomize_all=True)
     ad = ref.init_lora_params(cfg, lora, seed=1, b_init="normal")
     oracle = ref.OracleTrainer(cfg, lora, opt, base, ad)
-    eng = _engine(cfg, lora, opt, base, ad, batch, seq)
+    eng = _engine(cfg, lora, opt, base, ad, batch, seq, **kw)
     for s in range(steps):
         ids, labels = ref.synthetic_batch(cfg, batch, seq, seed=1234 + s)
         l_ref = oracle.step(ids, labels)
@@ -132,3 +132,15 @@ def test_llama_one_layer_real_width():
     # Llama-3.2-1B width / heads / GQA ratio / llama3 rope, one layer, small vocab to keep the CPU oracle quick
     cfg = ref.LlamaConfig(n_layer=1, d_model=2048, n_head=32, n_kv_head=8, d_ff=8192, vocab=4099, ctx=131072)
     _parity(cfg, batch=1, seq=256, r=16, steps=2)
+
+
+def test_llama_real_width_with_own_attention_kernels():
+    """attention="own" at Llama-3.2-1B's head geometry (32 q heads over 8 kv heads of 64): the step with no
+    library kernel in it."""
+    cfg = ref.LlamaConfig(n_layer=1, d_model=2048, n_head=32, n_kv_head=8, d_ff=8192, vocab=4099, ctx=131072)
+    _parity(cfg, batch=1, seq=256, r=16, steps=2, attention="own")
+
+
+def test_own_attention_rejects_other_head_sizes():
+    with pytest.raises(ValueError):
+        _parity(ref.LLAMA_TINY, batch=2, seq=32, r=16, steps=1, attention="own")   # d_head 16

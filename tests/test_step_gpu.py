@@ -36,13 +36,13 @@ def _rel_l2(a, b):
     return float((a.double() - b.double()).norm() / (b.double().norm() + 1e-30))
 
 
-def _run_parity(cfg, batch, seq, r, steps, max_grad_norm=0.0, b_init="normal"):
+def _run_parity(cfg, batch, seq, r, steps, max_grad_norm=0.0, b_init="normal", **engine_kw):
     lora = ref.LoRAConfig(r=r, alpha=2.0 * r)
     opt = ref.AdamWConfig(lr=1e-3, max_grad_norm=max_grad_norm)
     base = ref.init_base_params(cfg, seed=0, randomize_all=True)
     ad = ref.init_lora_params(cfg, lora, seed=1, b_init=b_init)
     oracle = ref.OracleTrainer(cfg, lora, opt, base, ad)
-    eng = _engine(cfg, lora, opt, base, ad, batch, seq)
+    eng = _engine(cfg, lora, opt, base, ad, batch, seq, **engine_kw)
     ad0 = {k: v.clone() for k, v in ad.items()}
     for s in range(steps):
         ids, labels = ref.synthetic_batch(cfg, batch, seq, seed=1234 + s)
@@ -98,6 +98,13 @@ def test_full_gpt2_124m_at_config_c1_one_step():
     GPU against the oracle on the host cores (the configuration the CPU baseline is timed at)."""
     eng, oracle = _run_parity(ref.GPT2_124M, batch=8, seq=512, r=8, steps=1)
     assert eng.M == 4096
+
+
+def test_step_with_own_attention_kernels():
+    """attention="own": the whole step without a library kernel (tcgen05 flash-attention forward and
+    backward of this repo, d_head 64), same tolerances.  T = 200 is ragged against the 128-row tiles."""
+    cfg = ref.GPT2Config(n_layer=2, d_model=256, n_head=4, d_ff=512, vocab=1000, ctx=256)
+    _run_parity(cfg, batch=2, seq=200, r=8, steps=2, attention="own")
 
 
 def test_golden_fixture():

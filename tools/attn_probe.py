@@ -31,3 +31,16 @@ for (B, T, H, KV) in SHAPES:
     o_lib = F.scaled_dot_product_attention(q, k, v, is_causal=True, enable_gqa=(H != KV)).permute(0, 2, 1, 3).reshape(B * T, H * dh)
     err = (out.float() - o_lib.float()).abs().max().item()
     print(f"B={B} T={T} H={H} KV={KV}: own {us:8.1f} us ({flops/us/1e6:6.0f} TF)   SDPA {us_lib:8.1f} us ({flops/us_lib/1e6:6.0f} TF)   max|diff| {err:.4f}")
+    # ---- backward: own (delta + dk|dv + dq kernels) vs SDPA's autograd (cuDNN) ----
+    dout = torch.randn(B * T, H * dh, device=dev).to(torch.bfloat16)
+    dqkv = torch.empty(B * T, ld, dtype=torch.bfloat16, device=dev)
+    delta = torch.empty(B * H, T, device=dev)
+    kw = dict(batch=B, seq=T, n_head=H, n_kv_head=KV, d_head=dh, q_off=0, k_off=H * dh, v_off=(H + KV) * dh,
+              scale=1 / math.sqrt(dh))
+    us_b = timeit(lambda: ops.attn_bwd(qkv, out, dout, lse, delta, dqkv, **kw))
+    qg, kg, vg = (t.detach().requires_grad_(True) for t in (q, k, v))
+    og = F.scaled_dot_product_attention(qg, kg, vg, is_causal=True, enable_gqa=(H != KV))
+    go = dout.view(B, T, H, dh).permute(0, 2, 1, 3)
+    us_bl = timeit(lambda: torch.autograd.grad(og, (qg, kg, vg), go, retain_graph=True))
+    fb = 2.5 * flops
+    print(f"      backward: own {us_b:8.1f} us ({fb/us_b/1e6:6.0f} TF)   SDPA {us_bl:8.1f} us ({fb/us_bl/1e6:6.0f} TF)")
