@@ -3,18 +3,20 @@
 // per-row log-sum-exp, and writes dq | dk | dv into a buffer with the projection's own column layout.
 //
 // Three launches:
-//   delta     D[row] = sum_d do[row,d] * o[row,d]                              (one warp per token and head)
+//   delta     D[row] = sum_d do[row,d] * o[row,d]                              (one warp per token)
 //   MODE 0    one CTA per (kv tile j, batch, kv head): K_j, V_j resident; streams (Q_i, dO_i) over the q heads
 //             of the group and the q tiles i >= j; dV_j += P^T dO_i and dK_j += dS^T Q_i accumulate in TMEM
 //   MODE 1    one CTA per (q tile i, batch, head): Q_i, dO_i resident; streams (K_j, V_j), j <= i;
 //             dQ_i += dS K_j accumulates in TMEM
 // Both modes recompute S = Q K^T and dP = dO V^T per tile pair on the tensor core (no atomics, no fp32 dQ
 // buffer; 7 instead of 5 tile GEMMs).  Per pair: warps 4-7 (one thread per query row) read S and dP from
-// TMEM, form P = exp2(S*scale*log2e - lse2) and dS = P * (dP - D) * scale, and write them as bf16 into
+// TMEM, form P = exp2(S*scale*log2e - lse2) and dS' = P * (dP - D) (the softmax scale multiplies the dK / dQ
+// accumulators once, at the end), and write them as bf16 into
 // 128B-swizzled shared tiles [q rows][kv columns] — the byte layout TMA would produce — which the second
 // group of UMMAs consumes MN-major (P^T, dS^T: reduction over q) or K-major (dS: reduction over kv).
 // Q, dO, K, V tiles are used in both roles too: K-major for S / dP, MN-major as the B operand of the
-// gradient GEMMs.  256 threads: warp 0 TMA, warp 1 MMA issue, warp 2 TMEM allocation, warps 4-7 softmax.
+// gradient GEMMs.  384 threads: warp 0 TMA, warp 1 MMA issue, warp 2 TMEM allocation, warps 4-11 softmax / dS
+// (two per TMEM lane quarter, each owning one 64-key half of the tile).
 #include <cuda.h>
 #include <mutex>
 #include "common.cuh"
@@ -24,16 +26,17 @@ namespace {
 
 constexpr int kDH = 64;
 constexpr int kB = 128;                       // tile edge in queries and in keys
-constexpr int kThreads = 256;
+constexpr int kThreads = 384;
 constexpr int kTile = kB * kDH * 2;           // 16 KB: one Q / dO / K / V tile
 constexpr int kPTile = kB * kB * 2;           // 32 KB: P or dS, two 64-column chunks of 16 KB
 constexpr int kOffF = 0;                      // resident pair
-constexpr int kOffS = 2 * kTile;              // stream ring: 2 stages x (tile0, tile1)
-constexpr int kOffP = kOffS + 4 * kTile;
+constexpr int kRing = 3;                      // stream ring: pair g feeds its gradient UMMAs while g+1 feeds dP and g+2 feeds S
+constexpr int kOffS = 2 * kTile;              // ring stages of (tile0, tile1)
+constexpr int kOffP = kOffS + kRing * 2 * kTile;
 constexpr int kOffDS = kOffP + kPTile;
-constexpr int kOffBar = kOffDS + kPTile;      // 160 KB
+constexpr int kOffBar = kOffDS + kPTile;      // 192 KB
 constexpr int kSmemBytes = kOffBar + 256;
-constexpr uint32_t kColS = 0, kColDP = 128, kColAcc0 = 256, kColAcc1 = 320;
+constexpr uint32_t kColS = 0, kColDP = 256, kColAcc0 = 384, kColAcc1 = 448;   // S is double-buffered (+128)
 constexpr long long kWaitLimit = 4000000000ll;
 
 struct BwdParams {
@@ -124,24 +127,63 @@ __device__ __forceinline__ uint32_t idesc(int n, int a_mn, int b_mn) {
 }
 
 // ------------------------------------------------------------------------------------------------
-// D[bh, t] = sum_d do[t, h*64 + d] * o[t, h*64 + d]; one warp per (token, head)
+// D[bh, t] = sum_d do[t, h*64 + d] * o[t, h*64 + d].  One warp per token: lanes walk the row in 16-byte units
+// (8 units = one head), partial dot products meet across the 8 lanes of a head by shuffle.
 __global__ void __launch_bounds__(256)
 attn_delta_kernel(const __nv_bfloat16* __restrict__ o, int64_t ld_o, const __nv_bfloat16* __restrict__ dout,
                   int64_t ld_do, float* __restrict__ delta, int batch, int seq, int n_head) {
-  const int64_t w = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
-  const int64_t total = (int64_t)batch * seq * n_head;
-  if (w >= total) return;
+  const int64_t tok = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);   // b * seq + t
+  if (tok >= (int64_t)batch * seq) return;
   const int lane = threadIdx.x & 31;
-  const int h = (int)(w % n_head);
-  const int64_t tok = w / n_head;           // b * seq + t
   const int b = (int)(tok / seq), t = (int)(tok % seq);
-  const float2 a = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(o + tok * ld_o + h * kDH + 2 * lane));
-  const float2 g = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(dout + tok * ld_do + h * kDH + 2 * lane));
-  const float s = warp_sum(a.x * g.x + a.y * g.y);
-  if (lane == 0) delta[((int64_t)b * n_head + h) * seq + t] = s;
+  const int units = n_head * (kDH / 8);
+  for (int u0 = 0; u0 < units; u0 += 32) {       // 32 units = 4 heads per pass; all lanes stay in the shuffles
+    const int u = u0 + lane;
+    float acc = 0.f;
+    if (u < units) {
+      float a[8], g[8];
+      unpack8(ld_stream16(o + tok * ld_o + 8 * u), a);
+      unpack8(ld_stream16(dout + tok * ld_do + 8 * u), g);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc = fmaf(a[j], g[j], acc);
+    }
+    acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+    acc += __shfl_xor_sync(0xffffffffu, acc, 2);
+    acc += __shfl_xor_sync(0xffffffffu, acc, 4);
+    if (u < units && (lane & 7) == 0) delta[((int64_t)b * n_head + (u >> 3)) * seq + t] = acc;
+  }
 }
 
 // ------------------------------------------------------------------------------------------------
+// Work item of a CTA.  MODE 0: (kv tile ascending, batch, kv head); MODE 1: (q tile descending, batch, head):
+// heaviest first.  Every warp role walks the same item sequence w = blockIdx.x, += gridDim.x.
+struct Item {
+  int fixed_tile, b, hx, hk, per_head, n_iter;
+};
+template <int MODE>
+__device__ __forceinline__ Item decode_item(const BwdParams& p, int w, int G) {
+  Item it;
+  const int heads = MODE == 0 ? p.n_kv_head : p.n_head;
+  const int per_tile = p.batch * heads;
+  const int tile_ord = w / per_tile, rest = w % per_tile;
+  it.fixed_tile = MODE == 0 ? tile_ord : p.n_tiles - 1 - tile_ord;
+  it.b = rest / heads;
+  it.hx = rest % heads;                       // kv head (MODE 0) or q head (MODE 1)
+  it.hk = MODE == 0 ? it.hx : it.hx / G;
+  it.per_head = MODE == 0 ? p.n_tiles - it.fixed_tile : it.fixed_tile + 1;   // streamed tiles per head
+  it.n_iter = MODE == 0 ? G * it.per_head : it.per_head;
+  return it;
+}
+
+// Persistent: one CTA per SM walks work items.  Barrier parities run on two counters shared by all roles:
+// `g` = tile pairs processed so far by this CTA (stream ring stage g % 3; S buffer g & 1; dP and P/dS hand-offs),
+// `n` = items processed so far (resident tiles, accumulators).
+//
+// Software pipeline (what hides the tensor core behind the softmax warps and vice versa): S is double-buffered
+// in TMEM, so S(g+1) is already there when the softmax warps finish pair g and they start exponentiating at
+// once (phase A: P = exp2(S*c - lse), the MUFU-bound part, needs S only); meanwhile the tensor core produces
+// dP(g+1) and the gradient UMMAs of pair g; phase B (dS' = P * (dP - D)) picks dP(g+1) up when it is done.
+// MMA warp, at "softmax of pair g complete":  dP(g+1), gradients(g), S(g+2).
 template <int MODE>
 __global__ void __launch_bounds__(kThreads, 1)
 attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constant__ CUtensorMap tm_do,
@@ -150,37 +192,30 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
   const uint32_t raw = smem_u32(smem_raw);
   if (raw & 1023u) __trap();  // dynamic shared memory starts 1024-aligned (no static smem in this kernel)
   const uint32_t sF0 = raw + kOffF, sF1 = sF0 + kTile;
-  auto sS0 = [&](int st) { return raw + kOffS + (uint32_t)st * 2u * kTile; };
-  auto sS1 = [&](int st) { return raw + kOffS + (uint32_t)st * 2u * kTile + kTile; };
+  auto sS0 = [&](uint32_t st) { return raw + kOffS + st * 2u * kTile; };
+  auto sS1 = [&](uint32_t st) { return raw + kOffS + st * 2u * kTile + kTile; };
   const uint32_t sP = raw + kOffP, sDS = raw + kOffDS;
   const uint32_t bars = raw + kOffBar;
-  const uint32_t f_full = bars;
-  auto st_full = [&](int s) { return bars + 8u * (1 + s); };
-  auto st_empty = [&](int s) { return bars + 8u * (3 + s); };
-  const uint32_t sdp_full = bars + 8u * 5, sdp_free = bars + 8u * 6;
-  const uint32_t pds_full = bars + 8u * 7, pds_free = bars + 8u * 8, acc_full = bars + 8u * 9;
-  const uint32_t tmem_slot = bars + 8u * 10;
+  const uint32_t f_full = bars, f_empty = bars + 8u;
+  auto st_full = [&](uint32_t s) { return bars + 8u * (2 + s); };
+  auto st_empty = [&](uint32_t s) { return bars + 8u * (5 + s); };
+  auto s_full = [&](uint32_t bf) { return bars + 8u * (8 + bf); };
+  auto s_free = [&](uint32_t bf) { return bars + 8u * (10 + bf); };
+  const uint32_t dp_full = bars + 8u * 12, pds_full = bars + 8u * 13, pds_free = bars + 8u * 14;
+  const uint32_t acc_full = bars + 8u * 15, acc_free = bars + 8u * 16;
+  const uint32_t tmem_slot = bars + 8u * 17;
   volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - raw));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int G = p.n_head / p.n_kv_head;
-  // work item of this CTA, heaviest first.  MODE 0: (kv tile jt ascending, batch, kv head);
-  // MODE 1: (q tile it descending, batch, head)
-  const int per_tile = p.batch * (MODE == 0 ? p.n_kv_head : p.n_head);
-  const int tile_ord = (int)(blockIdx.x / per_tile);
-  const int rest = (int)(blockIdx.x % per_tile);
-  const int fixed_tile = MODE == 0 ? tile_ord : p.n_tiles - 1 - tile_ord;
-  const int b = rest / (MODE == 0 ? p.n_kv_head : p.n_head);
-  const int hx = rest % (MODE == 0 ? p.n_kv_head : p.n_head);   // kv head (MODE 0) or q head (MODE 1)
-  const int hk = MODE == 0 ? hx : hx / G;
-  const int per_head = MODE == 0 ? p.n_tiles - fixed_tile : fixed_tile + 1;  // streamed tiles per head
-  const int n_iter = MODE == 0 ? G * per_head : per_head;
+  const int num_items = p.n_tiles * p.batch * (MODE == 0 ? p.n_kv_head : p.n_head);
 
   if (warp == 1 && lane == 0) {
-    mbar_init(f_full, 1);
-    for (int s = 0; s < 2; ++s) { mbar_init(st_full(s), 1); mbar_init(st_empty(s), 1); }
-    mbar_init(sdp_full, 1); mbar_init(sdp_free, 4); mbar_init(pds_full, 4); mbar_init(pds_free, 1);
-    mbar_init(acc_full, 1);
+    mbar_init(f_full, 1); mbar_init(f_empty, 1);
+    for (uint32_t s = 0; s < kRing; ++s) { mbar_init(st_full(s), 1); mbar_init(st_empty(s), 1); }
+    for (uint32_t bf = 0; bf < 2; ++bf) { mbar_init(s_full(bf), 1); mbar_init(s_free(bf), 8); }
+    mbar_init(dp_full, 1); mbar_init(pds_full, 8); mbar_init(pds_free, 1);
+    mbar_init(acc_full, 1); mbar_init(acc_free, 8);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 2) {
@@ -195,32 +230,37 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
   if (warp == 0) {
     // ================================ TMA producer ================================
     const bool issuer = elect_one();
-    if (issuer) {
-      mbar_expect_tx(f_full, 2 * kTile);
-      if (MODE == 0) {
-        tma_load_3d(sF0, &tm_qkv, p.k_off + hk * kDH, fixed_tile * kB, b, f_full);
-        tma_load_3d(sF1, &tm_qkv, p.v_off + hk * kDH, fixed_tile * kB, b, f_full);
-      } else {
-        tma_load_3d(sF0, &tm_qkv, p.q_off + hx * kDH, fixed_tile * kB, b, f_full);
-        tma_load_3d(sF1, &tm_do, hx * kDH, fixed_tile * kB, b, f_full);
-      }
-    }
-    for (int t = 0; t < n_iter; ++t) {
-      const int st = t & 1;
-      const uint32_t ph = (uint32_t)(t >> 1) & 1u;
-      mbar_wait(st_empty(st), ph ^ 1u);
+    uint32_t g = 0, n = 0;
+    for (int w = blockIdx.x; w < num_items; w += gridDim.x, ++n) {
+      const Item it = decode_item<MODE>(p, w, G);
+      if (n > 0) mbar_wait(f_empty, (n - 1) & 1u);   // the previous item's last dP UMMAs have read the resident pair
       if (issuer) {
-        mbar_expect_tx(st_full(st), 2 * kTile);
+        mbar_expect_tx(f_full, 2 * kTile);
         if (MODE == 0) {
-          const int hq = hk * G + t / per_head, it = fixed_tile + t % per_head;
-          tma_load_3d(sS0(st), &tm_qkv, p.q_off + hq * kDH, it * kB, b, st_full(st));
-          tma_load_3d(sS1(st), &tm_do, hq * kDH, it * kB, b, st_full(st));
+          tma_load_3d(sF0, &tm_qkv, p.k_off + it.hk * kDH, it.fixed_tile * kB, it.b, f_full);
+          tma_load_3d(sF1, &tm_qkv, p.v_off + it.hk * kDH, it.fixed_tile * kB, it.b, f_full);
         } else {
-          tma_load_3d(sS0(st), &tm_qkv, p.k_off + hk * kDH, t * kB, b, st_full(st));
-          tma_load_3d(sS1(st), &tm_qkv, p.v_off + hk * kDH, t * kB, b, st_full(st));
+          tma_load_3d(sF0, &tm_qkv, p.q_off + it.hx * kDH, it.fixed_tile * kB, it.b, f_full);
+          tma_load_3d(sF1, &tm_do, it.hx * kDH, it.fixed_tile * kB, it.b, f_full);
         }
       }
       __syncwarp();
+      for (int t = 0; t < it.n_iter; ++t, ++g) {
+        const uint32_t st = g % kRing;
+        mbar_wait(st_empty(st), ((g / kRing) & 1u) ^ 1u);
+        if (issuer) {
+          mbar_expect_tx(st_full(st), 2 * kTile);
+          if (MODE == 0) {
+            const int hq = it.hk * G + t / it.per_head, qt = it.fixed_tile + t % it.per_head;
+            tma_load_3d(sS0(st), &tm_qkv, p.q_off + hq * kDH, qt * kB, it.b, st_full(st));
+            tma_load_3d(sS1(st), &tm_do, hq * kDH, qt * kB, it.b, st_full(st));
+          } else {
+            tma_load_3d(sS0(st), &tm_qkv, p.k_off + it.hk * kDH, t * kB, it.b, st_full(st));
+            tma_load_3d(sS1(st), &tm_qkv, p.v_off + it.hk * kDH, t * kB, it.b, st_full(st));
+          }
+        }
+        __syncwarp();
+      }
     }
   } else if (warp == 1) {
     // ================================ MMA issuer ================================
@@ -228,21 +268,34 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
     const uint32_t id_s = idesc(kB, 0, 0);     // S, dP: 128 x 128 x 64, both operands K-major
     const uint32_t id_g0 = idesc(kDH, 1, 1);   // dV, dK: 128 (keys) x 64 x 128 (queries): A = P^T / dS^T, B = dO / Q, MN-major
     const uint32_t id_g1 = idesc(kDH, 0, 1);   // dQ: 128 (queries) x 64 x 128 (keys): A = dS K-major, B = K MN-major
-    auto issue_sdp = [&](int st) {
+    auto issue_s = [&](uint32_t gg) {          // S(gg) = Q K^T into S buffer gg & 1
+      const uint32_t st = gg % kRing, bf = gg & 1u;
+      mbar_wait(st_full(st), (gg / kRing) & 1u);
+      if (gg >= 2) mbar_wait(s_free(bf), ((gg >> 1) - 1) & 1u);   // phase A of pair gg-2 has read this buffer
+      tc_fence_after();
       const uint32_t aq = MODE == 0 ? sS0(st) : sF0, bk = MODE == 0 ? sF0 : sS0(st);
+      if (issuer) {
+#pragma unroll
+        for (int k = 0; k < kDH / 16; ++k)
+          umma(tmem + kColS + 128u * bf, sdesc(aq + 32 * k, 16, 1024), sdesc(bk + 32 * k, 16, 1024), id_s, k > 0);
+        umma_commit(s_full(bf));
+      }
+      __syncwarp();
+    };
+    auto issue_dp = [&](uint32_t gg, bool last_of_item) {   // dP(gg) = dO V^T (the caller knows the dP buffer is free)
+      const uint32_t st = gg % kRing;
       const uint32_t ado = MODE == 0 ? sS1(st) : sF1, bv = MODE == 0 ? sF1 : sS1(st);
       if (issuer) {
 #pragma unroll
         for (int k = 0; k < kDH / 16; ++k)
-          umma(tmem + kColS, sdesc(aq + 32 * k, 16, 1024), sdesc(bk + 32 * k, 16, 1024), id_s, k > 0);
-#pragma unroll
-        for (int k = 0; k < kDH / 16; ++k)
           umma(tmem + kColDP, sdesc(ado + 32 * k, 16, 1024), sdesc(bv + 32 * k, 16, 1024), id_s, k > 0);
-        umma_commit(sdp_full);
+        umma_commit(dp_full);
+        if (last_of_item) umma_commit(f_empty);   // nothing of this item reads the resident pair any more
       }
       __syncwarp();
     };
-    auto issue_grads = [&](int st, bool first) {
+    auto issue_grads = [&](uint32_t gg, bool first) {
+      const uint32_t st = gg % kRing;
       if (issuer) {
         if (MODE == 0) {
 #pragma unroll
@@ -264,117 +317,157 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
       }
       __syncwarp();
     };
-    mbar_wait(f_full, 0);
-    mbar_wait(st_full(0), 0);
-    tc_fence_after();
-    issue_sdp(0);
-    for (int t = 0; t < n_iter; ++t) {
-      const int st = t & 1;
-      const uint32_t par = (uint32_t)(t & 1);
-      // the next pair's scores first (the softmax warps will be waiting for them), then this pair's gradients
-      mbar_wait(sdp_free, par);           // S(t), dP(t) have been read out of TMEM
-      if (t + 1 < n_iter) {
-        mbar_wait(st_full(st ^ 1), (uint32_t)((t + 1) >> 1) & 1u);
+    uint32_t g = 0, n = 0;
+    for (int w = blockIdx.x; w < num_items; w += gridDim.x, ++n) {
+      const Item it = decode_item<MODE>(p, w, G);
+      const int N = it.n_iter;
+      mbar_wait(f_full, n & 1u);
+      // item prologue: S(first), dP(first), S(second).  The dP buffer is free: the previous item's last pair
+      // was waited for below before its gradients were issued.
+      issue_s(g);
+      issue_dp(g, N == 1);
+      if (N > 1) issue_s(g + 1);
+      for (int t = 0; t < N; ++t, ++g) {
+        mbar_wait(pds_full, g & 1u);        // softmax warps are done with pair g: P, dS in smem, dP read out
         tc_fence_after();
-        issue_sdp(st ^ 1);
+        if (t + 1 < N) issue_dp(g + 1, t + 2 == N);
+        if (t == 0 && n > 0) { mbar_wait(acc_free, (n - 1) & 1u); tc_fence_after(); }  // previous item's accumulators read out
+        issue_grads(g, t == 0);
+        if (t + 2 < N) issue_s(g + 2);
       }
-      mbar_wait(pds_full, par);           // P(t), dS(t) are in shared memory
-      tc_fence_after();
-      issue_grads(st, t == 0);
+      if (issuer) umma_commit(acc_full);
+      __syncwarp();
     }
-    if (issuer) umma_commit(acc_full);
-    __syncwarp();
   } else if (warp >= 4) {
-    // ================================ softmax / dS, one thread per query row ================================
+    // ================================ softmax / dS ================================
+    // Two warps per TMEM lane quarter (= per scheduler, so each hides the other's tcgen05.ld / MUFU / st.shared
+    // latencies): a thread owns one query row and one 64-key half of the tile, i.e. one swizzled smem chunk.
     const int quarter = warp & 3;
+    const int half = (warp - 4) >> 2;
     const int row = quarter * 32 + lane;
-    const uint32_t t_s = tmem + ((uint32_t)(quarter * 32) << 16) + kColS;
-    const uint32_t t_dp = tmem + ((uint32_t)(quarter * 32) << 16) + kColDP;
+    const uint32_t t_lane = tmem + ((uint32_t)(quarter * 32) << 16);
+    const uint32_t t_dp = t_lane + kColDP + 64u * half;
     const uint32_t swz = (uint32_t)(row & 7);
-    const uint32_t row_off = (uint32_t)row * 128u;
-    float lse = INFINITY, dl = 0.f;
-    if (MODE == 1) {
-      const int qrow = fixed_tile * kB + row;
-      if (qrow < p.seq) {
-        const int64_t idx = ((int64_t)b * p.n_head + hx) * p.seq + qrow;
-        lse = p.lse2[idx]; dl = p.delta[idx];
+    const uint32_t tile_off = (uint32_t)half * 16384u + (uint32_t)row * 128u;
+    const f32x2_t sc2 = pk2(p.scale_log2, p.scale_log2);
+    auto store_chunk = [&](uint32_t base, int c, const uint32_t* wv) {   // 32 bf16 of this row -> four swizzled 16-byte units
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const uint32_t unit = ((uint32_t)(4 * c + u)) ^ swz;
+        st_shared_v4(base + tile_off + unit * 16u, wv[4 * u], wv[4 * u + 1], wv[4 * u + 2], wv[4 * u + 3]);
       }
-    }
-    for (int t = 0; t < n_iter; ++t) {
-      const uint32_t par = (uint32_t)(t & 1);
-      int qt, kt;
-      if (MODE == 0) {
-        const int hq = hk * G + t / per_head;
-        qt = fixed_tile + t % per_head; kt = fixed_tile;
-        const int qrow = qt * kB + row;
-        lse = INFINITY; dl = 0.f;          // rows past the end of the sequence: P = dS = 0
-        if (qrow < p.seq) {
-          const int64_t idx = ((int64_t)b * p.n_head + hq) * p.seq + qrow;
+    };
+    uint32_t g = 0, n = 0;
+    for (int w = blockIdx.x; w < num_items; w += gridDim.x, ++n) {
+      const Item it = decode_item<MODE>(p, w, G);
+      float lse = INFINITY, dl = 0.f;      // rows past the end of the sequence: P = dS = 0
+      if (MODE == 1) {
+        const int qr = it.fixed_tile * kB + row;
+        if (qr < p.seq) {
+          const int64_t idx = ((int64_t)it.b * p.n_head + it.hx) * p.seq + qr;
           lse = p.lse2[idx]; dl = p.delta[idx];
         }
-      } else {
-        qt = fixed_tile; kt = t;
       }
-      const bool diag = qt == kt;
-      const int qrow = qt * kB + row;
-      mbar_wait(sdp_full, par);
-      tc_fence_after();
-#pragma unroll 1
-      for (int c = 0; c < kB / 32; ++c) {
-        uint32_t rs[32], rd[32];
-        tmem_ld32(t_s + 32 * c, rs);
-        tmem_ld32(t_dp + 32 * c, rd);
-        tmem_wait_ld();
-        uint32_t wp[16], wd[16];
-#pragma unroll
-        for (int i = 0; i < 32; i += 2) {
-          float p0 = ex2(fmaf(__uint_as_float(rs[i]), p.scale_log2, -lse));
-          float p1 = ex2(fmaf(__uint_as_float(rs[i + 1]), p.scale_log2, -lse));
-          if (diag) {
-            if (kt * kB + 32 * c + i > qrow) p0 = 0.f;
-            if (kt * kB + 32 * c + i + 1 > qrow) p1 = 0.f;
+      for (int t = 0; t < it.n_iter; ++t, ++g) {
+        int qt, kt;
+        if (MODE == 0) {
+          const int hq = it.hk * G + t / it.per_head;
+          qt = it.fixed_tile + t % it.per_head; kt = it.fixed_tile;
+          const int qr = qt * kB + row;
+          lse = INFINITY; dl = 0.f;
+          if (qr < p.seq) {
+            const int64_t idx = ((int64_t)it.b * p.n_head + hq) * p.seq + qr;
+            lse = p.lse2[idx]; dl = p.delta[idx];
           }
-          const float d0 = p0 * (__uint_as_float(rd[i]) - dl) * p.scale;
-          const float d1 = p1 * (__uint_as_float(rd[i + 1]) - dl) * p.scale;
-          wp[i >> 1] = pack_bf16x2(p0, p1);
-          wd[i >> 1] = pack_bf16x2(d0, d1);
+        } else {
+          qt = it.fixed_tile; kt = t;
         }
-        if (c == 0 && t > 0) mbar_wait(pds_free, par ^ 1u);  // the previous pair's gradient UMMAs are done with the tiles
-        // columns 32c .. 32c+31 of this row: four 16-byte units in chunk c/2, units 4*(c&1) .. +3, XOR-swizzled
-        const uint32_t chunk = (uint32_t)(c >> 1) * 16384u + row_off;
+        const int qrow = qt * kB + row;
+        const int kcol0 = kt * kB + 64 * half;
+        const bool diag = qt == kt;
+        const f32x2_t nl2 = pk2(-lse, -lse), dl2 = pk2(dl, dl);
+        const uint32_t bf = g & 1u;
+        const uint32_t t_s = t_lane + kColS + 128u * bf + 64u * half;
+        // ---- phase A: P = exp2(S*c - lse) for this thread's 64 keys (kept in registers for phase B) ----
+        f32x2_t P2[32];
+        mbar_wait(s_full(bf), (g >> 1) & 1u);
+        tc_fence_after();
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
-          const uint32_t unit = ((uint32_t)(4 * (c & 1) + u)) ^ swz;
-          if (MODE == 0) st_shared_v4(sP + chunk + unit * 16u, wp[4 * u], wp[4 * u + 1], wp[4 * u + 2], wp[4 * u + 3]);
-          st_shared_v4(sDS + chunk + unit * 16u, wd[4 * u], wd[4 * u + 1], wd[4 * u + 2], wd[4 * u + 3]);
+        for (int c = 0; c < 2; ++c) {
+          uint32_t rs[32];
+          tmem_ld32(t_s + 32 * c, rs);
+          tmem_wait_ld();
+#pragma unroll
+          for (int i = 0; i < 32; i += 2) {
+            float e0, e1;
+            upk2(fma2(pk2(__uint_as_float(rs[i]), __uint_as_float(rs[i + 1])), sc2, nl2), e0, e1);
+            float p0 = ex2(e0), p1 = ex2(e1);
+            if (diag) {   // warp-uniform
+              if (kcol0 + 32 * c + i > qrow) p0 = 0.f;
+              if (kcol0 + 32 * c + i + 1 > qrow) p1 = 0.f;
+            }
+            P2[16 * c + (i >> 1)] = pk2(p0, p1);
+          }
         }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(s_free(bf));          // S(g+2) may overwrite this buffer
+        if (MODE == 0) {
+          if (g > 0) mbar_wait(pds_free, (g - 1) & 1u);  // the previous pair's gradient UMMAs are done with the tiles
+#pragma unroll
+          for (int c = 0; c < 2; ++c) {
+            uint32_t wp[16];
+#pragma unroll
+            for (int i = 0; i < 16; ++i) wp[i] = f32x2_to_bf16x2(P2[16 * c + i]);
+            store_chunk(sP, c, wp);
+          }
+        }
+        // ---- phase B: dS' = P * (dP - D) ----
+        mbar_wait(dp_full, g & 1u);
+        tc_fence_after();
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+          uint32_t rd[32];
+          tmem_ld32(t_dp + 32 * c, rd);
+          tmem_wait_ld();
+          uint32_t wd[16];
+#pragma unroll
+          for (int i = 0; i < 16; ++i)
+            wd[i] = f32x2_to_bf16x2(mul2(P2[16 * c + i],
+                                         sub2(pk2(__uint_as_float(rd[2 * i]), __uint_as_float(rd[2 * i + 1])), dl2)));
+          if (MODE == 1 && c == 0 && g > 0) mbar_wait(pds_free, (g - 1) & 1u);
+          store_chunk(sDS, c, wd);
+        }
+        tc_fence_before();
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy stores -> visible to the UMMAs
+        __syncwarp();
+        if (lane == 0) mbar_arrive(pds_full);
       }
+      // ---- accumulators -> (x softmax scale for dK, dQ) -> bf16 -> the gradient buffer ----
+      mbar_wait(acc_full, n & 1u);
+      tc_fence_after();
+      const int orow = it.fixed_tile * kB + row;   // key row (MODE 0) or query row (MODE 1)
+      // MODE 0: warps 4-7 write dV (accumulator 0), warps 8-11 dK (accumulator 1), 64 columns each;
+      // MODE 1: the two warps of a quarter split dQ's 64 columns
+      const uint32_t t_acc = t_lane + (MODE == 0 ? (half == 0 ? kColAcc0 : kColAcc1) : kColAcc0 + 32u * half);
+      const int col = MODE == 0 ? (half == 0 ? p.v_off : p.k_off) + it.hk * kDH : p.q_off + it.hx * kDH + 32 * half;
+      const float oscale = (MODE == 0 && half == 0) ? 1.f : p.scale;
+      uint32_t r[MODE == 0 ? 64 : 32];
+      tmem_ld32(t_acc, r);
+      if (MODE == 0) tmem_ld32(t_acc + 32, r + 32);
+      tmem_wait_ld();
       tc_fence_before();
-      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy stores -> visible to the UMMAs
       __syncwarp();
-      if (lane == 0) { mbar_arrive(sdp_free); mbar_arrive(pds_full); }
-    }
-    // ---- accumulators -> bf16 -> the gradient buffer ----
-    mbar_wait(acc_full, 0);
-    tc_fence_after();
-    const int orow = fixed_tile * kB + row;   // key row (MODE 0) or query row (MODE 1)
-    const int n_out = MODE == 0 ? 2 : 1;
-    for (int a = 0; a < n_out; ++a) {
-      const uint32_t t_acc = tmem + ((uint32_t)(quarter * 32) << 16) + (a == 0 ? kColAcc0 : kColAcc1);
-      // MODE 0: accumulator 0 = dV, 1 = dK; MODE 1: dQ
-      const int col = MODE == 0 ? (a == 0 ? p.v_off : p.k_off) + hk * kDH : p.q_off + hx * kDH;
+      if (lane == 0) mbar_arrive(acc_free);    // the next item's gradient UMMAs may overwrite the accumulators
+      if (orow < p.seq) {
+        __nv_bfloat16* dst = p.dqkv + ((int64_t)it.b * p.seq + orow) * p.ld_d + col;
 #pragma unroll
-      for (int c = 0; c < kDH / 32; ++c) {
-        uint32_t r[32];
-        tmem_ld32(t_acc + 32 * c, r);
-        tmem_wait_ld();
-        if (orow < p.seq) {
-          __nv_bfloat16* dst = p.dqkv + ((int64_t)b * p.seq + orow) * p.ld_d + col + 32 * c;
-          float f[32];
+        for (int c = 0; c < (MODE == 0 ? 2 : 1); ++c) {
+          float fv[32];
 #pragma unroll
-          for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(r[i]);
+          for (int i = 0; i < 32; ++i) fv[i] = __uint_as_float(r[32 * c + i]) * oscale;
 #pragma unroll
-          for (int v = 0; v < 4; ++v) *reinterpret_cast<uint4*>(dst + 8 * v) = pack8(f + 8 * v);
+          for (int v = 0; v < 4; ++v) *reinterpret_cast<uint4*>(dst + 32 * c + 8 * v) = pack8(fv + 8 * v);
         }
       }
     }
@@ -460,14 +553,16 @@ extern "C" int b200ft_attn_bwd(const void* qkv, int64_t ld, int q_off, int k_off
     attr_dev = dev;
   }
   cudaStream_t st = (cudaStream_t)stream;
-  const int64_t rows = (int64_t)batch * seq * n_head;
+  const int64_t rows = (int64_t)batch * seq;
   attn_delta_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, st>>>((const __nv_bfloat16*)out, ld_out,
                                                                 (const __nv_bfloat16*)dout, ld_dout, delta, batch,
                                                                 seq, n_head);
   B200FT_LAUNCH_CHECK();
-  attn_bwd_kernel<0><<<(unsigned)(p.n_tiles * batch * n_kv_head), kThreads, kSmemBytes, st>>>(tm_qkv, tm_do, p);
+  // persistent: one CTA per SM walks the work items (heaviest first, round-robin)
+  const int items0 = p.n_tiles * batch * n_kv_head, items1 = p.n_tiles * batch * n_head;
+  attn_bwd_kernel<0><<<(unsigned)(items0 < B200FT_NUM_SMS ? items0 : B200FT_NUM_SMS), kThreads, kSmemBytes, st>>>(tm_qkv, tm_do, p);
   B200FT_LAUNCH_CHECK();
-  attn_bwd_kernel<1><<<(unsigned)(p.n_tiles * batch * n_head), kThreads, kSmemBytes, st>>>(tm_qkv, tm_do, p);
+  attn_bwd_kernel<1><<<(unsigned)(items1 < B200FT_NUM_SMS ? items1 : B200FT_NUM_SMS), kThreads, kSmemBytes, st>>>(tm_qkv, tm_do, p);
   B200FT_LAUNCH_CHECK();
   return 0;
 }
