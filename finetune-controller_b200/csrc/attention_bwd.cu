@@ -392,21 +392,27 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
         f32x2_t P2[32];
         mbar_wait(s_full(bf), (g >> 1) & 1u);
         tc_fence_after();
-#pragma unroll
-        for (int c = 0; c < 2; ++c) {
-          uint32_t rs[32];
-          tmem_ld32(t_s + 32 * c, rs);
+        {
+          uint32_t rs[64];
+          tmem_ld32(t_s, rs);           // both 32-key chunks in flight before the first use
+          tmem_ld32(t_s + 32, rs + 32);
           tmem_wait_ld();
+          if (diag) {                   // warp-uniform; only the diagonal pair carries masking code
 #pragma unroll
-          for (int i = 0; i < 32; i += 2) {
-            float e0, e1;
-            upk2(fma2(pk2(__uint_as_float(rs[i]), __uint_as_float(rs[i + 1])), sc2, nl2), e0, e1);
-            float p0 = ex2(e0), p1 = ex2(e1);
-            if (diag) {   // warp-uniform
-              if (kcol0 + 32 * c + i > qrow) p0 = 0.f;
-              if (kcol0 + 32 * c + i + 1 > qrow) p1 = 0.f;
+            for (int i = 0; i < 64; i += 2) {
+              float e0, e1;
+              upk2(fma2(pk2(__uint_as_float(rs[i]), __uint_as_float(rs[i + 1])), sc2, nl2), e0, e1);
+              const float p0 = kcol0 + i > qrow ? 0.f : ex2(e0);
+              const float p1 = kcol0 + i + 1 > qrow ? 0.f : ex2(e1);
+              P2[i >> 1] = pk2(p0, p1);
             }
-            P2[16 * c + (i >> 1)] = pk2(p0, p1);
+          } else {
+#pragma unroll
+            for (int i = 0; i < 64; i += 2) {
+              float e0, e1;
+              upk2(fma2(pk2(__uint_as_float(rs[i]), __uint_as_float(rs[i + 1])), sc2, nl2), e0, e1);
+              P2[i >> 1] = pk2(ex2(e0), ex2(e1));
+            }
           }
         }
         tc_fence_before();
@@ -425,18 +431,21 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
         // ---- phase B: dS' = P * (dP - D) ----
         mbar_wait(dp_full, g & 1u);
         tc_fence_after();
-#pragma unroll
-        for (int c = 0; c < 2; ++c) {
-          uint32_t rd[32];
-          tmem_ld32(t_dp + 32 * c, rd);
+        {
+          uint32_t rd[64];
+          tmem_ld32(t_dp, rd);
+          tmem_ld32(t_dp + 32, rd + 32);
           tmem_wait_ld();
-          uint32_t wd[16];
+          if (MODE == 1 && g > 0) mbar_wait(pds_free, (g - 1) & 1u);
 #pragma unroll
-          for (int i = 0; i < 16; ++i)
-            wd[i] = f32x2_to_bf16x2(mul2(P2[16 * c + i],
-                                         sub2(pk2(__uint_as_float(rd[2 * i]), __uint_as_float(rd[2 * i + 1])), dl2)));
-          if (MODE == 1 && c == 0 && g > 0) mbar_wait(pds_free, (g - 1) & 1u);
-          store_chunk(sDS, c, wd);
+          for (int c = 0; c < 2; ++c) {
+            uint32_t wd[16];
+#pragma unroll
+            for (int i = 0; i < 16; ++i)
+              wd[i] = f32x2_to_bf16x2(mul2(P2[16 * c + i], sub2(pk2(__uint_as_float(rd[32 * c + 2 * i]),
+                                                                    __uint_as_float(rd[32 * c + 2 * i + 1])), dl2)));
+            store_chunk(sDS, c, wd);
+          }
         }
         tc_fence_before();
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy stores -> visible to the UMMAs
