@@ -15,6 +15,7 @@ LIB_PATH = os.path.join(_HERE, "libb200ft.so")
 
 EPI_NONE, EPI_RESIDUAL, EPI_GELU, EPI_DGELU, EPI_ATOMIC_F32_T = 0, 1, 2, 3, 4
 A_MN_MAJOR, B_MN_MAJOR = 1, 2
+ATTN_BWD_DETERMINISTIC = 1
 
 
 class GemmArgs(ctypes.Structure):
@@ -80,8 +81,10 @@ SIGNATURES = {
     "b200ft_swiglu_bwd_act": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_void_p]),
     "b200ft_attn_fwd": (c_int, [c_void_p, c_int64, c_int, c_int, c_int, c_void_p, c_int64, c_void_p, c_int, c_int,
                                 c_int, c_int, c_int, c_float, c_void_p]),
+    "b200ft_attn_bwd_workspace_bytes": (c_size_t, [c_int, c_int, c_int, c_int]),
     "b200ft_attn_bwd": (c_int, [c_void_p, c_int64, c_int, c_int, c_int, c_void_p, c_int64, c_void_p, c_int64, c_void_p,
-                                c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_int, c_int, c_float, c_void_p]),
+                                c_void_p, c_size_t, c_void_p, c_int64, c_int, c_int, c_int, c_int, c_int, c_float, c_int,
+                                c_void_p]),
     "b200ft_embed_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_void_p]),
     "b200ft_rmsnorm_bwd_dgamma": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int, c_void_p]),
     "b200ft_embed_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int, c_void_p]),

@@ -24,7 +24,7 @@ class OwnAttentionMixin:
         self._att_cols = (nq, nkv)
         self.att_out = [torch.empty(self.M, nq, **bf) for _ in range(n_layer)]
         self.att_lse = [torch.empty(self.B * n_head, self.T, **f32) for _ in range(n_layer)]
-        self.att_delta = torch.empty(self.B * n_head, self.T, **f32)
+        self.att_ws = ops.attn_bwd_workspace(self.B, self.T, n_head, d_head, self.dev)
         if not hasattr(self, "dqkv"):
             self.dqkv = torch.empty(self.M, nq + 2 * nkv, **bf)
 
@@ -33,6 +33,6 @@ class OwnAttentionMixin:
 
     def _own_attn_bwd(self, l: int, da: torch.Tensor):
         """dq | dk | dv land in self.dqkv; returns the three column-block views."""
-        ops.attn_bwd(self.qkv[l], self.att_out[l], da, self.att_lse[l], self.att_delta, self.dqkv, **self._att)
+        ops.attn_bwd(self.qkv[l], self.att_out[l], da, self.att_lse[l], self.att_ws, self.dqkv, **self._att)
         nq, nkv = self._att_cols
         return self.dqkv[:, :nq], self.dqkv[:, nq: nq + nkv], self.dqkv[:, nq + nkv:]

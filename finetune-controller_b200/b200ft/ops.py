@@ -286,17 +286,23 @@ def attn_fwd(qkv, out, lse2, *, batch, seq, n_head, n_kv_head, d_head, q_off, k_
     return out
 
 
-def attn_bwd(qkv, out, dout, lse2, delta, dqkv, *, batch, seq, n_head, n_kv_head, d_head, q_off, k_off, v_off, scale):
+def attn_bwd_workspace(batch, seq, n_head, d_head, device):
+    return torch.empty(lib().b200ft_attn_bwd_workspace_bytes(batch, seq, n_head, d_head), dtype=torch.uint8, device=device)
+
+
+def attn_bwd(qkv, out, dout, lse2, workspace, dqkv, *, batch, seq, n_head, n_kv_head, d_head, q_off, k_off, v_off, scale,
+             deterministic=False):
     """Causal attention backward: dq | dk | dv into `dqkv` at the fused projection's column offsets."""
     global LAUNCHES
-    _need_cuda(qkv, out, dout, lse2, delta, dqkv)
+    _need_cuda(qkv, out, dout, lse2, workspace, dqkv)
     assert qkv.dtype == out.dtype == dout.dtype == dqkv.dtype == torch.bfloat16
-    assert lse2.dtype == delta.dtype == torch.float32 and delta.numel() >= batch * n_head * seq
+    assert lse2.dtype == torch.float32 and workspace.dtype == torch.uint8
     flops = 10.0 * batch * n_head * d_head * seq * (seq + 128) / 2  # five tile GEMMs per visible pair
     with _timed("attn_bwd", flops):
         check(lib().b200ft_attn_bwd(_p(qkv), qkv.stride(0), q_off, k_off, v_off, _p(out), out.stride(0), _p(dout),
-                                    dout.stride(0), _p(lse2), _p(delta), _p(dqkv), dqkv.stride(0), batch, seq, n_head,
-                                    n_kv_head, d_head, scale, _stream()), "attn_bwd")
+                                    dout.stride(0), _p(lse2), _p(workspace), workspace.numel(), _p(dqkv), dqkv.stride(0),
+                                    batch, seq, n_head, n_kv_head, d_head, scale,
+                                    _lib.ATTN_BWD_DETERMINISTIC if deterministic else 0, _stream()), "attn_bwd")
     LAUNCHES += 3
     return dqkv
 

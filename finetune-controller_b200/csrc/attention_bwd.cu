@@ -34,9 +34,12 @@ constexpr int kRing = 3;                      // stream ring: pair g feeds its g
 constexpr int kOffS = 2 * kTile;              // ring stages of (tile0, tile1)
 constexpr int kOffP = kOffS + kRing * 2 * kTile;
 constexpr int kOffDS = kOffP + kPTile;
-constexpr int kOffBar = kOffDS + kPTile;      // 192 KB
+constexpr int kOffDQ = kOffDS + kPTile;       // MODE 2: eight 4 KB staging tiles (32 rows x 32 fp32) for the dQ reduce
+constexpr int kOffBar = kOffDQ + 8 * 4096;    // 224 KB
 constexpr int kSmemBytes = kOffBar + 256;
-constexpr uint32_t kColS = 0, kColDP = 256, kColAcc0 = 384, kColAcc1 = 448;   // S is double-buffered (+128)
+// S is double-buffered (+128) in the split modes; the fused mode keeps one S buffer and puts its two dQ-partial
+// buffers (64 columns each) where the second one would be
+constexpr uint32_t kColS = 0, kColDQ = 128, kColDP = 256, kColAcc0 = 384, kColAcc1 = 448;
 constexpr long long kWaitLimit = 4000000000ll;
 
 struct BwdParams {
@@ -155,6 +158,23 @@ attn_delta_kernel(const __nv_bfloat16* __restrict__ o, int64_t ld_o, const __nv_
 }
 
 // ------------------------------------------------------------------------------------------------
+// dq (bf16, into the gradient buffer's q columns) = scale * fp32 accumulator; 8 elements per thread
+__global__ void __launch_bounds__(256)
+attn_dq_convert_kernel(const float* __restrict__ acc, __nv_bfloat16* __restrict__ dqkv, int64_t ld_d, int q_off,
+                       int64_t rows, int cols, float scale) {
+  const int vpr = cols >> 3;
+  const int64_t total = rows * vpr;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const int64_t r = i / vpr;
+    const int v = (int)(i % vpr);
+    const float4 a = *reinterpret_cast<const float4*>(acc + r * cols + 8 * v);
+    const float4 b = *reinterpret_cast<const float4*>(acc + r * cols + 8 * v + 4);
+    float f8[8] = {a.x * scale, a.y * scale, a.z * scale, a.w * scale, b.x * scale, b.y * scale, b.z * scale, b.w * scale};
+    *reinterpret_cast<uint4*>(dqkv + r * ld_d + q_off + 8 * v) = pack8(f8);
+  }
+}
+
 // Work item of a CTA.  MODE 0: (kv tile ascending, batch, kv head); MODE 1: (q tile descending, batch, head):
 // heaviest first.  Every warp role walks the same item sequence w = blockIdx.x, += gridDim.x.
 struct Item {
@@ -163,15 +183,15 @@ struct Item {
 template <int MODE>
 __device__ __forceinline__ Item decode_item(const BwdParams& p, int w, int G) {
   Item it;
-  const int heads = MODE == 0 ? p.n_kv_head : p.n_head;
+  const int heads = MODE != 1 ? p.n_kv_head : p.n_head;
   const int per_tile = p.batch * heads;
   const int tile_ord = w / per_tile, rest = w % per_tile;
-  it.fixed_tile = MODE == 0 ? tile_ord : p.n_tiles - 1 - tile_ord;
+  it.fixed_tile = MODE != 1 ? tile_ord : p.n_tiles - 1 - tile_ord;
   it.b = rest / heads;
   it.hx = rest % heads;                       // kv head (MODE 0) or q head (MODE 1)
-  it.hk = MODE == 0 ? it.hx : it.hx / G;
-  it.per_head = MODE == 0 ? p.n_tiles - it.fixed_tile : it.fixed_tile + 1;   // streamed tiles per head
-  it.n_iter = MODE == 0 ? G * it.per_head : it.per_head;
+  it.hk = MODE != 1 ? it.hx : it.hx / G;
+  it.per_head = MODE != 1 ? p.n_tiles - it.fixed_tile : it.fixed_tile + 1;   // streamed tiles per head
+  it.n_iter = MODE != 1 ? G * it.per_head : it.per_head;
   return it;
 }
 
@@ -187,7 +207,7 @@ __device__ __forceinline__ Item decode_item(const BwdParams& p, int w, int G) {
 template <int MODE>
 __global__ void __launch_bounds__(kThreads, 1)
 attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constant__ CUtensorMap tm_do,
-                const BwdParams p) {
+                const __grid_constant__ CUtensorMap tm_dq, const BwdParams p) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
   if (raw & 1023u) __trap();  // dynamic shared memory starts 1024-aligned (no static smem in this kernel)
@@ -203,12 +223,14 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
   auto s_free = [&](uint32_t bf) { return bars + 8u * (10 + bf); };
   const uint32_t dp_full = bars + 8u * 12, pds_full = bars + 8u * 13, pds_free = bars + 8u * 14;
   const uint32_t acc_full = bars + 8u * 15, acc_free = bars + 8u * 16;
-  const uint32_t tmem_slot = bars + 8u * 17;
+  auto dq_full = [&](uint32_t bf) { return bars + 8u * (17 + bf); };   // MODE 2: dQ partial of a pair is in TMEM
+  auto dq_free = [&](uint32_t bf) { return bars + 8u * (19 + bf); };   //         ... and has been read out
+  const uint32_t tmem_slot = bars + 8u * 21;
   volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - raw));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int G = p.n_head / p.n_kv_head;
-  const int num_items = p.n_tiles * p.batch * (MODE == 0 ? p.n_kv_head : p.n_head);
+  const int num_items = p.n_tiles * p.batch * (MODE != 1 ? p.n_kv_head : p.n_head);
 
   if (warp == 1 && lane == 0) {
     mbar_init(f_full, 1); mbar_init(f_empty, 1);
@@ -216,6 +238,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
     for (uint32_t bf = 0; bf < 2; ++bf) { mbar_init(s_full(bf), 1); mbar_init(s_free(bf), 8); }
     mbar_init(dp_full, 1); mbar_init(pds_full, 8); mbar_init(pds_free, 1);
     mbar_init(acc_full, 1); mbar_init(acc_free, 8);
+    for (uint32_t bf = 0; bf < 2; ++bf) { mbar_init(dq_full(bf), 1); mbar_init(dq_free(bf), 8); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 2) {
@@ -236,7 +259,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
       if (n > 0) mbar_wait(f_empty, (n - 1) & 1u);   // the previous item's last dP UMMAs have read the resident pair
       if (issuer) {
         mbar_expect_tx(f_full, 2 * kTile);
-        if (MODE == 0) {
+        if (MODE != 1) {
           tma_load_3d(sF0, &tm_qkv, p.k_off + it.hk * kDH, it.fixed_tile * kB, it.b, f_full);
           tma_load_3d(sF1, &tm_qkv, p.v_off + it.hk * kDH, it.fixed_tile * kB, it.b, f_full);
         } else {
@@ -250,7 +273,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
         mbar_wait(st_empty(st), ((g / kRing) & 1u) ^ 1u);
         if (issuer) {
           mbar_expect_tx(st_full(st), 2 * kTile);
-          if (MODE == 0) {
+          if (MODE != 1) {
             const int hq = it.hk * G + t / it.per_head, qt = it.fixed_tile + t % it.per_head;
             tma_load_3d(sS0(st), &tm_qkv, p.q_off + hq * kDH, qt * kB, it.b, st_full(st));
             tma_load_3d(sS1(st), &tm_do, hq * kDH, qt * kB, it.b, st_full(st));
@@ -268,12 +291,13 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
     const uint32_t id_s = idesc(kB, 0, 0);     // S, dP: 128 x 128 x 64, both operands K-major
     const uint32_t id_g0 = idesc(kDH, 1, 1);   // dV, dK: 128 (keys) x 64 x 128 (queries): A = P^T / dS^T, B = dO / Q, MN-major
     const uint32_t id_g1 = idesc(kDH, 0, 1);   // dQ: 128 (queries) x 64 x 128 (keys): A = dS K-major, B = K MN-major
-    auto issue_s = [&](uint32_t gg) {          // S(gg) = Q K^T into S buffer gg & 1
-      const uint32_t st = gg % kRing, bf = gg & 1u;
+    auto issue_s = [&](uint32_t gg) {          // S(gg) = Q K^T into S buffer gg & 1 (MODE 2: the only buffer)
+      const uint32_t st = gg % kRing, bf = MODE == 2 ? 0u : gg & 1u;
       mbar_wait(st_full(st), (gg / kRing) & 1u);
-      if (gg >= 2) mbar_wait(s_free(bf), ((gg >> 1) - 1) & 1u);   // phase A of pair gg-2 has read this buffer
+      if (MODE == 2) { if (gg >= 1) mbar_wait(s_free(0), (gg - 1) & 1u); }   // phase A of the previous pair has read S
+      else if (gg >= 2) mbar_wait(s_free(bf), ((gg >> 1) - 1) & 1u);         // phase A of pair gg-2 has read this buffer
       tc_fence_after();
-      const uint32_t aq = MODE == 0 ? sS0(st) : sF0, bk = MODE == 0 ? sF0 : sS0(st);
+      const uint32_t aq = MODE != 1 ? sS0(st) : sF0, bk = MODE != 1 ? sF0 : sS0(st);
       if (issuer) {
 #pragma unroll
         for (int k = 0; k < kDH / 16; ++k)
@@ -284,20 +308,20 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
     };
     auto issue_dp = [&](uint32_t gg, bool last_of_item) {   // dP(gg) = dO V^T (the caller knows the dP buffer is free)
       const uint32_t st = gg % kRing;
-      const uint32_t ado = MODE == 0 ? sS1(st) : sF1, bv = MODE == 0 ? sF1 : sS1(st);
+      const uint32_t ado = MODE != 1 ? sS1(st) : sF1, bv = MODE != 1 ? sF1 : sS1(st);
       if (issuer) {
 #pragma unroll
         for (int k = 0; k < kDH / 16; ++k)
           umma(tmem + kColDP, sdesc(ado + 32 * k, 16, 1024), sdesc(bv + 32 * k, 16, 1024), id_s, k > 0);
         umma_commit(dp_full);
-        if (last_of_item) umma_commit(f_empty);   // nothing of this item reads the resident pair any more
+        if (MODE != 2 && last_of_item) umma_commit(f_empty);   // nothing of this item reads the resident pair any more
       }
       __syncwarp();
     };
     auto issue_grads = [&](uint32_t gg, bool first) {
       const uint32_t st = gg % kRing;
       if (issuer) {
-        if (MODE == 0) {
+        if (MODE != 1) {
 #pragma unroll
           for (int k = 0; k < kB / 16; ++k)   // reduction over 16 query rows per step
             umma(tmem + kColAcc0, sdesc(sP + 2048 * k, 16384, 1024), sdesc(sS1(st) + 2048 * k, 8192, 1024), id_g0,
@@ -312,8 +336,17 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
             umma(tmem + kColAcc0, sdesc(sDS + 16384 * (k >> 2) + 32 * (k & 3), 16, 1024),
                  sdesc(sS0(st) + 2048 * k, 8192, 1024), id_g1, !(first && k == 0));
         }
+        if (MODE == 2) {
+          // dQ partial of this pair: 128 (queries) x 64 x 128 (keys), A = dS K-major, B = the resident K tile MN-major
+          const uint32_t dq_col = kColDQ + 64u * (gg & 1u);
+#pragma unroll
+          for (int k = 0; k < kB / 16; ++k)
+            umma(tmem + dq_col, sdesc(sDS + 16384 * (k >> 2) + 32 * (k & 3), 16, 1024),
+                 sdesc(sF0 + 2048 * k, 8192, 1024), id_g1, k > 0);
+        }
         umma_commit(pds_free);      // P / dS tiles may be overwritten
         umma_commit(st_empty(st));  // and the streamed pair's slot refilled
+        if (MODE == 2) umma_commit(dq_full(gg & 1u));
       }
       __syncwarp();
     };
@@ -326,16 +359,21 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
       // was waited for below before its gradients were issued.
       issue_s(g);
       issue_dp(g, N == 1);
-      if (N > 1) issue_s(g + 1);
+      if (MODE != 2 && N > 1) issue_s(g + 1);
       for (int t = 0; t < N; ++t, ++g) {
+        if (MODE == 2 && t + 1 < N) issue_s(g + 1);   // waits for phase A of pair g; S is single-buffered here
         mbar_wait(pds_full, g & 1u);        // softmax warps are done with pair g: P, dS in smem, dP read out
         tc_fence_after();
         if (t + 1 < N) issue_dp(g + 1, t + 2 == N);
         if (t == 0 && n > 0) { mbar_wait(acc_free, (n - 1) & 1u); tc_fence_after(); }  // previous item's accumulators read out
+        if (MODE == 2 && g >= 2) { mbar_wait(dq_free(g & 1u), ((g >> 1) - 1) & 1u); tc_fence_after(); }
         issue_grads(g, t == 0);
-        if (t + 2 < N) issue_s(g + 2);
+        if (MODE != 2 && t + 2 < N) issue_s(g + 2);
       }
-      if (issuer) umma_commit(acc_full);
+      if (issuer) {
+        umma_commit(acc_full);
+        if (MODE == 2) umma_commit(f_empty);   // the dQ partials read the resident K tile to the end of the item
+      }
       __syncwarp();
     }
   } else if (warp >= 4) {
@@ -357,6 +395,34 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
         st_shared_v4(base + tile_off + unit * 16u, wv[4 * u], wv[4 * u + 1], wv[4 * u + 2], wv[4 * u + 3]);
       }
     };
+    // MODE 2: dQ partial of pair gg (32 rows x 32 columns per warp) -> swizzled staging tile -> TMA reduce-add into
+    // the fp32 dQ accumulator [batch][seq][heads*64]; rows past the end of the sequence are clipped by TMA
+    const uint32_t stage_dq = raw + kOffDQ + (uint32_t)(warp - 4) * 4096u;
+    auto drain_dq = [&](uint32_t gg, int hq, int qt, int bb) {
+      const uint32_t bq = gg & 1u;
+      mbar_wait(dq_full(bq), (gg >> 1) & 1u);
+      tc_fence_after();
+      uint32_t r[32];
+      tmem_ld32(t_lane + kColDQ + 64u * bq + 32u * half, r);
+      tmem_wait_ld();
+      tc_fence_before();
+      if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // the previous reduce has read the tile
+      __syncwarp();
+      if (lane == 0) mbar_arrive(dq_free(bq));
+#pragma unroll
+      for (int u = 0; u < 8; ++u)
+        st_shared_v4(stage_dq + (uint32_t)lane * 128u + ((((uint32_t)u) ^ (uint32_t)(lane & 7)) << 4), r[4 * u], r[4 * u + 1],
+                     r[4 * u + 2], r[4 * u + 3]);
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      __syncwarp();
+      if (lane == 0) {
+        asm volatile(
+            "cp.reduce.async.bulk.tensor.3d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3, %4}], [%1];"
+            ::"l"(reinterpret_cast<uint64_t>(&tm_dq)), "r"(stage_dq), "r"(hq * kDH + 32 * half),
+              "r"(qt * kB + 32 * quarter), "r"(bb) : "memory");
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+      }
+    };
     uint32_t g = 0, n = 0;
     for (int w = blockIdx.x; w < num_items; w += gridDim.x, ++n) {
       const Item it = decode_item<MODE>(p, w, G);
@@ -370,7 +436,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
       }
       for (int t = 0; t < it.n_iter; ++t, ++g) {
         int qt, kt;
-        if (MODE == 0) {
+        if (MODE != 1) {
           const int hq = it.hk * G + t / it.per_head;
           qt = it.fixed_tile + t % it.per_head; kt = it.fixed_tile;
           const int qr = qt * kB + row;
@@ -386,11 +452,11 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
         const int kcol0 = kt * kB + 64 * half;
         const bool diag = qt == kt;
         const f32x2_t nl2 = pk2(-lse, -lse), dl2 = pk2(dl, dl);
-        const uint32_t bf = g & 1u;
+        const uint32_t bf = MODE == 2 ? 0u : g & 1u;
         const uint32_t t_s = t_lane + kColS + 128u * bf + 64u * half;
         // ---- phase A: P = exp2(S*c - lse) for this thread's 64 keys (kept in registers for phase B) ----
         f32x2_t P2[32];
-        mbar_wait(s_full(bf), (g >> 1) & 1u);
+        mbar_wait(s_full(bf), MODE == 2 ? g & 1u : (g >> 1) & 1u);
         tc_fence_after();
         {
           uint32_t rs[64];
@@ -418,7 +484,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(s_free(bf));          // S(g+2) may overwrite this buffer
-        if (MODE == 0) {
+        if (MODE != 1) {
           if (g > 0) mbar_wait(pds_free, (g - 1) & 1u);  // the previous pair's gradient UMMAs are done with the tiles
 #pragma unroll
           for (int c = 0; c < 2; ++c) {
@@ -451,19 +517,23 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy stores -> visible to the UMMAs
         __syncwarp();
         if (lane == 0) mbar_arrive(pds_full);
+        if (MODE == 2 && t > 0)   // the previous pair's dQ partial: its UMMAs ran while this pair was exponentiated
+          drain_dq(g - 1, it.hk * G + (t - 1) / it.per_head, it.fixed_tile + (t - 1) % it.per_head, it.b);
       }
+      if (MODE == 2)
+        drain_dq(g - 1, it.hk * G + (it.n_iter - 1) / it.per_head, it.fixed_tile + (it.n_iter - 1) % it.per_head, it.b);
       // ---- accumulators -> (x softmax scale for dK, dQ) -> bf16 -> the gradient buffer ----
       mbar_wait(acc_full, n & 1u);
       tc_fence_after();
       const int orow = it.fixed_tile * kB + row;   // key row (MODE 0) or query row (MODE 1)
       // MODE 0: warps 4-7 write dV (accumulator 0), warps 8-11 dK (accumulator 1), 64 columns each;
       // MODE 1: the two warps of a quarter split dQ's 64 columns
-      const uint32_t t_acc = t_lane + (MODE == 0 ? (half == 0 ? kColAcc0 : kColAcc1) : kColAcc0 + 32u * half);
-      const int col = MODE == 0 ? (half == 0 ? p.v_off : p.k_off) + it.hk * kDH : p.q_off + it.hx * kDH + 32 * half;
-      const float oscale = (MODE == 0 && half == 0) ? 1.f : p.scale;
-      uint32_t r[MODE == 0 ? 64 : 32];
+      const uint32_t t_acc = t_lane + (MODE != 1 ? (half == 0 ? kColAcc0 : kColAcc1) : kColAcc0 + 32u * half);
+      const int col = MODE != 1 ? (half == 0 ? p.v_off : p.k_off) + it.hk * kDH : p.q_off + it.hx * kDH + 32 * half;
+      const float oscale = (MODE != 1 && half == 0) ? 1.f : p.scale;
+      uint32_t r[MODE != 1 ? 64 : 32];
       tmem_ld32(t_acc, r);
-      if (MODE == 0) tmem_ld32(t_acc + 32, r + 32);
+      if (MODE != 1) tmem_ld32(t_acc + 32, r + 32);
       tmem_wait_ld();
       tc_fence_before();
       __syncwarp();
@@ -471,7 +541,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
       if (orow < p.seq) {
         __nv_bfloat16* dst = p.dqkv + ((int64_t)it.b * p.seq + orow) * p.ld_d + col;
 #pragma unroll
-        for (int c = 0; c < (MODE == 0 ? 2 : 1); ++c) {
+        for (int c = 0; c < (MODE != 1 ? 2 : 1); ++c) {
           float fv[32];
 #pragma unroll
           for (int i = 0; i < 32; ++i) fv[i] = __uint_as_float(r[32 * c + i]) * oscale;
@@ -480,6 +550,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
         }
       }
     }
+    if (MODE == 2 && lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");  // reductions complete before exit
     tc_fence_before();
   }
 
@@ -522,11 +593,20 @@ int make_map(EncodeTiledFn enc, CUtensorMap* tm, const void* base, int64_t ld, i
 
 }  // namespace
 
+// workspace: delta [batch*n_head*seq] fp32 | dQ accumulator [batch*seq, n_head*64] fp32 (fused path only)
+static size_t delta_bytes(int batch, int seq, int n_head) {
+  return (((size_t)batch * n_head * seq * sizeof(float)) + 255) & ~(size_t)255;
+}
+
+extern "C" size_t b200ft_attn_bwd_workspace_bytes(int batch, int seq, int n_head, int d_head) {
+  return delta_bytes(batch, seq, n_head) + (size_t)batch * seq * n_head * d_head * sizeof(float);
+}
+
 extern "C" int b200ft_attn_bwd(const void* qkv, int64_t ld, int q_off, int k_off, int v_off, const void* out,
-                               int64_t ld_out, const void* dout, int64_t ld_dout, const float* lse2, float* delta,
-                               void* dqkv, int64_t ld_dqkv, int batch, int seq, int n_head, int n_kv_head,
-                               int d_head, float scale, void* stream) {
-  B200FT_CHECK_ARG(qkv && out && dout && lse2 && delta && dqkv, "attn_bwd: null buffer");
+                               int64_t ld_out, const void* dout, int64_t ld_dout, const float* lse2, void* workspace,
+                               size_t workspace_bytes, void* dqkv, int64_t ld_dqkv, int batch, int seq, int n_head,
+                               int n_kv_head, int d_head, float scale, int flags, void* stream) {
+  B200FT_CHECK_ARG(qkv && out && dout && lse2 && workspace && dqkv, "attn_bwd: null buffer");
   if (d_head != kDH) {
     b200ft_set_error("attn_bwd: d_head=%d is not built (only 64)", d_head);
     return B200FT_ERR_UNSUPPORTED;
@@ -536,16 +616,37 @@ extern "C" int b200ft_attn_bwd(const void* qkv, int64_t ld, int q_off, int k_off
   B200FT_CHECK_ARG(ld % 8 == 0 && ld_out % 8 == 0 && ld_dout % 8 == 0 && ld_dqkv % 8 == 0 && q_off % 8 == 0 &&
                        k_off % 8 == 0 && v_off % 8 == 0 &&
                        ((uintptr_t)qkv | (uintptr_t)out | (uintptr_t)dout | (uintptr_t)dqkv) % 16 == 0 &&
-                       ld_out >= (int64_t)n_head * kDH && ld_dout >= (int64_t)n_head * kDH,
+                       (uintptr_t)workspace % 256 == 0 && ld_out >= (int64_t)n_head * kDH &&
+                       ld_dout >= (int64_t)n_head * kDH,
                    "attn_bwd: alignment (ld=%lld ld_out=%lld ld_dout=%lld ld_dqkv=%lld offsets %d/%d/%d)",
                    (long long)ld, (long long)ld_out, (long long)ld_dout, (long long)ld_dqkv, q_off, k_off, v_off);
+  const bool split = (flags & B200FT_ATTN_BWD_DETERMINISTIC) != 0;
+  const size_t need = split ? delta_bytes(batch, seq, n_head) : b200ft_attn_bwd_workspace_bytes(batch, seq, n_head, d_head);
+  if (workspace_bytes < need) {
+    b200ft_set_error("attn_bwd: workspace %zu < %zu", workspace_bytes, need);
+    return B200FT_ERR_WORKSPACE;
+  }
+  float* delta = (float*)workspace;
+  float* dq_acc = (float*)((uint8_t*)workspace + delta_bytes(batch, seq, n_head));
   EncodeTiledFn enc = encode_fn();
   if (!enc) { b200ft_set_error("attn_bwd: cuTensorMapEncodeTiled unavailable"); return B200FT_ERR_UNSUPPORTED; }
-  CUtensorMap tm_qkv, tm_do;
+  CUtensorMap tm_qkv, tm_do, tm_dq;
   int rc = make_map(enc, &tm_qkv, qkv, ld, seq, batch);
   if (rc) return rc;
   rc = make_map(enc, &tm_do, dout, ld_dout, seq, batch);
   if (rc) return rc;
+  tm_dq = tm_do;  // unused by the split kernels
+  if (!split) {
+    // fp32 accumulator as [batch][seq][heads*64], boxes of 32 columns x 32 rows, 128B swizzle
+    cuuint64_t dims[3] = {(cuuint64_t)n_head * kDH, (cuuint64_t)seq, (cuuint64_t)batch};
+    cuuint64_t strides[2] = {(cuuint64_t)n_head * kDH * 4, (cuuint64_t)n_head * kDH * 4 * (cuuint64_t)seq};
+    cuuint32_t box[3] = {32, 32, 1};
+    cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = enc(&tm_dq, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, dq_acc, dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { b200ft_set_error("attn_bwd: cuTensorMapEncodeTiled(dq) failed (%d)", (int)r); return B200FT_ERR_ARG; }
+  }
   BwdParams p;
   p.batch = batch; p.seq = seq; p.n_head = n_head; p.n_kv_head = n_kv_head;
   p.q_off = q_off; p.k_off = k_off; p.v_off = v_off;
@@ -559,6 +660,7 @@ extern "C" int b200ft_attn_bwd(const void* qkv, int64_t ld, int q_off, int k_off
   if (dev != attr_dev) {
     B200FT_CUDA(cudaFuncSetAttribute(attn_bwd_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
     B200FT_CUDA(cudaFuncSetAttribute(attn_bwd_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+    B200FT_CUDA(cudaFuncSetAttribute(attn_bwd_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
     attr_dev = dev;
   }
   cudaStream_t st = (cudaStream_t)stream;
@@ -569,9 +671,22 @@ extern "C" int b200ft_attn_bwd(const void* qkv, int64_t ld, int q_off, int k_off
   B200FT_LAUNCH_CHECK();
   // persistent: one CTA per SM walks the work items (heaviest first, round-robin)
   const int items0 = p.n_tiles * batch * n_kv_head, items1 = p.n_tiles * batch * n_head;
-  attn_bwd_kernel<0><<<(unsigned)(items0 < B200FT_NUM_SMS ? items0 : B200FT_NUM_SMS), kThreads, kSmemBytes, st>>>(tm_qkv, tm_do, p);
+  const unsigned grid0 = (unsigned)(items0 < B200FT_NUM_SMS ? items0 : B200FT_NUM_SMS);
+  if (split) {
+    attn_bwd_kernel<0><<<grid0, kThreads, kSmemBytes, st>>>(tm_qkv, tm_do, tm_dq, p);
+    B200FT_LAUNCH_CHECK();
+    attn_bwd_kernel<1><<<(unsigned)(items1 < B200FT_NUM_SMS ? items1 : B200FT_NUM_SMS), kThreads, kSmemBytes, st>>>(
+        tm_qkv, tm_do, tm_dq, p);
+    B200FT_LAUNCH_CHECK();
+    return 0;
+  }
+  B200FT_CUDA(cudaMemsetAsync(dq_acc, 0, (size_t)rows * n_head * kDH * sizeof(float), st));
+  attn_bwd_kernel<2><<<grid0, kThreads, kSmemBytes, st>>>(tm_qkv, tm_do, tm_dq, p);
   B200FT_LAUNCH_CHECK();
-  attn_bwd_kernel<1><<<(unsigned)(items1 < B200FT_NUM_SMS ? items1 : B200FT_NUM_SMS), kThreads, kSmemBytes, st>>>(tm_qkv, tm_do, p);
+  const int cols = n_head * kDH;
+  int64_t want = (rows * (cols / 8) + 255) / 256;
+  const int blocks = (int)(want > B200FT_NUM_SMS * 16 ? B200FT_NUM_SMS * 16 : want);
+  attn_dq_convert_kernel<<<blocks, 256, 0, st>>>(dq_acc, (__nv_bfloat16*)dqkv, ld_dqkv, q_off, rows, cols, scale);
   B200FT_LAUNCH_CHECK();
   return 0;
 }

@@ -218,16 +218,22 @@ int b200ft_attn_fwd(const void* qkv, int64_t ld, int q_off, int k_off, int v_off
 
 /* Causal flash-attention backward on tcgen05, the counterpart of b200ft_attn_fwd (same layout
  * conventions; oracle: autograd of causal_attention()).  out / dout [batch*seq, ld_*] carry head h at
- * column h*d_head; lse2 is the forward's output; delta [batch*n_head, seq] is scratch the call fills
- * (row sums of dout*out).  dqkv [batch*seq, ld_dqkv] receives dq of head h at q_off + h*d_head and
- * dk / dv of kv head g at k_off / v_off + g*d_head (summed over the q heads of the group), i.e. the
- * column layout of the fused projection output itself; every element of those column ranges is
- * written.  d_head must be 64; other sizes return B200FT_ERR_UNSUPPORTED.  Three launches (delta,
- * dk|dv, dq); no atomics, bit-reproducible. */
+ * column h*d_head; lse2 is the forward's output.  dqkv [batch*seq, ld_dqkv] receives dq of head h at
+ * q_off + h*d_head and dk / dv of kv head g at k_off / v_off + g*d_head (summed over the q heads of the
+ * group), i.e. the column layout of the fused projection output itself; every element of those
+ * column ranges is written.  d_head must be 64; other sizes return B200FT_ERR_UNSUPPORTED.
+ * workspace: 256-byte aligned scratch of b200ft_attn_bwd_workspace_bytes() bytes (row sums of
+ * dout*out, and the fp32 dQ accumulator of the default path).
+ * flags = 0: one fused kernel per (kv tile, batch, kv head) computes dK, dV in TMEM and adds its dQ
+ * partials into the fp32 accumulator with TMA reduce-add (summation order varies run to run in the
+ * last bits of dq).  flags = B200FT_ATTN_BWD_DETERMINISTIC: two kernels (dK|dV, then dQ), no atomics,
+ * bit-reproducible, ~1.4x the time. */
+#define B200FT_ATTN_BWD_DETERMINISTIC 1
+size_t b200ft_attn_bwd_workspace_bytes(int batch, int seq, int n_head, int d_head);
 int b200ft_attn_bwd(const void* qkv, int64_t ld, int q_off, int k_off, int v_off, const void* out,
-                    int64_t ld_out, const void* dout, int64_t ld_dout, const float* lse2, float* delta,
-                    void* dqkv, int64_t ld_dqkv, int batch, int seq, int n_head, int n_kv_head, int d_head,
-                    float scale, void* stream);
+                    int64_t ld_out, const void* dout, int64_t ld_dout, const float* lse2, void* workspace,
+                    size_t workspace_bytes, void* dqkv, int64_t ld_dqkv, int batch, int seq, int n_head,
+                    int n_kv_head, int d_head, float scale, int flags, void* stream);
 
 /* Token + position embedding (oracle forward(): F.embedding(ids,wte)+F.embedding(pos,wpe)).
  * wte bf16 [vocab, d], wpe bf16 [ctx, d], x bf16 [rows, d], position = row % seq.  wpe may be NULL

@@ -59,9 +59,10 @@ def test_attn_fwd_rejects_other_head_sizes():
                      batch=1, seq=128, n_head=1, n_kv_head=1, d_head=128, q_off=0, k_off=128, v_off=256, scale=0.1)
 
 
+@pytest.mark.parametrize("deterministic", [False, True])
 @pytest.mark.parametrize("B,T,H,KV", [(1, 128, 1, 1), (2, 256, 3, 3), (1, 1024, 2, 2), (2, 384, 8, 2), (3, 200, 4, 1),
-                                      (1, 40, 2, 2)])
-def test_attn_bwd_matches_oracle_autograd(B, T, H, KV):
+                                      (1, 40, 2, 2), (40, 512, 4, 4)])
+def test_attn_bwd_matches_oracle_autograd(B, T, H, KV, deterministic):
     """dq | dk | dv of the own backward (fed by the own forward's out and log-sum-exp) against autograd
     through the explicit fp32 attention; GQA sums the group's heads into dk / dv; ragged lengths."""
     from b200ft import ops
@@ -81,8 +82,8 @@ def test_attn_bwd_matches_oracle_autograd(B, T, H, KV):
               scale=1.0 / math.sqrt(dh))
     ops.attn_fwd(qd, out, lse2, **kw)
     dqkv = torch.full((B * T, ld), float("nan"), dtype=torch.bfloat16, device=DEV)
-    delta = torch.empty(B * H, T, device=DEV)
-    ops.attn_bwd(qd, out, dod, lse2, delta, dqkv, **kw)
+    ws = ops.attn_bwd_workspace(B, T, H, dh, DEV)
+    ops.attn_bwd(qd, out, dod, lse2, ws, dqkv, deterministic=deterministic, **kw)
     torch.cuda.synchronize()
     got = dqkv.cpu().float()
     assert not torch.isnan(got).any(), "backward left gradient elements unwritten"
@@ -95,7 +96,7 @@ def test_attn_bwd_matches_oracle_autograd(B, T, H, KV):
         torch.testing.assert_close(a, r, rtol=5e-2, atol=3e-2 * float(r.abs().max()))
 
 
-def test_attn_bwd_is_bit_reproducible():
+def test_attn_bwd_deterministic_path_is_bit_reproducible():
     from b200ft import ops
     B, T, H, KV, dh = 2, 384, 4, 2, 64
     g = torch.Generator().manual_seed(1)
@@ -105,11 +106,16 @@ def test_attn_bwd_is_bit_reproducible():
     kw = dict(batch=B, seq=T, n_head=H, n_kv_head=KV, d_head=dh, q_off=0, k_off=H * dh, v_off=(H + KV) * dh,
               scale=0.125)
     out = torch.empty(B * T, H * dh, dtype=torch.bfloat16, device=DEV)
-    lse2, delta = torch.empty(B * H, T, device=DEV), torch.empty(B * H, T, device=DEV)
+    lse2, ws = torch.empty(B * H, T, device=DEV), ops.attn_bwd_workspace(B, T, H, dh, DEV)
     ops.attn_fwd(qd, out, lse2, **kw)
     res = []
     for _ in range(2):
         dqkv = torch.zeros(B * T, ld, dtype=torch.bfloat16, device=DEV)
-        ops.attn_bwd(qd, out, dod, lse2, delta, dqkv, **kw)
+        ops.attn_bwd(qd, out, dod, lse2, ws, dqkv, deterministic=True, **kw)
         res.append(dqkv.clone())
     assert torch.equal(res[0], res[1])
+    # the fused default: dk, dv are exact too, dq differs only in the summation order of its fp32 partials
+    fused = torch.zeros(B * T, ld, dtype=torch.bfloat16, device=DEV)
+    ops.attn_bwd(qd, out, dod, lse2, ws, fused, **kw)
+    assert torch.equal(fused[:, H * dh:], res[0][:, H * dh:])
+    torch.testing.assert_close(fused[:, : H * dh].float(), res[0][:, : H * dh].float(), rtol=2 ** -7, atol=1e-3)

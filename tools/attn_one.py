@@ -10,9 +10,9 @@ ld = (H + 2 * KV) * dh
 qkv = torch.randn(B * T, ld, device="cuda").to(torch.bfloat16)
 dout = torch.randn(B * T, H * dh, device="cuda").to(torch.bfloat16)
 out = torch.empty(B * T, H * dh, dtype=torch.bfloat16, device="cuda"); lse = torch.empty(B * H, T, device="cuda")
-delta = torch.empty(B * H, T, device="cuda"); dqkv = torch.empty(B * T, ld, dtype=torch.bfloat16, device="cuda")
+ws = ops.attn_bwd_workspace(B, T, H, dh, "cuda"); dqkv = torch.empty(B * T, ld, dtype=torch.bfloat16, device="cuda")
 kw = dict(batch=B, seq=T, n_head=H, n_kv_head=KV, d_head=dh, q_off=0, k_off=H * dh, v_off=(H + KV) * dh, scale=1 / math.sqrt(dh))
 for _ in range(2):
     ops.attn_fwd(qkv, out, lse, **kw)
-    ops.attn_bwd(qkv, out, dout, lse, delta, dqkv, **kw)
+    ops.attn_bwd(qkv, out, dout, lse, ws, dqkv, **kw)
 torch.cuda.synchronize(); print("ok")

@@ -34,13 +34,14 @@ for (B, T, H, KV) in SHAPES:
     # ---- backward: own (delta + dk|dv + dq kernels) vs SDPA's autograd (cuDNN) ----
     dout = torch.randn(B * T, H * dh, device=dev).to(torch.bfloat16)
     dqkv = torch.empty(B * T, ld, dtype=torch.bfloat16, device=dev)
-    delta = torch.empty(B * H, T, device=dev)
+    ws = ops.attn_bwd_workspace(B, T, H, dh, dev)
     kw = dict(batch=B, seq=T, n_head=H, n_kv_head=KV, d_head=dh, q_off=0, k_off=H * dh, v_off=(H + KV) * dh,
               scale=1 / math.sqrt(dh))
-    us_b = timeit(lambda: ops.attn_bwd(qkv, out, dout, lse, delta, dqkv, **kw))
+    us_b = timeit(lambda: ops.attn_bwd(qkv, out, dout, lse, ws, dqkv, **kw))
+    us_bd = timeit(lambda: ops.attn_bwd(qkv, out, dout, lse, ws, dqkv, deterministic=True, **kw))
     qg, kg, vg = (t.detach().requires_grad_(True) for t in (q, k, v))
     og = F.scaled_dot_product_attention(qg, kg, vg, is_causal=True, enable_gqa=(H != KV))
     go = dout.view(B, T, H, dh).permute(0, 2, 1, 3)
     us_bl = timeit(lambda: torch.autograd.grad(og, (qg, kg, vg), go, retain_graph=True))
     fb = 2.5 * flops
-    print(f"      backward: own {us_b:8.1f} us ({fb/us_b/1e6:6.0f} TF)   SDPA {us_bl:8.1f} us ({fb/us_bl/1e6:6.0f} TF)")
+    print(f"      backward: own {us_b:8.1f} us ({fb/us_b/1e6:6.0f} TF)  [two-kernel {us_bd:8.1f} us]   SDPA {us_bl:8.1f} us ({fb/us_bl/1e6:6.0f} TF)")
