@@ -426,25 +426,27 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
     uint32_t g = 0, n = 0;
     for (int w = blockIdx.x; w < num_items; w += gridDim.x, ++n) {
       const Item it = decode_item<MODE>(p, w, G);
-      float lse = INFINITY, dl = 0.f;      // rows past the end of the sequence: P = dS = 0
-      if (MODE == 1) {
-        const int qr = it.fixed_tile * kB + row;
+      // per-row log-sum-exp and D.  Rows past the end of the sequence get lse = +inf: P = dS = 0.  With the kv tile
+      // fixed (MODE 0, 2) every pair has its own query rows: the values of pair t+1 are requested while pair t
+      // is processed, so their global-memory latency is never on the critical path.
+      auto load_row_stats = [&](int t, float& lse_o, float& dl_o) {
+        const int hq = MODE == 1 ? it.hx : it.hk * G + t / it.per_head;
+        const int qt_ = MODE == 1 ? it.fixed_tile : it.fixed_tile + t % it.per_head;
+        const int qr = qt_ * kB + row;
+        lse_o = INFINITY; dl_o = 0.f;
         if (qr < p.seq) {
-          const int64_t idx = ((int64_t)it.b * p.n_head + it.hx) * p.seq + qr;
-          lse = p.lse2[idx]; dl = p.delta[idx];
+          const int64_t idx = ((int64_t)it.b * p.n_head + hq) * p.seq + qr;
+          lse_o = __ldg(p.lse2 + idx); dl_o = __ldg(p.delta + idx);
         }
-      }
+      };
+      float lse, dl, lse_next = INFINITY, dl_next = 0.f;
+      load_row_stats(0, lse, dl);
       for (int t = 0; t < it.n_iter; ++t, ++g) {
         int qt, kt;
         if (MODE != 1) {
-          const int hq = it.hk * G + t / it.per_head;
           qt = it.fixed_tile + t % it.per_head; kt = it.fixed_tile;
-          const int qr = qt * kB + row;
-          lse = INFINITY; dl = 0.f;
-          if (qr < p.seq) {
-            const int64_t idx = ((int64_t)it.b * p.n_head + hq) * p.seq + qr;
-            lse = p.lse2[idx]; dl = p.delta[idx];
-          }
+          if (t > 0) { lse = lse_next; dl = dl_next; }
+          if (t + 1 < it.n_iter) load_row_stats(t + 1, lse_next, dl_next);
         } else {
           qt = it.fixed_tile; kt = t;
         }
