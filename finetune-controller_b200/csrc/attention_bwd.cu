@@ -15,8 +15,8 @@
 // 128B-swizzled shared tiles [q rows][kv columns] — the byte layout TMA would produce — which the second
 // group of UMMAs consumes MN-major (P^T, dS^T: reduction over q) or K-major (dS: reduction over kv).
 // Q, dO, K, V tiles are used in both roles too: K-major for S / dP, MN-major as the B operand of the
-// gradient GEMMs.  384 threads: warp 0 TMA, warp 1 MMA issue, warp 2 TMEM allocation, warps 4-11 softmax / dS
-// (two per TMEM lane quarter, each owning one 64-key half of the tile).
+// gradient GEMMs.  640 threads: warp 0 TMA, warp 1 MMA issue, warp 2 TMEM allocation, warps 4-19 softmax / dS
+// (four per TMEM lane quarter, each owning one 32-key slice of the tile).
 #include <cuda.h>
 #include <mutex>
 #include "common.cuh"
@@ -26,7 +26,7 @@ namespace {
 
 constexpr int kDH = 64;
 constexpr int kB = 128;                       // tile edge in queries and in keys
-constexpr int kThreads = 384;
+constexpr int kThreads = 640;                 // warps 0-2 TMA / MMA / TMEM, 4-19 softmax
 constexpr int kTile = kB * kDH * 2;           // 16 KB: one Q / dO / K / V tile
 constexpr int kPTile = kB * kB * 2;           // 32 KB: P or dS, two 64-column chunks of 16 KB
 constexpr int kOffF = 0;                      // resident pair
@@ -103,11 +103,23 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* r) {
         "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
       : "r"(taddr) : "memory");
 }
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t* r) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr) : "memory");
+}
 __device__ __forceinline__ void tmem_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ float ex2(float x) {
+#ifdef B200FT_EXP_NO_EX2   // bottleneck experiment (tools/attn_exp.sh): no MUFU work, wrong numbers
+  return x * 0.001f;
+#else
   float y;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
+#endif
 }
 __device__ __forceinline__ bool elect_one() {
   uint32_t pred;
@@ -235,9 +247,9 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
   if (warp == 1 && lane == 0) {
     mbar_init(f_full, 1); mbar_init(f_empty, 1);
     for (uint32_t s = 0; s < kRing; ++s) { mbar_init(st_full(s), 1); mbar_init(st_empty(s), 1); }
-    for (uint32_t bf = 0; bf < 2; ++bf) { mbar_init(s_full(bf), 1); mbar_init(s_free(bf), 8); }
-    mbar_init(dp_full, 1); mbar_init(pds_full, 8); mbar_init(pds_free, 1);
-    mbar_init(acc_full, 1); mbar_init(acc_free, 8);
+    for (uint32_t bf = 0; bf < 2; ++bf) { mbar_init(s_full(bf), 1); mbar_init(s_free(bf), 16); }
+    mbar_init(dp_full, 1); mbar_init(pds_full, 16); mbar_init(pds_free, 1);
+    mbar_init(acc_full, 1); mbar_init(acc_free, 16);
     for (uint32_t bf = 0; bf < 2; ++bf) { mbar_init(dq_full(bf), 1); mbar_init(dq_free(bf), 8); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -321,6 +333,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
     auto issue_grads = [&](uint32_t gg, bool first) {
       const uint32_t st = gg % kRing;
       if (issuer) {
+#ifndef B200FT_EXP_NO_GRADS   // bottleneck experiment: skip the gradient UMMAs (commits stay), wrong numbers
         if (MODE != 1) {
 #pragma unroll
           for (int k = 0; k < kB / 16; ++k)   // reduction over 16 query rows per step
@@ -344,6 +357,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
             umma(tmem + dq_col, sdesc(sDS + 16384 * (k >> 2) + 32 * (k & 3), 16, 1024),
                  sdesc(sF0 + 2048 * k, 8192, 1024), id_g1, k > 0);
         }
+#endif
         umma_commit(pds_free);      // P / dS tiles may be overwritten
         umma_commit(st_empty(st));  // and the streamed pair's slot refilled
         if (MODE == 2) umma_commit(dq_full(gg & 1u));
@@ -378,32 +392,35 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
     }
   } else if (warp >= 4) {
     // ================================ softmax / dS ================================
-    // Two warps per TMEM lane quarter (= per scheduler, so each hides the other's tcgen05.ld / MUFU / st.shared
-    // latencies): a thread owns one query row and one 64-key half of the tile, i.e. one swizzled smem chunk.
+    // Four warps per TMEM lane quarter (= per scheduler: they hide each other's tcgen05.ld / MUFU / st.shared
+    // latencies): a thread owns one query row and one 32-key slice of the tile.
     const int quarter = warp & 3;
-    const int half = (warp - 4) >> 2;
+    const int part = (warp - 4) >> 2;            // 32-key slice 0..3
     const int row = quarter * 32 + lane;
     const uint32_t t_lane = tmem + ((uint32_t)(quarter * 32) << 16);
-    const uint32_t t_dp = t_lane + kColDP + 64u * half;
+    const uint32_t t_dp = t_lane + kColDP + 32u * part;
     const uint32_t swz = (uint32_t)(row & 7);
-    const uint32_t tile_off = (uint32_t)half * 16384u + (uint32_t)row * 128u;
+    // slice -> 64-key smem chunk part/2, 16-byte units 4*(part&1) .. +3 of the row
+    const uint32_t tile_off = (uint32_t)(part >> 1) * 16384u + (uint32_t)row * 128u;
+    const uint32_t unit0 = 4u * (uint32_t)(part & 1);
     const f32x2_t sc2 = pk2(p.scale_log2, p.scale_log2);
-    auto store_chunk = [&](uint32_t base, int c, const uint32_t* wv) {   // 32 bf16 of this row -> four swizzled 16-byte units
+    auto store_slice = [&](uint32_t base, const uint32_t* wv) {   // 32 bf16 of this row -> four swizzled 16-byte units
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
-        const uint32_t unit = ((uint32_t)(4 * c + u)) ^ swz;
+        const uint32_t unit = (unit0 + (uint32_t)u) ^ swz;
         st_shared_v4(base + tile_off + unit * 16u, wv[4 * u], wv[4 * u + 1], wv[4 * u + 2], wv[4 * u + 3]);
       }
     };
-    // MODE 2: dQ partial of pair gg (32 rows x 32 columns per warp) -> swizzled staging tile -> TMA reduce-add into
-    // the fp32 dQ accumulator [batch][seq][heads*64]; rows past the end of the sequence are clipped by TMA
-    const uint32_t stage_dq = raw + kOffDQ + (uint32_t)(warp - 4) * 4096u;
+    // MODE 2: dQ partial of pair gg -> swizzled staging tile -> TMA reduce-add into the fp32 dQ accumulator
+    // [batch][seq][heads*64]; rows past the end of the sequence are clipped by TMA.  Slices 0 and 1 do it (32 rows x
+    // 32 columns per warp); the other two warps of the quarter run ahead into the next pair's exponentials.
+    const uint32_t stage_dq = raw + kOffDQ + (uint32_t)((part & 1) * 4 + quarter) * 4096u;
     auto drain_dq = [&](uint32_t gg, int hq, int qt, int bb) {
       const uint32_t bq = gg & 1u;
       mbar_wait(dq_full(bq), (gg >> 1) & 1u);
       tc_fence_after();
       uint32_t r[32];
-      tmem_ld32(t_lane + kColDQ + 64u * bq + 32u * half, r);
+      tmem_ld32(t_lane + kColDQ + 64u * bq + 32u * part, r);
       tmem_wait_ld();
       tc_fence_before();
       if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // the previous reduce has read the tile
@@ -418,11 +435,12 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
       if (lane == 0) {
         asm volatile(
             "cp.reduce.async.bulk.tensor.3d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3, %4}], [%1];"
-            ::"l"(reinterpret_cast<uint64_t>(&tm_dq)), "r"(stage_dq), "r"(hq * kDH + 32 * half),
+            ::"l"(reinterpret_cast<uint64_t>(&tm_dq)), "r"(stage_dq), "r"(hq * kDH + 32 * part),
               "r"(qt * kB + 32 * quarter), "r"(bb) : "memory");
         asm volatile("cp.async.bulk.commit_group;" ::: "memory");
       }
     };
+    const bool drains = MODE == 2 && part < 2;
     uint32_t g = 0, n = 0;
     for (int w = blockIdx.x; w < num_items; w += gridDim.x, ++n) {
       const Item it = decode_item<MODE>(p, w, G);
@@ -451,23 +469,22 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
           qt = it.fixed_tile; kt = t;
         }
         const int qrow = qt * kB + row;
-        const int kcol0 = kt * kB + 64 * half;
+        const int kcol0 = kt * kB + 32 * part;
         const bool diag = qt == kt;
         const f32x2_t nl2 = pk2(-lse, -lse), dl2 = pk2(dl, dl);
         const uint32_t bf = MODE == 2 ? 0u : g & 1u;
-        const uint32_t t_s = t_lane + kColS + 128u * bf + 64u * half;
-        // ---- phase A: P = exp2(S*c - lse) for this thread's 64 keys (kept in registers for phase B) ----
-        f32x2_t P2[32];
+        const uint32_t t_s = t_lane + kColS + 128u * bf + 32u * part;
+        // ---- phase A: P = exp2(S*c - lse) for this thread's 32 keys (kept in registers for phase B) ----
+        f32x2_t P2[16];
         mbar_wait(s_full(bf), MODE == 2 ? g & 1u : (g >> 1) & 1u);
         tc_fence_after();
         {
-          uint32_t rs[64];
-          tmem_ld32(t_s, rs);           // both 32-key chunks in flight before the first use
-          tmem_ld32(t_s + 32, rs + 32);
+          uint32_t rs[32];
+          tmem_ld32(t_s, rs);
           tmem_wait_ld();
           if (diag) {                   // warp-uniform; only the diagonal pair carries masking code
 #pragma unroll
-            for (int i = 0; i < 64; i += 2) {
+            for (int i = 0; i < 32; i += 2) {
               float e0, e1;
               upk2(fma2(pk2(__uint_as_float(rs[i]), __uint_as_float(rs[i + 1])), sc2, nl2), e0, e1);
               const float p0 = kcol0 + i > qrow ? 0.f : ex2(e0);
@@ -476,7 +493,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
             }
           } else {
 #pragma unroll
-            for (int i = 0; i < 64; i += 2) {
+            for (int i = 0; i < 32; i += 2) {
               float e0, e1;
               upk2(fma2(pk2(__uint_as_float(rs[i]), __uint_as_float(rs[i + 1])), sc2, nl2), e0, e1);
               P2[i >> 1] = pk2(ex2(e0), ex2(e1));
@@ -485,74 +502,79 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
         }
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(s_free(bf));          // S(g+2) may overwrite this buffer
+        if (lane == 0) mbar_arrive(s_free(bf));          // the next S into this buffer may be issued
         if (MODE != 1) {
           if (g > 0) mbar_wait(pds_free, (g - 1) & 1u);  // the previous pair's gradient UMMAs are done with the tiles
+          uint32_t wp[16];
 #pragma unroll
-          for (int c = 0; c < 2; ++c) {
-            uint32_t wp[16];
-#pragma unroll
-            for (int i = 0; i < 16; ++i) wp[i] = f32x2_to_bf16x2(P2[16 * c + i]);
-            store_chunk(sP, c, wp);
-          }
+          for (int i = 0; i < 16; ++i) wp[i] = f32x2_to_bf16x2(P2[i]);
+          store_slice(sP, wp);
         }
         // ---- phase B: dS' = P * (dP - D) ----
         mbar_wait(dp_full, g & 1u);
         tc_fence_after();
         {
-          uint32_t rd[64];
+          uint32_t rd[32];
           tmem_ld32(t_dp, rd);
-          tmem_ld32(t_dp + 32, rd + 32);
           tmem_wait_ld();
           if (MODE == 1 && g > 0) mbar_wait(pds_free, (g - 1) & 1u);
+          uint32_t wd[16];
 #pragma unroll
-          for (int c = 0; c < 2; ++c) {
-            uint32_t wd[16];
-#pragma unroll
-            for (int i = 0; i < 16; ++i)
-              wd[i] = f32x2_to_bf16x2(mul2(P2[16 * c + i], sub2(pk2(__uint_as_float(rd[32 * c + 2 * i]),
-                                                                    __uint_as_float(rd[32 * c + 2 * i + 1])), dl2)));
-            store_chunk(sDS, c, wd);
-          }
+          for (int i = 0; i < 16; ++i)
+            wd[i] = f32x2_to_bf16x2(mul2(P2[i], sub2(pk2(__uint_as_float(rd[2 * i]), __uint_as_float(rd[2 * i + 1])), dl2)));
+          store_slice(sDS, wd);
         }
         tc_fence_before();
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy stores -> visible to the UMMAs
         __syncwarp();
         if (lane == 0) mbar_arrive(pds_full);
-        if (MODE == 2 && t > 0)   // the previous pair's dQ partial: its UMMAs ran while this pair was exponentiated
+        if (drains && t > 0)   // the previous pair's dQ partial: its UMMAs ran while this pair was exponentiated
           drain_dq(g - 1, it.hk * G + (t - 1) / it.per_head, it.fixed_tile + (t - 1) % it.per_head, it.b);
       }
-      if (MODE == 2)
+      if (drains)
         drain_dq(g - 1, it.hk * G + (it.n_iter - 1) / it.per_head, it.fixed_tile + (it.n_iter - 1) % it.per_head, it.b);
-      // ---- accumulators -> (x softmax scale for dK, dQ) -> bf16 -> the gradient buffer ----
+      // ---- accumulators -> (x softmax scale for dK) -> bf16 -> the gradient buffer ----
       mbar_wait(acc_full, n & 1u);
       tc_fence_after();
-      const int orow = it.fixed_tile * kB + row;   // key row (MODE 0) or query row (MODE 1)
-      // MODE 0: warps 4-7 write dV (accumulator 0), warps 8-11 dK (accumulator 1), 64 columns each;
-      // MODE 1: the two warps of a quarter split dQ's 64 columns
-      const uint32_t t_acc = t_lane + (MODE != 1 ? (half == 0 ? kColAcc0 : kColAcc1) : kColAcc0 + 32u * half);
-      const int col = MODE != 1 ? (half == 0 ? p.v_off : p.k_off) + it.hk * kDH : p.q_off + it.hx * kDH + 32 * half;
-      const float oscale = (MODE != 1 && half == 0) ? 1.f : p.scale;
-      uint32_t r[MODE != 1 ? 64 : 32];
-      tmem_ld32(t_acc, r);
-      if (MODE != 1) tmem_ld32(t_acc + 32, r + 32);
-      tmem_wait_ld();
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(acc_free);    // the next item's gradient UMMAs may overwrite the accumulators
-      if (orow < p.seq) {
-        __nv_bfloat16* dst = p.dqkv + ((int64_t)it.b * p.seq + orow) * p.ld_d + col;
-#pragma unroll
-        for (int c = 0; c < (MODE != 1 ? 2 : 1); ++c) {
+      const int orow = it.fixed_tile * kB + row;   // key row (MODE 0, 2) or query row (MODE 1)
+      if (MODE != 1) {
+        // slices 0, 1 write the two 32-column halves of dV (accumulator 0), slices 2, 3 those of dK (accumulator 1)
+        const uint32_t t_acc = t_lane + ((part >> 1) == 0 ? kColAcc0 : kColAcc1) + 32u * (uint32_t)(part & 1);
+        const int col = ((part >> 1) == 0 ? p.v_off : p.k_off) + it.hk * kDH + 32 * (part & 1);
+        const float oscale = (part >> 1) == 0 ? 1.f : p.scale;
+        uint32_t r[32];
+        tmem_ld32(t_acc, r);
+        tmem_wait_ld();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(acc_free);    // the next item's gradient UMMAs may overwrite the accumulators
+        if (orow < p.seq) {
+          __nv_bfloat16* dst = p.dqkv + ((int64_t)it.b * p.seq + orow) * p.ld_d + col;
           float fv[32];
 #pragma unroll
-          for (int i = 0; i < 32; ++i) fv[i] = __uint_as_float(r[32 * c + i]) * oscale;
+          for (int i = 0; i < 32; ++i) fv[i] = __uint_as_float(r[i]) * oscale;
 #pragma unroll
-          for (int v = 0; v < 4; ++v) *reinterpret_cast<uint4*>(dst + 32 * c + 8 * v) = pack8(fv + 8 * v);
+          for (int v = 0; v < 4; ++v) *reinterpret_cast<uint4*>(dst + 8 * v) = pack8(fv + 8 * v);
+        }
+      } else {
+        // dQ: the four slices write 16 columns each
+        uint32_t r[16];
+        tmem_ld16(t_lane + kColAcc0 + 16u * part, r);
+        tmem_wait_ld();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(acc_free);
+        if (orow < p.seq) {
+          __nv_bfloat16* dst = p.dqkv + ((int64_t)it.b * p.seq + orow) * p.ld_d + p.q_off + it.hx * kDH + 16 * part;
+          float fv[16];
+#pragma unroll
+          for (int i = 0; i < 16; ++i) fv[i] = __uint_as_float(r[i]) * p.scale;
+#pragma unroll
+          for (int v = 0; v < 2; ++v) *reinterpret_cast<uint4*>(dst + 8 * v) = pack8(fv + 8 * v);
         }
       }
     }
-    if (MODE == 2 && lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");  // reductions complete before exit
+    if (drains && lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");  // reductions complete before exit
     tc_fence_before();
   }
 
