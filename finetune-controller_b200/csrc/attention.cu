@@ -19,13 +19,11 @@
 //
 // Work per (batch, head): T^2/2 * 64 * 4 FLOP (causal); per 128x128 tile the tensor pipe needs 512
 // cycles, the special-function unit 1024 (exp2 at 16/clk/SM): the kernel is bound by MUFU.
-#include <cuda.h>
-#include <mutex>
 #include <stdlib.h>
-#include "common.cuh"
-#include "../../include/b200ft.h"
+#include "attn_common.cuh"
 
 namespace {
+using namespace b200ft_attn;
 
 constexpr int kDH = 64;
 constexpr int kBQ = 128, kBK = 128;
@@ -38,7 +36,6 @@ constexpr int kSmemBytes = kTiles + 256;        // + barriers; no alignment slac
 constexpr int kTmemCols = 512;
 constexpr uint32_t kColS = 0, kColPV = 256, kColP = 384;  // + 128*g, + 64*g, + 64*g (P: bf16 pairs, 64 columns)
 constexpr float kRescaleThreshold = 8.0f;       // log2 units: p stays below 2^8
-constexpr long long kWaitLimit = 4000000000ll;
 
 struct AttnParams {
   int batch, seq, n_head, n_kv_head;
@@ -49,93 +46,6 @@ struct AttnParams {
   float* lse2;              // [batch*n_head, seq]: reference max + log2(row sum), log2 domain incl. scale
 };
 
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-  uint32_t done = 0;
-  long long t0 = 0;
-  while (true) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-        "selp.u32 %0, 1, 0, p;\n\t}"
-        : "=r"(done) : "r"(bar), "r"(parity) : "memory");
-    if (done) break;
-    if (t0 == 0) t0 = clock64();
-    else if (clock64() - t0 > kWaitLimit) __trap();  // deadlock guard
-  }
-}
-__device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* map, int c0, int c1, int c2, uint32_t bar) {
-  asm volatile(
-      "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
-      ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(c0), "r"(c1), "r"(c2), "r"(bar) : "memory");
-}
-__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void umma(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
-  asm volatile(
-      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
-      ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc) : "memory");
-}
-__device__ __forceinline__ void umma_commit(uint32_t bar) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* r) {
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-      "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,"
-      "%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
-      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
-        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
-        "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
-        "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
-      : "r"(taddr) : "memory");
-}
-__device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t* w) {
-  asm volatile(
-      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
-      "{%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16};"
-      ::"r"(taddr), "r"(w[0]), "r"(w[1]), "r"(w[2]), "r"(w[3]), "r"(w[4]), "r"(w[5]), "r"(w[6]), "r"(w[7]),
-        "r"(w[8]), "r"(w[9]), "r"(w[10]), "r"(w[11]), "r"(w[12]), "r"(w[13]), "r"(w[14]), "r"(w[15]) : "memory");
-}
-__device__ __forceinline__ void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
-// D[tmem] (+)= A[tmem] * B[smem descriptor]
-__device__ __forceinline__ void umma_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
-  asm volatile(
-      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
-      ::"r"(d_tmem), "r"(a_tmem), "l"(bdesc), "r"(idesc), "r"(acc) : "memory");
-}
-__device__ __forceinline__ void tmem_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
-__device__ __forceinline__ float ex2(float x) {
-  float y;
-  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
-  return y;
-}
-__device__ __forceinline__ bool elect_one() {
-  uint32_t pred;
-  asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
-  return pred != 0;
-}
-// smem matrix descriptor words (SW128): lo = start>>4 | LBO>>4 << 16, hi = SBO>>4 | version 1 | swizzle 128B
-__device__ __forceinline__ uint64_t sdesc(uint32_t addr, uint32_t lbo, uint32_t sbo) {
-  const uint32_t lo = ((addr & 0x3FFFFu) >> 4) | (((lbo >> 4) & 0x3FFFu) << 16);
-  const uint32_t hi = ((sbo >> 4) & 0x3FFFu) | (1u << 14) | (2u << 29);
-  return ((uint64_t)hi << 32) | lo;
-}
-// kind::f16 instruction descriptor: fp32 accumulate, bf16 x bf16, M = 128
-__device__ __forceinline__ uint32_t idesc(int n, int b_mn) {
-  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)b_mn << 16) | ((uint32_t)(n >> 3) << 17) | (8u << 24);
-}
 
 
 // One sweep over a 128-key score tile of this thread's query row: p = exp2(s*scale - m_ref) -> bf16 P in
@@ -264,8 +174,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm, const AttnParams p) {
   } else if (warp == 1) {
     // ================================ MMA issuer ================================
     const bool issuer = elect_one();
-    const uint32_t id_s = idesc(kBK, 0);   // S: N = 128 keys, K-major B (K_j rows = keys, d_head contiguous)
-    const uint32_t id_pv = idesc(kDH, 1);  // PV: N = 64, MN-major B (V_j rows = keys = reduction index)
+    const uint32_t id_s = idesc(kBK, 0, 0);   // S: N = 128 keys, K-major B (K_j rows = keys, d_head contiguous)
+    const uint32_t id_pv = idesc(kDH, 0, 1);  // PV: N = 64, MN-major B (V_j rows = keys = reduction index)
     auto issue_s = [&](int g, int st) {    // S_g = Q_g K^T
       if (issuer) {
 #pragma unroll
@@ -428,22 +338,6 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm, const AttnParams p) {
   }
 }
 
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
-                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
-                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-EncodeTiledFn encode_fn() {
-  static EncodeTiledFn fn = nullptr;
-  static std::once_flag once;
-  std::call_once(once, [] {
-    void* f = nullptr;
-    cudaDriverEntryPointQueryResult q;
-    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) == cudaSuccess &&
-        q == cudaDriverEntryPointSuccess)
-      fn = (EncodeTiledFn)f;
-  });
-  return fn;
-}
-
 }  // namespace
 
 extern "C" int b200ft_attn_fwd(const void* qkv, int64_t ld, int q_off, int k_off, int v_off, void* out,
@@ -464,14 +358,7 @@ extern "C" int b200ft_attn_fwd(const void* qkv, int64_t ld, int q_off, int k_off
   if (!enc) { b200ft_set_error("attn_fwd: cuTensorMapEncodeTiled unavailable"); return B200FT_ERR_UNSUPPORTED; }
   // the fused buffer as [batch][seq][columns]: rows past the end of a sequence are zero-filled by TMA
   CUtensorMap tm;
-  cuuint64_t dims[3] = {(cuuint64_t)ld, (cuuint64_t)seq, (cuuint64_t)batch};
-  cuuint64_t strides[2] = {(cuuint64_t)ld * 2, (cuuint64_t)ld * 2 * (cuuint64_t)seq};
-  cuuint32_t box[3] = {kDH, kBQ, 1};
-  cuuint32_t estr[3] = {1, 1, 1};
-  CUresult r = enc(&tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(qkv), dims, strides, box, estr,
-                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  if (r != CUDA_SUCCESS) { b200ft_set_error("attn_fwd: cuTensorMapEncodeTiled failed (%d)", (int)r); return B200FT_ERR_ARG; }
+  if (int rc = make_map(enc, &tm, qkv, ld, seq, batch)) return rc;
   AttnParams p;
   p.batch = batch; p.seq = seq; p.n_head = n_head; p.n_kv_head = n_kv_head;
   p.q_off = q_off; p.k_off = k_off; p.v_off = v_off;

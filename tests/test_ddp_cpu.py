@@ -67,3 +67,53 @@ def test_layer_buckets_partition():
     assert layer_buckets(12, 2) == [(6, 12), (0, 6)]
     assert layer_buckets(12, 1) == [(0, 12)]
     assert layer_buckets(3, 8) == [(2, 3), (1, 2), (0, 1)]
+
+
+class FakeFullEngine:
+    """grad_views() of the full-parameter engine in miniature: a layer slice per bucket, the head on the top
+    bucket, the embedding table and the norm gains on the bottom one."""
+
+    def __init__(self, n_layer, rank):
+        g = torch.Generator().manual_seed(200 + rank)
+        self.n_layer = n_layer
+        self.G = torch.randn(n_layer * 32, generator=g)
+        self.head, self.embed, self.Gn = (torch.randn(n, generator=g) for n in (24, 40, 7))
+
+    def grad_views(self, lo, hi):
+        out = [self.G[lo * 32: hi * 32]]
+        if hi == self.n_layer:
+            out.append(self.head)
+        if lo == 0:
+            out += [self.embed, self.Gn]
+        return out
+
+
+def _worker_two_groups(rank, world, port, n_layer, out_dir):
+    sys.path.insert(0, PKG)
+    os.environ.update(RANK=str(rank), WORLD_SIZE=str(world), LOCAL_RANK=str(rank), MASTER_ADDR="127.0.0.1",
+                      MASTER_PORT=str(port))
+    from b200ft import ddp
+    ddp.init_process_group_from_env("gloo")
+    overlap = dist.new_group(backend="gloo")      # stands in for ddp.overlap_group(k), which is NCCL-only
+    eng = FakeFullEngine(n_layer, rank)
+    sync = ddp.BucketedGradSync(n_layer, n_buckets=n_layer, group=overlap, reserve_ctas=8, use_tail_group=True)
+    assert sync.group is overlap and sync.tail_group is None and sync.reserve_ctas == 8
+    for l in range(n_layer - 1, -1, -1):
+        sync(eng, l)
+    sync(eng, -1)
+    torch.save({k: getattr(eng, k) for k in ("G", "head", "embed", "Gn")}, os.path.join(out_dir, f"g{rank}.pt"))
+    dist.destroy_process_group()
+
+
+def test_per_layer_buckets_on_overlap_group_and_tail_on_default_group(tmp_path):
+    """The full-parameter configuration: one bucket per layer on the (CTA-limited) overlap communicator, the bottom
+    bucket — nothing left to overlap with — on the default one; every gradient is summed exactly once."""
+    sys.path.insert(0, PKG)
+    from b200ft import ddp
+    world, n_layer = 2, 4
+    mp.spawn(_worker_two_groups, args=(world, ddp.free_port(), n_layer, str(tmp_path)), nprocs=world, join=True)
+    outs = [torch.load(tmp_path / f"g{r}.pt") for r in range(world)]
+    for k in ("G", "head", "embed", "Gn"):
+        expect = sum(getattr(FakeFullEngine(n_layer, r), k) for r in range(world))
+        for o in outs:
+            torch.testing.assert_close(o[k], expect)
