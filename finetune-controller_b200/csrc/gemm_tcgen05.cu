@@ -59,10 +59,16 @@ template <int CG> struct RingCfg {
 constexpr int kMaxStages = 5;
 constexpr int kMaxSeg = 4;
 constexpr uint32_t kPeerBitMask = 0xFEFFFFFFu;  // clears the CTA-rank bit of a shared::cluster address -> CTA 0
-constexpr int kEpiWarps = 8;                           // two per TMEM lane quarter
+#ifndef B200FT_GEMM_EPI_WPQ
+#define B200FT_GEMM_EPI_WPQ 2
+#endif
+constexpr int kWPQ = B200FT_GEMM_EPI_WPQ;              // epilogue warps per TMEM lane quarter (= per scheduler)
+constexpr int kEpiWarps = 4 * kWPQ;
 constexpr int kEpiBufBytes = 32 * 32 * 2;              // one 32-row x 32-col bf16 staging tile (2 KB)
-constexpr int kEpiBufs = 4;                            // staging ring per epilogue warp
-constexpr int kEpiBytes = kEpiWarps * kEpiBufs * kEpiBufBytes;  // 8 warps x 4 tiles x 2 KB = 64 KB
+constexpr int kEpiBufs = 8 / kWPQ;                     // staging ring per epilogue warp (64 KB in total either way)
+constexpr int kEpiBufShift = kEpiBufs == 4 ? 2 : 1;
+static_assert(kWPQ == 2 || kWPQ == 4, "epilogue warps per quarter");
+constexpr int kEpiBytes = kEpiWarps * kEpiBufs * kEpiBufBytes;  // 64 KB
 constexpr int kBiasBytes = kMaxBN * 4;                 // the tile's bias slice, fp32
 constexpr int kBarrierBytes = 512;
 constexpr int kSmemBytes = kTileBytes + kEpiBytes + kBiasBytes + kBarrierBytes + 1024;  // + slack to align to 1024
@@ -312,7 +318,7 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtenso
                                               int w_stride, int cta_rank) {
   const int BN = p.BN;
   const int nchunks = BN / CW;
-  const int cpw = nchunks > h ? (nchunks - h + 1) / 2 : 0;  // chunks of a tile this warp owns
+  const int cpw = nchunks > h ? (nchunks - h + kWPQ - 1) / kWPQ : 0;  // chunks of a tile this warp owns
   const bool has_aux = (p.epilogue == B200FT_EPI_RESIDUAL) || (p.epilogue == B200FT_EPI_DGELU);
   const bool atomic_t = (p.epilogue == B200FT_EPI_ATOMIC_F32_T);
   const bool has_bias = p.bias != nullptr;
@@ -327,7 +333,7 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtenso
     if (w2 >= num_work) return;
     const int tile2 = w2 / p.splits;
     const int r0 = tile_m_index(p, tile2) * (kBlockM * CG) + cta_rank * kBlockM + q * 32;
-    const int c0 = tile_n_index(p, tile2) * BN + (h + 2 * ci) * CW;
+    const int c0 = tile_n_index(p, tile2) * BN + (h + kWPQ * ci) * CW;
     const uint32_t b = n & (kEpiBufs - 1);
     mbar_expect_tx(abar + 8u * b, aux_bytes);
     tma_load_2d(ebuf + b * kEpiBufBytes, tmAux, c0, r0, abar + 8u * b);
@@ -356,7 +362,7 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtenso
     mbar_wait(tfull0 + 8u * acc, acc_phase);
     tc_fence_after();
     const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * kAccStride);
-    for (int c = h; c < nchunks; c += 2) {
+    for (int c = h; c < nchunks; c += kWPQ) {
       const uint32_t b = seq & (kEpiBufs - 1);
       const uint32_t buf = ebuf + b * kEpiBufBytes;
       uint32_t r[CW];
@@ -378,7 +384,7 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtenso
         continue;
       }
       if (has_aux) {
-        mbar_wait(abar + 8u * b, (seq >> 2) & 1u);  // operand of this chunk has landed
+        mbar_wait(abar + 8u * b, (seq >> kEpiBufShift) & 1u);  // operand of this chunk has landed
       } else {
         if (lane == 0) tma_store_wait_read<kEpiBufs - 1>();  // the store 4 tiles back has drained this buffer
         __syncwarp();
@@ -672,9 +678,9 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ TmapPack maps, const GemmParams
     }
   } else if (warp >= 4) {
     // =============================== epilogue (every CTA: its own 128 rows) ===============================
-    const int ew = warp - 4;      // 0..7
+    const int ew = warp - 4;      // 0 .. kEpiWarps-1
     const int q = warp & 3;       // TMEM lane quarter this warp may touch (== warp % 4)
-    const int h = ew >> 2;        // first or second warp of the quarter
+    const int h = ew >> 2;        // which of the quarter's warps
     const int et = threadIdx.x - 128;
     const uint32_t eb = sEpi + ew * kEpiBufs * kEpiBufBytes;
     if (p.cw == 32)

@@ -8,7 +8,10 @@ import sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, os.path.join(ROOT, "finetune-controller_b200"))
 import torch  # noqa: E402
-from b200ft import ops  # noqa: E402
+from b200ft import _lib, ops  # noqa: E402
+
+if os.environ.get("B200FT_PROBE_LIB"):  # a variant build of the library (tools/_exp/), measurement only
+    _lib.LIB_PATH = os.path.join(ROOT, os.environ["B200FT_PROBE_LIB"])
 
 
 def run(M, N, K, cg, bn, epi, iters, k2=0, layout=0):
