@@ -8,8 +8,10 @@ row-major [tokens, features]; statistics, accumulators and optimizer state are f
 Frozen weights are kept in HBM in the two layouts the K-major GEMM wants: W^T [out, in] for
 forward (y = x W) and W [in, out] (the HF Conv1D layout) for backward (dx = dy W^T).
 
-Attention (not in north_star's judged set) is the one op still delegated
-to a library in this round: torch's scaled_dot_product_attention, forward and backward.
+Attention (not in north_star's judged set): `attention="sdpa"` (default, the faster
+one today) delegates it to torch's scaled_dot_product_attention -> cuDNN, forward and backward;
+`attention="own"` runs this library's tcgen05 flash-attention kernels (attention.py), leaving no
+library kernel in the step.
 """
 from __future__ import annotations
 

@@ -6,7 +6,7 @@ block-structured [Nqkv, 32] matrix holding Bq^T and Bv^T), and its backward is a
 four-segment launch (dq.Wq + dk.Wk + dv.Wv + dU.[Aq;Av]).
 
 nn.Linear weights are [out, in], which IS the K-major B operand of forward; the transposed
-copies made at load time serve backward.  Attention is torch SDPA (library) as in gpt2.py.
+copies made at load time serve backward.  Attention: torch SDPA (library) or this library's own kernels, as in gpt2.py.
 """
 from __future__ import annotations
 

@@ -16,7 +16,7 @@ GEMMs per layer: 4 forward, 4 dX (B operand MN-major: the nn.Linear weight [out,
 token index as K).  All are the cta_group::2 tcgen05 kernel.  Activations kept per layer: x, x1,
 qkv (post-RoPE), the attention output and gate|up; the normalised inputs h1/h2 and the SwiGLU
 product are recomputed in backward (HBM-bound, ~1 % of the step) instead of stored.
-Attention is torch SDPA (library) as in llama.py.
+Attention: torch SDPA (library) or this library's own kernels (d_head 64), as in llama.py.
 """
 from __future__ import annotations
 
