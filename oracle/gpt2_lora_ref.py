@@ -270,7 +270,7 @@ class OracleTrainer:
             logits = forward(self.base, self.adapters, bi, self.cfg, self.lora)
             loss = causal_lm_loss(logits, bl) / len(batches)
             loss.backward()
-            total += float(loss)
+            total += float(loss.detach())
         if self.opt_cfg.max_grad_norm > 0:
             torch.nn.utils.clip_grad_norm_(list(self.trainable.values()), self.opt_cfg.max_grad_norm)
         self.last_grads = {k: t.grad.detach().clone() for k, t in self.trainable.items()}
