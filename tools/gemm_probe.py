@@ -14,7 +14,7 @@ if os.environ.get("B200FT_PROBE_LIB"):  # a variant build of the library (tools/
     _lib.LIB_PATH = os.path.join(ROOT, os.environ["B200FT_PROBE_LIB"])
 
 
-def run(M, N, K, cg, bn, epi, iters, k2=0, layout=0):
+def run(M, N, K, cg, bn, epi, iters, k2=0, layout=0, max_ctas=0):
     dev = "cuda:0"
     a_mn, b_mn = bool(layout & 1), bool(layout & 2)
     a = torch.randn((K, M) if a_mn else (M, K), device=dev).to(torch.bfloat16)
@@ -30,12 +30,12 @@ def run(M, N, K, cg, bn, epi, iters, k2=0, layout=0):
         kw["b2"] = torch.randn(N, k2, device=dev).to(torch.bfloat16)
     bias = torch.randn(N, device=dev)
     for _ in range(3):
-        ops.gemm(a, b, out, a_mn=a_mn, b_mn=b_mn, epilogue=epi, bias=bias, block_n=bn, cta_group=cg, **kw)
+        ops.gemm(a, b, out, a_mn=a_mn, b_mn=b_mn, epilogue=epi, bias=bias, block_n=bn, cta_group=cg, max_ctas=max_ctas, **kw)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     torch.cuda.synchronize()
     e0.record()
     for _ in range(iters):
-        ops.gemm(a, b, out, a_mn=a_mn, b_mn=b_mn, epilogue=epi, bias=bias, block_n=bn, cta_group=cg, **kw)
+        ops.gemm(a, b, out, a_mn=a_mn, b_mn=b_mn, epilogue=epi, bias=bias, block_n=bn, cta_group=cg, max_ctas=max_ctas, **kw)
     e1.record()
     torch.cuda.synchronize()
     us = e0.elapsed_time(e1) * 1e3 / iters
@@ -50,6 +50,7 @@ if __name__ == "__main__":
     ap.add_argument("--layout", type=int, default=0, help="1 = A MN-major, 2 = B MN-major, 3 = both")
     ap.add_argument("--bns", default="128,192,256")
     ap.add_argument("--iters", type=int, default=20)
+    ap.add_argument("--max-ctas", type=int, default=0, help="run on this many CTAs only (0 = all SMs)")
     ap.add_argument("--out", default="")
     args = ap.parse_args()
     rows = []
@@ -57,7 +58,7 @@ if __name__ == "__main__":
         M, N, K, epi = (int(x) for x in sh.split("x"))
         for cg in (int(x) for x in args.cgs.split(",")):
             for bn in (int(x) for x in args.bns.split(",")):
-                us, tf = run(M, N, K, cg, bn, epi, args.iters, layout=args.layout)
+                us, tf = run(M, N, K, cg, bn, epi, args.iters, layout=args.layout, max_ctas=args.max_ctas)
                 rows.append({"M": M, "N": N, "K": K, "epi": epi, "cg": cg, "bn": bn, "layout": args.layout, "us": us, "tflops": tf})
                 print(f"M={M} N={N} K={K} epi={epi} layout={args.layout} cg={cg} bn={bn:3d}: {us:9.1f} us  {tf:7.1f} TFLOP/s", flush=True)
     if args.out:
