@@ -219,9 +219,11 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
       tc_fence_after();
       const uint32_t aq = MODE != 1 ? sS0(st) : sF0, bk = MODE != 1 ? sF0 : sS0(st);
       if (issuer) {
+#ifndef B200FT_EXP_NO_SDP
 #pragma unroll
         for (int k = 0; k < kDH / 16; ++k)
           umma(tmem + kColS + 128u * bf, sdesc(aq + 32 * k, 16, 1024), sdesc(bk + 32 * k, 16, 1024), id_s, k > 0);
+#endif
         umma_commit(s_full(bf));
       }
       __syncwarp();
@@ -230,9 +232,11 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
       const uint32_t st = gg % kRing;
       const uint32_t ado = MODE != 1 ? sS1(st) : sF1, bv = MODE != 1 ? sF1 : sS1(st);
       if (issuer) {
+#ifndef B200FT_EXP_NO_SDP
 #pragma unroll
         for (int k = 0; k < kDH / 16; ++k)
           umma(tmem + kColDP, sdesc(ado + 32 * k, 16, 1024), sdesc(bv + 32 * k, 16, 1024), id_s, k > 0);
+#endif
         umma_commit(dp_full);
         if (MODE != 2 && last_of_item) umma_commit(f_empty);   // nothing of this item reads the resident pair any more
       }
@@ -316,6 +320,9 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
         const uint32_t unit = (unit0 + (uint32_t)u) ^ swz;
+#ifdef B200FT_EXP_NO_STORE
+        if (wv[4 * u] == 0x12345678u)   // practically never: the stores are compiled but not executed
+#endif
         st_shared_v4(base + tile_off + unit * 16u, wv[4 * u], wv[4 * u + 1], wv[4 * u + 2], wv[4 * u + 3]);
       }
     };
@@ -327,6 +334,12 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
       const uint32_t bq = gg & 1u;
       mbar_wait(dq_full(bq), (gg >> 1) & 1u);
       tc_fence_after();
+#ifdef B200FT_EXP_NO_DRAIN
+      __syncwarp();
+      if (lane == 0) mbar_arrive(dq_free(bq));
+      (void)hq; (void)qt; (void)bb;
+      return;
+#endif
       uint32_t r[32];
       tmem_ld32(t_lane + kColDQ + 64u * bq + 32u * part, r);
       tmem_wait_ld();
