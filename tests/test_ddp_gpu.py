@@ -126,7 +126,12 @@ def _rank_full(rank, world, port, out_dir):
     eng = llama_full.LlamaFullStep(dims, gpt2.OptSpec(opt.lr, opt.beta1, opt.beta2, opt.eps, opt.weight_decay,
                                                       opt.max_grad_norm), base, batch=2, seq=32,
                                    device=f"cuda:{rank}", world_size=world,
-                                   grad_sync=ddp.BucketedGradSync(cfg.n_layer, n_buckets=cfg.n_layer))
+                                   # the production configuration of bench.py / train.py: per-layer buckets on a
+                                   # CTA-limited communicator, SMs reserved in the backward GEMMs, tail on the default group
+                                   grad_sync=ddp.BucketedGradSync(cfg.n_layer, n_buckets=cfg.n_layer,
+                                                                  group=ddp.overlap_group(8), reserve_ctas=8,
+                                                                  use_tail_group=True))
+    assert eng.bwd_ctas == 148 - 16
     losses = []
     for s in range(2):
         ids, labels = ref.synthetic_batch(cfg, 2, 32, seed=500 + 10 * s, rank=rank)
