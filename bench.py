@@ -199,7 +199,7 @@ def run_ours(args) -> None:
     # random-init weights; B drawn at random (not PEFT's zero) so every gradient path carries data
     eng, dims = params.build_engine(model, lora, opt, batch=BATCH, seq=SEQ, device=dev, seed=0, world_size=world,
                                     grad_sync=sync, randomize_b=True, mode="full" if full else "lora",
-                                    attention=args.attention)
+                                    attention=args.attention, overlap_optimizer=args.overlap_optimizer)
     g = torch.Generator().manual_seed(1234 + rank)
     n_sets = 4
     host = [torch.randint(0, dims.vocab, (BATCH, SEQ), generator=g, dtype=torch.int64).pin_memory()
@@ -363,6 +363,9 @@ def main():
     ap.add_argument("--attention", default="sdpa", choices=["sdpa", "own"],
                     help="sdpa: torch SDPA (cuDNN, library; faster today); own: this repo's tcgen05 attention kernels "
                          "(d_head 64 models), i.e. a step with no library kernel in it")
+    ap.add_argument("--overlap-optimizer", action="store_true",
+                    help="full-parameter workloads: per-layer AdamW launches on a second stream beside backward instead "
+                         "of one launch after it (measured slower under the power cap; A/B measurement)")
     ap.add_argument("--detail", default="", help="write per-shape GEMM timings of the instrumented pass to this JSON file")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup

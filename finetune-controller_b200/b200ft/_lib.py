@@ -64,6 +64,8 @@ SIGNATURES = {
     "b200ft_shift_targets": (c_int, [c_void_p, c_void_p, c_int64, c_int, c_int64, c_void_p]),
     "b200ft_adamw_step": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_int64, c_float,
                                   c_float, c_float, c_float, c_float, c_int, c_float, c_void_p, c_void_p]),
+    "b200ft_adamw_step_limited": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_int64, c_float,
+                                          c_float, c_float, c_float, c_float, c_int, c_float, c_void_p, c_int, c_void_p]),
     "b200ft_gradnorm_sq_workspace_bytes": (c_size_t, [c_int64]),
     "b200ft_gradnorm_sq": (c_int, [c_void_p, c_int, c_int64, c_void_p, c_void_p, c_size_t, c_void_p]),
     "b200ft_clip_coef": (c_int, [c_void_p, c_float, c_float, c_void_p, c_void_p]),

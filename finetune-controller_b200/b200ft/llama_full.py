@@ -41,7 +41,7 @@ class LlamaFullStep(StepHostMixin, OwnAttentionMixin):
 
     def __init__(self, dims: LlamaDims, opt: OptSpec, base: dict | None, *, batch: int, seq: int,
                  device="cuda:0", world_size: int = 1, grad_sync=None, seed: int = 0, init_std: float = 0.02,
-                 attention: str = "sdpa"):
+                 attention: str = "sdpa", overlap_optimizer: bool = False):
         if not torch.cuda.is_available():
             raise RuntimeError("LlamaFullStep needs a CUDA device: there is no CPU path")
         assert attention in ("sdpa", "own")
@@ -55,6 +55,14 @@ class LlamaFullStep(StepHostMixin, OwnAttentionMixin):
         # pairs, so each reserved collective CTA may cost a whole TPC
         reserve = getattr(grad_sync, "reserve_ctas", 0) if grad_sync is not None else 0
         self.bwd_ctas = 0 if reserve <= 0 else max(2, ops.NUM_SMS - 2 * reserve)
+        # Option (off: measured slower): the HBM-bound AdamW of layer l on a second stream as soon as that layer's
+        # gradients are final (and, with data parallelism, reduced), beside the backward GEMMs of the layers below.
+        # Needs the final gradient per layer: no global-norm clipping, one all-reduce bucket per layer.
+        # Llama-3-8B, 1 GPU: 247.7 ms/step with it vs 234.3 without — the chip sits at its power cap during the
+        # GEMMs, so the co-running update only lowers their clock and pollutes L2 (GEMMs 1174 -> 899 TFLOP/s).
+        per_layer_sync = grad_sync is None or len(getattr(grad_sync, "buckets", ())) == dims.n_layer
+        self.overlap_opt = bool(overlap_optimizer) and opt.max_grad_norm <= 0 and per_layer_sync
+        self.opt_stream = torch.cuda.Stream(device=self.dev) if self.overlap_opt else None
         self.Nq, self.Nkv = dims.n_head * dims.d_head, dims.n_kv_head * dims.d_head
         self.Nqkv = self.Nq + 2 * self.Nkv
         self._layout()
@@ -315,8 +323,29 @@ class LlamaFullStep(StepHostMixin, OwnAttentionMixin):
                 if not D.tie_embeddings:
                     dW["embed"].zero_()
                 ops.embed_bwd(self.ids.view(-1), dx, dW["embed"], vocab=D.vocab)
+            n_pending = len(self.grad_sync.pending) if self.grad_sync is not None else 0
             if self.grad_sync is not None:
                 self.grad_sync(self, l)
+            if self.overlap_opt:
+                self._update_layer(l, self.grad_sync.pending[n_pending:] if self.grad_sync is not None else ())
+
+    def _adam_kw(self, step: int, coef=None) -> dict:
+        o = self.opt
+        return dict(step=step, lr=o.lr, beta1=o.beta1, beta2=o.beta2, eps=o.eps, weight_decay=o.weight_decay,
+                    grad_scale=1.0 / self.world, grad_scale_dev=coef)
+
+    def _update_layer(self, l: int, reductions) -> None:
+        """AdamW on layer l's slice of the flat group, on the optimizer stream, one block per SM so that the
+        persistent GEMM's CTAs stay resident beside it."""
+        lo, hi = self.layer_off[l], self.layer_off[l + 1]
+        done = torch.cuda.Event()
+        done.record()                                   # every gradient GEMM of the layer has been issued
+        with torch.cuda.stream(self.opt_stream):
+            self.opt_stream.wait_event(done)
+            for work in reductions:                     # and its all-reduce bucket has been summed
+                work.wait()
+            ops.adamw_step(self.P[lo:hi], self.Mo[lo:hi], self.Vo[lo:hi], self.G[lo:hi], shadow=self.S[lo:hi],
+                           max_blocks=ops.NUM_SMS, **self._adam_kw(self.step_count + 1))
 
     @torch.no_grad()
     def optimizer_step(self) -> None:
@@ -331,9 +360,16 @@ class LlamaFullStep(StepHostMixin, OwnAttentionMixin):
             self.norm_sq[0:1].add_(self.norm_sq[1:2])
             ops.clip_coef(self.norm_sq[0:1], self.clip, max_norm=o.max_grad_norm, pre_scale=gs)
             coef = self.clip
-        kw = dict(step=self.step_count, lr=o.lr, beta1=o.beta1, beta2=o.beta2, eps=o.eps,
-                  weight_decay=o.weight_decay, grad_scale=gs, grad_scale_dev=coef)
-        ops.adamw_step(self.P, self.Mo, self.Vo, self.G, shadow=self.S, **kw)
+        kw = self._adam_kw(self.step_count, coef)
+        if self.overlap_opt:
+            # the layers were updated during backward; what is left is the embedding table, an untied lm_head
+            # and the norm gains
+            for lo, hi in ((0, self.layer_off[0]), (self.layer_off[-1], self.n_mat)):
+                if hi > lo:
+                    ops.adamw_step(self.P[lo:hi], self.Mo[lo:hi], self.Vo[lo:hi], self.G[lo:hi], shadow=self.S[lo:hi], **kw)
+            torch.cuda.current_stream().wait_stream(self.opt_stream)
+        else:
+            ops.adamw_step(self.P, self.Mo, self.Vo, self.G, shadow=self.S, **kw)
         ops.adamw_step(self.Pn, self.Mn, self.Vn, self.Gn, **kw)
 
     def step(self, ids: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:

@@ -152,7 +152,7 @@ def shift_targets(labels, targets, ignore_index=-100):
 
 
 def adamw_step(p, m, v, g, *, step, lr, beta1, beta2, eps, weight_decay, shadow=None, grad_scale=1.0,
-               grad_scale_dev=None):
+               grad_scale_dev=None, max_blocks=0):
     global LAUNCHES
     _need_cuda(p, m, v, g, shadow, grad_scale_dev)
     assert p.dtype == m.dtype == v.dtype == torch.float32
@@ -161,9 +161,9 @@ def adamw_step(p, m, v, g, *, step, lr, beta1, beta2, eps, weight_decay, shadow=
     assert m.numel() == n and v.numel() == n and g.numel() == n
     per = 24 + g.element_size() + (2 if shadow is not None else 0)
     with _timed("adamw", float(per) * n):
-        check(lib().b200ft_adamw_step(_p(p), _p(m), _p(v), _p(g), int(g.dtype == torch.bfloat16), _p(shadow), n,
-                                      lr, beta1, beta2, eps, weight_decay, step, grad_scale, _p(grad_scale_dev),
-                                      _stream()), "adamw_step")
+        check(lib().b200ft_adamw_step_limited(_p(p), _p(m), _p(v), _p(g), int(g.dtype == torch.bfloat16), _p(shadow),
+                                              n, lr, beta1, beta2, eps, weight_decay, step, grad_scale,
+                                              _p(grad_scale_dev), max_blocks, _stream()), "adamw_step")
     LAUNCHES += 1
 
 

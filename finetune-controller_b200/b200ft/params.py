@@ -96,7 +96,8 @@ def init_lora_llama(dims: LlamaDims, lora: LoRASpec, seed: int, device="cpu") ->
 
 
 def build_engine(model: str, lora: LoRASpec, opt, *, batch: int, seq: int, device, seed: int = 0, world_size: int = 1,
-                 grad_sync=None, randomize_b: bool = False, mode: str = "lora", attention: str = "sdpa"):
+                 grad_sync=None, randomize_b: bool = False, mode: str = "lora", attention: str = "sdpa",
+                 overlap_optimizer: bool = False):
     """Random-init model (+ adapters) of the named architecture on `device`, wrapped in its step engine.
     mode "lora" trains adapters on a frozen base; mode "full" (Llama family) trains every tensor."""
     from . import gpt2, llama
@@ -106,7 +107,8 @@ def build_engine(model: str, lora: LoRASpec, opt, *, batch: int, seq: int, devic
             raise ValueError("mode=full is implemented for the Llama family (BASELINE.json configs[4])")
         from . import llama_full
         return llama_full.LlamaFullStep(dims, opt, None, batch=batch, seq=seq, device=device, world_size=world_size,
-                                        grad_sync=grad_sync, seed=seed, attention=attention), dims
+                                        grad_sync=grad_sync, seed=seed, attention=attention,
+                                        overlap_optimizer=overlap_optimizer), dims
     if mode != "lora":
         raise ValueError(f"unknown mode {mode!r}")
     if is_llama(dims):

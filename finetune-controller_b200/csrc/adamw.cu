@@ -136,6 +136,15 @@ extern "C" int b200ft_adamw_step(float* p, float* m, float* v, const void* g, in
                                  void* shadow_bf16, int64_t n, float lr, float beta1, float beta2,
                                  float eps, float weight_decay, int step, float grad_scale,
                                  const float* grad_scale_dev, void* stream) {
+  return b200ft_adamw_step_limited(p, m, v, g, g_is_bf16, shadow_bf16, n, lr, beta1, beta2, eps, weight_decay, step,
+                                   grad_scale, grad_scale_dev, 0, stream);
+}
+
+extern "C" int b200ft_adamw_step_limited(float* p, float* m, float* v, const void* g, int g_is_bf16,
+                                         void* shadow_bf16, int64_t n, float lr, float beta1, float beta2,
+                                         float eps, float weight_decay, int step, float grad_scale,
+                                         const float* grad_scale_dev, int max_blocks, void* stream) {
+  B200FT_CHECK_ARG(max_blocks >= 0, "adamw_step: max_blocks=%d", max_blocks);
   B200FT_CHECK_ARG(p && m && v && g, "adamw_step: null buffer");
   B200FT_CHECK_ARG(n >= 0 && step >= 1, "adamw_step: n=%lld step=%d", (long long)n, step);
   B200FT_CHECK_ARG(((uintptr_t)p | (uintptr_t)m | (uintptr_t)v | (uintptr_t)g | (uintptr_t)shadow_bf16) % 16 == 0,
@@ -153,6 +162,7 @@ extern "C" int b200ft_adamw_step(float* p, float* m, float* v, const void* g, in
   int64_t nvec = n >> 3;
   int64_t want = (nvec + 255) / 256;
   int blocks = (int)(want < 1 ? 1 : (want > B200FT_NUM_SMS * 8 ? B200FT_NUM_SMS * 8 : want));
+  if (max_blocks > 0 && blocks > max_blocks) blocks = max_blocks;
   cudaStream_t st = (cudaStream_t)stream;
   if (g_is_bf16)
     adamw_kernel<true><<<blocks, 256, 0, st>>>(p, m, v, g, (__nv_bfloat16*)shadow_bf16, n, s, grad_scale_dev);

@@ -160,6 +160,13 @@ int b200ft_adamw_step(float* p, float* m, float* v, const void* g, int g_is_bf16
                       int64_t n, float lr, float beta1, float beta2, float eps,
                       float weight_decay, int step, float grad_scale,
                       const float* grad_scale_dev, void* stream);
+/* Same update on at most max_blocks thread blocks of 256 threads (0 = no limit: up to 8 per SM).  For a launch
+ * that runs BESIDE other kernels: the full-parameter step updates a layer on a second stream while backward
+ * still computes the layers below it, and one block per SM (148) leaves the GEMM's CTAs room to stay resident. */
+int b200ft_adamw_step_limited(float* p, float* m, float* v, const void* g, int g_is_bf16, void* shadow_bf16,
+                              int64_t n, float lr, float beta1, float beta2, float eps, float weight_decay,
+                              int step, float grad_scale, const float* grad_scale_dev, int max_blocks,
+                              void* stream);
 
 /* Sum of squares of a flat gradient buffer -> out_sq[0] (fp32), and the clip factor
  * coef[0] = min(1, max_norm / (pre_scale*sqrt(norm_sq) + 1e-6))  (torch clip_grad_norm_). */

@@ -143,3 +143,22 @@ def test_full_ft_in_place_init_and_state_roundtrip():
     assert abs(l1 - l2) <= 1e-6 * abs(l1)
     torch.testing.assert_close(a.P, b.P, rtol=0, atol=2e-5)
     torch.testing.assert_close(a.Pn, b.Pn, rtol=0, atol=2e-5)
+
+
+def test_full_ft_overlapped_optimizer_option_matches():
+    """overlap_optimizer=True (per-layer AdamW on a second stream during backward; off by default because it
+    measured slower) must land on the same parameters as the single launch after backward."""
+    from b200ft import gpt2, llama_full, params
+    dims = params.MODELS["llama-tiny"]
+    opt = gpt2.OptSpec(1e-3, 0.9, 0.999, 1e-8, 0.01, 0.0)
+    a = llama_full.LlamaFullStep(dims, opt, None, batch=2, seq=32, device=DEV, seed=5)
+    b = llama_full.LlamaFullStep(dims, opt, None, batch=2, seq=32, device=DEV, seed=5, overlap_optimizer=True)
+    assert b.overlap_opt and not a.overlap_opt
+    g = torch.Generator().manual_seed(0)
+    for _ in range(3):
+        ids = torch.randint(0, dims.vocab, (2, 32), generator=g).to(DEV)
+        la, lb = float(a.step(ids, ids).cpu()), float(b.step(ids, ids).cpu())
+        assert abs(la - lb) <= 1e-5 * abs(la)
+    torch.cuda.synchronize()
+    torch.testing.assert_close(a.P, b.P, rtol=0, atol=2e-5)
+    torch.testing.assert_close(a.S.float(), b.S.float(), rtol=0, atol=2 ** -7 * 0.2)
