@@ -88,6 +88,9 @@ __device__ __forceinline__ void softmax_sweep(uint32_t t_s, uint32_t t_p, float 
       mbar_wait(pv_bar, pv_parity);
       tc_fence_after();
     }
+#ifdef B200FT_EXP_NO_PSTORE
+    if (w[0] == 0x12345678u)   // practically never
+#endif
     tmem_st16(t_p + 16 * c, w);  // keys 32c .. 32c+31 of this row = 16 packed columns of P
   }
   max_out = fmaxf(fmaxf(ma[0], ma[1]), fmaxf(ma[2], ma[3]));
@@ -211,10 +214,12 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm, const AttnParams p) {
     };
     auto issue_pv = [&](int g, int st) {   // PV_g = P_g V: reduction over keys; P from TMEM (8 columns = 16 keys per step), V rows 16 per step
       if (issuer) {
+#ifndef B200FT_EXP_NO_PV   // bottleneck experiment (tools/attn_exp.py): skip the P V UMMAs, wrong numbers
 #pragma unroll
         for (int k = 0; k < kBK / 16; ++k)
           umma_ts(tmem + kColPV + 64u * g, tmem + kColP + 64u * g + 8u * k,
                   sdesc(sV + st * kKVBytes + 2048 * k, 8192, 1024), id_pv, k > 0);
+#endif
         umma_commit(pv_full(g));
       }
       __syncwarp();
