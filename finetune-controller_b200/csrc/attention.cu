@@ -14,7 +14,8 @@
 //             TMEM with tcgen05.st (the PV UMMA takes its A operand from TMEM: no smem round trip for P,
 //             whose 6 KB of reads per 32-cycle UMMA would exceed the shared-memory port) — repeated only if
 //             some row's max grew by more than 2^8 over its reference (lazy rescaling; exact after the final
-//             normalisation).  The running output O stays in registers: PV_{j-1} is folded in one tile later.
+//             normalisation).  The output tile O accumulates in TMEM over the kv tiles (the P V UMMAs add into it);
+//             the softmax warps rescale it in place only when a reference max moves, and read it once at the end.
 // V_j is consumed as an MN-major B operand ([keys, d_head] rows as TMA delivers them): nothing is
 // transposed.  Registers are the per-scheduler resource that decides the shape: 12 warps x 168.
 //
@@ -212,13 +213,16 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm, const AttnParams p) {
       }
       __syncwarp();
     };
-    auto issue_pv = [&](int g, int st) {   // PV_g = P_g V: reduction over keys; P from TMEM (8 columns = 16 keys per step), V rows 16 per step
+    // O_g (+)= P_g V: reduction over keys; P from TMEM (8 columns = 16 keys per step), V rows 16 per step.  The output
+    // tile accumulates in TMEM over all kv tiles of the item (`first` starts it): with lazy rescaling the softmax
+    // warps have to touch it only when a row's reference max moves.
+    auto issue_pv = [&](int g, int st, bool first) {
       if (issuer) {
 #ifndef B200FT_EXP_NO_PV   // bottleneck experiment (tools/attn_exp.py): skip the P V UMMAs, wrong numbers
 #pragma unroll
         for (int k = 0; k < kBK / 16; ++k)
           umma_ts(tmem + kColPV + 64u * g, tmem + kColP + 64u * g + 8u * k,
-                  sdesc(sV + st * kKVBytes + 2048 * k, 8192, 1024), id_pv, k > 0);
+                  sdesc(sV + st * kKVBytes + 2048 * k, 8192, 1024), id_pv, !(first && k == 0));
 #endif
         umma_commit(pv_full(g));
       }
@@ -254,9 +258,9 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm, const AttnParams p) {
         issue_s(0, nst);
       }
       if (j < nA) {
-        mbar_wait(p_full(0), parA);      // P_A(j) is in TMEM and PV_A(j-1) has been read out
+        mbar_wait(p_full(0), parA);      // P_A(j) is in TMEM (and O_A rescaled if its reference moved)
         tc_fence_after();
-        issue_pv(0, st);
+        issue_pv(0, st, j == 0);
       }
       if (j + 1 < nB) {
         if (!k_next_ready) mbar_wait(k_full(nst), nph);
@@ -267,7 +271,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm, const AttnParams p) {
       if (j < nB) {
         mbar_wait(p_full(1), parB);
         tc_fence_after();
-        issue_pv(1, st);
+        issue_pv(1, st, j == 0);
       }
       if (issuer) umma_commit(v_empty(st));
       __syncwarp();
@@ -296,9 +300,6 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm, const AttnParams p) {
     const int qt = g ? it.qtB : it.qtA;
     const int n_mine = g ? it.nB : it.nA;
     const int qrow = qt * kBQ + row;              // position in the sequence
-    float o[kDH];
-#pragma unroll
-    for (int i = 0; i < kDH; ++i) o[i] = 0.f;
     float m_ref = -INFINITY, l = 0.f;
     for (int j = 0; j < n_mine; ++j) {
       const uint32_t par = (cg + (uint32_t)j) & 1u;
@@ -325,27 +326,31 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm, const AttnParams p) {
         const bool wait_pv = first_pass && j > 0;
         if (diag) softmax_sweep<true>(t_s, t_p, p.scale_log2, m_ref, kbase, qrow, wait_pv, pv_full(g), par ^ 1u, sum, mx);
         else      softmax_sweep<false>(t_s, t_p, p.scale_log2, m_ref, kbase, qrow, wait_pv, pv_full(g), par ^ 1u, sum, mx);
-        if (wait_pv) {  // fold the previous tile's P V into O (it was taken against the same reference max)
+        first_pass = false;
+        // lazy rescaling: keep the old reference unless this row's max outgrew it by 2^8
+        const bool grow = mx * p.scale_log2 > m_ref + kRescaleThreshold;
+        if (!__any_sync(0xffffffffu, grow)) break;
+        float alpha = 1.f;
+        if (grow) {
+          const float m_new = mx * p.scale_log2;
+          alpha = ex2(m_ref - m_new);
+          l *= alpha;
+          m_ref = m_new;
+        }
+        if (j > 0) {
+          // rare: rescale this warp's rows of O in TMEM (the P V UMMAs of tile j-1 have retired: the sweep waited
+          // for them; those of tile j are not issued before p_full); rows whose reference stays use alpha = 1
 #pragma unroll
           for (int c = 0; c < kDH / 32; ++c) {
             uint32_t r[32];
             tmem_ld32(t_pv + 32 * c, r);
             tmem_wait_ld();
 #pragma unroll
-            for (int i = 0; i < 32; ++i) o[32 * c + i] += __uint_as_float(r[i]);
+            for (int i = 0; i < 32; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * alpha);
+            tmem_st16(t_pv + 32 * c, r);
+            tmem_st16(t_pv + 32 * c + 16, r + 16);
           }
-        }
-        first_pass = false;
-        // lazy rescaling: keep the old reference unless this row's max outgrew it by 2^8
-        const bool grow = mx * p.scale_log2 > m_ref + kRescaleThreshold;
-        if (!__any_sync(0xffffffffu, grow)) break;
-        if (grow) {
-          const float m_new = mx * p.scale_log2;
-          const float alpha = ex2(m_ref - m_new);
-          l *= alpha;
-#pragma unroll
-          for (int i = 0; i < kDH; ++i) o[i] *= alpha;
-          m_ref = m_new;
+          tmem_wait_st();
         }
       }
       l += sum;
@@ -355,17 +360,18 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm, const AttnParams p) {
       if (lane == 0) { mbar_arrive(s_free(g)); mbar_arrive(p_full(g)); }
     }
     if (n_mine > 0) {
-      // ---- last tile's P V, normalise, write o and the log-sum-exp ----
+      // ---- all P V UMMAs of the item have retired: normalise O, write it and the log-sum-exp ----
       mbar_wait(pv_full(g), (cg + (uint32_t)n_mine - 1u) & 1u);
       tc_fence_after();
       const float inv_l = 1.f / l;
+      float o[kDH];
 #pragma unroll
       for (int c = 0; c < kDH / 32; ++c) {
         uint32_t r[32];
         tmem_ld32(t_pv + 32 * c, r);
         tmem_wait_ld();
 #pragma unroll
-        for (int i = 0; i < 32; ++i) o[32 * c + i] = (o[32 * c + i] + __uint_as_float(r[i])) * inv_l;
+        for (int i = 0; i < 32; ++i) o[32 * c + i] = __uint_as_float(r[i]) * inv_l;
       }
       if (qrow < p.seq) {
         __nv_bfloat16* dst = p.out + ((int64_t)b * p.seq + qrow) * p.ld_out + h * kDH;

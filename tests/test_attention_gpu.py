@@ -119,3 +119,26 @@ def test_attn_bwd_deterministic_path_is_bit_reproducible():
     ops.attn_bwd(qd, out, dod, lse2, ws, fused, **kw)
     assert torch.equal(fused[:, H * dh:], res[0][:, H * dh:])
     torch.testing.assert_close(fused[:, : H * dh].float(), res[0][:, : H * dh].float(), rtol=2 ** -7, atol=1e-3)
+
+
+def test_attn_fwd_rescales_output_accumulator_when_the_row_max_grows():
+    """Keys whose magnitude rises tile after tile force the lazy-rescaling path on every kv tile: the reference max
+    moves by far more than 2^8, so the output tile accumulated in TMEM has to be rescaled in place."""
+    from b200ft import ops
+    B, T, H, KV, dh = 1, 640, 2, 2, 64
+    g = torch.Generator().manual_seed(3)
+    ld = (H + 2 * KV) * dh
+    x = torch.randn(B * T, ld, generator=g)
+    ramp = (1.0 + 3.0 * (torch.arange(T) // 128).float())[:, None]       # x1, x4, x7, ... per 128-key tile
+    x[:, H * dh: (H + KV) * dh] *= ramp
+    qkv = x.to(torch.bfloat16)
+    q_off, k_off, v_off = 0, H * dh, (H + KV) * dh
+    o_ref, lse_ref = ref_attention(qkv, B, T, H, KV, dh, q_off, k_off, v_off)
+    out = torch.full((B * T, H * dh), float("nan"), dtype=torch.bfloat16, device=DEV)
+    lse2 = torch.empty(B * H, T, device=DEV)
+    ops.attn_fwd(qkv.to(DEV), out, lse2, batch=B, seq=T, n_head=H, n_kv_head=KV, d_head=dh, q_off=q_off, k_off=k_off,
+                 v_off=v_off, scale=1.0 / math.sqrt(dh))
+    got = out.cpu().float()
+    assert not torch.isnan(got).any()
+    torch.testing.assert_close(got, o_ref, rtol=2e-2, atol=2e-2)
+    torch.testing.assert_close(lse2.cpu().view(B, H, T) * math.log(2.0), lse_ref, rtol=1e-3, atol=5e-3)
