@@ -37,6 +37,10 @@ constexpr int kTiles = 2 * kQBytes + 2 * kStages * kKVBytes;  // 96 KB
 constexpr int kSmemBytes = kTiles + 256;        // + barriers; no alignment slack (the kernel checks the base)
 constexpr int kTmemCols = 512;
 constexpr uint32_t kColS = 0, kColPV = 256, kColP = 384;  // + 128*g, + 64*g, + 64*g (P: bf16 pairs, 64 columns)
+#ifndef B200FT_ATTN_SWEEP_LD
+#define B200FT_ATTN_SWEEP_LD 64
+#endif
+constexpr int kSweepLd = B200FT_ATTN_SWEEP_LD;  // 32, 64 or 128
 constexpr float kRescaleThreshold = 8.0f;       // log2 units: p stays below 2^8
 
 struct AttnParams {
@@ -64,35 +68,43 @@ __device__ __forceinline__ void softmax_sweep(uint32_t t_s, uint32_t t_p, float 
   // scheduler a single 64-deep dependent chain cannot be hidden
   f32x2_t sa[4] = {pk2(0.f, 0.f), pk2(0.f, 0.f), pk2(0.f, 0.f), pk2(0.f, 0.f)};
   float ma[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+  // kSweepLd score columns are requested per TMEM round trip (one tcgen05.wait::ld each): with one softmax warp
+  // per query group and scheduler, every round trip is exposed latency
 #pragma unroll
-  for (int c = 0; c < kBK / 32; ++c) {
-    uint32_t r[32];
-    tmem_ld32(t_s + 32 * c, r);
+  for (int cc = 0; cc < kBK / kSweepLd; ++cc) {
+    uint32_t rr[kSweepLd];
+#pragma unroll
+    for (int q = 0; q < kSweepLd / 32; ++q) tmem_ld32(t_s + kSweepLd * cc + 32 * q, rr + 32 * q);
     tmem_wait_ld();
-    uint32_t w[16];
 #pragma unroll
-    for (int i = 0; i < 32; i += 2) {
-      float s0 = __uint_as_float(r[i]), s1 = __uint_as_float(r[i + 1]);
-      if (DIAG) {
-        if (kbase + 32 * c + i > qrow) s0 = -INFINITY;
-        if (kbase + 32 * c + i + 1 > qrow) s1 = -INFINITY;
+    for (int q = 0; q < kSweepLd / 32; ++q) {
+      const int c = cc * (kSweepLd / 32) + q;
+      const uint32_t* r = rr + 32 * q;
+      uint32_t w[16];
+#pragma unroll
+      for (int i = 0; i < 32; i += 2) {
+        float s0 = __uint_as_float(r[i]), s1 = __uint_as_float(r[i + 1]);
+        if (DIAG) {
+          if (kbase + 32 * c + i > qrow) s0 = -INFINITY;
+          if (kbase + 32 * c + i + 1 > qrow) s1 = -INFINITY;
+        }
+        const int a = (i >> 1) & 3;
+        ma[a] = fmaxf(ma[a], fmaxf(s0, s1));
+        float e0, e1;
+        upk2(fma2(pk2(s0, s1), sc2, nm2), e0, e1);
+        const float p0 = ex2(e0), p1 = ex2(e1);  // exp2(-inf) = 0 for masked keys
+        sa[a] = add2(sa[a], pk2(p0, p1));
+        w[i >> 1] = pack_bf16x2(p0, p1);
       }
-      const int a = (i >> 1) & 3;
-      ma[a] = fmaxf(ma[a], fmaxf(s0, s1));
-      float e0, e1;
-      upk2(fma2(pk2(s0, s1), sc2, nm2), e0, e1);
-      const float p0 = ex2(e0), p1 = ex2(e1);  // exp2(-inf) = 0 for masked keys
-      sa[a] = add2(sa[a], pk2(p0, p1));
-      w[i >> 1] = pack_bf16x2(p0, p1);
-    }
-    if (c == 0 && wait_pv) {
-      mbar_wait(pv_bar, pv_parity);
-      tc_fence_after();
-    }
+      if (c == 0 && wait_pv) {
+        mbar_wait(pv_bar, pv_parity);
+        tc_fence_after();
+      }
 #ifdef B200FT_EXP_NO_PSTORE
-    if (w[0] == 0x12345678u)   // practically never
+      if (w[0] == 0x12345678u)   // practically never
 #endif
-    tmem_st16(t_p + 16 * c, w);  // keys 32c .. 32c+31 of this row = 16 packed columns of P
+      tmem_st16(t_p + 16 * c, w);  // keys 32c .. 32c+31 of this row = 16 packed columns of P
+    }
   }
   max_out = fmaxf(fmaxf(ma[0], ma[1]), fmaxf(ma[2], ma[3]));
   float s_lo, s_hi;
