@@ -85,8 +85,8 @@ class StepHostMixin:
 
     def state_dict(self) -> dict:
         """Everything needed to continue training: fp32 master adapters, Adam moments, step."""
-        return {"P": self.P.detach().cpu().clone(), "m": self.Mo.detach().cpu().clone(),
-                "v": self.Vo.detach().cpu().clone(), "step": self.step_count,
+        return {"P": self.P.detach().cpu(), "m": self.Mo.detach().cpu(),
+                "v": self.Vo.detach().cpu(), "step": self.step_count,
                 "r": self.lora.r, "alpha": self.lora.alpha, "n_layer": self.dims.n_layer, "d_model": self.dims.d_model}
 
     def load_state_dict(self, st: dict) -> None:

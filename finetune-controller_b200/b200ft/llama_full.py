@@ -181,9 +181,9 @@ class LlamaFullStep(StepHostMixin, OwnAttentionMixin):
         return out
 
     def state_dict(self) -> dict:
-        return {"P": self.P.detach().cpu().clone(), "m": self.Mo.detach().cpu().clone(),
-                "v": self.Vo.detach().cpu().clone(), "Pn": self.Pn.detach().cpu().clone(),
-                "mn": self.Mn.detach().cpu().clone(), "vn": self.Vn.detach().cpu().clone(),
+        return {"P": self.P.detach().cpu(), "m": self.Mo.detach().cpu(),
+                "v": self.Vo.detach().cpu(), "Pn": self.Pn.detach().cpu(),
+                "mn": self.Mn.detach().cpu(), "vn": self.Vn.detach().cpu(),
                 "step": self.step_count, "mode": "full", "n_layer": self.dims.n_layer, "d_model": self.dims.d_model}
 
     def load_state_dict(self, st: dict) -> None:

@@ -1,5 +1,5 @@
-"""Parameter construction for the payload (random init — the image has no network, so no
-pretrained checkpoint can be fetched; a checkpoint under the dataset mount is used if present).
+"""Parameter construction for the payload: pretrained base weights from the dataset mount when the job
+names them (weights.load_base_weights), random init otherwise (benchmarks, smoke runs).
 
 Naming/layout is HF GPT-2's: Conv1D weights are [in, out]; see GPT2LoRAStep._upload_base.
 """
@@ -97,25 +97,30 @@ def init_lora_llama(dims: LlamaDims, lora: LoRASpec, seed: int, device="cpu") ->
 
 def build_engine(model: str, lora: LoRASpec, opt, *, batch: int, seq: int, device, seed: int = 0, world_size: int = 1,
                  grad_sync=None, randomize_b: bool = False, mode: str = "lora", attention: str = "sdpa",
-                 overlap_optimizer: bool = False):
-    """Random-init model (+ adapters) of the named architecture on `device`, wrapped in its step engine.
-    mode "lora" trains adapters on a frozen base; mode "full" (Llama family) trains every tensor."""
+                 overlap_optimizer: bool = False, base_weights: str = ""):
+    """Model (+ adapters) of the named architecture on `device`, wrapped in its step engine.  The base comes
+    from `base_weights` (a Hugging Face checkpoint file / directory, see weights.py) or, if empty, is drawn at
+    random.  mode "lora" trains adapters on a frozen base; mode "full" (Llama family) trains every tensor."""
     from . import gpt2, llama
     dims = MODELS[model]
+    loaded = None
+    if base_weights:
+        from . import weights
+        loaded = weights.load_base_weights(base_weights, dims, is_llama(dims))
     if mode == "full":
         if not is_llama(dims):
             raise ValueError("mode=full is implemented for the Llama family (BASELINE.json configs[4])")
         from . import llama_full
-        return llama_full.LlamaFullStep(dims, opt, None, batch=batch, seq=seq, device=device, world_size=world_size,
+        return llama_full.LlamaFullStep(dims, opt, loaded, batch=batch, seq=seq, device=device, world_size=world_size,
                                         grad_sync=grad_sync, seed=seed, attention=attention,
                                         overlap_optimizer=overlap_optimizer), dims
     if mode != "lora":
         raise ValueError(f"unknown mode {mode!r}")
     if is_llama(dims):
-        base, ad = init_llama(dims, seed, device), init_lora_llama(dims, lora, seed + 1, device)
+        base, ad = loaded or init_llama(dims, seed, device), init_lora_llama(dims, lora, seed + 1, device)
         cls = llama.LlamaLoRAStep
     else:
-        base, ad = init_gpt2(dims, seed, device), init_lora(dims, lora, seed + 1, device)
+        base, ad = loaded or init_gpt2(dims, seed, device), init_lora(dims, lora, seed + 1, device)
         cls = gpt2.GPT2LoRAStep
     if randomize_b:  # benchmarks: every gradient path carries non-trivial data from step 1
         gen = torch.Generator(device=device).manual_seed(seed + 99)

@@ -15,8 +15,10 @@ app/jobs/kubeflow/PyTorchJobDeployer.py:93-119).  Contract with the controller:
     (reference PyTorchJobDeployer.py:30-32); any CUDA/NCCL error propagates as non-zero so the
     operator's restart policy applies.
 
-The pod gets ``--gpus`` devices; the operator's RANK/WORLD_SIZE describe pods, so this process
-spawns one worker per local GPU itself unless it is already running under torchrun.
+The pod gets ``--gpus`` devices; the operator's RANK / WORLD_SIZE / MASTER_ADDR / MASTER_PORT describe PODS
+(Master + Workers, reference PyTorchJobDeployer.py:186-249), so this process spawns one worker per local GPU
+itself — global rank = pod rank x gpus + local GPU, world = pods x gpus — unless it is already running under
+torchrun.  Only global rank 0 (on the Master pod, the one with the s3-sync sidecar) writes artifacts.
 """
 from __future__ import annotations
 
@@ -52,8 +54,14 @@ def build_parser() -> argparse.ArgumentParser:
     ap.add_argument("--save_model", action="store_true")
     ap.add_argument("--synthetic", action="store_true")
     ap.add_argument("--save_interval", type=int, default=0,
-                    help="steps between resume points (state.pt); 0 = only at the end of each epoch")
+                    help="steps between resume points (resume.state); 0 = only at the end of each epoch, -1 = never")
+    ap.add_argument("--base_weights", default="",
+                    help="pretrained base weights (HF *.safetensors file / directory or a .pt state dict); a relative "
+                         "path is taken under --dataset_path; empty = random init")
     ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--nodes", type=int, default=1,
+                    help="pods of the PyTorchJob (the plugin's cluster_nodes); > 1 needs the operator's "
+                         "RANK / WORLD_SIZE / MASTER_ADDR / MASTER_PORT in the environment")
     ap.add_argument("--dataset_path", default="/data/dataset")
     ap.add_argument("--checkpoint_path", default="/data/artifacts")
     return ap
@@ -83,9 +91,21 @@ def load_token_stream(dataset_path: str):
     return torch.tensor(ids, dtype=torch.int64) if ids else None
 
 
+def check_token_range(stream, vocab: int) -> None:
+    """A token id outside [0, vocab) is a data error (wrong tokenizer for the selected model): the job
+    stops with a message instead of training on clamped ids."""
+    if stream.numel() == 0:
+        raise ValueError("dataset holds no tokens")
+    lo, hi = int(stream.min()), int(stream.max())
+    if lo < 0 or hi >= vocab:
+        raise ValueError(f"dataset token ids span [{lo}, {hi}] but the selected model's vocabulary is [0, {vocab}): "
+                         "was it tokenised for another model?")
+
+
 def batch_from_stream(stream, global_step: int, rank: int, world: int, batch: int, seq: int, vocab: int):
     """Deterministic [batch, seq] window of the token stream for (step, rank): consecutive
-    batch*seq spans, ranks interleaved, wrapping around at the end of the stream."""
+    batch*seq spans, ranks interleaved, wrapping around at the end of the stream.  The stream has
+    been range-checked once at load (check_token_range)."""
     import torch
     span = batch * seq
     n_chunks = max(1, stream.numel() // span)
@@ -94,10 +114,13 @@ def batch_from_stream(stream, global_step: int, rank: int, world: int, batch: in
     if chunk.numel() < span:
         reps = (span + stream.numel() - 1) // stream.numel()
         chunk = torch.cat([chunk] + [stream] * reps)[:span]
-    return chunk.view(batch, seq).clamp(0, vocab - 1)
+    return chunk.view(batch, seq)
 
 
-STATE_FILE = "state.pt"
+# The resume point must NOT match the controller's artifact patterns (``*.pt`` is one of them, reference
+# app/models/base/finetuning.py:94-97): the sidecar re-syncs every match to S3 each AWS_JOB_SYNC_INTERVAL
+# (reference PyTorchJobDeployer.py:122-139) and in full-parameter mode this file is 96 GB of optimizer state.
+STATE_FILE = "resume.state"
 
 
 def save_state(eng, checkpoint_path: str, epoch: int, it: int, gstep: int) -> None:
@@ -134,11 +157,15 @@ def worker(args, rank: int, world: int, local: int) -> None:
     elif world > 1:
         sync = ddp.BucketedGradSync(n_layer, n_buckets=2)
     # random init, identical on every rank (same seed): the image has no network for checkpoints
+    bw = args.base_weights
+    if bw and not os.path.isabs(bw):
+        bw = os.path.join(args.dataset_path, bw)
     eng, dims = params.build_engine(args.model, lora, opt, batch=args.batch_size, seq=args.seq_len, device=dev,
                                     seed=args.seed, world_size=world, grad_sync=sync, mode=args.mode,
-                                    attention=args.attention)
-    targets = ["q_proj", "v_proj"] if params.is_llama(dims) else ["c_attn"]
+                                    attention=args.attention, base_weights=bw)
     stream = None if args.synthetic else load_token_stream(args.dataset_path)
+    if stream is not None:
+        check_token_range(stream, dims.vocab)
     B, T = args.batch_size, args.seq_len
     ids_host = torch.empty(B, T, dtype=torch.int64).pin_memory()
 
@@ -190,7 +217,8 @@ def worker(args, rank: int, world: int, local: int) -> None:
                 fh.flush()
             if loss != loss:
                 raise RuntimeError("loss is NaN")
-            if rank == 0 and ((args.save_interval > 0 and it % args.save_interval == 0) or it == args.steps_per_epoch):
+            if rank == 0 and args.save_interval >= 0 and (
+                    (args.save_interval > 0 and it % args.save_interval == 0) or it == args.steps_per_epoch):
                 save_state(eng, args.checkpoint_path, epoch, it, gstep)
     if rank == 0:
         fh.close()
@@ -204,18 +232,33 @@ def worker(args, rank: int, world: int, local: int) -> None:
                                                             "vocab", "rms_eps", "rope_theta", "tie_embeddings")}},
                           f, indent=1)
         elif args.save_model:
-            torch.save({k: v for k, v in eng.adapters_state().items()}, os.path.join(args.checkpoint_path, "adapter.pt"))
-            with open(os.path.join(args.checkpoint_path, "adapter_config.json"), "w") as f:
-                json.dump({"peft_type": "LORA", "base_model": args.model, "r": args.lora_r,
-                           "lora_alpha": args.lora_alpha, "target_modules": targets,
-                           "fan_in_fan_out": not params.is_llama(dims),
-                           "lora_dropout": 0.0, "steps": gstep}, f, indent=1)
+            from . import weights
+            ad = eng.adapters_state()
+            torch.save(dict(ad), os.path.join(args.checkpoint_path, "adapter.pt"))     # engine / oracle naming
+            weights.save_peft_adapter(args.checkpoint_path, ad, model=args.model, llama=params.is_llama(dims),
+                                      r=args.lora_r, alpha=args.lora_alpha, steps=gstep)  # PEFT naming
         print(f"Epoch {args.epochs}/{args.epochs} done: {gstep} steps in {time.time() - t_start:.1f}s", flush=True)
 
 
-def _spawned(local: int, args, world: int, port: int) -> None:
-    os.environ.update(RANK=str(local), LOCAL_RANK=str(local), WORLD_SIZE=str(world),
-                      MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+def pod_world(args, env) -> tuple[int, int, str, int | None]:
+    """(first global rank of this pod, world size, master address, master port or None = pick a free one).
+    One pod: everything is local.  Several pods (plugin cluster_nodes > 1): the Kubeflow training operator
+    gives every pod RANK = pod index, WORLD_SIZE = pod count and the Master's address / port."""
+    if args.nodes <= 1:
+        return 0, args.gpus, "127.0.0.1", None
+    try:
+        pod, pods = int(env["RANK"]), int(env["WORLD_SIZE"])
+        addr, port = env["MASTER_ADDR"], int(env["MASTER_PORT"])
+    except KeyError as e:
+        raise SystemExit(f"b200ft.train: --nodes={args.nodes} but the operator's {e.args[0]} is not set") from None
+    if pods != args.nodes or not 0 <= pod < pods:
+        raise SystemExit(f"b200ft.train: --nodes={args.nodes} but WORLD_SIZE={pods}, RANK={pod}")
+    return pod * args.gpus, pods * args.gpus, addr, port
+
+
+def _spawned(local: int, args, rank0: int, world: int, addr: str, port: int) -> None:
+    os.environ.update(RANK=str(rank0 + local), LOCAL_RANK=str(local), WORLD_SIZE=str(world),
+                      MASTER_ADDR=addr, MASTER_PORT=str(port))
     from . import ddp
     rank, world, local = ddp.init_process_group_from_env("nccl")
     try:
@@ -237,12 +280,13 @@ def main(argv=None) -> int:
         rank, world, local = ddp.init_process_group_from_env("nccl")
         worker(args, rank, world, local)
         return 0
-    if args.gpus <= 1:
+    if args.gpus <= 1 and args.nodes <= 1:
         worker(args, 0, 1, 0)
         return 0
     import torch.multiprocessing as mp
     from . import ddp
-    mp.spawn(_spawned, args=(args, args.gpus, ddp.free_port()), nprocs=args.gpus, join=True)
+    rank0, world, addr, port = pod_world(args, os.environ)
+    mp.spawn(_spawned, args=(args, rank0, world, addr, port or ddp.free_port()), nprocs=args.gpus, join=True)
     return 0
 
 

@@ -43,15 +43,19 @@ class B200LoRAConfig(TrainingArguments):
     max_grad_norm: float = Field(default=0.0, description="Global gradient-norm clip; 0 disables")
     seed: int = Field(default=0, description="Seed for weight init and synthetic data")
     log_interval: int = Field(default=10, description="Steps between metric rows / log lines")
-    save_interval: int = Field(default=0, description="Steps between resume points (state.pt); 0 = once per epoch")
-    save_model: bool = Field(default=True, description="Write adapter.pt + adapter_config.json (lora) or model.pt + config.json (full) at the end")
+    save_interval: int = Field(default=0, description="Steps between resume points (resume.state, not uploaded); 0 = once per epoch, -1 = never")
+    save_model: bool = Field(default=True, description="Write adapter_model.safetensors (PEFT key names) + adapter.pt + adapter_config.json (lora) or model.pt + config.json (full) at the end")
+    base_weights: str = Field(default="", description="Pretrained base weights: a Hugging Face *.safetensors file or directory (or a .pt state dict), relative to the dataset mount; empty = random init")
     synthetic: bool = Field(default=True, description="Use synthetic token ids instead of the mounted dataset")
 
 
 class B200LoRA(BaseFineTuneModel):
     """Job spec: GPT-2-class LoRA fine-tuning on B200 GPUs with hand-written sm_100a kernels."""
 
-    name: str = "B200.LoRA"  # lower-cases to a DNS-1123 label for the PyTorchJob name
+    # the controller derives the PyTorchJob name as name.lower().replace("_", "-") + "-" + uuid8
+    # (reference app/main.py:422) and the operator derives "<job>-master-0" Service / pod host names
+    # from it: "b200-lora-xxxxxxxx" is a DNS-1035 label, a dotted name would not be
+    name: str = "B200_LoRA"
     inference_name: str | None = None
     description: str = "GPT-2 LoRA fine-tune on NVIDIA B200 (tcgen05 GEMMs, fused CE, fused AdamW)"
     project_url: str = ""
@@ -78,6 +82,11 @@ class B200LoRA(BaseFineTuneModel):
         ge=1,
         description="Number of gpu devices to use for training per worker",
     )
+    # the base patterns (reference app/models/base/finetuning.py:94-97) plus the PEFT adapter file
+    store_asset_patterns: list[str] = Field(
+        default=["*.json", "*.yaml", "*.csv", "*.pt", "*.ckpt", "*.safetensors"],
+        description="Pattern match a list of files to store.",
+    )
     promotion_path: str = Field(
         default="language/gpt2/b200_lora",
         description="s3 path to upload artifacts. Based on Inference path `domain/algorithm_name/algorithm_application`",
@@ -89,14 +98,20 @@ class B200LoRA(BaseFineTuneModel):
         cmd = self.command.copy()
         ta = self.training_arguments
         args = []
-        for flag in ("save_model", "synthetic"):
-            if getattr(ta, flag):
-                args.append(f"--{flag}")
-        for key in ("model", "mode", "lora_r", "lora_alpha", "seq_len", "batch_size", "epochs",
-                    "steps_per_epoch", "lr", "weight_decay", "beta1", "beta2", "eps", "max_grad_norm",
-                    "seed", "log_interval", "save_interval"):
-            args.append(f"--{key}={getattr(ta, key)}")
+        # every declared argument goes on the command line (a field added to B200LoRAConfig can
+        # not be forgotten here): booleans as bare flags like the exemplar (reference
+        # app/models/examples/mnist.py:75-99), the rest as --key=value; empty strings are left out
+        for key in type(ta).model_fields:
+            val = getattr(ta, key)
+            if isinstance(val, bool):
+                if val:
+                    args.append(f"--{key}")
+            elif val != "":
+                args.append(f"--{key}={val}")
         args.append(f"--gpus={self.accelerator_count}")
+        # Master + Workers of the PyTorchJob (reference PyTorchJobDeployer.py:186-249): the entrypoint
+        # builds its world as pods x gpus from the operator's per-pod RANK / WORLD_SIZE
+        args.append(f"--nodes={self.cluster_nodes}")
         # the two mounts every payload must honour (reference mnist.py:93-95)
         args.append(f"--dataset_path={self.dataset_mount}")
         args.append(f"--checkpoint_path={self.checkpoint_mount}")

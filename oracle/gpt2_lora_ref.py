@@ -281,12 +281,11 @@ class OracleTrainer:
 # --------------------------------------------------------------------------------------
 # pinning the restatement against an independent implementation
 # --------------------------------------------------------------------------------------
-def hf_crosscheck(cfg: GPT2Config = GPT2_TINY, batch: int = 2, seq: int = 32, seed: int = 0) -> dict:
-    """Build transformers' GPT2LMHeadModel from config (no pretrained weights needed), copy
-    this module's parameters into it, and compare logits / loss / input-embedding grads."""
+def hf_model(cfg: GPT2Config, p: dict):
+    """transformers' GPT2LMHeadModel built from config (no pretrained weights needed) holding this module's
+    parameters `p`: the independent implementation the restatement is pinned against."""
     from transformers import GPT2Config as HFConfig, GPT2LMHeadModel
 
-    p = init_base_params(cfg, seed, randomize_all=True)
     hf = GPT2LMHeadModel(HFConfig(
         vocab_size=cfg.vocab, n_positions=cfg.ctx, n_embd=cfg.d_model, n_layer=cfg.n_layer,
         n_head=cfg.n_head, n_inner=cfg.d_ff, activation_function="gelu_new",
@@ -308,6 +307,13 @@ def hf_crosscheck(cfg: GPT2Config = GPT2_TINY, batch: int = 2, seq: int = 32, se
         sd["transformer.ln_f.weight"].copy_(p["lnf.g"])
         sd["transformer.ln_f.bias"].copy_(p["lnf.b"])
     hf.tie_weights()
+    return hf
+
+
+def hf_crosscheck(cfg: GPT2Config = GPT2_TINY, batch: int = 2, seq: int = 32, seed: int = 0) -> dict:
+    """Compare logits / loss / gradients of this restatement with transformers' GPT-2 on the same weights."""
+    p = init_base_params(cfg, seed, randomize_all=True)
+    hf = hf_model(cfg, p)
     ids, labels = synthetic_batch(cfg, batch, seq)
 
     mine = {k: v.clone().requires_grad_(True) for k, v in p.items()}
@@ -319,7 +325,7 @@ def hf_crosscheck(cfg: GPT2Config = GPT2_TINY, batch: int = 2, seq: int = 32, se
     out.loss.backward()
     return {
         "logits_max_abs_diff": float((logits.detach() - out.logits.detach()).abs().max()),
-        "loss_mine": float(loss), "loss_hf": float(out.loss),
+        "loss_mine": float(loss.detach()), "loss_hf": float(out.loss.detach()),
         "wte_grad_max_abs_diff": float((mine["wte"].grad - hf.transformer.wte.weight.grad).abs().max()),
         "c_attn0_grad_max_abs_diff": float(
             (mine["h0.c_attn.w"].grad - hf.transformer.h[0].attn.c_attn.weight.grad).abs().max()),

@@ -246,11 +246,10 @@ class FullOracleTrainer:
         return sum(losses) / len(losses)
 
 
-def hf_crosscheck(cfg: LlamaConfig = LLAMA_TINY, batch: int = 2, seq: int = 24, seed: int = 0) -> dict:
-    """transformers' LlamaForCausalLM from config with this module's weights: logits / loss / grads."""
+def hf_model(cfg: LlamaConfig, p: dict):
+    """transformers' LlamaForCausalLM built from config holding this module's parameters `p`."""
     from transformers import LlamaConfig as HFConfig, LlamaForCausalLM
 
-    p = init_base_params(cfg, seed, randomize_all=True)
     rope = {"rope_type": "default", "rope_theta": cfg.rope_theta}
     if cfg.rope_llama3:
         rope = {"rope_type": "llama3", "rope_theta": cfg.rope_theta, "factor": cfg.rope_factor,
@@ -278,6 +277,13 @@ def hf_crosscheck(cfg: LlamaConfig = LLAMA_TINY, batch: int = 2, seq: int = 24, 
             sd["lm_head.weight"].copy_(p["lm_head.w"])
     if cfg.tie_embeddings:
         hf.tie_weights()
+    return hf
+
+
+def hf_crosscheck(cfg: LlamaConfig = LLAMA_TINY, batch: int = 2, seq: int = 24, seed: int = 0) -> dict:
+    """transformers' LlamaForCausalLM with this module's weights: logits / loss / grads."""
+    p = init_base_params(cfg, seed, randomize_all=True)
+    hf = hf_model(cfg, p)
     ids, labels = synthetic_batch(cfg, batch, seq)
     mine = {k: v.clone().requires_grad_(True) for k, v in p.items()}
     logits = forward(mine, None, ids, cfg, None)

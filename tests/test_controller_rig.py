@@ -3,6 +3,7 @@ the PyTorchJob for our plugin; the rig (tests/rig/render_manifest.py) only fakes
 client, the settings object and the logger.  Skipped where /root/reference is not mounted."""
 import json
 import os
+import re
 import subprocess
 import sys
 
@@ -25,10 +26,12 @@ def render(n_gpu, targs=None):
 
 
 def test_manifest_for_an_8_gpu_job():
-    sub = render(8, {"epochs": 2, "lora_r": 16})
+    sub = render(8, {"epochs": 2, "lora_r": 16, "attention": "own"})
     assert (sub["group"], sub["version"], sub["plural"]) == ("kubeflow.org", "v1", "pytorchjobs")
     body = sub["body"]
-    assert body["kind"] == "PyTorchJob" and body["metadata"]["name"] == "b200.lora-0a1b2c3d"
+    assert body["kind"] == "PyTorchJob" and body["metadata"]["name"] == "b200-lora-0a1b2c3d"
+    # DNS-1035 label: the operator names the "<job>-master-0" Service and pod after it
+    assert re.fullmatch(r"[a-z]([-a-z0-9]*[a-z0-9])?", body["metadata"]["name"])
     assert body["spec"]["runPolicy"]["suspend"] is True            # Kueue local queue
     assert body["metadata"]["labels"]["kueue.x-k8s.io/queue-name"] == "finetune-queue"
     assert body["metadata"]["labels"]["job.accelerators"] == "8"
@@ -40,7 +43,7 @@ def test_manifest_for_an_8_gpu_job():
     cmd = main["command"]
     assert cmd[:2] == ["/bin/bash", "-c"]
     assert cmd[2].startswith("python -m b200ft.train ") and cmd[2].endswith("&& touch /data/artifacts/done.txt")
-    for flag in ("--gpus=8", "--epochs=2", "--lora_r=16", "--dataset_path=/data/dataset",
+    for flag in ("--gpus=8", "--epochs=2", "--lora_r=16", "--attention=own", "--nodes=1", "--dataset_path=/data/dataset",
                  "--checkpoint_path=/data/artifacts"):
         assert flag in cmd[2], flag
     res = main["resources"]
@@ -53,6 +56,7 @@ def test_manifest_for_an_8_gpu_job():
     assert pod["initContainers"] == []                              # no dataset uploaded
     # the sidecar's sync patterns pick up what the payload writes
     assert "--include '*.csv'" in sidecar["args"][1] and "--include '*.pt'" in sidecar["args"][1]
+    assert "--include '*.safetensors'" in sidecar["args"][1] and "state" not in sidecar["args"][1]
 
 
 def test_manifest_single_gpu_and_entrypoint_accepts_the_command():

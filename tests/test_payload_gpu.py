@@ -30,7 +30,7 @@ def test_entrypoint_outputs_and_resume(tmp_path, capsys):
     assert train.main(_args(a, data, 6)) == 0
     out = capsys.readouterr().out
     assert out.splitlines()[0].startswith("Epoch"), "the controller's log stream is gated on an 'Epoch' line"
-    for f in ("metrics.csv", "adapter.pt", "adapter_config.json", "state.pt"):
+    for f in ("metrics.csv", "adapter.pt", "adapter_config.json", "adapter_model.safetensors", "resume.state"):
         assert (a / f).exists(), f
     import pandas as pd
     rec = pd.read_csv(a / "metrics.csv").fillna(0).to_dict("records")
@@ -87,7 +87,7 @@ def test_entrypoint_full_parameter_mode_and_resume(tmp_path, capsys):
     a, b = tmp_path / "fa", tmp_path / "fb"
     assert train.main(args(a, 6)) == 0
     assert "mode=full" in capsys.readouterr().out.splitlines()[0]
-    for f in ("metrics.csv", "model.pt", "config.json", "state.pt"):
+    for f in ("metrics.csv", "model.pt", "config.json", "resume.state"):
         assert (a / f).exists(), f
     assert not (a / "adapter.pt").exists()
     cfg = __import__("json").load(open(a / "config.json"))
@@ -103,3 +103,39 @@ def test_entrypoint_full_parameter_mode_and_resume(tmp_path, capsys):
     for k in w:
         d = (wb[k].float() - w[k].float()).abs()
         assert float((d > 2 ** -7 * 0.1).float().mean()) <= 1e-2 and float(d.max()) <= 6 * 0.003, k
+
+
+def test_entrypoint_starts_from_pretrained_base_weights(tmp_path):
+    """--base_weights: a Hugging Face-named safetensors checkpoint under the dataset mount becomes the frozen
+    base.  The first logged loss (PEFT init: B = 0, so the adapters do not act yet) must be the oracle's loss of
+    THAT checkpoint on the same batch, not the loss of a random model; the PEFT-named adapter file is written."""
+    from safetensors.torch import load_file, save_file
+    from b200ft import train
+    from oracle import gpt2_lora_ref as ref
+    cfg = ref.GPT2_TINY
+    p = ref.init_base_params(cfg, seed=11, randomize_all=True)
+    p = {k: v * 5.0 if k == "wte" else v for k, v in p.items()}              # loss 6.96: far from a random init's 6.25
+    sd = {k: v.detach().clone().contiguous() for k, v in ref.hf_model(cfg, p).state_dict().items() if k != "lm_head.weight"}
+    data = tmp_path / "dataset"; (data / "hf").mkdir(parents=True)
+    save_file(sd, str(data / "hf" / "model.safetensors"))
+    out = tmp_path / "o"
+    args = ["--model=gpt2-tiny", "--seq_len=32", "--batch_size=2", "--epochs=1", "--steps_per_epoch=2", "--lr=0.001",
+            "--log_interval=1", "--save_model", "--synthetic", "--base_weights=hf", "--save_interval=-1",
+            f"--dataset_path={data}", f"--checkpoint_path={out}"]
+    assert train.main(args) == 0
+    import pandas as pd
+    first = pd.read_csv(out / "metrics.csv").to_dict("records")[0]
+    ids = torch.randint(0, cfg.vocab, (2, 32), generator=torch.Generator().manual_seed(1234), dtype=torch.int64)
+    want = float(ref.causal_lm_loss(ref.forward(p, None, ids, cfg, None), ids))
+    rand = float(ref.causal_lm_loss(ref.forward(ref.init_base_params(cfg, 0), None, ids, cfg, None), ids))
+    assert abs(first["loss"] - want) / want <= 2e-2 and abs(want - rand) / rand > 5e-2
+    assert not (out / "resume.state").exists()                               # --save_interval=-1
+    t = load_file(str(out / "adapter_model.safetensors"))
+    assert t["base_model.model.transformer.h.0.attn.c_attn.lora_A.weight"].shape == (8, 64)
+    w = torch.load(out / "adapter.pt")
+    assert torch.equal(t["base_model.model.transformer.h.1.attn.c_attn.lora_B.weight"], w["h1.c_attn.lora_B"].t())
+    with pytest.raises(ValueError, match="vocabulary"):                      # ids beyond the model's vocabulary
+        bad = tmp_path / "bad"; bad.mkdir()
+        np.full(4000, 60000, dtype=np.uint16).tofile(bad / "tokens.bin")
+        train.main(["--model=gpt2-tiny", "--seq_len=32", "--batch_size=2", "--steps_per_epoch=1",
+                    f"--dataset_path={bad}", f"--checkpoint_path={tmp_path / 'x'}"])

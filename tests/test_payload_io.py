@@ -40,7 +40,16 @@ def test_batches_are_deterministic_disjoint_across_ranks_and_wrap():
     short = torch.arange(40)
     w = train.batch_from_stream(short, 0, 0, 1, 4, 16, vocab=50257)  # stream shorter than one batch: wraps
     assert w.flatten().tolist() == [i % 40 for i in range(64)]
-    assert int(train.batch_from_stream(torch.tensor([10 ** 6] * 64), 0, 0, 1, 4, 16, vocab=100).max()) == 99  # clamped
+
+
+def test_out_of_range_token_ids_stop_the_job_instead_of_being_clamped():
+    train.check_token_range(torch.arange(100), vocab=100)
+    with pytest.raises(ValueError, match="vocabulary"):
+        train.check_token_range(torch.tensor([1, 2, 100]), vocab=100)
+    with pytest.raises(ValueError, match="vocabulary"):
+        train.check_token_range(torch.tensor([-1, 2]), vocab=100)
+    with pytest.raises(ValueError):
+        train.check_token_range(torch.tensor([], dtype=torch.int64), vocab=100)
 
 
 def test_metrics_csv_is_what_the_controller_parses(tmp_path):
