@@ -141,7 +141,7 @@ def cpu_oracle_tokens_per_s(batch: int, seq: int, steps: int, warmup: int) -> tu
         dt = time.perf_counter() - t0
         if s >= warmup:
             times.append(dt)
-    per_step = sum(times) / len(times)
+    per_step = statistics.median(times)
     return batch * seq / per_step, torch.get_num_threads(), per_step
 
 
@@ -168,6 +168,101 @@ def run_reference(args) -> None:
 
 
 # ----------------------------------------------------------------------------------------
+# multi-rank parity check (N > 1 only; runs BEFORE the timed region): the data-parallel step on the real NCCL
+# ranks against the oracle's data-parallel emulation (mean of the per-rank gradients), for the two exchange
+# paths the payload uses — LoRA (two buckets on the default communicator) and full-parameter (one bucket per
+# layer on the CTA-limited communicator, SMs reserved in the backward GEMMs, tail on the default group).
+# The GPU test box has one GPU, so tests/test_ddp_gpu.py can only run where 2+ GPUs are leased; this puts the
+# same check in front of every multi-GPU bench line.
+# ----------------------------------------------------------------------------------------
+def dp_parity(rank: int, world: int, dev, nccl_ctas: int) -> dict:
+    import torch.distributed as dist
+    from b200ft import ddp, gpt2, llama, llama_full
+    from oracle import gpt2_lora_ref as gref
+    from oracle import llama_lora_ref as lref
+
+    def cos(a, b):
+        a, b = a.flatten().double(), b.flatten().double()
+        return float((a @ b) / (a.norm() * b.norm() + 1e-30))
+
+    def identical(flat: torch.Tensor) -> bool:
+        """bit-equality of a rank's trained parameters with rank 0's"""
+        mine = flat.detach().clone()
+        dist.broadcast(flat0 := mine.clone(), src=0)
+        same = torch.tensor([float(torch.equal(mine, flat0))], device=dev)
+        dist.all_reduce(same, op=dist.ReduceOp.MIN)
+        return bool(same.item() == 1.0)
+
+    def mean_loss(l: torch.Tensor) -> float:
+        t = l.detach().clone().float()
+        dist.all_reduce(t)
+        return float(t.item()) / world
+
+    out, steps = {}, 2
+    # --- LoRA path (GPT-2 tiny) ---
+    cfg, lora, opt = gref.GPT2_TINY, gref.LoRAConfig(r=8, alpha=16.0), gref.AdamWConfig(lr=1e-3)
+    base = gref.init_base_params(cfg, seed=0, randomize_all=True)
+    ad = gref.init_lora_params(cfg, lora, seed=1, b_init="normal")
+    dims = gpt2.GPT2Dims(cfg.n_layer, cfg.d_model, cfg.n_head, cfg.d_ff, cfg.vocab, cfg.ctx, cfg.ln_eps)
+    eng = gpt2.GPT2LoRAStep(dims, gpt2.LoRASpec(8, 16.0), gpt2.OptSpec(opt.lr, opt.beta1, opt.beta2, opt.eps,
+                                                                     opt.weight_decay), base, ad, batch=2, seq=32,
+                            device=dev, world_size=world, grad_sync=ddp.BucketedGradSync(cfg.n_layer, n_buckets=2))
+    got = []
+    for s in range(steps):
+        ids, labels = gref.synthetic_batch(cfg, 2, 32, seed=1234 + 10 * s, rank=rank)
+        got.append(mean_loss(eng.step(ids.to(dev), labels.to(dev))))
+    same_lora = identical(eng.P)
+    rel_lora, cos_lora = 0.0, 1.0
+    if rank == 0:
+        tr = gref.OracleTrainer(cfg, lora, opt, base, ad)
+        for s in range(steps):
+            want = tr.step(None, None, world_grads=[gref.synthetic_batch(cfg, 2, 32, seed=1234 + 10 * s, rank=r)
+                                                    for r in range(world)])
+            rel_lora = max(rel_lora, abs(got[s] - want) / want)
+        new = eng.adapters_state()
+        cos_lora = min(cos(new[k] - ad[k], t.detach() - ad[k]) for k, t in tr.trainable.items())
+    # --- full-parameter path (Llama tiny, 3 layers, untied), production all-reduce configuration ---
+    cfg = lref.LlamaConfig(n_layer=3, d_model=64, n_head=4, n_kv_head=2, d_ff=128, vocab=503, ctx=128,
+                           rope_theta=10000.0, rope_llama3=False, tie_embeddings=False)
+    opt = gref.AdamWConfig(lr=1e-3, max_grad_norm=1.0)
+    base = lref.init_base_params(cfg, seed=0, randomize_all=True)
+    ldims = llama.LlamaDims(cfg.n_layer, cfg.d_model, cfg.n_head, cfg.n_kv_head, cfg.d_ff, cfg.vocab, cfg.ctx,
+                            cfg.rms_eps, cfg.rope_theta, cfg.rope_llama3, tie_embeddings=cfg.tie_embeddings)
+    k = nccl_ctas if nccl_ctas > 0 else 8
+    sync = ddp.BucketedGradSync(cfg.n_layer, n_buckets=cfg.n_layer, group=ddp.overlap_group(k), reserve_ctas=k,
+                                use_tail_group=True)
+    feng = llama_full.LlamaFullStep(ldims, gpt2.OptSpec(opt.lr, opt.beta1, opt.beta2, opt.eps, opt.weight_decay,
+                                                        opt.max_grad_norm), base, batch=2, seq=32, device=dev,
+                                    world_size=world, grad_sync=sync)
+    got = []
+    for s in range(steps):
+        ids, labels = lref.synthetic_batch(cfg, 2, 32, seed=500 + 10 * s, rank=rank)
+        got.append(mean_loss(feng.step(ids.to(dev), labels.to(dev))))
+    same_full = identical(feng.P) and identical(feng.Pn)
+    rel_full, cos_full = 0.0, 1.0
+    if rank == 0:
+        tr = lref.FullOracleTrainer(cfg, opt, base)
+        for s in range(steps):
+            want = tr.step(None, None, world_grads=[lref.synthetic_batch(cfg, 2, 32, seed=500 + 10 * s, rank=r)
+                                                    for r in range(world)])
+            rel_full = max(rel_full, abs(got[s] - want) / want)
+        new = feng.params_state()
+        cos_full = min(cos(new[k2] - base[k2], t.detach() - base[k2]) for k2, t in tr.trainable.items())
+    del eng, feng
+    torch.cuda.empty_cache()
+    out = {"ok": bool(same_lora and same_full and rel_lora <= 2e-2 and rel_full <= 2e-2 and cos_lora >= 0.99
+                      and cos_full >= 0.97),
+           "loss_rel": max(rel_lora, rel_full), "ranks_identical": bool(same_lora and same_full),
+           "lora": {"loss_rel": rel_lora, "delta_cos_min": cos_lora, "ranks_identical": same_lora},
+           "full": {"loss_rel": rel_full, "delta_cos_min": cos_full, "ranks_identical": same_full,
+                    "nccl_ctas": k},
+           "what": f"{steps} steps of tiny GPT-2 LoRA and tiny Llama full-parameter on the {world} NCCL ranks vs the CPU "
+                   "oracle's data-parallel emulation; tolerances: loss 2e-2 rel, parameter-delta cosine 0.99 / 0.97, "
+                   "bit-identical parameters across ranks"}
+    return out
+
+
+# ----------------------------------------------------------------------------------------
 # the CUDA arm
 # ----------------------------------------------------------------------------------------
 def run_ours(args) -> None:
@@ -184,6 +279,7 @@ def run_ours(args) -> None:
     dev = torch.device("cuda", local)
     model, BATCH, SEQ, lora_r, lora_alpha, workload_desc = WORKLOADS[args.workload]
     full = lora_r == 0
+    parity = dp_parity(rank, world, dev, args.nccl_ctas) if world > 1 and not args.no_dp_parity else None
     lora = gpt2.LoRASpec(lora_r or 8, lora_alpha or 16.0)
     opt = gpt2.OptSpec()
     n_layer = params.MODELS[model].n_layer
@@ -304,10 +400,10 @@ def run_ours(args) -> None:
         others.append(adamw_large_buffer(ops, dev, pk))
     cpu = None
     if world == 1 and not args.no_cpu_baseline and args.workload == "c2":
-        tps, cores, per_step = cpu_oracle_tokens_per_s(8, 512, steps=2, warmup=1)
+        tps, cores, per_step = cpu_oracle_tokens_per_s(8, 512, steps=3, warmup=1)
         cpu = {"value": tps, "unit": UNIT, "cores": cores, "kind": "port",
                "sample": "oracle/gpt2_lora_ref.py at BASELINE.json configs[0] (GPT-2 124M LoRA r=8 fp32, batch 8, "
-                         f"seq 512): mean of 2 steps after 1 warm-up, {per_step:.2f} s/step"}
+                         f"seq 512): median of 3 steps after 1 warm-up (BASELINE.md §4), {per_step:.2f} s/step"}
     line = {
         "metric": METRIC, "value": tokens / (ms * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
@@ -326,6 +422,8 @@ def run_ours(args) -> None:
         "roofline_others": others,
         "cpu_baseline": cpu,
     }
+    if parity is not None:
+        line["dp_parity"] = parity
     print(json.dumps(line), flush=True)
 
 
@@ -356,6 +454,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-dp-parity", action="store_true", help="N > 1: skip the multi-rank parity check")
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
     ap.add_argument("--nccl-ctas", type=int, default=8,
                     help="full-parameter workloads: CTAs of the overlapped all-reduce (and SMs x2 left free by the "
