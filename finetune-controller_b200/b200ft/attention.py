@@ -1,6 +1,6 @@
 """The repo's own causal flash-attention (csrc/attention.cu, csrc/attention_bwd.cu) as a step-engine
 mixin.  Engines take ``attention="sdpa"`` (torch SDPA -> cuDNN, the faster one today and the default)
-or ``attention="own"`` (tcgen05 kernels of this library, d_head 64 only: GPT-2 and Llama-3.2-1B).
+or ``attention="own"`` (tcgen05 kernels of this library: d_head 64 — GPT-2, Llama-3.2-1B — and 128 — Llama-3-8B).
 SURVEY.md §8 a2.8 / (f)-1."""
 from __future__ import annotations
 
@@ -15,8 +15,8 @@ class OwnAttentionMixin:
     """Expects B, T, M, dev and per-layer fused projection outputs ``self.qkv[l]`` laid out q | k | v."""
 
     def _own_attn_setup(self, n_head: int, n_kv_head: int, d_head: int, n_layer: int) -> None:
-        if d_head != 64:
-            raise ValueError(f"attention='own' is built for d_head 64 (this model has {d_head}); use 'sdpa'")
+        if d_head not in (64, 128):
+            raise ValueError(f"attention='own' is built for d_head 64 and 128 (this model has {d_head}); use 'sdpa'")
         bf, f32 = dict(dtype=torch.bfloat16, device=self.dev), dict(dtype=torch.float32, device=self.dev)
         nq, nkv = n_head * d_head, n_kv_head * d_head
         self._att = dict(batch=self.B, seq=self.T, n_head=n_head, n_kv_head=n_kv_head, d_head=d_head, q_off=0,

@@ -142,6 +142,12 @@ def softmax_xent_fwd_bwd(logits, targets, loss_out, workspace, *, vocab, grad_sc
     return loss_out
 
 
+def softmax_xent_bad_targets(workspace) -> int:
+    """Targets of the LAST softmax_xent_fwd_bwd call on this workspace that were neither ignore_index nor inside
+    [0, vocab): the kernel treats them as ignored and counts them in scratch word 2.  Synchronises (reads 4 bytes)."""
+    return int(workspace[8:12].view(torch.int32).item())
+
+
 def shift_targets(labels, targets, ignore_index=-100):
     global LAUNCHES
     _need_cuda(labels, targets)

@@ -27,16 +27,27 @@
 namespace {
 using namespace b200ft_attn;
 
-constexpr int kDH = 64;
 constexpr int kBQ = 128, kBK = 128;
 constexpr int kThreads = 384;
-constexpr int kQBytes = kBQ * kDH * 2;          // 16 KB per query tile
-constexpr int kKVBytes = kBK * kDH * 2;         // 16 KB
 constexpr int kStages = 2;
-constexpr int kTiles = 2 * kQBytes + 2 * kStages * kKVBytes;  // 96 KB
-constexpr int kSmemBytes = kTiles + 256;        // + barriers; no alignment slack (the kernel checks the base)
+constexpr int kBoxBytes = 128 * 64 * 2;         // one TMA box: 128 rows x 64 columns, 128B-swizzled = 16 KB
 constexpr int kTmemCols = 512;
-constexpr uint32_t kColS = 0, kColPV = 256, kColP = 384;  // + 128*g, + 64*g, + 64*g (P: bf16 pairs, 64 columns)
+// Per head size.  A [128 x DH] tile is DH/64 boxes side by side.  TMEM: S_g at 128*g; O_g at 256 + DH*g; P_g (bf16
+// pairs, 64 columns) in its own columns for DH = 64 and ON TOP OF S_g for DH = 128, where S (256) + O (256) fill
+// the 512 columns: the exponentials then overwrite the scores they came from, the row maximum is found in a
+// read-only pass first, and the issue order per query tile becomes P V (j) before S (j+1).
+template <int DH> struct Cfg {
+  static_assert(DH == 64 || DH == 128, "head sizes built: 64, 128");
+  static constexpr int kBoxes = DH / 64;
+  static constexpr int kQBytes = kBQ * DH * 2;          // 16 / 32 KB per query tile
+  static constexpr int kKVBytes = kBK * DH * 2;
+  static constexpr int kTiles = 2 * kQBytes + 2 * kStages * kKVBytes;   // 96 / 192 KB
+  static constexpr int kSmemBytes = kTiles + 256;       // + barriers; no alignment slack (the kernel checks the base)
+  static constexpr bool kAliasP = DH == 128;
+  static constexpr uint32_t kColS = 0, kColPV = 256;
+  static constexpr uint32_t kColP = kAliasP ? 0u : 384u;
+  static constexpr uint32_t kStrideP = kAliasP ? 128u : 64u;   // column distance between P_A and P_B
+};
 #ifndef B200FT_ATTN_SWEEP_LD
 #define B200FT_ATTN_SWEEP_LD 64
 #endif
@@ -135,8 +146,12 @@ __device__ __forceinline__ FwdItem decode_item(const AttnParams& p, int w) {
 // every role advances identically: kc = kv tiles streamed so far, cA / cB = tiles each query group has processed,
 // n = items.  The producer requests the next item's query tiles as soon as the last UMMAs of the current one retire
 // and keeps the K / V ring running across the boundary, so an item's prologue hides behind its predecessor's tail.
+template <int DH>
 __global__ void __launch_bounds__(kThreads, 1)
 attn_fwd_kernel(const __grid_constant__ CUtensorMap tm, const AttnParams p) {
+  using C = Cfg<DH>;
+  constexpr int kDH = DH, kQBytes = C::kQBytes, kKVBytes = C::kKVBytes, kTiles = C::kTiles;
+  constexpr uint32_t kColS = C::kColS, kColPV = C::kColPV, kColP = C::kColP;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
   if (raw & 1023u) __trap();  // dynamic shared memory starts 1024-aligned (no static smem in this kernel)
@@ -189,8 +204,11 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm, const AttnParams p) {
     if (n > 0) mbar_wait(q_empty, (n - 1) & 1u);   // the previous item's UMMAs are done with the query tiles
     if (issuer) {
       mbar_expect_tx(q_full, it.hasB ? 2 * kQBytes : kQBytes);
-      tma_load_3d(sQ, &tm, p.q_off + h * kDH, it.qtA * kBQ, b, q_full);
-      if (it.hasB) tma_load_3d(sQ + kQBytes, &tm, p.q_off + h * kDH, it.qtB * kBQ, b, q_full);
+#pragma unroll
+      for (int bx = 0; bx < C::kBoxes; ++bx) {
+        tma_load_3d(sQ + bx * kBoxBytes, &tm, p.q_off + h * kDH + 64 * bx, it.qtA * kBQ, b, q_full);
+        if (it.hasB) tma_load_3d(sQ + kQBytes + bx * kBoxBytes, &tm, p.q_off + h * kDH + 64 * bx, it.qtB * kBQ, b, q_full);
+      }
     }
     __syncwarp();
     for (int j = 0; j < it.n_kv; ++j, ++kc) {
@@ -199,13 +217,17 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm, const AttnParams p) {
       mbar_wait(k_empty(st), ph ^ 1u);
       if (issuer) {
         mbar_expect_tx(k_full(st), kKVBytes);
-        tma_load_3d(sK + st * kKVBytes, &tm, p.k_off + hk * kDH, j * kBK, b, k_full(st));
+#pragma unroll
+        for (int bx = 0; bx < C::kBoxes; ++bx)
+          tma_load_3d(sK + st * kKVBytes + bx * kBoxBytes, &tm, p.k_off + hk * kDH + 64 * bx, j * kBK, b, k_full(st));
       }
       __syncwarp();
       mbar_wait(v_empty(st), ph ^ 1u);
       if (issuer) {
         mbar_expect_tx(v_full(st), kKVBytes);
-        tma_load_3d(sV + st * kKVBytes, &tm, p.v_off + hk * kDH, j * kBK, b, v_full(st));
+#pragma unroll
+        for (int bx = 0; bx < C::kBoxes; ++bx)
+          tma_load_3d(sV + st * kKVBytes + bx * kBoxBytes, &tm, p.v_off + hk * kDH + 64 * bx, j * kBK, b, v_full(st));
       }
       __syncwarp();
     }
@@ -214,13 +236,13 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm, const AttnParams p) {
     // ================================ MMA issuer ================================
     const bool issuer = elect_one();
     const uint32_t id_s = idesc(kBK, 0, 0);   // S: N = 128 keys, K-major B (K_j rows = keys, d_head contiguous)
-    const uint32_t id_pv = idesc(kDH, 0, 1);  // PV: N = 64, MN-major B (V_j rows = keys = reduction index)
+    const uint32_t id_pv = idesc(kDH, 0, 1);  // PV: N = d_head, MN-major B (V_j rows = keys = reduction index)
     auto issue_s = [&](int g, int st) {    // S_g = Q_g K^T
       if (issuer) {
 #pragma unroll
         for (int k = 0; k < kDH / 16; ++k)
-          umma(tmem + kColS + 128u * g, sdesc(sQ + g * kQBytes + 32 * k, 16, 1024),
-               sdesc(sK + st * kKVBytes + 32 * k, 16, 1024), id_s, k > 0);
+          umma(tmem + kColS + 128u * g, sdesc(sQ + g * kQBytes + (k >> 2) * kBoxBytes + 32 * (k & 3), 16, 1024),
+               sdesc(sK + st * kKVBytes + (k >> 2) * kBoxBytes + 32 * (k & 3), 16, 1024), id_s, k > 0);
         umma_commit(s_full(g));
       }
       __syncwarp();
@@ -233,8 +255,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm, const AttnParams p) {
 #ifndef B200FT_EXP_NO_PV   // bottleneck experiment (tools/attn_exp.py): skip the P V UMMAs, wrong numbers
 #pragma unroll
         for (int k = 0; k < kBK / 16; ++k)
-          umma_ts(tmem + kColPV + 64u * g, tmem + kColP + 64u * g + 8u * k,
-                  sdesc(sV + st * kKVBytes + 2048 * k, 8192, 1024), id_pv, !(first && k == 0));
+          umma_ts(tmem + kColPV + (uint32_t)kDH * g, tmem + kColP + C::kStrideP * g + 8u * k,
+                  sdesc(sV + st * kKVBytes + 2048 * k, kBoxBytes, 1024), id_pv, !(first && k == 0));
 #endif
         umma_commit(pv_full(g));
       }
@@ -262,28 +284,56 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm, const AttnParams p) {
       const uint32_t parA = (cA + (uint32_t)j) & 1u, parB = (cB + (uint32_t)j) & 1u;
       bool k_next_ready = false;
       mbar_wait(v_full(st), ph);
-      // per tile g: the next scores S_g(j+1) first (the softmax is waiting for them), then P_g V(j)
-      if (j + 1 < nA) {
-        mbar_wait(k_full(nst), nph); k_next_ready = true;
-        mbar_wait(s_free(0), parA);      // softmax A has drained S_A(j)
-        tc_fence_after();
-        issue_s(0, nst);
-      }
-      if (j < nA) {
-        mbar_wait(p_full(0), parA);      // P_A(j) is in TMEM (and O_A rescaled if its reference moved)
-        tc_fence_after();
-        issue_pv(0, st, j == 0);
-      }
-      if (j + 1 < nB) {
-        if (!k_next_ready) mbar_wait(k_full(nst), nph);
-        mbar_wait(s_free(1), parB);
-        tc_fence_after();
-        issue_s(1, nst);
-      }
-      if (j < nB) {
-        mbar_wait(p_full(1), parB);
-        tc_fence_after();
-        issue_pv(1, st, j == 0);
+      if (!C::kAliasP) {
+        // per tile g: the next scores S_g(j+1) first (the softmax is waiting for them), then P_g V(j)
+        if (j + 1 < nA) {
+          mbar_wait(k_full(nst), nph); k_next_ready = true;
+          mbar_wait(s_free(0), parA);      // softmax A has drained S_A(j)
+          tc_fence_after();
+          issue_s(0, nst);
+        }
+        if (j < nA) {
+          mbar_wait(p_full(0), parA);      // P_A(j) is in TMEM (and O_A rescaled if its reference moved)
+          tc_fence_after();
+          issue_pv(0, st, j == 0);
+        }
+        if (j + 1 < nB) {
+          if (!k_next_ready) mbar_wait(k_full(nst), nph);
+          mbar_wait(s_free(1), parB);
+          tc_fence_after();
+          issue_s(1, nst);
+        }
+        if (j < nB) {
+          mbar_wait(p_full(1), parB);
+          tc_fence_after();
+          issue_pv(1, st, j == 0);
+        }
+      } else {
+        // P_g lives on top of S_g: P_g V(j) first, then S_g(j+1) into the same columns (UMMAs execute in issue
+        // order, so the new scores land after P has been read); while tile A's softmax works on S_A(j+1) the
+        // tensor core runs P_B V(j) and S_B(j+1)
+        if (j < nA) {
+          mbar_wait(p_full(0), parA);
+          tc_fence_after();
+          issue_pv(0, st, j == 0);
+        }
+        if (j + 1 < nA) {
+          mbar_wait(k_full(nst), nph); k_next_ready = true;
+          mbar_wait(s_free(0), parA);
+          tc_fence_after();
+          issue_s(0, nst);
+        }
+        if (j < nB) {
+          mbar_wait(p_full(1), parB);
+          tc_fence_after();
+          issue_pv(1, st, j == 0);
+        }
+        if (j + 1 < nB) {
+          if (!k_next_ready) mbar_wait(k_full(nst), nph);
+          mbar_wait(s_free(1), parB);
+          tc_fence_after();
+          issue_s(1, nst);
+        }
       }
       if (issuer) umma_commit(v_empty(st));
       __syncwarp();
@@ -302,8 +352,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm, const AttnParams p) {
     const int quarter = warp & 3;                 // TMEM lanes this warp may touch
     const int row = quarter * 32 + lane;          // row within the query tile
     const uint32_t t_s = tmem + ((uint32_t)(quarter * 32) << 16) + kColS + 128u * g;
-    const uint32_t t_pv = tmem + ((uint32_t)(quarter * 32) << 16) + kColPV + 64u * g;
-    const uint32_t t_p = tmem + ((uint32_t)(quarter * 32) << 16) + kColP + 64u * g;
+    const uint32_t t_pv = tmem + ((uint32_t)(quarter * 32) << 16) + kColPV + (uint32_t)kDH * g;
+    const uint32_t t_p = tmem + ((uint32_t)(quarter * 32) << 16) + kColP + C::kStrideP * g;
     uint32_t cg = 0;                              // tiles this group has processed so far
     for (int w = blockIdx.x; w < num_items; w += gridDim.x) {
     const FwdItem it = decode_item(p, w);
@@ -319,7 +369,25 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm, const AttnParams p) {
       tc_fence_after();
       const bool diag = (j == qt);
       const int kbase = j * kBK;
-      if (j == 0) {  // the first tile has no reference yet: one extra sweep for the row max
+      // rescale this warp's rows of O in TMEM by alpha (rows whose reference stays pass alpha = 1).  Only legal while
+      // no P V UMMA of this query tile is in flight: those of tile j-1 have retired, those of tile j are not issued
+      // before p_full.
+      auto rescale_o = [&](float alpha) {
+#pragma unroll
+        for (int c = 0; c < kDH / 32; ++c) {
+          uint32_t r[32];
+          tmem_ld32(t_pv + 32 * c, r);
+          tmem_wait_ld();
+#pragma unroll
+          for (int i = 0; i < 32; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * alpha);
+          tmem_st16(t_pv + 32 * c, r);
+          tmem_st16(t_pv + 32 * c + 16, r + 16);
+        }
+        tmem_wait_st();
+      };
+      if (j == 0 || C::kAliasP) {
+        // read-only pass for the row maximum: always on the first tile (no reference yet), and on every tile when P
+        // overwrites S (the reference has to be settled before the scores are destroyed)
         float mx0 = -INFINITY;
 #pragma unroll
         for (int c = 0; c < kBK / 32; ++c) {
@@ -330,7 +398,23 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm, const AttnParams p) {
           for (int i = 0; i < 32; ++i)
             mx0 = fmaxf(mx0, (diag && kbase + 32 * c + i > qrow) ? -INFINITY : __uint_as_float(r[i]));
         }
-        m_ref = mx0 * p.scale_log2;
+        if (j == 0) {
+          m_ref = mx0 * p.scale_log2;
+        } else {
+          // lazy rescaling, decided up front: keep the old reference unless this row's max outgrew it by 2^8.
+          // s_full(j) was committed after P V (j-1) in issue order, so O is quiescent here.
+          const bool grow = mx0 * p.scale_log2 > m_ref + kRescaleThreshold;
+          if (__any_sync(0xffffffffu, grow)) {
+            float alpha = 1.f;
+            if (grow) {
+              const float m_new = mx0 * p.scale_log2;
+              alpha = ex2(m_ref - m_new);
+              l *= alpha;
+              m_ref = m_new;
+            }
+            rescale_o(alpha);
+          }
+        }
       }
       float sum, mx;
       bool first_pass = true;
@@ -339,6 +423,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm, const AttnParams p) {
         if (diag) softmax_sweep<true>(t_s, t_p, p.scale_log2, m_ref, kbase, qrow, wait_pv, pv_full(g), par ^ 1u, sum, mx);
         else      softmax_sweep<false>(t_s, t_p, p.scale_log2, m_ref, kbase, qrow, wait_pv, pv_full(g), par ^ 1u, sum, mx);
         first_pass = false;
+        if (C::kAliasP) break;   // the reference was settled before the sweep; the scores are gone now
         // lazy rescaling: keep the old reference unless this row's max outgrew it by 2^8
         const bool grow = mx * p.scale_log2 > m_ref + kRescaleThreshold;
         if (!__any_sync(0xffffffffu, grow)) break;
@@ -349,21 +434,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm, const AttnParams p) {
           l *= alpha;
           m_ref = m_new;
         }
-        if (j > 0) {
-          // rare: rescale this warp's rows of O in TMEM (the P V UMMAs of tile j-1 have retired: the sweep waited
-          // for them; those of tile j are not issued before p_full); rows whose reference stays use alpha = 1
-#pragma unroll
-          for (int c = 0; c < kDH / 32; ++c) {
-            uint32_t r[32];
-            tmem_ld32(t_pv + 32 * c, r);
-            tmem_wait_ld();
-#pragma unroll
-            for (int i = 0; i < 32; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * alpha);
-            tmem_st16(t_pv + 32 * c, r);
-            tmem_st16(t_pv + 32 * c + 16, r + 16);
-          }
-          tmem_wait_st();
-        }
+        if (j > 0) rescale_o(alpha);   // rare (the sweep waited for the P V UMMAs of tile j-1)
       }
       l += sum;
       tmem_wait_st();
@@ -376,21 +447,21 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm, const AttnParams p) {
       mbar_wait(pv_full(g), (cg + (uint32_t)n_mine - 1u) & 1u);
       tc_fence_after();
       const float inv_l = 1.f / l;
-      float o[kDH];
+      __nv_bfloat16* dst = p.out + ((int64_t)b * p.seq + qrow) * p.ld_out + h * kDH;
 #pragma unroll
-      for (int c = 0; c < kDH / 32; ++c) {
+      for (int c = 0; c < kDH / 32; ++c) {   // 32 columns (64 bytes of output) per TMEM round trip
         uint32_t r[32];
+        float o[32];
         tmem_ld32(t_pv + 32 * c, r);
         tmem_wait_ld();
 #pragma unroll
-        for (int i = 0; i < 32; ++i) o[32 * c + i] = __uint_as_float(r[i]) * inv_l;
-      }
-      if (qrow < p.seq) {
-        __nv_bfloat16* dst = p.out + ((int64_t)b * p.seq + qrow) * p.ld_out + h * kDH;
+        for (int i = 0; i < 32; ++i) o[i] = __uint_as_float(r[i]) * inv_l;
+        if (qrow < p.seq) {
 #pragma unroll
-        for (int v = 0; v < kDH / 8; ++v) *reinterpret_cast<uint4*>(dst + 8 * v) = pack8(o + 8 * v);
-        p.lse2[(int64_t)bh * p.seq + qrow] = m_ref + log2f(l);
+          for (int v = 0; v < 4; ++v) *reinterpret_cast<uint4*>(dst + 32 * c + 8 * v) = pack8(o + 8 * v);
+        }
       }
+      if (qrow < p.seq) p.lse2[(int64_t)bh * p.seq + qrow] = m_ref + log2f(l);
     }
     cg += (uint32_t)n_mine;
     }  // items
@@ -410,10 +481,11 @@ extern "C" int b200ft_attn_fwd(const void* qkv, int64_t ld, int q_off, int k_off
                                int64_t ld_out, float* lse2, int batch, int seq, int n_head, int n_kv_head,
                                int d_head, float scale, void* stream) {
   B200FT_CHECK_ARG(qkv && out && lse2, "attn_fwd: null buffer");
-  if (d_head != kDH) {
-    b200ft_set_error("attn_fwd: d_head=%d is not built (only 64)", d_head);
+  if (d_head != 64 && d_head != 128) {
+    b200ft_set_error("attn_fwd: d_head=%d is not built (64 and 128 are)", d_head);
     return B200FT_ERR_UNSUPPORTED;
   }
+  const int kDH = d_head;
   B200FT_CHECK_ARG(batch > 0 && seq > 0 && n_head > 0 && n_kv_head > 0 && n_head % n_kv_head == 0,
                    "attn_fwd: batch=%d seq=%d heads=%d kv_heads=%d", batch, seq, n_head, n_kv_head);
   B200FT_CHECK_ARG(ld % 8 == 0 && ld_out % 8 == 0 && q_off % 8 == 0 && k_off % 8 == 0 && v_off % 8 == 0 &&
@@ -436,15 +508,9 @@ extern "C" int b200ft_attn_fwd(const void* qkv, int64_t ld, int q_off, int k_off
   int dev = -1;
   B200FT_CUDA(cudaGetDevice(&dev));
   if (dev != attr_dev) {
-    B200FT_CUDA(cudaFuncSetAttribute(attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+    B200FT_CUDA(cudaFuncSetAttribute(attn_fwd_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<64>::kSmemBytes));
+    B200FT_CUDA(cudaFuncSetAttribute(attn_fwd_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<128>::kSmemBytes));
     attr_dev = dev;
-  }
-  static int occ_reported = 0;
-  if (!occ_reported && getenv("B200FT_DEBUG")) {
-    int nb = 0;
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, attn_fwd_kernel, kThreads, kSmemBytes);
-    fprintf(stderr, "[b200ft] attn_fwd_kernel: %d CTAs/SM (smem %d B)\n", nb, kSmemBytes);
-    occ_reported = 1;
   }
   const int items = p.nq_pairs * batch * n_head;
   // Short sequences (few kv tiles per item): persistent CTAs, so that an item's prologue hides behind its
@@ -452,7 +518,8 @@ extern "C" int b200ft_attn_fwd(const void* qkv, int64_t ld, int q_off, int k_off
   // placement balances the very unequal items better than the static walk (T >= 2048: 2-3 % faster).
   const bool persistent = p.nq_tiles <= 8 && items > B200FT_NUM_SMS;
   const unsigned grid = (unsigned)(persistent ? B200FT_NUM_SMS : items);
-  attn_fwd_kernel<<<grid, kThreads, kSmemBytes, (cudaStream_t)stream>>>(tm, p);
+  if (d_head == 64) attn_fwd_kernel<64><<<grid, kThreads, Cfg<64>::kSmemBytes, (cudaStream_t)stream>>>(tm, p);
+  else              attn_fwd_kernel<128><<<grid, kThreads, Cfg<128>::kSmemBytes, (cudaStream_t)stream>>>(tm, p);
   B200FT_LAUNCH_CHECK();
   return 0;
 }

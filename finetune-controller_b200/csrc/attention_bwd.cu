@@ -50,16 +50,18 @@ struct BwdParams {
 };
 
 // ------------------------------------------------------------------------------------------------
-// D[bh, t] = sum_d do[t, h*64 + d] * o[t, h*64 + d].  One warp per token: lanes walk the row in 16-byte units
-// (8 units = one head), partial dot products meet across the 8 lanes of a head by shuffle.
+// D[bh, t] = sum_d do[t, h*DH + d] * o[t, h*DH + d].  One warp per token: lanes walk the row in 16-byte units
+// (8 or 16 units = one head), partial dot products meet across the lanes of a head by shuffle.
+template <int DH>
 __global__ void __launch_bounds__(256)
 attn_delta_kernel(const __nv_bfloat16* __restrict__ o, int64_t ld_o, const __nv_bfloat16* __restrict__ dout,
                   int64_t ld_do, float* __restrict__ delta, int batch, int seq, int n_head) {
+  constexpr int kUPH = DH / 8;                                        // 16-byte units per head: 8 or 16 lanes
   const int64_t tok = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);   // b * seq + t
   if (tok >= (int64_t)batch * seq) return;
   const int lane = threadIdx.x & 31;
   const int b = (int)(tok / seq), t = (int)(tok % seq);
-  const int units = n_head * (kDH / 8);
+  const int units = n_head * kUPH;
   for (int u0 = 0; u0 < units; u0 += 32) {       // 32 units = 4 heads per pass; all lanes stay in the shuffles
     const int u = u0 + lane;
     float acc = 0.f;
@@ -73,7 +75,8 @@ attn_delta_kernel(const __nv_bfloat16* __restrict__ o, int64_t ld_o, const __nv_
     acc += __shfl_xor_sync(0xffffffffu, acc, 1);
     acc += __shfl_xor_sync(0xffffffffu, acc, 2);
     acc += __shfl_xor_sync(0xffffffffu, acc, 4);
-    if (u < units && (lane & 7) == 0) delta[((int64_t)b * n_head + (u >> 3)) * seq + t] = acc;
+    if (kUPH == 16) acc += __shfl_xor_sync(0xffffffffu, acc, 8);
+    if (u < units && (lane & (kUPH - 1)) == 0) delta[((int64_t)b * n_head + u / kUPH) * seq + t] = acc;
   }
 }
 
@@ -508,12 +511,13 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
 
 }  // namespace
 
-// workspace: delta [batch*n_head*seq] fp32 | dQ accumulator [batch*seq, n_head*64] fp32 (fused path only)
+// workspace: delta [batch*n_head*seq] fp32 | dQ accumulator [batch*seq, n_head*64] fp32 (fused d_head-64 path only)
 static size_t delta_bytes(int batch, int seq, int n_head) {
   return (((size_t)batch * n_head * seq * sizeof(float)) + 255) & ~(size_t)255;
 }
 
 extern "C" size_t b200ft_attn_bwd_workspace_bytes(int batch, int seq, int n_head, int d_head) {
+  if (d_head == 128) return delta_bytes(batch, seq, n_head);   // two-kernel form: no fp32 dQ accumulator
   return delta_bytes(batch, seq, n_head) + (size_t)batch * seq * n_head * d_head * sizeof(float);
 }
 
@@ -522,8 +526,8 @@ extern "C" int b200ft_attn_bwd(const void* qkv, int64_t ld, int q_off, int k_off
                                size_t workspace_bytes, void* dqkv, int64_t ld_dqkv, int batch, int seq, int n_head,
                                int n_kv_head, int d_head, float scale, int flags, void* stream) {
   B200FT_CHECK_ARG(qkv && out && dout && lse2 && workspace && dqkv, "attn_bwd: null buffer");
-  if (d_head != kDH) {
-    b200ft_set_error("attn_bwd: d_head=%d is not built (only 64)", d_head);
+  if (d_head != 64 && d_head != 128) {
+    b200ft_set_error("attn_bwd: d_head=%d is not built (64 and 128 are)", d_head);
     return B200FT_ERR_UNSUPPORTED;
   }
   B200FT_CHECK_ARG(batch > 0 && seq > 0 && n_head > 0 && n_kv_head > 0 && n_head % n_kv_head == 0,
@@ -531,11 +535,13 @@ extern "C" int b200ft_attn_bwd(const void* qkv, int64_t ld, int q_off, int k_off
   B200FT_CHECK_ARG(ld % 8 == 0 && ld_out % 8 == 0 && ld_dout % 8 == 0 && ld_dqkv % 8 == 0 && q_off % 8 == 0 &&
                        k_off % 8 == 0 && v_off % 8 == 0 &&
                        ((uintptr_t)qkv | (uintptr_t)out | (uintptr_t)dout | (uintptr_t)dqkv) % 16 == 0 &&
-                       (uintptr_t)workspace % 256 == 0 && ld_out >= (int64_t)n_head * kDH &&
-                       ld_dout >= (int64_t)n_head * kDH,
+                       (uintptr_t)workspace % 256 == 0 && ld_out >= (int64_t)n_head * d_head &&
+                       ld_dout >= (int64_t)n_head * d_head,
                    "attn_bwd: alignment (ld=%lld ld_out=%lld ld_dout=%lld ld_dqkv=%lld offsets %d/%d/%d)",
                    (long long)ld, (long long)ld_out, (long long)ld_dout, (long long)ld_dqkv, q_off, k_off, v_off);
-  const bool split = (flags & B200FT_ATTN_BWD_DETERMINISTIC) != 0;
+  // d_head 128: always the two-kernel form (dK|dV per kv tile, dQ per q tile; no atomics, bit-reproducible) of
+  // attention_bwd_d128.cu — TMEM has no room for a dQ partial beside S, dP, dK and dV at that head size
+  const bool split = (flags & B200FT_ATTN_BWD_DETERMINISTIC) != 0 || d_head == 128;
   const size_t need = split ? delta_bytes(batch, seq, n_head) : b200ft_attn_bwd_workspace_bytes(batch, seq, n_head, d_head);
   if (workspace_bytes < need) {
     b200ft_set_error("attn_bwd: workspace %zu < %zu", workspace_bytes, need);
@@ -580,9 +586,20 @@ extern "C" int b200ft_attn_bwd(const void* qkv, int64_t ld, int q_off, int k_off
   }
   cudaStream_t st = (cudaStream_t)stream;
   const int64_t rows = (int64_t)batch * seq;
-  attn_delta_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, st>>>((const __nv_bfloat16*)out, ld_out,
-                                                                (const __nv_bfloat16*)dout, ld_dout, delta, batch,
-                                                                seq, n_head);
+  if (d_head == 128) {
+    attn_delta_kernel<128><<<(unsigned)((rows + 7) / 8), 256, 0, st>>>((const __nv_bfloat16*)out, ld_out,
+                                                                       (const __nv_bfloat16*)dout, ld_dout, delta,
+                                                                       batch, seq, n_head);
+    B200FT_LAUNCH_CHECK();
+    Bwd128Args a;
+    a.batch = batch; a.seq = seq; a.n_head = n_head; a.n_kv_head = n_kv_head;
+    a.q_off = q_off; a.k_off = k_off; a.v_off = v_off; a.scale = scale;
+    a.lse2 = lse2; a.delta = delta; a.dqkv = (__nv_bfloat16*)dqkv; a.ld_d = ld_dqkv;
+    return launch_bwd_d128(tm_qkv, tm_do, a, st);
+  }
+  attn_delta_kernel<64><<<(unsigned)((rows + 7) / 8), 256, 0, st>>>((const __nv_bfloat16*)out, ld_out,
+                                                                    (const __nv_bfloat16*)dout, ld_dout, delta, batch,
+                                                                    seq, n_head);
   B200FT_LAUNCH_CHECK();
   // persistent: one CTA per SM walks the work items (heaviest first, round-robin)
   const int items0 = p.n_tiles * batch * n_kv_head, items1 = p.n_tiles * batch * n_head;

@@ -1,0 +1,407 @@
+// Causal flash-attention BACKWARD on tcgen05 for d_head = 128 (Llama-3-8B: BASELINE.json configs[3], [4]).
+//
+// At this head size a [128 x 128] bf16 tile is 32 KB and an fp32 accumulator tile 128 TMEM columns, so the d_head-64
+// design (attention_bwd.cu: P and dS staged in shared memory, dQ partials beside S, dP, dK, dV in TMEM) does not
+// fit.  Here P and dS never leave tensor memory: the softmax warps write them as bf16 over the S / dP columns they
+// were computed from and the gradient UMMAs take them as the A operand straight from TMEM.  That fixes the
+// orientation of every product — the A operand's rows are TMEM lanes — and gives two kernels of ONE template:
+//
+//   MODE 0  dK | dV   work item (kv tile j, batch, kv head): K_j, V_j resident; streams (Q_i, dO_i), i >= j, over the
+//           q heads of the group.  S^T = K_j Q_i^T and dP^T = V_j dO_i^T (lanes = keys, columns = queries);
+//           dV_j += P^T dO_i, dK_j += dS^T Q_i.  lse / D are per COLUMN: staged per pair in shared memory.
+//   MODE 1  dQ        work item (q tile i, batch, head): Q_i, dO_i resident; streams (K_j, V_j), j <= i.
+//           S = Q_i K_j^T, dP = dO_i V_j^T (lanes = queries); dQ_i += dS K_j.  lse / D are per thread.
+//
+// In both: product A operand = resident tile (K-major), B = streamed tile (K-major); gradient A = bf16 P / dS in
+// TMEM, B = streamed tile read MN-major ([128 rows = reduction index] x [d_head], two 64-column boxes).  No atomics,
+// no fp32 scratch: results are bit-reproducible.  TMEM: S 0..127 | dP 128..255 | acc0 256..383 | acc1 384..511; a
+// thread of slice `part` owns columns 32*part..+31 of S / dP and writes its 32 bf16 results into the first 16 of
+// them, so nobody overwrites scores another thread still has to read; the k-th gradient UMMA (16 reduction
+// indices) reads its A operand at column 32*(k/2) + 8*(k%2).
+//
+// 640 threads: warp 0 TMA producer, warp 1 UMMA issue, warp 2 TMEM allocation, warps 4-19 softmax / dS (four per
+// TMEM lane quarter, one 32-column slice each).  Shared memory: resident pair 64 KB + two stream stages of 64 KB.
+#include "attn_common.cuh"
+
+namespace {
+using namespace b200ft_attn;
+
+constexpr int kDH = 128;
+constexpr int kB = 128;                       // tile edge in queries and in keys
+constexpr int kThreads = 640;
+constexpr int kBox = kB * 64 * 2;             // 16 KB: one TMA box (128 rows x 64 columns, 128B swizzle)
+constexpr int kTile = 2 * kBox;               // 32 KB: one Q / dO / K / V tile
+constexpr int kRing = 2;
+constexpr int kOffF = 0;                      // resident pair
+constexpr int kOffS = 2 * kTile;              // ring stages of (tile0, tile1)
+constexpr int kOffStat = kOffS + kRing * 2 * kTile;   // MODE 0: [2 buffers][lse | D][128] fp32
+constexpr int kOffBar = kOffStat + 2 * 2 * kB * 4;
+constexpr int kSmemBytes = kOffBar + 256;     // 194.25 KB
+constexpr uint32_t kColS = 0, kColDP = 128, kColAcc0 = 256, kColAcc1 = 384;
+
+struct Params {
+  int batch, seq, n_head, n_kv_head;
+  int q_off, k_off, v_off;
+  int n_tiles;
+  float scale, scale_log2;
+  const float* lse2;
+  const float* delta;
+  __nv_bfloat16* dqkv; int64_t ld_d;
+};
+
+// Work item of a CTA.  MODE 0: (kv tile ascending, batch, kv head); MODE 1: (q tile descending, batch, head):
+// heaviest first.  Every warp role walks the same item sequence w = blockIdx.x, += gridDim.x.
+struct Item {
+  int fixed_tile, b, hx, hk, per_head, n_iter;
+};
+template <int MODE>
+__device__ __forceinline__ Item decode_item(const Params& p, int w, int G) {
+  Item it;
+  const int heads = MODE == 0 ? p.n_kv_head : p.n_head;
+  const int per_tile = p.batch * heads;
+  const int tile_ord = w / per_tile, rest = w % per_tile;
+  it.fixed_tile = MODE == 0 ? tile_ord : p.n_tiles - 1 - tile_ord;
+  it.b = rest / heads;
+  it.hx = rest % heads;                       // kv head (MODE 0) or q head (MODE 1)
+  it.hk = MODE == 0 ? it.hx : it.hx / G;
+  it.per_head = MODE == 0 ? p.n_tiles - it.fixed_tile : it.fixed_tile + 1;   // streamed tiles per head
+  it.n_iter = MODE == 0 ? G * it.per_head : it.per_head;
+  return it;
+}
+
+static __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
+// Persistent: one CTA per SM walks work items.  Barrier parities run on two counters shared by all roles:
+// `g` = tile pairs processed so far by this CTA (stream ring stage g % 2, statistics buffer g & 1, hand-offs),
+// `n` = items processed so far (resident tiles, accumulators).
+// Tensor-core order per pair: S(g), dP(g) | <softmax warps: P, dS into TMEM> | gradients(g), S(g+1), dP(g+1) | ...
+// S(g+1) overwrites the columns P(g) lives in; UMMAs execute in issue order, so it lands after the gradient UMMAs
+// have read P(g) and dS(g).
+template <int MODE>
+__global__ void __launch_bounds__(kThreads, 1)
+attn_bwd_d128_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constant__ CUtensorMap tm_do,
+                     const Params p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw = smem_u32(smem_raw);
+  if (raw & 1023u) __trap();  // dynamic shared memory starts 1024-aligned (no static smem in this kernel)
+  const uint32_t sF0 = raw + kOffF, sF1 = sF0 + kTile;
+  auto sS0 = [&](uint32_t st) { return raw + kOffS + st * 2u * kTile; };
+  auto sS1 = [&](uint32_t st) { return raw + kOffS + st * 2u * kTile + kTile; };
+  float* stat = reinterpret_cast<float*>(smem_raw + kOffStat);      // [buffer][lse | D][128]
+  const uint32_t bars = raw + kOffBar;
+  const uint32_t f_full = bars, f_empty = bars + 8u;
+  auto st_full = [&](uint32_t s) { return bars + 8u * (2 + s); };
+  auto st_empty = [&](uint32_t s) { return bars + 8u * (4 + s); };
+  const uint32_t s_full = bars + 8u * 6, dp_full = bars + 8u * 7, pds_full = bars + 8u * 8;
+  const uint32_t acc_full = bars + 8u * 9, acc_free = bars + 8u * 10;
+  const uint32_t tmem_slot = bars + 8u * 11;
+  volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - raw));
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int G = p.n_head / p.n_kv_head;
+  const int num_items = p.n_tiles * p.batch * (MODE == 0 ? p.n_kv_head : p.n_head);
+
+  if (warp == 1 && lane == 0) {
+    mbar_init(f_full, 1); mbar_init(f_empty, 1);
+    for (uint32_t s = 0; s < kRing; ++s) { mbar_init(st_full(s), 1); mbar_init(st_empty(s), 1); }
+    mbar_init(s_full, 1); mbar_init(dp_full, 1); mbar_init(pds_full, 16);
+    mbar_init(acc_full, 1); mbar_init(acc_free, 16);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 2) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(512) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot_ptr;
+
+  // a [128 x 128] tile = two boxes of 64 columns
+  auto load_tile = [&](uint32_t dst, const CUtensorMap* map, int col, int row, int b, uint32_t bar) {
+    tma_load_3d(dst, map, col, row, b, bar);
+    tma_load_3d(dst + kBox, map, col + 64, row, b, bar);
+  };
+
+  if (warp == 0) {
+    // ================================ TMA producer ================================
+    const bool issuer = elect_one();
+    uint32_t g = 0, n = 0;
+    for (int w = blockIdx.x; w < num_items; w += gridDim.x, ++n) {
+      const Item it = decode_item<MODE>(p, w, G);
+      if (n > 0) mbar_wait(f_empty, (n - 1) & 1u);   // the previous item's last dP UMMAs have read the resident pair
+      if (issuer) {
+        mbar_expect_tx(f_full, 2 * kTile);
+        if (MODE == 0) {
+          load_tile(sF0, &tm_qkv, p.k_off + it.hk * kDH, it.fixed_tile * kB, it.b, f_full);
+          load_tile(sF1, &tm_qkv, p.v_off + it.hk * kDH, it.fixed_tile * kB, it.b, f_full);
+        } else {
+          load_tile(sF0, &tm_qkv, p.q_off + it.hx * kDH, it.fixed_tile * kB, it.b, f_full);
+          load_tile(sF1, &tm_do, it.hx * kDH, it.fixed_tile * kB, it.b, f_full);
+        }
+      }
+      __syncwarp();
+      for (int t = 0; t < it.n_iter; ++t, ++g) {
+        const uint32_t st = g % kRing;
+        mbar_wait(st_empty(st), ((g / kRing) & 1u) ^ 1u);
+        if (issuer) {
+          mbar_expect_tx(st_full(st), 2 * kTile);
+          if (MODE == 0) {
+            const int hq = it.hk * G + t / it.per_head, qt = it.fixed_tile + t % it.per_head;
+            load_tile(sS0(st), &tm_qkv, p.q_off + hq * kDH, qt * kB, it.b, st_full(st));
+            load_tile(sS1(st), &tm_do, hq * kDH, qt * kB, it.b, st_full(st));
+          } else {
+            load_tile(sS0(st), &tm_qkv, p.k_off + it.hk * kDH, t * kB, it.b, st_full(st));
+            load_tile(sS1(st), &tm_qkv, p.v_off + it.hk * kDH, t * kB, it.b, st_full(st));
+          }
+        }
+        __syncwarp();
+      }
+    }
+  } else if (warp == 1) {
+    // ================================ UMMA issuer ================================
+    const bool issuer = elect_one();
+    const uint32_t id_kk = idesc(kB, 0, 0);    // S, dP: 128 x 128 x 128, both operands K-major (d_head contiguous)
+    const uint32_t id_g = idesc(kDH, 0, 1);    // gradients: 128 x 128 (d_head) x 128, A from TMEM, B MN-major
+    // K-major operand, k-th step of 16 d_head elements: box k/4, 32 bytes per step inside the 128-byte swizzle row
+    auto kdesc = [&](uint32_t tile, int k) { return sdesc(tile + (uint32_t)(k >> 2) * kBox + 32u * (uint32_t)(k & 3), 16, 1024); };
+    // MN-major B operand, k-th step of 16 rows (reduction index): 2 KB per step, the second 64 columns one box on
+    auto mdesc = [&](uint32_t tile, int k) { return sdesc(tile + 2048u * (uint32_t)k, kBox, 1024); };
+    auto issue_products = [&](uint32_t gg, bool last_of_item) {
+      const uint32_t st = gg % kRing;
+      mbar_wait(st_full(st), (gg / kRing) & 1u);
+      tc_fence_after();
+      if (issuer) {
+#pragma unroll
+        for (int k = 0; k < kDH / 16; ++k) umma(tmem + kColS, kdesc(sF0, k), kdesc(sS0(st), k), id_kk, k > 0);
+        umma_commit(s_full);
+#pragma unroll
+        for (int k = 0; k < kDH / 16; ++k) umma(tmem + kColDP, kdesc(sF1, k), kdesc(sS1(st), k), id_kk, k > 0);
+        umma_commit(dp_full);
+        if (last_of_item) umma_commit(f_empty);   // nothing of this item reads the resident pair any more
+      }
+      __syncwarp();
+    };
+    auto issue_grads = [&](uint32_t gg, bool first) {
+      const uint32_t st = gg % kRing;
+      if (issuer) {
+        if (MODE == 0) {
+#pragma unroll
+          for (int k = 0; k < kB / 16; ++k)   // dV += P^T dO: 16 queries per step
+            umma_ts(tmem + kColAcc0, tmem + kColS + 32u * (uint32_t)(k >> 1) + 8u * (uint32_t)(k & 1), mdesc(sS1(st), k),
+                    id_g, !(first && k == 0));
+#pragma unroll
+          for (int k = 0; k < kB / 16; ++k)   // dK += dS^T Q
+            umma_ts(tmem + kColAcc1, tmem + kColDP + 32u * (uint32_t)(k >> 1) + 8u * (uint32_t)(k & 1), mdesc(sS0(st), k),
+                    id_g, !(first && k == 0));
+        } else {
+#pragma unroll
+          for (int k = 0; k < kB / 16; ++k)   // dQ += dS K: 16 keys per step
+            umma_ts(tmem + kColAcc0, tmem + kColDP + 32u * (uint32_t)(k >> 1) + 8u * (uint32_t)(k & 1), mdesc(sS0(st), k),
+                    id_g, !(first && k == 0));
+        }
+        umma_commit(st_empty(st));   // the streamed pair's slot may be refilled
+      }
+      __syncwarp();
+    };
+    uint32_t g = 0, n = 0;
+    for (int w = blockIdx.x; w < num_items; w += gridDim.x, ++n) {
+      const Item it = decode_item<MODE>(p, w, G);
+      const int N = it.n_iter;
+      mbar_wait(f_full, n & 1u);
+      issue_products(g, N == 1);
+      for (int t = 0; t < N; ++t, ++g) {
+        mbar_wait(pds_full, g & 1u);        // softmax warps are done with pair g: P, dS are in TMEM
+        tc_fence_after();
+        if (t == 0 && n > 0) { mbar_wait(acc_free, (n - 1) & 1u); tc_fence_after(); }  // previous accumulators read out
+        issue_grads(g, t == 0);
+        if (t + 1 < N) issue_products(g + 1, t + 2 == N);
+      }
+      if (issuer) umma_commit(acc_full);
+      __syncwarp();
+    }
+  } else if (warp >= 4) {
+    // ================================ softmax / dS ================================
+    // Four warps per TMEM lane quarter; a thread owns one lane L (a key in MODE 0, a query in MODE 1) and the 32
+    // columns 32*part .. +31 (queries in MODE 0, keys in MODE 1).
+    const int quarter = warp & 3;
+    const int part = (warp - 4) >> 2;
+    const int L = quarter * 32 + lane;
+    const int sm_tid = (warp - 4) * 32 + lane;             // 0..511 among the softmax warps
+    const uint32_t t_lane = tmem + ((uint32_t)(quarter * 32) << 16);
+    const uint32_t t_s = t_lane + kColS + 32u * (uint32_t)part;
+    const uint32_t t_dp = t_lane + kColDP + 32u * (uint32_t)part;
+    const f32x2_t sc2 = pk2(p.scale_log2, p.scale_log2);
+    uint32_t g = 0, n = 0;
+    for (int w = blockIdx.x; w < num_items; w += gridDim.x, ++n) {
+      const Item it = decode_item<MODE>(p, w, G);
+      // log-sum-exp and D of a query row; rows past the end of the sequence get lse = +inf: P = dS = 0
+      auto row_stats = [&](int hq, int qt_, int r, float& lse_o, float& dl_o) {
+        const int qr = qt_ * kB + r;
+        lse_o = INFINITY; dl_o = 0.f;
+        if (qr < p.seq) {
+          const int64_t idx = ((int64_t)it.b * p.n_head + hq) * p.seq + qr;
+          lse_o = __ldg(p.lse2 + idx); dl_o = __ldg(p.delta + idx);
+        }
+      };
+      // MODE 0: the statistics belong to the COLUMNS and change with every pair.  Threads 0..127 of the softmax
+      // warps fetch the next pair's values one pair ahead (global-memory latency off the critical path) and publish
+      // them in shared memory, double-buffered, at the start of the pair.
+      float lse = INFINITY, dl = 0.f, lse_next = INFINITY, dl_next = 0.f;
+      if (MODE == 1) row_stats(it.hx, it.fixed_tile, L, lse, dl);
+      else if (sm_tid < kB) row_stats(it.hk * G, it.fixed_tile, sm_tid, lse_next, dl_next);
+      for (int t = 0; t < it.n_iter; ++t, ++g) {
+        int qt, kt;
+        if (MODE == 0) { qt = it.fixed_tile + t % it.per_head; kt = it.fixed_tile; }
+        else           { qt = it.fixed_tile; kt = t; }
+        const bool diag = qt == kt;
+        const float* st_lse = stat + (g & 1u) * 2 * kB;
+        const float* st_dl = st_lse + kB;
+        if (MODE == 0) {
+          if (sm_tid < kB) {
+            stat[(g & 1u) * 2 * kB + sm_tid] = lse_next;
+            stat[(g & 1u) * 2 * kB + kB + sm_tid] = dl_next;
+            if (t + 1 < it.n_iter)
+              row_stats(it.hk * G + (t + 1) / it.per_head, it.fixed_tile + (t + 1) % it.per_head, sm_tid, lse_next, dl_next);
+          }
+          named_bar_sync(1, 512);   // the 16 softmax warps: this pair's statistics are visible
+        }
+        // ---- phase A: P = exp2(S*c - lse) for this thread's 32 columns (kept in registers for phase B) ----
+        f32x2_t P2[16];
+        mbar_wait(s_full, g & 1u);
+        tc_fence_after();
+        {
+          uint32_t rs[32];
+          tmem_ld32(t_s, rs);
+          tmem_wait_ld();
+#pragma unroll
+          for (int i = 0; i < 32; i += 2) {
+            const int c = 32 * part + i;
+            f32x2_t nl2;
+            if (MODE == 0) nl2 = pk2(-st_lse[c], -st_lse[c + 1]); else nl2 = pk2(-lse, -lse);
+            float e0, e1;
+            upk2(fma2(pk2(__uint_as_float(rs[i]), __uint_as_float(rs[i + 1])), sc2, nl2), e0, e1);
+            float p0 = ex2(e0), p1 = ex2(e1);   // lse = +inf (row past the sequence): exp2(-inf) = 0
+            if (diag) {                        // warp-uniform; causal: key index > query index contributes nothing
+              const bool m0 = MODE == 0 ? (L > c) : (c > L);
+              const bool m1 = MODE == 0 ? (L > c + 1) : (c + 1 > L);
+              if (m0) p0 = 0.f;
+              if (m1) p1 = 0.f;
+            }
+            P2[i >> 1] = pk2(p0, p1);
+          }
+        }
+        if (MODE == 0) {   // P^T as bf16 over this thread's own first 16 score columns: A operand of dV += P^T dO
+          uint32_t wp[16];
+#pragma unroll
+          for (int i = 0; i < 16; ++i) wp[i] = f32x2_to_bf16x2(P2[i]);
+          tmem_st16(t_s, wp);
+        }
+        // ---- phase B: dS' = P * (dP - D) (the softmax scale multiplies the dK / dQ accumulators once, at the end) ----
+        mbar_wait(dp_full, g & 1u);
+        tc_fence_after();
+        {
+          uint32_t rd[32];
+          tmem_ld32(t_dp, rd);
+          tmem_wait_ld();
+          uint32_t wd[16];
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            const int c = 32 * part + 2 * i;
+            f32x2_t dl2;
+            if (MODE == 0) dl2 = pk2(st_dl[c], st_dl[c + 1]); else dl2 = pk2(dl, dl);
+            wd[i] = f32x2_to_bf16x2(mul2(P2[i], sub2(pk2(__uint_as_float(rd[2 * i]), __uint_as_float(rd[2 * i + 1])), dl2)));
+          }
+          tmem_st16(t_dp, wd);
+        }
+        tmem_wait_st();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(pds_full);
+      }
+      // ---- accumulators -> (x softmax scale for dK, dQ) -> bf16 -> the gradient buffer ----
+      mbar_wait(acc_full, n & 1u);
+      tc_fence_after();
+      const int orow = it.fixed_tile * kB + L;   // key row (MODE 0) or query row (MODE 1)
+      if (MODE == 0) {
+        // slices 0, 1 write the two 64-column halves of dV (accumulator 0), slices 2, 3 those of dK (accumulator 1)
+        const uint32_t t_acc = t_lane + ((part >> 1) == 0 ? kColAcc0 : kColAcc1) + 64u * (uint32_t)(part & 1);
+        const int col = ((part >> 1) == 0 ? p.v_off : p.k_off) + it.hk * kDH + 64 * (part & 1);
+        const float oscale = (part >> 1) == 0 ? 1.f : p.scale;
+        uint32_t r[64];
+        tmem_ld32(t_acc, r);
+        tmem_ld32(t_acc + 32, r + 32);
+        tmem_wait_ld();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(acc_free);    // the next item's gradient UMMAs may overwrite the accumulators
+        if (orow < p.seq) {
+          __nv_bfloat16* dst = p.dqkv + ((int64_t)it.b * p.seq + orow) * p.ld_d + col;
+#pragma unroll
+          for (int v = 0; v < 8; ++v) {
+            float fv[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) fv[i] = __uint_as_float(r[8 * v + i]) * oscale;
+            *reinterpret_cast<uint4*>(dst + 8 * v) = pack8(fv);
+          }
+        }
+      } else {
+        // dQ: the four slices write 32 columns each
+        uint32_t r[32];
+        tmem_ld32(t_lane + kColAcc0 + 32u * (uint32_t)part, r);
+        tmem_wait_ld();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(acc_free);
+        if (orow < p.seq) {
+          __nv_bfloat16* dst = p.dqkv + ((int64_t)it.b * p.seq + orow) * p.ld_d + p.q_off + it.hx * kDH + 32 * part;
+#pragma unroll
+          for (int v = 0; v < 4; ++v) {
+            float fv[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) fv[i] = __uint_as_float(r[8 * v + i]) * p.scale;
+            *reinterpret_cast<uint4*>(dst + 8 * v) = pack8(fv);
+          }
+        }
+      }
+    }
+    tc_fence_before();
+  }
+
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512) : "memory");
+  }
+}
+
+}  // namespace
+
+int b200ft_attn::launch_bwd_d128(const CUtensorMap& tm_qkv, const CUtensorMap& tm_do, const Bwd128Args& a,
+                                 cudaStream_t st) {
+  Params p;
+  p.batch = a.batch; p.seq = a.seq; p.n_head = a.n_head; p.n_kv_head = a.n_kv_head;
+  p.q_off = a.q_off; p.k_off = a.k_off; p.v_off = a.v_off;
+  p.n_tiles = (a.seq + kB - 1) / kB;
+  p.scale = a.scale; p.scale_log2 = a.scale * 1.4426950408889634f;
+  p.lse2 = a.lse2; p.delta = a.delta; p.dqkv = a.dqkv; p.ld_d = a.ld_d;
+  static thread_local int attr_dev = -1;
+  int dev = -1;
+  B200FT_CUDA(cudaGetDevice(&dev));
+  if (dev != attr_dev) {
+    B200FT_CUDA(cudaFuncSetAttribute(attn_bwd_d128_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+    B200FT_CUDA(cudaFuncSetAttribute(attn_bwd_d128_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+    attr_dev = dev;
+  }
+  // persistent: one CTA per SM walks the work items (heaviest first, round-robin)
+  const int items0 = p.n_tiles * a.batch * a.n_kv_head, items1 = p.n_tiles * a.batch * a.n_head;
+  attn_bwd_d128_kernel<0><<<(unsigned)(items0 < B200FT_NUM_SMS ? items0 : B200FT_NUM_SMS), kThreads, kSmemBytes, st>>>(
+      tm_qkv, tm_do, p);
+  B200FT_LAUNCH_CHECK();
+  attn_bwd_d128_kernel<1><<<(unsigned)(items1 < B200FT_NUM_SMS ? items1 : B200FT_NUM_SMS), kThreads, kSmemBytes, st>>>(
+      tm_qkv, tm_do, p);
+  B200FT_LAUNCH_CHECK();
+  return 0;
+}

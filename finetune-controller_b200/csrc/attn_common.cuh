@@ -147,5 +147,15 @@ static inline int make_map(EncodeTiledFn enc, CUtensorMap* tm, const void* base,
   return 0;
 }
 
+// d_head 128 backward (attention_bwd_d128.cu): dK|dV kernel + dQ kernel; `delta` has been computed by the caller
+struct Bwd128Args {
+  int batch, seq, n_head, n_kv_head;
+  int q_off, k_off, v_off;
+  float scale;
+  const float* lse2;     // [batch*n_head, seq], log2 domain incl. the softmax scale
+  const float* delta;    // [batch*n_head, seq]
+  __nv_bfloat16* dqkv; int64_t ld_d;
+};
+int launch_bwd_d128(const CUtensorMap& tm_qkv, const CUtensorMap& tm_do, const Bwd128Args& a, cudaStream_t st);
 
 }  // namespace b200ft_attn

@@ -23,18 +23,18 @@ def ref_attention(qkv, B, T, H, KV, dh, q_off, k_off, v_off):
     return o.transpose(1, 2).reshape(B * T, H * dh), lse
 
 
+@pytest.mark.parametrize("dh", [64, 128])
 @pytest.mark.parametrize("B,T,H,KV", [(1, 128, 1, 1), (2, 256, 3, 3), (1, 1024, 2, 2), (2, 384, 8, 2), (3, 200, 4, 1),
-                                      (1, 40, 2, 2)])
-def test_attn_fwd_matches_oracle(B, T, H, KV):
+                                      (1, 40, 2, 2), (3, 2048, 8, 2)])
+def test_attn_fwd_matches_oracle(B, T, H, KV, dh):
     from b200ft import ops
     from oracle import gpt2_lora_ref as ref
-    dh = 64
     g = torch.Generator().manual_seed(T + H)
     ld = (H + 2 * KV) * dh
     qkv = (torch.randn(B * T, ld, generator=g) * 1.5).to(torch.bfloat16)
     q_off, k_off, v_off = 0, H * dh, (H + KV) * dh
     o_ref, lse_ref = ref_attention(qkv, B, T, H, KV, dh, q_off, k_off, v_off)
-    if H == KV:  # the GPT-2 oracle's own function on the same buffer
+    if H == KV and dh == 64:  # the GPT-2 oracle's own function on the same buffer
         o2 = ref.causal_attention(qkv.float().view(B, T, ld), H).reshape(B * T, H * dh)
         torch.testing.assert_close(o2, o_ref, rtol=1e-5, atol=1e-5)
     qd = qkv.to(DEV)
@@ -53,20 +53,20 @@ def test_attn_fwd_matches_oracle(B, T, H, KV):
 def test_attn_fwd_rejects_other_head_sizes():
     from b200ft import ops
     from b200ft._lib import B200FTError
-    x = torch.zeros(128, 3 * 128, dtype=torch.bfloat16, device=DEV)
+    x = torch.zeros(128, 3 * 96, dtype=torch.bfloat16, device=DEV)
     with pytest.raises(B200FTError):
-        ops.attn_fwd(x, torch.zeros(128, 128, dtype=torch.bfloat16, device=DEV), torch.zeros(1, 128, device=DEV),
-                     batch=1, seq=128, n_head=1, n_kv_head=1, d_head=128, q_off=0, k_off=128, v_off=256, scale=0.1)
+        ops.attn_fwd(x, torch.zeros(128, 96, dtype=torch.bfloat16, device=DEV), torch.zeros(1, 128, device=DEV),
+                     batch=1, seq=128, n_head=1, n_kv_head=1, d_head=96, q_off=0, k_off=96, v_off=192, scale=0.1)
 
 
-@pytest.mark.parametrize("deterministic", [False, True])
+@pytest.mark.parametrize("dh,deterministic", [(64, False), (64, True), (128, False)])
 @pytest.mark.parametrize("B,T,H,KV", [(1, 128, 1, 1), (2, 256, 3, 3), (1, 1024, 2, 2), (2, 384, 8, 2), (3, 200, 4, 1),
                                       (1, 40, 2, 2), (40, 512, 4, 4)])
-def test_attn_bwd_matches_oracle_autograd(B, T, H, KV, deterministic):
+def test_attn_bwd_matches_oracle_autograd(B, T, H, KV, dh, deterministic):
     """dq | dk | dv of the own backward (fed by the own forward's out and log-sum-exp) against autograd
-    through the explicit fp32 attention; GQA sums the group's heads into dk / dv; ragged lengths."""
+    through the explicit fp32 attention; GQA sums the group's heads into dk / dv; ragged lengths.  d_head 128
+    has one form (two kernels, no atomics); d_head 64 the fused default and the two-kernel deterministic one."""
     from b200ft import ops
-    dh = 64
     g = torch.Generator().manual_seed(7 * T + H)
     ld = (H + 2 * KV) * dh
     qkv = (torch.randn(B * T, ld, generator=g) * 1.2).to(torch.bfloat16)
@@ -96,6 +96,38 @@ def test_attn_bwd_matches_oracle_autograd(B, T, H, KV, deterministic):
         torch.testing.assert_close(a, r, rtol=5e-2, atol=3e-2 * float(r.abs().max()))
 
 
+def test_attn_bwd_d128_is_bit_reproducible_and_handles_long_gqa():
+    """Llama-3-8B's head geometry (4 q heads per kv head, d_head 128) at T = 2048: two runs give identical bits, and
+    the result matches autograd of the explicit attention."""
+    from b200ft import ops
+    B, T, H, KV, dh = 1, 2048, 8, 2, 128
+    g = torch.Generator().manual_seed(11)
+    ld = (H + 2 * KV) * dh
+    qkv = (torch.randn(B * T, ld, generator=g) * 1.2).to(torch.bfloat16)
+    dout = torch.randn(B * T, H * dh, generator=g).to(torch.bfloat16)
+    q_off, k_off, v_off = 0, H * dh, (H + KV) * dh
+    x = qkv.float().clone().requires_grad_(True)
+    o_ref, _ = ref_attention(x, B, T, H, KV, dh, q_off, k_off, v_off)
+    o_ref.backward(dout.float())
+    qd, dod = qkv.to(DEV), dout.to(DEV)
+    kw = dict(batch=B, seq=T, n_head=H, n_kv_head=KV, d_head=dh, q_off=q_off, k_off=k_off, v_off=v_off,
+              scale=1.0 / math.sqrt(dh))
+    out = torch.empty(B * T, H * dh, dtype=torch.bfloat16, device=DEV)
+    lse2, ws = torch.empty(B * H, T, device=DEV), ops.attn_bwd_workspace(B, T, H, dh, DEV)
+    ops.attn_fwd(qd, out, lse2, **kw)
+    res = []
+    for _ in range(2):
+        dqkv = torch.full((B * T, ld), float("nan"), dtype=torch.bfloat16, device=DEV)
+        ops.attn_bwd(qd, out, dod, lse2, ws, dqkv, **kw)
+        res.append(dqkv.clone())
+    assert torch.equal(res[0], res[1])
+    got, ref_g = res[0].cpu().float(), x.grad
+    for name, lo, hi in (("dq", q_off, k_off), ("dk", k_off, v_off), ("dv", v_off, ld)):
+        a, r = got[:, lo:hi], ref_g[:, lo:hi]
+        cos = float((a.double().flatten() @ r.double().flatten()) / (a.double().norm() * r.double().norm()))
+        assert cos >= 0.999 and float((a - r).norm() / r.norm()) <= 3e-2, name
+
+
 def test_attn_bwd_deterministic_path_is_bit_reproducible():
     from b200ft import ops
     B, T, H, KV, dh = 2, 384, 4, 2, 64
@@ -121,11 +153,12 @@ def test_attn_bwd_deterministic_path_is_bit_reproducible():
     torch.testing.assert_close(fused[:, : H * dh].float(), res[0][:, : H * dh].float(), rtol=2 ** -7, atol=1e-3)
 
 
-def test_attn_fwd_rescales_output_accumulator_when_the_row_max_grows():
+@pytest.mark.parametrize("dh", [64, 128])
+def test_attn_fwd_rescales_output_accumulator_when_the_row_max_grows(dh):
     """Keys whose magnitude rises tile after tile force the lazy-rescaling path on every kv tile: the reference max
     moves by far more than 2^8, so the output tile accumulated in TMEM has to be rescaled in place."""
     from b200ft import ops
-    B, T, H, KV, dh = 1, 640, 2, 2, 64
+    B, T, H, KV = 1, 640, 2, 2
     g = torch.Generator().manual_seed(3)
     ld = (H + 2 * KV) * dh
     x = torch.randn(B * T, ld, generator=g)

@@ -125,6 +125,53 @@ def test_softmax_xent_all_ignored_and_scale(ops):
     torch.testing.assert_close(zd.cpu().float(), 0.25 * dz_ref, rtol=2 ** -7, atol=1e-7)
 
 
+def test_softmax_xent_out_of_range_targets_are_ignored_and_counted(ops):
+    """A target >= vocab or < 0 (other than ignore_index) gets no loss and a zero gradient row, is left out of the
+    mean's denominator, and is counted for the host — loss and gradient stay consistent (torch raises here)."""
+    rows, vocab = 6, 200
+    g = torch.Generator().manual_seed(5)
+    z = bf16_round(torch.randn(rows, vocab, generator=g) * 2)
+    targets = torch.randint(0, vocab, (rows,), generator=g)
+    bad = targets.clone()
+    bad[0], bad[4] = vocab, -7
+    as_ignored = targets.clone()
+    as_ignored[0] = as_ignored[4] = -100
+    loss_ref, dz_ref = ref.softmax_xent_ref(z, as_ignored)
+    zd = z.to(DEV, torch.bfloat16)
+    loss = torch.zeros(1, device=DEV)
+    ws = ops.softmax_xent_workspace(rows, DEV)
+    ops.softmax_xent_fwd_bwd(zd, bad.to(DEV), loss, ws, vocab=vocab)
+    assert abs(float(loss.cpu()) - float(loss_ref)) <= 1e-5 * max(1.0, abs(float(loss_ref)))
+    torch.testing.assert_close(zd.cpu().float(), dz_ref, rtol=2 ** -7, atol=1e-7)
+    assert torch.all(zd[0] == 0) and torch.all(zd[4] == 0)
+    assert ops.softmax_xent_bad_targets(ws) == 2
+    zd = z.to(DEV, torch.bfloat16)
+    ops.softmax_xent_fwd_bwd(zd, targets.to(DEV), loss, ws, vocab=vocab)
+    assert ops.softmax_xent_bad_targets(ws) == 0
+
+
+@pytest.mark.parametrize("rows,vocab,ld", [(700, 1000, 1024), (9, 40000, 40000), (5, 262144, 262144), (3, 300000, 300000)])
+def test_softmax_xent_many_rows_and_cluster_sizes(ops, rows, vocab, ld):
+    """More rows than resident clusters (every CTA loops, the 3-stage ring wraps), ignored rows in between, and row
+    lengths that select cluster sizes 1, 2, 8 and the one-CTA-per-row fallback (> 262144 logits)."""
+    g = torch.Generator().manual_seed(rows + vocab)
+    z = bf16_round(torch.randn(rows, vocab, generator=g) * 3.0)
+    targets = torch.randint(0, vocab, (rows,), generator=g)
+    targets[::7] = -100
+    targets[-1] = vocab - 1
+    loss_ref, dz_ref = ref.softmax_xent_ref(z, targets)
+    zz = torch.full((rows, ld), 3.0)
+    zz[:, :vocab] = z
+    zd = zz.to(DEV, torch.bfloat16)
+    loss = torch.zeros(1, device=DEV)
+    ws = ops.softmax_xent_workspace(rows, DEV)
+    for _ in range(2):      # the scratch words are reusable
+        zd.copy_(zz)
+        ops.softmax_xent_fwd_bwd(zd, targets.to(DEV), loss, ws, vocab=vocab)
+        assert abs(float(loss.cpu()) - float(loss_ref)) <= 1e-5 * max(1.0, abs(float(loss_ref)))
+        torch.testing.assert_close(zd.cpu().float()[:, :vocab], dz_ref, rtol=2 ** -7, atol=1e-7)
+
+
 def test_shift_targets(ops):
     labels = torch.arange(24).view(3, 8)
     out = torch.empty(3, 8, dtype=torch.int64, device=DEV)

@@ -143,4 +143,4 @@ def test_llama_real_width_with_own_attention_kernels():
 
 def test_own_attention_rejects_other_head_sizes():
     with pytest.raises(ValueError):
-        _parity(ref.LLAMA_TINY, batch=2, seq=32, r=16, steps=1, attention="own")   # d_head 16
+        _parity(ref.LLAMA_TINY, batch=2, seq=32, r=16, steps=1, attention="own")   # d_head 16: neither 64 nor 128

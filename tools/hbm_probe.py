@@ -17,12 +17,15 @@ def run(fn, bytes_):
     us = e0.elapsed_time(e1) * 1e3 / iters
     print(f"{what}: {us:.1f} us/launch, {bytes_/us/1e3:.0f} GB/s algorithmic")
 if what == "xent":
-    M, V, ld = 32768, 50257, 50304
-    z = torch.randn(M, ld, device=dev).to(torch.bfloat16)
+    # python tools/hbm_probe.py xent [iters] [rows] [vocab]: the kernel alone, in place on a buffer far larger than L2
+    # (after the first launch the buffer holds gradients: still a valid input, same traffic and instruction count)
+    M = int(sys.argv[3]) if len(sys.argv) > 3 else 32768
+    V = int(sys.argv[4]) if len(sys.argv) > 4 else 50257
+    ld = (V + 127) // 128 * 128
+    z = (torch.randn(M, ld, device=dev) * 3).to(torch.bfloat16)
     t = torch.randint(0, V, (M,), device=dev); loss = torch.zeros(1, device=dev); ws = ops.softmax_xent_workspace(M, dev)
-    src = z.clone()
     def f():
-        z.copy_(src); ops.softmax_xent_fwd_bwd(z, t, loss, ws, vocab=V)
+        ops.softmax_xent_fwd_bwd(z, t, loss, ws, vocab=V)
     run(f, 2.0 * M * V * 2 + 12 * M)
 elif what == "adamw":
     n = 256 * 1024 * 1024
