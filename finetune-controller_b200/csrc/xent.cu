@@ -1,20 +1,13 @@
 // Fused softmax-cross-entropy forward + backward over bf16 logits, in place.
 //
-// Main kernel (softmax_xent_cluster_kernel): a row never leaves the chip between its read and its write.
-// A thread-block CLUSTER of 1, 2, 4 or 8 CTAs owns a row; each CTA's share (at most 32768 logits = 64 KB) is
-// brought into shared memory by one bulk-copy (TMA) per row, three rows deep, so HBM reads for the next two
-// rows are in flight while the current one is processed.  Each of the 512 threads takes its 64 logits into
-// registers ONCE: e = exp2(z*log2e - m_thread) against the thread's own maximum (one MUFU op per element; a
-// re-reading kernel needs two, and MUFU at 16/clk/SM is what bounded the previous version at 62 % busy),
-// (max, sum) pairs are merged across the warp, the CTA and — through distributed shared memory, one cluster
-// barrier per row — the cluster; the thread then scales its registers by 2^(m_thread - M) * grad_scale /
-// (n_valid * sum), subtracts the one-hot, writes bf16 back into the same shared-memory bytes, and one bulk
-// store per CTA sends them to HBM.  DRAM traffic is exactly one read + one write of the row whatever the
-// vocabulary (the previous kernel re-read the row from L2, which at V = 128256 with 8 CTAs x 148 SMs x 256 KB
-// in flight no longer held it: ~3 sweeps instead of 2).  Algorithmic bytes: 2*rows*ld*2 + 12*rows.
+// Two kernels, chosen by row length (launch_xent below; algorithmic bytes 2*rows*ld*2 + 12*rows either way):
 //
-// Fallback (softmax_xent_kernel, rows longer than 8 x 32768 logits, or B200FT_XENT_LEGACY=1): one CTA per row,
-// two sweeps with the second served by L2.
+//   softmax_xent_staged_kernel   rows of at most 32768 logits.  The row is brought into shared memory by one bulk copy
+//       (TMA), three rows deep, passes through registers ONCE (one MUFU exponential per logit) and leaves by one bulk
+//       store: DRAM traffic is exactly one read + one write.
+//   softmax_xent_kernel          longer rows.  One CTA per row, two sweeps: online (max, sum) from HBM, then the
+//       gradient with the row re-read from L2.  The number of CTAs per SM is capped so that the rows in flight fit
+//       the 126 MB L2 (uncapped, V = 128256 put 303 MB in flight and the second sweep went back to HBM).
 //
 // Targets outside [0, vocab) that are not ignore_index are treated exactly like ignored ones — no loss, zero
 // gradient, not counted in n_valid — and counted in scratch word [2] so the host can report them.
@@ -29,7 +22,6 @@
 
 namespace {
 
-constexpr int kThreads = 256;
 constexpr int kUnroll = 4;
 
 __device__ __forceinline__ float ex2_approx(float x) {
@@ -85,17 +77,7 @@ __device__ __forceinline__ MS ms_merge(MS a, MS b) {
   return r;
 }
 
-// the same merge on the MUFU approximation (inputs are maxima and sums of exp2: ~2^-22 relative is ample)
-__device__ __forceinline__ MS ms_merge_fast(MS a, MS b) {
-  const float M = fmaxf(a.m, b.m);
-  MS r;
-  r.m = M;
-  const float ea = (a.m == -INFINITY) ? 0.f : ex2_approx(a.m - M);
-  const float eb = (b.m == -INFINITY) ? 0.f : ex2_approx(b.m - M);
-  r.s = a.s * ea + b.s * eb;
-  return r;
-}
-
+template <int kThreads>
 __global__ void __launch_bounds__(kThreads)
 softmax_xent_kernel(__nv_bfloat16* __restrict__ logits, int64_t rows, int vocab, int64_t ld,
                     const int64_t* __restrict__ targets, int64_t ignore_index, float grad_scale,
@@ -240,14 +222,14 @@ softmax_xent_kernel(__nv_bfloat16* __restrict__ logits, int64_t rows, int vocab,
 }
 
 // ---------------------------------------------------------------------------------------
-// Cluster kernel: rows staged in shared memory by bulk copies, one pass through registers.
+// Staged kernel (rows of at most 32768 logits): the row stays on the chip between its read and its write.
 // ---------------------------------------------------------------------------------------
 constexpr int kCThreads = 1024;
 constexpr int kCU = 4;                           // 16-byte vectors (8 logits each) per thread
-constexpr int kCChunkVecs = kCThreads * kCU;     // 4096 vectors = 32768 logits = 64 KB per CTA and row
+constexpr int kCChunkVecs = kCThreads * kCU;     // 4096 vectors = 32768 logits = 64 KB per row
 constexpr int kCStages = 3;
 constexpr int kCStageBytes = kCChunkVecs * 16;
-constexpr int kCSmemBytes = kCStages * kCStageBytes;   // 192 KB dynamic; barriers and exchange slots are static
+constexpr int kCSmemBytes = kCStages * kCStageBytes;   // 192 KB dynamic; barriers are static
 constexpr long long kCWaitLimit = 4000000000ll;  // clock64 ticks (~2 s) before a barrier wait traps
 
 __device__ __forceinline__ uint32_t cx_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -262,51 +244,28 @@ __device__ __forceinline__ void cx_mbar_wait(uint32_t bar, uint32_t parity) {
     else if (clock64() - t0 > kCWaitLimit) __trap();   // never hang the GPU
   }
 }
-// wait for a phase completed by another CTA's st.async: acquire at cluster scope
-__device__ __forceinline__ void cx_mbar_wait_cluster(uint32_t bar, uint32_t parity) {
-  uint32_t done = 0;
-  long long t0 = 0;
-  while (true) {
-    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
-                 : "=r"(done) : "r"(bar), "r"(parity) : "memory");
-    if (done) break;
-    if (t0 == 0) t0 = clock64();
-    else if (clock64() - t0 > kCWaitLimit) __trap();
-  }
-}
-__device__ __forceinline__ uint32_t cx_cluster_rank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
-__device__ __forceinline__ uint32_t cx_cluster_size() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_nctarank;" : "=r"(r)); return r; }
-__device__ __forceinline__ void cx_cluster_sync() {
-  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
-}
-__device__ __forceinline__ float cx_ld_remote_f32(uint32_t local_addr, uint32_t rank) {
-  uint32_t ra;
-  float v;
-  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(ra) : "r"(local_addr), "r"(rank));
-  asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(ra) : "memory");
-  return v;
-}
 
+// Persistent: one CTA per SM walks rows r = blockIdx.x, += gridDim.x.  A row is brought into shared memory by ONE bulk
+// copy (TMA), three rows deep, so the HBM reads of the next two rows are in flight while the current one is processed.
+// Each of the 1024 threads takes its 32 logits into registers once: CTA maximum first (packed-bf16 HMNMX2, shuffles,
+// one barrier), then e = exp2(z*log2e - max) — ONE MUFU op per logit; a re-reading kernel needs two, and at 16/clk/SM
+// the special-function unit is what the two-sweep kernel runs into — then the sum, the scaling by grad_scale /
+// (n_valid * sum) in registers, bf16 back into the same shared-memory bytes and one bulk store to HBM.  DRAM traffic is
+// exactly one read and one write of the row, whatever L2 does.
 __global__ void __launch_bounds__(kCThreads, 1)
-softmax_xent_cluster_kernel(__nv_bfloat16* __restrict__ logits, int64_t rows, int vocab, int64_t ld,
-                            const int64_t* __restrict__ targets, int64_t ignore_index, float grad_scale,
-                            float* __restrict__ loss_out, unsigned int* __restrict__ ws, int chunk_vecs) {
+softmax_xent_staged_kernel(__nv_bfloat16* __restrict__ logits, int64_t rows, int vocab, int64_t ld,
+                           const int64_t* __restrict__ targets, int64_t ignore_index, float grad_scale,
+                           float* __restrict__ loss_out, unsigned int* __restrict__ ws) {
   extern __shared__ __align__(128) uint8_t cx_smem[];
   __shared__ __align__(8) unsigned long long full_bar[kCStages];
-  __shared__ __align__(16) float xch[2][8][4];   // [row parity][sending CTA]: (max, sum, target logit, -)
-  __shared__ __align__(8) unsigned long long xch_bar[2];
   __shared__ float red_m[kCThreads / 32], red_s[kCThreads / 32];
   __shared__ bool s_last;
   __shared__ float fr[kCThreads / 32];
 
   const int tid = threadIdx.x;
-  const uint32_t crank = cx_cluster_rank(), csize = cx_cluster_size();
-  const int64_t cid = blockIdx.x / csize, G = gridDim.x / csize;
+  const int64_t G = gridDim.x;
   const int nvec = (int)(ld >> 3);
-  const int v0 = (int)crank * chunk_vecs;                                   // first vector of this CTA's share
-  const int my_vecs = max(0, min(chunk_vecs, nvec - v0));
-  const uint32_t my_bytes = (uint32_t)my_vecs * 16u;
-  const int col_lo = v0 << 3, col_hi = (v0 + my_vecs) << 3;
+  const uint32_t row_bytes = (uint32_t)nvec * 16u;
   const uint32_t smem0 = cx_smem_u32(cx_smem);
   float* row_loss = reinterpret_cast<float*>(ws + 16);
   const unsigned int n_valid = ws[0];
@@ -315,75 +274,88 @@ softmax_xent_cluster_kernel(__nv_bfloat16* __restrict__ logits, int64_t rows, in
   if (tid == 0) {
     for (int s = 0; s < kCStages; ++s)
       asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(cx_smem_u32(&full_bar[s])) : "memory");
-    for (int s = 0; s < 2; ++s)
-      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(cx_smem_u32(&xch_bar[s])) : "memory");
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
-  if (csize > 1) cx_cluster_sync();   // once: nobody sends into a neighbour's exchange barrier before it exists
 
   auto is_valid = [&](int64_t t) { return t != ignore_index && t >= 0 && t < vocab; };
   // producer state (thread 0 only): the next row to look at, how many valid rows have been requested
-  int64_t load_row = cid;
+  // (the target of `load_row` is fetched one call ahead: its global-memory latency never sits in the row loop)
+  int64_t load_row = blockIdx.x;
+  int64_t load_tgt = (tid == 0 && load_row < rows) ? targets[load_row] : ignore_index;
   uint32_t loads_issued = 0;
   auto issue_next_load = [&]() {
-    while (load_row < rows && !is_valid(targets[load_row])) load_row += G;
+    while (load_row < rows && !is_valid(load_tgt)) {
+      load_row += G;
+      if (load_row < rows) load_tgt = targets[load_row];
+    }
     if (load_row < rows) {
-      if (my_bytes) {
-        const uint32_t st = loads_issued % kCStages;
-        const uint32_t bar = cx_smem_u32(&full_bar[st]);
-        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(my_bytes) : "memory");
-        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                     ::"r"(smem0 + st * kCStageBytes), "l"(logits + load_row * ld + col_lo), "r"(my_bytes), "r"(bar)
-                     : "memory");
-      }
+      const uint32_t st = loads_issued % kCStages;
+      const uint32_t bar = cx_smem_u32(&full_bar[st]);
+      asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(row_bytes) : "memory");
+      asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                   ::"r"(smem0 + st * kCStageBytes), "l"(logits + load_row * ld), "r"(row_bytes), "r"(bar) : "memory");
       ++loads_issued;
       load_row += G;
+      if (load_row < rows) load_tgt = targets[load_row];
     }
   };
   if (tid == 0) { issue_next_load(); issue_next_load(); }
 
-  uint32_t k = 0;   // valid rows processed so far (stage = k % 3, exchange slot = k & 1)
-  for (int64_t r = cid; r < rows; r += G) {
-    const int64_t tgt = targets[r];
+  // row-invariant: how many leading logits of each of this thread's vectors are real (inside the row AND inside the
+  // vocabulary); 8 everywhere for all but the last few warps
+  int nkeep[kCU];
+  bool partial = false;
+#pragma unroll
+  for (int u = 0; u < kCU; ++u) {
+    const int v = u * kCThreads + tid;
+    nkeep[u] = v < nvec ? min(8, max(0, vocab - (v << 3))) : 0;
+    partial = partial || nkeep[u] < 8;
+  }
+  uint32_t k = 0;   // valid rows processed so far (stage = k % 3)
+  int64_t tgt_next = blockIdx.x < rows ? targets[blockIdx.x] : ignore_index;
+  for (int64_t r = blockIdx.x; r < rows; r += G) {
+    const int64_t tgt = tgt_next;
+    if (r + G < rows) tgt_next = targets[r + G];   // used one row later
     if (!is_valid(tgt)) {   // ignored (or out-of-range) target: zero gradient, no loss; nothing was loaded
       const uint4 zero = make_uint4(0u, 0u, 0u, 0u);
-      __nv_bfloat16* z = logits + r * ld + col_lo;
-      for (int v = tid; v < my_vecs; v += kCThreads) st_stream16(z + ((int64_t)v << 3), zero);
-      if (crank == 0 && tid == 0) row_loss[r] = 0.f;
+      __nv_bfloat16* z = logits + r * ld;
+      for (int v = tid; v < nvec; v += kCThreads) st_stream16(z + ((int64_t)v << 3), zero);
+      if (tid == 0) row_loss[r] = 0.f;
       continue;
     }
     const uint32_t st = k % kCStages;
     const uint32_t sbase = smem0 + st * kCStageBytes;
-    if (my_bytes) cx_mbar_wait(cx_smem_u32(&full_bar[st]), (k / kCStages) & 1u);
+    cx_mbar_wait(cx_smem_u32(&full_bar[st]), (k / kCStages) & 1u);
     const int tcol = (int)tgt;
-    float zt = -INFINITY;
-    if (tid == 0 && tcol >= col_lo && tcol < col_hi)   // read before anyone overwrites the stage
-      zt = __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(cx_smem + st * kCStageBytes)[tcol - col_lo]) * kLog2e;
+    float zt = 0.f;
+    if (tid == 0)   // read before anyone overwrites the stage
+      zt = __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(cx_smem + st * kCStageBytes)[tcol]) * kLog2e;
 
-    // ---- the thread's 32 logits: packed-bf16 maximum first (one HMNMX2 per two logits) ----
+    // ---- the thread's 32 logits: packed-bf16 maximum first (one HMNMX2 per two logits).  No per-vector guards: a
+    // vector index past the row still lies inside the 64 KB stage (stale bytes, masked below), and which of a thread's
+    // vectors reach past the vocabulary is the same for every row (`partial`, `nkeep`) ----
     uint4 q[kCU];
-    uint32_t mx2 = 0xff80ff80u;   // (-inf, -inf) in bf16
 #pragma unroll
-    for (int u = 0; u < kCU; ++u) {
-      const int v = u * kCThreads + tid;
-      q[u] = make_uint4(0xff80ff80u, 0xff80ff80u, 0xff80ff80u, 0xff80ff80u);
-      if (v < my_vecs) {
-        asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(q[u].x), "=r"(q[u].y), "=r"(q[u].z), "=r"(q[u].w)
-                     : "r"(sbase + (uint32_t)v * 16u) : "memory");
-        const int c0 = (v0 + v) << 3;
-        if (c0 + 8 > vocab) {   // the vector straddling (or beyond) the end of the vocabulary: padding -> -inf
-          uint32_t* w = reinterpret_cast<uint32_t*>(&q[u]);
+    for (int u = 0; u < kCU; ++u)
+      asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(q[u].x), "=r"(q[u].y), "=r"(q[u].z), "=r"(q[u].w)
+                   : "r"(sbase + (uint32_t)(u * kCThreads + tid) * 16u) : "memory");
+    if (partial) {   // a few warps at most: padding and out-of-row logits -> -inf
 #pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            if (c0 + 2 * j >= vocab) w[j] = (w[j] & 0xffff0000u) | 0xff80u;
-            if (c0 + 2 * j + 1 >= vocab) w[j] = (w[j] & 0x0000ffffu) | 0xff800000u;
-          }
+      for (int u = 0; u < kCU; ++u) {
+        uint32_t* w = reinterpret_cast<uint32_t*>(&q[u]);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          if (2 * j >= nkeep[u]) w[j] = (w[j] & 0xffff0000u) | 0xff80u;
+          if (2 * j + 1 >= nkeep[u]) w[j] = (w[j] & 0x0000ffffu) | 0xff800000u;
         }
-        mx2 = bf16x2_max(bf16x2_max(mx2, q[u].x), bf16x2_max(q[u].y, bf16x2_max(q[u].z, q[u].w)));
       }
     }
-    // ---- CTA maximum BEFORE any exponential (max-merges cost FMNMX + SHFL; merging (max, sum) pairs instead would
+    uint32_t mx2 = bf16x2_max(bf16x2_max(q[0].x, q[0].y), bf16x2_max(q[0].z, q[0].w));
+#pragma unroll
+    for (int u = 1; u < kCU; ++u)
+      mx2 = bf16x2_max(bf16x2_max(mx2, q[u].x), bf16x2_max(q[u].y, bf16x2_max(q[u].z, q[u].w)));
+    // ---- row maximum BEFORE any exponential (max-merges cost FMNMX + SHFL; merging (max, sum) pairs instead would
     // cost two MUFU ops per thread and round, as many again as the exponentials themselves) ----
     float m = fmaxf(bf16lo(mx2), bf16hi(mx2));
 #pragma unroll
@@ -393,11 +365,10 @@ softmax_xent_cluster_kernel(__nv_bfloat16* __restrict__ logits, int64_t rows, in
     m = red_m[tid & 31];
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
-    m *= kLog2e;                                      // CTA maximum, log2 domain
+    m *= kLog2e;                                      // row maximum, log2 domain (finite: the target is a real column)
     // ---- one exponential per logit: FFMA2 + 2 MUFU + FADD2 per pair ----
     f32x2_t e2[kCU][4];
-    const float nm = (m == -INFINITY) ? 0.f : -m;    // all-padding share: exp2(-inf + 0) = 0
-    const f32x2_t l2e2 = pk2(kLog2e, kLog2e), nm2 = pk2(nm, nm);
+    const f32x2_t l2e2 = pk2(kLog2e, kLog2e), nm2 = pk2(-m, -m);
     f32x2_t s2a = pk2(0.f, 0.f), s2b = pk2(0.f, 0.f);
 #pragma unroll
     for (int u = 0; u < kCU; ++u) {
@@ -406,7 +377,7 @@ softmax_xent_cluster_kernel(__nv_bfloat16* __restrict__ logits, int64_t rows, in
       for (int j = 0; j < 4; ++j) {
         float lo, hi;
         upk2(fma2(bf16x2_to_f32x2(w[j]), l2e2, nm2), lo, hi);
-        e2[u][j] = pk2(ex2_approx(lo), ex2_approx(hi));
+        e2[u][j] = pk2(ex2_approx(lo), ex2_approx(hi));   // padding: exp2(-inf) = 0
         if (j & 1) s2b = add2(s2b, e2[u][j]); else s2a = add2(s2a, e2[u][j]);
       }
     }
@@ -420,90 +391,39 @@ softmax_xent_cluster_kernel(__nv_bfloat16* __restrict__ logits, int64_t rows, in
     ssum = red_s[tid & 31];
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) ssum += __shfl_xor_sync(0xffffffffu, ssum, o);
-    MS acc{m, ssum};                                  // this CTA's share of the row
-    MS tot = acc;
-    float zt_all = zt;
-    if (csize > 1) {
-      // Exchange without a cluster-wide barrier: thread 0 PUSHES this CTA's triple into slot [k & 1][crank] of every
-      // CTA of the cluster (itself included) with st.async, which signals the receiver's mbarrier by byte count; every
-      // thread then waits on its own CTA's barrier and reads local shared memory.  Slot k & 1 is reused two rows
-      // later: a sender gets there only after it has received this CTA's message of row k+1, which this CTA sends
-      // after all of its threads have read the slots of row k.
-      const uint32_t xb = cx_smem_u32(&xch_bar[k & 1]);
-      if (tid == 0) {
-        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(xb), "r"(csize * 16u) : "memory");
-        const uint32_t slot = cx_smem_u32(&xch[k & 1][crank][0]);
-        for (uint32_t c = 0; c < csize; ++c) {
-          uint32_t rslot, rbar;
-          asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(rslot) : "r"(slot), "r"(c));
-          asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(rbar) : "r"(xb), "r"(c));
-          asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v4.f32 [%0], {%1, %2, %3, %4}, [%5];"
-                       ::"r"(rslot), "f"(acc.m), "f"(acc.s), "f"(zt), "f"(0.f), "r"(rbar) : "memory");
-        }
-      }
-      cx_mbar_wait_cluster(xb, (k >> 1) & 1u);
-      const uint32_t c = (uint32_t)(tid & 7);            // lane c takes CTA c's triple
-      MS o{-INFINITY, 0.f};
-      float ztc = -INFINITY;
-      if (c < csize) { o.m = xch[k & 1][c][0]; o.s = xch[k & 1][c][1]; ztc = xch[k & 1][c][2]; }
-#pragma unroll
-      for (int sh = 4; sh > 0; sh >>= 1) {
-        MS other;
-        other.m = __shfl_xor_sync(0xffffffffu, o.m, sh);
-        other.s = __shfl_xor_sync(0xffffffffu, o.s, sh);
-        ztc = fmaxf(ztc, __shfl_xor_sync(0xffffffffu, ztc, sh));
-        o = ms_merge_fast(o, other);
-      }
-      tot = o; zt_all = ztc;
-    } else {
-      // zt_all = zt: only thread 0 holds the target logit, and only thread 0 uses it (the row loss)
-    }
-    // ---- gradient: e * 2^(m_thread - M) * scale / sum, minus the one-hot; bf16 back into the same bytes ----
-    const float fac = (m == -INFINITY) ? 0.f : ex2_approx(m - tot.m) * __fdividef(scale, tot.s);
+    // ---- gradient: e * scale / sum; bf16 back into the same bytes (the one-hot is applied by thread 0 below) ----
+    const float fac = __fdividef(scale, ssum);
     const f32x2_t fac2 = pk2(fac, fac);
-    const int tvec = tcol >> 3, tj = tcol & 7;
 #pragma unroll
-    for (int u = 0; u < kCU; ++u) {
-      const int v = u * kCThreads + tid;
-      if (v < my_vecs) {
-        uint32_t w[4];
-        if (v0 + v == tvec) {
+    for (int u = 0; u < kCU; ++u) {   // unguarded: bytes past the row are never copied out
+      uint32_t w[4];
 #pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            float lo, hi;
-            upk2(mul2(e2[u][j], fac2), lo, hi);
-            if (2 * j == tj) lo -= scale;
-            if (2 * j + 1 == tj) hi -= scale;
-            w[j] = pack_bf16x2(lo, hi);
-          }
-        } else {
-#pragma unroll
-          for (int j = 0; j < 4; ++j) w[j] = f32x2_to_bf16x2(mul2(e2[u][j], fac2));   // padding columns carry e = 0
-        }
-        asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(sbase + (uint32_t)v * 16u), "r"(w[0]), "r"(w[1]),
-                     "r"(w[2]), "r"(w[3]) : "memory");
-      }
+      for (int j = 0; j < 4; ++j) w[j] = f32x2_to_bf16x2(mul2(e2[u][j], fac2));   // padding columns carry e = 0
+      asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(sbase + (uint32_t)(u * kCThreads + tid) * 16u), "r"(w[0]),
+                   "r"(w[1]), "r"(w[2]), "r"(w[3]) : "memory");
     }
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy stores -> visible to the bulk store
     __syncthreads();
     if (tid == 0) {
-      if (my_bytes) {
-        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
-                     ::"l"(logits + r * ld + col_lo), "r"(sbase), "r"(my_bytes) : "memory");
-        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-        // the stage the next load goes into was stored from one row ago: that store must have read it
-        asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
-      }
+      // the one-hot: softmax(target) * scale - scale in one rounding, over the plain product stored for that column
+      const float gt = ex2_approx(zt - m) * fac - scale;
+      reinterpret_cast<__nv_bfloat16*>(cx_smem + st * kCStageBytes)[tcol] = __float2bfloat16_rn(gt);
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
+                   ::"l"(logits + r * ld), "r"(sbase), "r"(row_bytes) : "memory");
+      asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+      // the stage the next load goes into was stored from one row ago: that store must have read it.  (Issuing the load
+      // earlier, in the middle of the row, measured 7 % slower: a 64 KB bulk store needs more than a max + exp phase to
+      // drain its stage, and the wait then sits on the row's critical path.)
+      asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
       issue_next_load();
-      if (crank == 0) row_loss[r] = (tot.m + log2f(tot.s) - zt_all) * kLn2;
+      row_loss[r] = (m + log2f(ssum) - zt) * kLn2;
     }
     ++k;
   }
   if (tid == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");   // every store of this CTA has landed
-  // (every message addressed to this CTA has been waited for above, so it may leave without a closing cluster barrier)
 
-  // ---- the last cluster to finish folds the per-row losses (fixed order: bit-reproducible) ----
-  if (crank != 0) return;
+  // ---- the last CTA to finish folds the per-row losses (fixed order: bit-reproducible) ----
   __syncthreads();
   if (tid == 0) {
     __threadfence();
@@ -542,45 +462,54 @@ int launch_xent(void* logits, int64_t rows, int vocab, int64_t ld, const int64_t
   count_valid_kernel<<<1, 256, 0, st>>>(targets, rows, ignore_index, vocab, ws);
   B200FT_LAUNCH_CHECK();
   const int64_t nvec = ld >> 3;
-  int csize = 1;
-  while (csize < 8 && (nvec + csize - 1) / csize > kCChunkVecs) csize <<= 1;
-  static const bool legacy = getenv("B200FT_XENT_LEGACY") != nullptr;
-  if (!legacy && (nvec + csize - 1) / csize <= kCChunkVecs) {
+  static const bool legacy = getenv("B200FT_XENT_LEGACY") != nullptr;   // A/B measurements: two-sweep kernel only
+  // Measured (tools/hbm_probe.py, B200, GB/s of algorithmic bytes): V = 32000: staged 5474, two-sweep 4882.  Rows
+  // longer than one CTA's registers hold were also tried as clusters of 2-8 CTAs exchanging (max, sum) through
+  // distributed shared memory: V = 50257 3600, V = 128256 4350-4500 — behind the two-sweep kernel (5089, 4740-4860
+  // with its rows in flight capped to what L2 holds), because the per-row chain (max, exp at the MUFU rate, exchange,
+  // store drain) stays while the bytes per CTA shrink; they are not built.
+  if (!legacy && nvec <= kCChunkVecs) {
     static thread_local int attr_dev = -1;
-    static thread_local int max_clusters[4] = {0, 0, 0, 0};   // co-resident clusters for sizes 1, 2, 4, 8
     int dev = -1;
     B200FT_CUDA(cudaGetDevice(&dev));
     if (dev != attr_dev) {
-      B200FT_CUDA(cudaFuncSetAttribute(softmax_xent_cluster_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+      B200FT_CUDA(cudaFuncSetAttribute(softmax_xent_staged_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        kCSmemBytes));
-      for (int i = 0; i < 4; ++i) max_clusters[i] = 0;
       attr_dev = dev;
     }
-    cudaLaunchConfig_t cfg = {};
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = (unsigned)csize; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
-    cfg.blockDim = dim3(kCThreads); cfg.dynamicSmemBytes = kCSmemBytes; cfg.stream = st;
-    cfg.attrs = attr; cfg.numAttrs = 1;
-    const int slot = csize == 1 ? 0 : csize == 2 ? 1 : csize == 4 ? 2 : 3;
-    if (max_clusters[slot] == 0) {
-      // persistent grid = what the chip holds at once (GPCs whose SM count is not a multiple of the cluster
-      // size strand a few SMs; a grid larger than this would run a second, mostly empty wave)
-      cfg.gridDim = dim3((unsigned)(B200FT_NUM_SMS / csize * csize));
-      int n = 0;
-      B200FT_CUDA(cudaOccupancyMaxActiveClusters(&n, softmax_xent_cluster_kernel, &cfg));
-      B200FT_CHECK_ARG(n > 0, "softmax_xent: no cluster of %d CTAs fits on this device", csize);
-      max_clusters[slot] = n;
-    }
-    const int64_t clusters = rows < max_clusters[slot] ? rows : max_clusters[slot];
-    cfg.gridDim = dim3((unsigned)(clusters * csize));
-    const int chunk_vecs = (int)((nvec + csize - 1) / csize);
-    B200FT_CUDA(cudaLaunchKernelEx(&cfg, softmax_xent_cluster_kernel, (__nv_bfloat16*)logits, rows, vocab, ld, targets,
-                                   ignore_index, grad_scale, loss_out, ws, chunk_vecs));
+    const unsigned grid = (unsigned)(rows < B200FT_NUM_SMS ? rows : B200FT_NUM_SMS);   // persistent, one CTA per SM
+    softmax_xent_staged_kernel<<<grid, kCThreads, kCSmemBytes, st>>>((__nv_bfloat16*)logits, rows, vocab, ld, targets,
+                                                                     ignore_index, grad_scale, loss_out, ws);
+    B200FT_LAUNCH_CHECK();
     return 0;
   }
-  softmax_xent_kernel<<<(unsigned)rows, kThreads, 0, st>>>((__nv_bfloat16*)logits, rows, vocab, ld, targets,
-                                                           ignore_index, grad_scale, loss_out, ws);
+  // Two-sweep kernel.  Its second sweep must find the row in L2 (126 MB): rows in flight = CTAs per SM x 148.  Rows up to
+  // ~105 KB run 8 CTAs of 256 threads per SM; longer rows run 512-thread CTAs whose number per SM is capped, by a dynamic
+  // shared-memory request they do not use, so that the rows in flight stay below ~120 MB.
+  // Measured at V = 128256 (256 KB rows), 512 threads: 1 / 2 / 3 CTAs per SM 3500 / 4480-4600 / 4740-4860 GB/s; the
+  // uncapped 8 x 256 threads (303 MB in flight, third sweep from HBM) 4270-4370.  V = 50257: 8 x 256 threads (119 MB in
+  // flight) 5089, 4 x 512 threads 4247.
+  const int64_t row_bytes = ld * 2;
+  int64_t cap = (120ll << 20) / (row_bytes * B200FT_NUM_SMS);
+  static const int force_cap = getenv("B200FT_XENT_CAP") ? atoi(getenv("B200FT_XENT_CAP")) : 0;   // experiments
+  if (force_cap > 0) cap = force_cap;
+  if (row_bytes * 8 * B200FT_NUM_SMS <= (126ll << 20) || force_cap >= 8) {
+    softmax_xent_kernel<256><<<(unsigned)rows, 256, 0, st>>>((__nv_bfloat16*)logits, rows, vocab, ld, targets,
+                                                            ignore_index, grad_scale, loss_out, ws);
+  } else {
+    if (cap < 1) cap = 1;
+    if (cap > 3) cap = 3;
+    const int pad = (int)(220 * 1024 / cap) - 2048;
+    static thread_local int attr_dev2 = -1;
+    int dev = -1;
+    B200FT_CUDA(cudaGetDevice(&dev));
+    if (dev != attr_dev2) {
+      B200FT_CUDA(cudaFuncSetAttribute(softmax_xent_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+      attr_dev2 = dev;
+    }
+    softmax_xent_kernel<512><<<(unsigned)rows, 512, pad, st>>>((__nv_bfloat16*)logits, rows, vocab, ld, targets,
+                                                              ignore_index, grad_scale, loss_out, ws);
+  }
   B200FT_LAUNCH_CHECK();
   return 0;
 }

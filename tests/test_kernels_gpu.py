@@ -151,9 +151,10 @@ def test_softmax_xent_out_of_range_targets_are_ignored_and_counted(ops):
 
 
 @pytest.mark.parametrize("rows,vocab,ld", [(700, 1000, 1024), (9, 40000, 40000), (5, 262144, 262144), (3, 300000, 300000)])
-def test_softmax_xent_many_rows_and_cluster_sizes(ops, rows, vocab, ld):
-    """More rows than resident clusters (every CTA loops, the 3-stage ring wraps), ignored rows in between, and row
-    lengths that select cluster sizes 1, 2, 8 and the one-CTA-per-row fallback (> 262144 logits)."""
+def test_softmax_xent_many_rows_and_every_kernel_choice(ops, rows, vocab, ld):
+    """More rows than SMs (every persistent CTA loops, the 3-stage ring wraps), ignored rows in between, and row
+    lengths that select the staged kernel (<= 32768 logits), the two-sweep kernel at 8 x 256 threads per SM and the
+    two-sweep kernel with capped 512-thread CTAs (long rows)."""
     g = torch.Generator().manual_seed(rows + vocab)
     z = bf16_round(torch.randn(rows, vocab, generator=g) * 3.0)
     targets = torch.randint(0, vocab, (rows,), generator=g)

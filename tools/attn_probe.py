@@ -13,9 +13,12 @@ def timeit(fn, n=20):
     e1.record(); torch.cuda.synchronize()
     return e0.elapsed_time(e1) * 1e3 / n
 import ast
-SHAPES = ast.literal_eval(sys.argv[1]) if len(sys.argv) > 1 else [(32, 1024, 12, 12), (4, 2048, 32, 8), (8, 4096, 12, 12)]
-for (B, T, H, KV) in SHAPES:
-    dh = 64
+# shapes: (batch, seq, heads, kv heads[, d_head = 64]); defaults = C2, C3, a long d_head-64 case, C4/C5 (Llama-3-8B)
+SHAPES = ast.literal_eval(sys.argv[1]) if len(sys.argv) > 1 else [(32, 1024, 12, 12), (4, 2048, 32, 8), (8, 4096, 12, 12),
+                                                                  (1, 4096, 32, 8, 128), (2, 4096, 32, 8, 128)]
+for shape in SHAPES:
+    B, T, H, KV = shape[:4]
+    dh = shape[4] if len(shape) > 4 else 64
     ld = (H + 2 * KV) * dh
     qkv = torch.randn(B * T, ld, device=dev).to(torch.bfloat16)
     out = torch.empty(B * T, H * dh, dtype=torch.bfloat16, device=dev)
@@ -30,7 +33,7 @@ for (B, T, H, KV) in SHAPES:
     us_lib = timeit(lambda: F.scaled_dot_product_attention(q, k, v, is_causal=True, enable_gqa=(H != KV)))
     o_lib = F.scaled_dot_product_attention(q, k, v, is_causal=True, enable_gqa=(H != KV)).permute(0, 2, 1, 3).reshape(B * T, H * dh)
     err = (out.float() - o_lib.float()).abs().max().item()
-    print(f"B={B} T={T} H={H} KV={KV}: own {us:8.1f} us ({flops/us/1e6:6.0f} TF)   SDPA {us_lib:8.1f} us ({flops/us_lib/1e6:6.0f} TF)   max|diff| {err:.4f}")
+    print(f"B={B} T={T} H={H} KV={KV} dh={dh}: own {us:8.1f} us ({flops/us/1e6:6.0f} TF)   SDPA {us_lib:8.1f} us ({flops/us_lib/1e6:6.0f} TF)   max|diff| {err:.4f}")
     # ---- backward: own (delta + dk|dv + dq kernels) vs SDPA's autograd (cuDNN) ----
     dout = torch.randn(B * T, H * dh, device=dev).to(torch.bfloat16)
     dqkv = torch.empty(B * T, ld, dtype=torch.bfloat16, device=dev)

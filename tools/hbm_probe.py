@@ -4,8 +4,8 @@ import os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, os.path.join(ROOT, "finetune-controller_b200"))
 import torch
-from b200ft import ops
 dev = "cuda:0"
+from b200ft import ops
 what = sys.argv[1]
 iters = int(sys.argv[2]) if len(sys.argv) > 2 else 5
 def run(fn, bytes_):
