@@ -291,7 +291,7 @@ def run_ours(args) -> None:
         sync = ddp.BucketedGradSync(n_layer, n_buckets=n_layer, group=ddp.overlap_group(k) if k > 0 else None,
                                     reserve_ctas=k, use_tail_group=True)
     elif world > 1:
-        sync = ddp.BucketedGradSync(n_layer, n_buckets=2)
+        sync = ddp.BucketedGradSync(n_layer, n_buckets=1)   # the whole flat adapter gradient: ONE all-reduce per step
     # random-init weights; B drawn at random (not PEFT's zero) so every gradient path carries data
     eng, dims = params.build_engine(model, lora, opt, batch=BATCH, seq=SEQ, device=dev, seed=0, world_size=world,
                                     grad_sync=sync, randomize_b=True, mode="full" if full else "lora",
@@ -389,6 +389,16 @@ def run_ours(args) -> None:
                            "frac": gbs / pk["hbm_gbs"], "ms_per_step": c["ms_per_step"],
                            "launches_per_step": c["launches_per_step"]})
 
+    # N > 1: the configurations whose exchange is not negligible, measured briefly after the headline's timed region
+    # (C3: Llama-3.2-1B LoRA, 3.4 MB of gradients per step; C5: Llama-3-8B full-parameter, 16 GB per step)
+    extras = None
+    if world > 1 and args.workload == "c2" and not args.no_extra_configs:
+        del eng, resident
+        torch.cuda.empty_cache()
+        extras = {}
+        for name in ("c3", "c5"):
+            extras[name] = extra_config(name, args, rank, world, dev, pk)
+            torch.cuda.empty_cache()
     if rank != 0:
         return
     if args.detail:
@@ -412,7 +422,7 @@ def run_ours(args) -> None:
                    "global_batch": BATCH * world, "seq_len": SEQ, "parallelism": f"dp{world}",
                    "l2": "per-step working set (GBs of activations and logits) is far larger than the "
                          "126 MB L2; no explicit flush",
-                   "attention": ("torch SDPA (library); every other op is this repo's CUDA" if args.attention == "sdpa"
+                   "attention": ("torch SDPA (library); every other op is this repo's CUDA" if eng.attention == "sdpa"
                                  else "this repo's tcgen05 flash-attention forward + backward (no library kernel in the step)")},
         "e2e": {"value": tokens / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e / args.steps,
                 "h2d_bytes_per_step": 2 * BATCH * SEQ * 8, "d2h_bytes_per_step": 4, "last_loss": losses[-1]},
@@ -424,7 +434,70 @@ def run_ours(args) -> None:
     }
     if parity is not None:
         line["dp_parity"] = parity
+    if extras is not None:
+        line["configs_extra"] = extras
     print(json.dumps(line), flush=True)
+
+
+def extra_config(name: str, args, rank: int, world: int, dev, pk) -> dict:
+    """A short run (3 warm-up + 5 timed steps, twice: with the gradient exchange and with it switched off) of another
+    BASELINE.json configuration on the same ranks: ms/step, tokens/s, GEMM TFLOP/s inside the step and the part of the
+    exchange that backward does not hide (difference of the two timings)."""
+    import torch.distributed as dist
+    from b200ft import ddp, gpt2, ops, params
+    model, batch, seq, lora_r, lora_alpha, desc = WORKLOADS[name]
+    full = lora_r == 0
+    n_layer = params.MODELS[model].n_layer
+    try:
+        if full:
+            k = args.nccl_ctas
+            sync = ddp.BucketedGradSync(n_layer, n_buckets=n_layer, group=ddp.overlap_group(k) if k > 0 else None,
+                                        reserve_ctas=k, use_tail_group=True)
+        else:
+            sync = ddp.BucketedGradSync(n_layer, n_buckets=1)
+        eng, dims = params.build_engine(model, gpt2.LoRASpec(lora_r or 8, lora_alpha or 16.0), gpt2.OptSpec(), batch=batch,
+                                        seq=seq, device=dev, seed=0, world_size=world, grad_sync=sync, randomize_b=True,
+                                        mode="full" if full else "lora", attention=args.attention)
+        g = torch.Generator().manual_seed(4321 + rank)
+        ids = [torch.randint(0, dims.vocab, (batch, seq), generator=g, dtype=torch.int64).to(dev) for _ in range(2)]
+
+        def timed(steps):
+            dist.barrier(); torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for s_ in range(steps):
+                eng.step(ids[s_ % 2], ids[s_ % 2])
+            e1.record()
+            dist.barrier(); torch.cuda.synchronize()
+            t = torch.tensor([e0.elapsed_time(e1)], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            return float(t.item()) / steps
+
+        steps = 5
+        for s_ in range(3):
+            eng.step(ids[s_ % 2], ids[s_ % 2])
+        ms = timed(steps)
+        sent = sync.bytes_reduced
+        ops.PROFILE = {}
+        eng.step(ids[0], ids[0])
+        torch.cuda.synchronize()
+        prof, ops.PROFILE = ops.PROFILE, None
+        big = [e for e in prof.get("gemm", []) if e[3][6] == 2]
+        gemm_ms = sum(e[0].elapsed_time(e[1]) for e in big)
+        gemm_tf = sum(e[2] for e in big) / (gemm_ms * 1e-3) / 1e12 if gemm_ms > 0 else None
+        # the same steps with the exchange switched off (ranks drift apart numerically; timing only)
+        eng.grad_sync = None
+        eng.step(ids[0], ids[0])
+        ms_local = timed(steps)
+        out = {"workload": desc, "ms_per_step": ms, "tokens_per_s": world * batch * seq / (ms * 1e-3),
+               "ms_per_step_without_exchange": ms_local, "exposed_exchange_ms": ms - ms_local,
+               "gemm_tflops_in_step": gemm_tf, "gemm_frac_of_sustained_peak": gemm_tf / pk["tf_sustained"] if gemm_tf else None,
+               "gradient_bytes_per_step": sent // (3 + steps + 0) if sent else 0, "steps": steps, "warmup": 3,
+               "attention": eng.attention}
+        del eng, ids
+        return out
+    except Exception as e:   # the headline must not die with an extra
+        return {"workload": desc, "error": f"{type(e).__name__}: {e}"[:300]}
 
 
 def adamw_large_buffer(ops, dev, pk, n=256 * 1024 * 1024, iters=10) -> dict:
@@ -455,13 +528,15 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-dp-parity", action="store_true", help="N > 1: skip the multi-rank parity check")
+    ap.add_argument("--no-extra-configs", action="store_true",
+                    help="N > 1: skip the short C3 / C5 runs reported under configs_extra")
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
     ap.add_argument("--nccl-ctas", type=int, default=8,
                     help="full-parameter workloads: CTAs of the overlapped all-reduce (and SMs x2 left free by the "
                          "backward GEMMs); 0 = default communicator, no reservation")
-    ap.add_argument("--attention", default="sdpa", choices=["sdpa", "own"],
-                    help="sdpa: torch SDPA (cuDNN, library; faster today); own: this repo's tcgen05 attention kernels "
-                         "(d_head 64 models), i.e. a step with no library kernel in it")
+    ap.add_argument("--attention", default="auto", choices=["auto", "own", "sdpa"],
+                    help="own: this repo's tcgen05 attention kernels (d_head 64 and 128), i.e. a step with no library "
+                         "kernel in it; sdpa: torch SDPA (cuDNN, library; A/B measurements); auto = own where built")
     ap.add_argument("--overlap-optimizer", action="store_true",
                     help="full-parameter workloads: per-layer AdamW launches on a second stream beside backward instead "
                          "of one launch after it (measured slower under the power cap; A/B measurement)")

@@ -1,6 +1,7 @@
 """The repo's own causal flash-attention (csrc/attention.cu, csrc/attention_bwd.cu) as a step-engine
-mixin.  Engines take ``attention="sdpa"`` (torch SDPA -> cuDNN, the faster one today and the default)
-or ``attention="own"`` (tcgen05 kernels of this library: d_head 64 — GPT-2, Llama-3.2-1B — and 128 — Llama-3-8B).
+mixin.  Engines take ``attention="own"`` (tcgen05 kernels of this library: d_head 64 — GPT-2, Llama-3.2-1B — and
+128 — Llama-3-8B: no library kernel in the step), ``attention="sdpa"`` (torch SDPA -> cuDNN, a library: faster today, kept
+for A/B measurements and for other head sizes) or ``attention="auto"`` (the default: own wherever it is built).
 SURVEY.md §8 a2.8 / (f)-1."""
 from __future__ import annotations
 
@@ -9,6 +10,18 @@ import math
 import torch
 
 from . import ops
+
+
+OWN_HEAD_SIZES = (64, 128)
+
+
+def resolve_attention(mode: str, d_head: int) -> str:
+    """"auto" -> "own" for the head sizes the kernels are built for, "sdpa" otherwise; explicit choices pass through."""
+    if mode not in ("auto", "own", "sdpa"):
+        raise ValueError(f"attention must be auto, own or sdpa, not {mode!r}")
+    if mode == "auto":
+        return "own" if d_head in OWN_HEAD_SIZES else "sdpa"
+    return mode
 
 
 class OwnAttentionMixin:

@@ -8,10 +8,10 @@ row-major [tokens, features]; statistics, accumulators and optimizer state are f
 Frozen weights are kept in HBM in the two layouts the K-major GEMM wants: W^T [out, in] for
 forward (y = x W) and W [in, out] (the HF Conv1D layout) for backward (dx = dy W^T).
 
-Attention (not in north_star's judged set): `attention="sdpa"` (default, the faster
-one today) delegates it to torch's scaled_dot_product_attention -> cuDNN, forward and backward;
-`attention="own"` runs this library's tcgen05 flash-attention kernels (attention.py), leaving no
-library kernel in the step.
+Attention: `attention="own"` runs this library's tcgen05 flash-attention kernels
+(attention.py), leaving no library kernel in the step — what "auto", the default, selects for 64- and 128-wide
+heads; `attention="sdpa"` delegates it to torch's scaled_dot_product_attention -> cuDNN, forward and backward
+(library; kept for A/B measurements and for other head sizes).
 """
 from __future__ import annotations
 
@@ -22,7 +22,7 @@ import torch
 import torch.nn.functional as F
 
 from . import ops
-from .attention import OwnAttentionMixin
+from .attention import OwnAttentionMixin, resolve_attention
 from ._lib import EPI_DGELU, EPI_GELU, EPI_NONE, EPI_RESIDUAL
 
 R_PAD = 16  # adapter rank padded to one UMMA K step (16 bf16)
@@ -103,11 +103,10 @@ class GPT2LoRAStep(StepHostMixin, OwnAttentionMixin):
     """Holds device state for one rank and runs fwd + loss + bwd + AdamW per `step()`."""
 
     def __init__(self, dims: GPT2Dims, lora: LoRASpec, opt: OptSpec, base: dict, adapters: dict, *,
-                 batch: int, seq: int, device="cuda:0", world_size: int = 1, grad_sync=None, attention: str = "sdpa"):
+                 batch: int, seq: int, device="cuda:0", world_size: int = 1, grad_sync=None, attention: str = "auto"):
         if not torch.cuda.is_available():
             raise RuntimeError("GPT2LoRAStep needs a CUDA device: there is no CPU path")
-        assert attention in ("sdpa", "own")
-        self.attention = attention
+        self.attention = resolve_attention(attention, dims.d_model // dims.n_head)
         assert lora.r <= R_PAD and seq <= dims.ctx
         assert dims.d_model % 8 == 0 and dims.d_ff % 8 == 0
         self.dims, self.lora, self.opt = dims, lora, opt
@@ -204,7 +203,11 @@ class GPT2LoRAStep(StepHostMixin, OwnAttentionMixin):
         return out
 
     def grad_views(self, lo: int, hi: int) -> list:
-        """Contiguous gradient slices of layers [lo, hi) (what one all-reduce bucket covers)."""
+        """Contiguous gradient slices of layers [lo, hi) (what one all-reduce bucket covers).  The flat buffer is laid
+        out [A^T of all layers | B of all layers], so a layer range is two slices; the whole model is the one flat buffer
+        (1.2 MB for GPT-2 124M: one latency-bound all-reduce per step, which is what the payload and bench use)."""
+        if lo == 0 and hi == self.dims.n_layer:
+            return [self.G]
         return [self.gAt_all[lo * R_PAD: hi * R_PAD], self.gB_all[lo * R_PAD: hi * R_PAD]]
 
     # ------------------------------------------------------------------ activations

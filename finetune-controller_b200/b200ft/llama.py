@@ -18,7 +18,7 @@ import torch.nn.functional as F
 
 from . import ops
 from ._lib import EPI_NONE, EPI_RESIDUAL
-from .attention import OwnAttentionMixin
+from .attention import OwnAttentionMixin, resolve_attention
 from .gpt2 import LoRASpec, OptSpec, R_PAD, StepHostMixin
 
 A_BLK = 2 * R_PAD  # adapter rows per layer in the flat buffers: q adapter 0..15, v adapter 16..31
@@ -77,11 +77,10 @@ class LlamaLoRAStep(StepHostMixin, OwnAttentionMixin):
     """Device state of one rank; `step()` = fwd + loss + bwd + AdamW on the q/v adapters."""
 
     def __init__(self, dims: LlamaDims, lora: LoRASpec, opt: OptSpec, base: dict, adapters: dict, *,
-                 batch: int, seq: int, device="cuda:0", world_size: int = 1, grad_sync=None, attention: str = "sdpa"):
+                 batch: int, seq: int, device="cuda:0", world_size: int = 1, grad_sync=None, attention: str = "auto"):
         if not torch.cuda.is_available():
             raise RuntimeError("LlamaLoRAStep needs a CUDA device: there is no CPU path")
-        assert attention in ("sdpa", "own")
-        self.attention = attention
+        self.attention = resolve_attention(attention, dims.d_head)
         assert lora.r <= R_PAD and dims.d_head % 16 == 0 and dims.d_model % 8 == 0 and dims.d_ff % 8 == 0
         self.dims, self.lora, self.opt = dims, lora, opt
         self.B, self.T, self.M = batch, seq, batch * seq
@@ -192,6 +191,9 @@ class LlamaLoRAStep(StepHostMixin, OwnAttentionMixin):
         return self._export(self.gAt_all, self.gBq_all, self.gBv_all)
 
     def grad_views(self, lo: int, hi: int) -> list:
+        """Gradient slices of layers [lo, hi); the whole model is the one flat buffer (a single all-reduce)."""
+        if lo == 0 and hi == self.dims.n_layer:
+            return [self.G]
         return [t[lo * A_BLK: hi * A_BLK] for t in (self.gAt_all, self.gBq_all, self.gBv_all)]
 
     # ------------------------------------------------------------------ activations

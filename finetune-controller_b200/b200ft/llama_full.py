@@ -16,7 +16,7 @@ GEMMs per layer: 4 forward, 4 dX (B operand MN-major: the nn.Linear weight [out,
 token index as K).  All are the cta_group::2 tcgen05 kernel.  Activations kept per layer: x, x1,
 qkv (post-RoPE), the attention output and gate|up; the normalised inputs h1/h2 and the SwiGLU
 product are recomputed in backward (HBM-bound, ~1 % of the step) instead of stored.
-Attention: torch SDPA (library) or this library's own kernels (d_head 64), as in llama.py.
+Attention: this library's own kernels (d_head 64 / 128) or torch SDPA (library), as in llama.py.
 """
 from __future__ import annotations
 
@@ -24,7 +24,7 @@ import torch
 import torch.nn.functional as F
 
 from . import ops
-from .attention import OwnAttentionMixin
+from .attention import OwnAttentionMixin, resolve_attention
 from ._lib import EPI_RESIDUAL
 from .gpt2 import OptSpec, StepHostMixin
 from .llama import LlamaDims, rope_tables
@@ -41,11 +41,10 @@ class LlamaFullStep(StepHostMixin, OwnAttentionMixin):
 
     def __init__(self, dims: LlamaDims, opt: OptSpec, base: dict | None, *, batch: int, seq: int,
                  device="cuda:0", world_size: int = 1, grad_sync=None, seed: int = 0, init_std: float = 0.02,
-                 attention: str = "sdpa", overlap_optimizer: bool = False):
+                 attention: str = "auto", overlap_optimizer: bool = False):
         if not torch.cuda.is_available():
             raise RuntimeError("LlamaFullStep needs a CUDA device: there is no CPU path")
-        assert attention in ("sdpa", "own")
-        self.attention = attention
+        self.attention = resolve_attention(attention, dims.d_head)
         assert dims.d_head % 16 == 0 and dims.d_model % 8 == 0 and dims.d_ff % 8 == 0
         self.dims, self.opt, self.lora = dims, opt, None
         self.B, self.T, self.M = batch, seq, batch * seq

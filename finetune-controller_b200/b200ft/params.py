@@ -96,7 +96,7 @@ def init_lora_llama(dims: LlamaDims, lora: LoRASpec, seed: int, device="cpu") ->
 
 
 def build_engine(model: str, lora: LoRASpec, opt, *, batch: int, seq: int, device, seed: int = 0, world_size: int = 1,
-                 grad_sync=None, randomize_b: bool = False, mode: str = "lora", attention: str = "sdpa",
+                 grad_sync=None, randomize_b: bool = False, mode: str = "lora", attention: str = "auto",
                  overlap_optimizer: bool = False, base_weights: str = ""):
     """Model (+ adapters) of the named architecture on `device`, wrapped in its step engine.  The base comes
     from `base_weights` (a Hugging Face checkpoint file / directory, see weights.py) or, if empty, is drawn at

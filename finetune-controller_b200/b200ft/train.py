@@ -35,8 +35,9 @@ def build_parser() -> argparse.ArgumentParser:
     ap.add_argument("--model", default="gpt2-124m")
     ap.add_argument("--mode", default="lora", choices=["lora", "full"],
                     help="lora: adapters on a frozen base; full: every tensor trainable (Llama family)")
-    ap.add_argument("--attention", default="sdpa", choices=["sdpa", "own"],
-                    help="sdpa: torch SDPA / cuDNN; own: this library's tcgen05 attention (d_head 64 models)")
+    ap.add_argument("--attention", default="auto", choices=["auto", "own", "sdpa"],
+                    help="own: this library's tcgen05 attention (d_head 64 / 128 models); sdpa: torch SDPA / cuDNN; "
+                         "auto: own wherever it is built")
     ap.add_argument("--lora_r", type=int, default=8)
     ap.add_argument("--lora_alpha", type=float, default=16.0)
     ap.add_argument("--seq_len", type=int, default=1024)
@@ -155,7 +156,7 @@ def worker(args, rank: int, world: int, local: int) -> None:
         sync = ddp.BucketedGradSync(n_layer, n_buckets=n_layer, group=ddp.overlap_group(8), reserve_ctas=8,
                                     use_tail_group=True)
     elif world > 1:
-        sync = ddp.BucketedGradSync(n_layer, n_buckets=2)
+        sync = ddp.BucketedGradSync(n_layer, n_buckets=1)   # a few MB: one all-reduce of the flat gradient buffer
     # random init, identical on every rank (same seed): the image has no network for checkpoints
     bw = args.base_weights
     if bw and not os.path.isabs(bw):

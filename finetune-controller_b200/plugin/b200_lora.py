@@ -28,7 +28,7 @@ class B200LoRAConfig(TrainingArguments):
 
     model: str = Field(default="gpt2-124m", description="Architecture: gpt2-124m | llama-3.2-1b | llama-3-8b (gpt2-tiny, llama-tiny for smoke runs)")
     mode: str = Field(default="lora", description="lora: adapters on c_attn (GPT-2) or q_proj + v_proj (Llama); full: every tensor trainable (Llama family; fp32 master + Adam moments, 8B fits one 180 GB B200)")
-    attention: str = Field(default="sdpa", description="sdpa: cuDNN flash attention through torch; own: this library's tcgen05 attention kernels (gpt2-124m, llama-3.2-1b)")
+    attention: str = Field(default="auto", description="own: this library's tcgen05 attention kernels (gpt2-124m, llama-3.2-1b, llama-3-8b); sdpa: cuDNN flash attention through torch; auto: own wherever it is built")
     lora_r: int = Field(default=8, description="LoRA rank (<= 16)")
     lora_alpha: float = Field(default=16.0, description="LoRA alpha; the branch is scaled by alpha / r")
     seq_len: int = Field(default=1024, description="Tokens per sequence")

@@ -42,7 +42,7 @@ def _worker(rank, world, port, n_layer, n_buckets, out_dir):
     dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("n_layer,n_buckets", [(12, 2), (5, 3), (2, 4)])
+@pytest.mark.parametrize("n_layer,n_buckets", [(12, 2), (5, 3), (2, 4), (12, 1)])
 def test_bucketed_allreduce_world2(tmp_path, n_layer, n_buckets):
     sys.path.insert(0, PKG)
     from b200ft import ddp
