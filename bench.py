@@ -392,6 +392,7 @@ def run_ours(args) -> None:
     # N > 1: the configurations whose exchange is not negligible, measured briefly after the headline's timed region
     # (C3: Llama-3.2-1B LoRA, 3.4 MB of gradients per step; C5: Llama-3-8B full-parameter, 16 GB per step)
     extras = None
+    attention_used = eng.attention
     if world > 1 and args.workload == "c2" and not args.no_extra_configs:
         del eng, resident
         torch.cuda.empty_cache()
@@ -422,7 +423,7 @@ def run_ours(args) -> None:
                    "global_batch": BATCH * world, "seq_len": SEQ, "parallelism": f"dp{world}",
                    "l2": "per-step working set (GBs of activations and logits) is far larger than the "
                          "126 MB L2; no explicit flush",
-                   "attention": ("torch SDPA (library); every other op is this repo's CUDA" if eng.attention == "sdpa"
+                   "attention": ("torch SDPA (library); every other op is this repo's CUDA" if attention_used == "sdpa"
                                  else "this repo's tcgen05 flash-attention forward + backward (no library kernel in the step)")},
         "e2e": {"value": tokens / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e / args.steps,
                 "h2d_bytes_per_step": 2 * BATCH * SEQ * 8, "d2h_bytes_per_step": 4, "last_loss": losses[-1]},
