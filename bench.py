@@ -42,8 +42,8 @@ import torch  # noqa: E402
 # DRAM bytes (read + write) per launch of the dominant kernel, averaged over the 98 launches of
 # one step: ncu `dram__bytes_read.sum + dram__bytes_write.sum` (see GEMM_DRAM_SOURCE).  None until
 # the capture for the current kernel has been taken.
-GEMM_DRAM_BYTES_PER_LAUNCH = 347.9e6
-GEMM_DRAM_SOURCE = ("profiles/r01_step_launch_summary_final.txt: 34.09 GB over the 98 launches of one step "
+GEMM_DRAM_BYTES_PER_LAUNCH = 351.8e6
+GEMM_DRAM_SOURCE = ("profiles/r02_step_launch_summary_c2.txt: 34.47 GB over the 98 launches of one step "
                     "(ncu dram__bytes_read.sum + dram__bytes_write.sum); algorithmic operand + output bytes of "
                     "those launches: 32.5 GB")
 

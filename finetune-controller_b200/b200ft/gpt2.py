@@ -308,7 +308,7 @@ class GPT2LoRAStep(StepHostMixin, OwnAttentionMixin):
         """Consumes d(loss)/d(logits) left in self.logits by forward_loss(); fills self.G."""
         D = self.dims
         s = self.lora.scale
-        self.G.zero_()
+        ops.zero(self.G)
         dx, dx1, dx0 = self.dxs
         ops.gemm(self.logits, self.wteT, self.dln)                      # d hf = dlogits . wte
         ops.layernorm_bwd_dx(self.dln, self.x[D.n_layer], self.lnf_g, *self.stf, dx)

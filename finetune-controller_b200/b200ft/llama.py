@@ -286,7 +286,7 @@ class LlamaLoRAStep(StepHostMixin, OwnAttentionMixin):
     def backward(self) -> None:
         D, s = self.dims, self.lora.scale
         Nq, Nkv, d = self.Nq, self.Nkv, D.d_model
-        self.G.zero_()
+        ops.zero(self.G)
         dx, dx1, dx0 = self.dxs
         ops.gemm(self.logits, self.headT, self.dln)
         ops.rmsnorm_bwd_dx(self.dln, self.x[D.n_layer], self.norm_g, self.rsf, dx)

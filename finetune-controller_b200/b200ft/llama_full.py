@@ -284,7 +284,7 @@ class LlamaFullStep(StepHostMixin, OwnAttentionMixin):
     def backward(self) -> None:
         D, W, dW = self.dims, self.W, self.dW
         L, mc = D.n_layer, self.bwd_ctas
-        self.Gn.zero_()
+        ops.zero(self.Gn)
         dx, dx1, dx0 = self.dxs
         # lm_head: dW = dlogits^T . hf (both MN-major), dhf = dlogits . W_head (B MN-major)
         ops.gemm(self.logits, self.hf, dW["head"], a_mn=True, b_mn=True, max_ctas=mc)
@@ -320,7 +320,7 @@ class LlamaFullStep(StepHostMixin, OwnAttentionMixin):
                 # embedding table: scatter-add of the residual-stream gradient; a tied table already
                 # holds the lm_head gradient and accumulates on top of it
                 if not D.tie_embeddings:
-                    dW["embed"].zero_()
+                    ops.zero(dW["embed"])
                 ops.embed_bwd(self.ids.view(-1), dx, dW["embed"], vocab=D.vocab)
             n_pending = len(self.grad_sync.pending) if self.grad_sync is not None else 0
             if self.grad_sync is not None:

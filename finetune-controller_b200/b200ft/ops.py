@@ -358,6 +358,14 @@ def transpose(inp, out, rows=None, cols=None):
     return out
 
 
+def zero(t):
+    """Stream-ordered zero fill of a contiguous tensor through the C ABI (a DMA memset: no kernel, no torch op)."""
+    _need_cuda(t)
+    assert t.is_contiguous()
+    check(lib().b200ft_zero(_p(t), t.numel() * t.element_size(), _stream()), "zero")
+    return t
+
+
 def cast_f32_to_bf16(inp, out):
     global LAUNCHES
     _need_cuda(inp, out)

@@ -92,6 +92,12 @@ extern "C" int b200ft_transpose_bf16(const void* in, int64_t ld_in, void* out, i
   return 0;
 }
 
+extern "C" int b200ft_zero(void* ptr, size_t bytes, void* stream) {
+  B200FT_CHECK_ARG(ptr || bytes == 0, "zero: null buffer");
+  if (bytes) B200FT_CUDA(cudaMemsetAsync(ptr, 0, bytes, (cudaStream_t)stream));
+  return 0;
+}
+
 extern "C" int b200ft_cast_f32_to_bf16(const float* in, void* out, int64_t n, void* stream) {
   B200FT_CHECK_ARG(in && out && n >= 0, "cast_f32_to_bf16: bad arguments");
   B200FT_CHECK_ARG(((uintptr_t)in | (uintptr_t)out) % 16 == 0, "cast_f32_to_bf16: 16-byte alignment required");

@@ -269,6 +269,10 @@ int b200ft_transpose_bf16(const void* in, int64_t ld_in, void* out, int64_t ld_o
 /* fp32 -> bf16 cast of a flat buffer (parameter upload). */
 int b200ft_cast_f32_to_bf16(const float* in, void* out, int64_t n, void* stream);
 
+/* Stream-ordered zero fill of `bytes` bytes (gradient accumulators that the split-K and atomic kernels add into:
+ * the step's "zero_grad").  A DMA memset, no kernel launch.  No counterpart in the reference (no compute there). */
+int b200ft_zero(void* ptr, size_t bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
