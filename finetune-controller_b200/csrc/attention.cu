@@ -194,11 +194,18 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm, const AttnParams p) {
   tc_fence_after();
   const uint32_t tmem = *tmem_slot_ptr;
 
+  // Persistent launches deal the items (heaviest first) out in a snake: round n hands item n*grid + b to CTA b when n
+  // is even and n*grid + (grid-1-b) when n is odd; with one CTA per item (grid = items) only round 0 exists.
+  auto item_at = [&](uint32_t round) -> int {
+    const int i = (round & 1u) ? (int)(gridDim.x - 1 - blockIdx.x) : (int)blockIdx.x;
+    return (int)(round * gridDim.x) + i;
+  };
+
   if (warp == 0) {
     // ================================ TMA producer ================================
     const bool issuer = elect_one();
     uint32_t kc = 0, n = 0;
-    for (int w = blockIdx.x; w < num_items; w += gridDim.x, ++n) {
+    for (int w = item_at(0); w < num_items; w = item_at(++n)) {
     const FwdItem it = decode_item(p, w);
     const int b = it.b, h = it.h, hk = it.hk;
     if (n > 0) mbar_wait(q_empty, (n - 1) & 1u);   // the previous item's UMMAs are done with the query tiles
@@ -263,7 +270,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm, const AttnParams p) {
       __syncwarp();
     };
     uint32_t kc = 0, cA = 0, cB = 0, n = 0;
-    for (int w = blockIdx.x; w < num_items; w += gridDim.x, ++n) {
+    for (int w = item_at(0); w < num_items; w = item_at(++n)) {
     const FwdItem it = decode_item(p, w);
     const int nA = it.nA, nB = it.nB, n_kv = it.n_kv;
     const bool hasB = it.hasB;
@@ -355,7 +362,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm, const AttnParams p) {
     const uint32_t t_pv = tmem + ((uint32_t)(quarter * 32) << 16) + kColPV + (uint32_t)kDH * g;
     const uint32_t t_p = tmem + ((uint32_t)(quarter * 32) << 16) + kColP + C::kStrideP * g;
     uint32_t cg = 0;                              // tiles this group has processed so far
-    for (int w = blockIdx.x; w < num_items; w += gridDim.x) {
+    uint32_t n = 0;
+    for (int w = item_at(0); w < num_items; w = item_at(++n)) {
     const FwdItem it = decode_item(p, w);
     const int b = it.b, h = it.h;
     const int bh = b * p.n_head + h;

@@ -173,11 +173,18 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
   tc_fence_after();
   const uint32_t tmem = *tmem_slot_ptr;
 
+  // Items are sorted heaviest first and dealt out in a snake: round n hands item n*grid + b to CTA b when n is even and
+  // n*grid + (grid-1-b) when n is odd, so a CTA that drew a heavy item in one round draws a light one in the next.
+  auto item_at = [&](uint32_t round) -> int {
+    const int i = (round & 1u) ? (int)(gridDim.x - 1 - blockIdx.x) : (int)blockIdx.x;
+    return (int)(round * gridDim.x) + i;
+  };
+
   if (warp == 0) {
     // ================================ TMA producer ================================
     const bool issuer = elect_one();
     uint32_t g = 0, n = 0;
-    for (int w = blockIdx.x; w < num_items; w += gridDim.x, ++n) {
+    for (int w = item_at(0); w < num_items; w = item_at(++n)) {
       const Item it = decode_item<MODE>(p, w, G);
       if (n > 0) mbar_wait(f_empty, (n - 1) & 1u);   // the previous item's last dP UMMAs have read the resident pair
       if (issuer) {
@@ -280,7 +287,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
       __syncwarp();
     };
     uint32_t g = 0, n = 0;
-    for (int w = blockIdx.x; w < num_items; w += gridDim.x, ++n) {
+    for (int w = item_at(0); w < num_items; w = item_at(++n)) {
       const Item it = decode_item<MODE>(p, w, G);
       const int N = it.n_iter;
       mbar_wait(f_full, n & 1u);
@@ -366,7 +373,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
     };
     const bool drains = MODE == 2 && part < 2;
     uint32_t g = 0, n = 0;
-    for (int w = blockIdx.x; w < num_items; w += gridDim.x, ++n) {
+    for (int w = item_at(0); w < num_items; w = item_at(++n)) {
       const Item it = decode_item<MODE>(p, w, G);
       // per-row log-sum-exp and D.  Rows past the end of the sequence get lse = +inf: P = dS = 0.  With the kv tile
       // fixed (MODE 0, 2) every pair has its own query rows: the values of pair t+1 are requested while pair t

@@ -14,13 +14,13 @@
 //
 // In both: product A operand = resident tile (K-major), B = streamed tile (K-major); gradient A = bf16 P / dS in
 // TMEM, B = streamed tile read MN-major ([128 rows = reduction index] x [d_head], two 64-column boxes).  No atomics,
-// no fp32 scratch: results are bit-reproducible.  TMEM: S 0..127 | dP 128..255 | acc0 256..383 | acc1 384..511; a
-// thread of slice `part` owns columns 32*part..+31 of S / dP and writes its 32 bf16 results into the first 16 of
-// them, so nobody overwrites scores another thread still has to read; the k-th gradient UMMA (16 reduction
-// indices) reads its A operand at column 32*(k/2) + 8*(k%2).
+// no fp32 scratch: results are bit-reproducible.  TMEM: S 2 x 64 columns at 0 | dP 2 x 64 at 128 | acc0 256..383 |
+// acc1 384..511; a thread of slice `part` owns columns 16*part..+15 of an S / dP buffer and writes its 16 bf16 results
+// into the first 8 of them, so nobody overwrites scores another thread still has to read; the k-th gradient UMMA
+// (16 reduction indices) reads its A operand at column 16*k of the buffer.
 //
 // 640 threads: warp 0 TMA producer, warp 1 UMMA issue, warp 2 TMEM allocation, warps 4-19 softmax / dS (four per
-// TMEM lane quarter, one 32-column slice each).  Shared memory: resident pair 64 KB + two stream stages of 64 KB.
+// TMEM lane quarter, one 16-column slice each).  Shared memory: resident pair 64 KB + two stream stages of 64 KB.
 #include "attn_common.cuh"
 
 namespace {
@@ -37,7 +37,8 @@ constexpr int kOffS = 2 * kTile;              // ring stages of (tile0, tile1)
 constexpr int kOffStat = kOffS + kRing * 2 * kTile;   // MODE 0: [2 buffers][lse | D][128] fp32
 constexpr int kOffBar = kOffStat + 2 * 2 * kB * 4;
 constexpr int kSmemBytes = kOffBar + 256;     // 194.25 KB
-constexpr uint32_t kColS = 0, kColDP = 128, kColAcc0 = 256, kColAcc1 = 384;
+constexpr uint32_t kSub = 64;                 // streamed rows per sub-pair: S / dP are [128 x 64] and double-buffered
+constexpr uint32_t kColS = 0, kColDP = 128, kColAcc0 = 256, kColAcc1 = 384;   // S, dP: two buffers of 64 columns each
 
 struct Params {
   int batch, seq, n_head, n_kv_head;
@@ -74,11 +75,14 @@ static __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
 }
 
 // Persistent: one CTA per SM walks work items.  Barrier parities run on two counters shared by all roles:
-// `g` = tile pairs processed so far by this CTA (stream ring stage g % 2, statistics buffer g & 1, hand-offs),
-// `n` = items processed so far (resident tiles, accumulators).
-// Tensor-core order per pair: S(g), dP(g) | <softmax warps: P, dS into TMEM> | gradients(g), S(g+1), dP(g+1) | ...
-// S(g+1) overwrites the columns P(g) lives in; UMMAs execute in issue order, so it lands after the gradient UMMAs
-// have read P(g) and dS(g).
+// `g` = SUB-PAIRS processed so far by this CTA — a sub-pair is one half (64 rows) of a streamed tile pair against the
+// resident pair; stream ring stage (g / 2) % 2, S / dP buffer g & 1 — and `n` = items processed so far (resident
+// tiles, accumulators).  Working on 64 streamed rows at a time makes S and dP [128 x 64]: two buffers of each fit the
+// 256 TMEM columns the accumulators leave, so the tensor core computes the products of sub-pair g+2 and the gradients
+// of sub-pair g while the softmax warps exponentiate sub-pair g+1 (with full 128-row S / dP tiles, single-buffered,
+// the two alternated: tensor pipe 25-32 % active).
+// Tensor-core order: S,dP(0) S,dP(1) | grads(0) S,dP(2) | grads(1) S,dP(3) | ...  The products of g+2 overwrite the
+// columns P(g), dS(g) live in; UMMAs execute in issue order, so they land after the gradient UMMAs have read them.
 template <int MODE>
 __global__ void __launch_bounds__(kThreads, 1)
 attn_bwd_d128_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constant__ CUtensorMap tm_do,
@@ -94,9 +98,12 @@ attn_bwd_d128_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_co
   const uint32_t f_full = bars, f_empty = bars + 8u;
   auto st_full = [&](uint32_t s) { return bars + 8u * (2 + s); };
   auto st_empty = [&](uint32_t s) { return bars + 8u * (4 + s); };
-  const uint32_t s_full = bars + 8u * 6, dp_full = bars + 8u * 7, pds_full = bars + 8u * 8;
-  const uint32_t acc_full = bars + 8u * 9, acc_free = bars + 8u * 10;
-  const uint32_t tmem_slot = bars + 8u * 11;
+  auto sdp_full = [&](uint32_t bf) { return bars + 8u * (6 + bf); };
+  // one hand-off barrier per S / dP buffer: a softmax warp may run a sub-pair ahead of the slowest one (the products are
+  // issued two sub-pairs ahead), and on a single barrier its arrival for g+1 would be counted towards phase g
+  auto pds_full = [&](uint32_t bf) { return bars + 8u * (8 + bf); };
+  const uint32_t acc_full = bars + 8u * 10, acc_free = bars + 8u * 11;
+  const uint32_t tmem_slot = bars + 8u * 12;
   volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - raw));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -106,7 +113,7 @@ attn_bwd_d128_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_co
   if (warp == 1 && lane == 0) {
     mbar_init(f_full, 1); mbar_init(f_empty, 1);
     for (uint32_t s = 0; s < kRing; ++s) { mbar_init(st_full(s), 1); mbar_init(st_empty(s), 1); }
-    mbar_init(s_full, 1); mbar_init(dp_full, 1); mbar_init(pds_full, 16);
+    mbar_init(sdp_full(0), 1); mbar_init(sdp_full(1), 1); mbar_init(pds_full(0), 16); mbar_init(pds_full(1), 16);
     mbar_init(acc_full, 1); mbar_init(acc_free, 16);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -119,6 +126,14 @@ attn_bwd_d128_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_co
   tc_fence_after();
   const uint32_t tmem = *tmem_slot_ptr;
 
+  // Items are sorted heaviest first and dealt out in a snake: round n hands item n*grid + b to CTA b when n is even and
+  // n*grid + (grid-1-b) when n is odd, so a CTA that drew a heavy item in one round draws a light one in the next.
+  // (The plain round-robin b, b+grid, ... gave the first CTAs 45 tile pairs and the last 14 at 1 x 4096 x 32/8: 63 %.)
+  auto item_at = [&](uint32_t round) -> int {
+    const int i = (round & 1u) ? (int)(gridDim.x - 1 - blockIdx.x) : (int)blockIdx.x;
+    return (int)(round * gridDim.x) + i;
+  };
+
   // a [128 x 128] tile = two boxes of 64 columns
   auto load_tile = [&](uint32_t dst, const CUtensorMap* map, int col, int row, int b, uint32_t bar) {
     tma_load_3d(dst, map, col, row, b, bar);
@@ -129,7 +144,7 @@ attn_bwd_d128_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_co
     // ================================ TMA producer ================================
     const bool issuer = elect_one();
     uint32_t g = 0, n = 0;
-    for (int w = blockIdx.x; w < num_items; w += gridDim.x, ++n) {
+    for (int w = item_at(0); w < num_items; w = item_at(++n)) {
       const Item it = decode_item<MODE>(p, w, G);
       if (n > 0) mbar_wait(f_empty, (n - 1) & 1u);   // the previous item's last dP UMMAs have read the resident pair
       if (issuer) {
@@ -162,80 +177,96 @@ attn_bwd_d128_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_co
     }
   } else if (warp == 1) {
     // ================================ UMMA issuer ================================
+    // Sub-pair g = 64 streamed rows (half h = g & 1 of a streamed tile pair); its products go to buffer g & 1.
     const bool issuer = elect_one();
-    const uint32_t id_kk = idesc(kB, 0, 0);    // S, dP: 128 x 128 x 128, both operands K-major (d_head contiguous)
-    const uint32_t id_g = idesc(kDH, 0, 1);    // gradients: 128 x 128 (d_head) x 128, A from TMEM, B MN-major
-    // K-major operand, k-th step of 16 d_head elements: box k/4, 32 bytes per step inside the 128-byte swizzle row
-    auto kdesc = [&](uint32_t tile, int k) { return sdesc(tile + (uint32_t)(k >> 2) * kBox + 32u * (uint32_t)(k & 3), 16, 1024); };
-    // MN-major B operand, k-th step of 16 rows (reduction index): 2 KB per step, the second 64 columns one box on
-    auto mdesc = [&](uint32_t tile, int k) { return sdesc(tile + 2048u * (uint32_t)k, kBox, 1024); };
+    const uint32_t id_kk = idesc(kSub, 0, 0);  // S, dP: 128 x 64 x 128, both operands K-major (d_head contiguous)
+    const uint32_t id_g = idesc(kDH, 0, 1);    // gradients: 128 x 128 (d_head) x 64, A from TMEM, B MN-major
+    // Shared-memory descriptors are built ONCE per tile; a UMMA's descriptor is that base plus a compile-time offset in
+    // the 16-byte units of its address field (the tiles lie below 256 KB, so the add never carries out of the field).
+    // The single issuing thread is on the critical path of every sub-pair: 24 UMMAs with two freshly assembled
+    // descriptors each measured ~3100 cycles per sub-pair with the tensor pipe 32 % active.
+    // K-major operand, k-th step of 16 d_head elements: box k/4, 32 bytes per step inside the 128-byte swizzle row;
+    // MN-major B operand, k-th step of 16 rows (reduction index): 2 KB per step, the second 64 columns one box on.
+    const uint64_t kF0 = sdesc(sF0, 16, 1024), kF1 = sdesc(sF1, 16, 1024);
+    uint64_t kS0[kRing], kS1[kRing], mS0[kRing], mS1[kRing];
+#pragma unroll
+    for (uint32_t st = 0; st < kRing; ++st) {
+      kS0[st] = sdesc(sS0(st), 16, 1024); kS1[st] = sdesc(sS1(st), 16, 1024);
+      mS0[st] = sdesc(sS0(st), kBox, 1024); mS1[st] = sdesc(sS1(st), kBox, 1024);
+    }
+    auto koff = [](int k) { return (uint64_t)((((uint32_t)(k >> 2) * kBox) + 32u * (uint32_t)(k & 3)) >> 4); };
+    auto moff = [](int k) { return (uint64_t)((2048u * (uint32_t)k) >> 4); };
     auto issue_products = [&](uint32_t gg, bool last_of_item) {
-      const uint32_t st = gg % kRing;
-      mbar_wait(st_full(st), (gg / kRing) & 1u);
+      const uint32_t pr = gg >> 1, h = gg & 1u, st = pr % kRing, bf = gg & 1u;
+      mbar_wait(st_full(st), (pr / kRing) & 1u);   // (passes at once for the second half of a tile pair)
       tc_fence_after();
+      // Buffer bf was last used by sub-pair gg-2: its softmax is over (pds_full was waited for before its gradient
+      // UMMAs were issued) and those UMMAs, which read P / dS from it, precede these in issue order.
+      const uint64_t rows = (uint64_t)(h * ((kSub * 128u) >> 4));   // 64 rows further into each box of the streamed tiles
+      const uint64_t b0 = (st ? kS0[1] : kS0[0]) + rows, b1 = (st ? kS1[1] : kS1[0]) + rows;
       if (issuer) {
 #pragma unroll
-        for (int k = 0; k < kDH / 16; ++k) umma(tmem + kColS, kdesc(sF0, k), kdesc(sS0(st), k), id_kk, k > 0);
-        umma_commit(s_full);
+        for (int k = 0; k < kDH / 16; ++k) umma(tmem + kColS + kSub * bf, kF0 + koff(k), b0 + koff(k), id_kk, k > 0);
 #pragma unroll
-        for (int k = 0; k < kDH / 16; ++k) umma(tmem + kColDP, kdesc(sF1, k), kdesc(sS1(st), k), id_kk, k > 0);
-        umma_commit(dp_full);
+        for (int k = 0; k < kDH / 16; ++k) umma(tmem + kColDP + kSub * bf, kF1 + koff(k), b1 + koff(k), id_kk, k > 0);
+        umma_commit(sdp_full(bf));
         if (last_of_item) umma_commit(f_empty);   // nothing of this item reads the resident pair any more
       }
       __syncwarp();
     };
     auto issue_grads = [&](uint32_t gg, bool first) {
-      const uint32_t st = gg % kRing;
+      const uint32_t pr = gg >> 1, h = gg & 1u, st = pr % kRing, bf = gg & 1u;
+      const uint64_t half = (uint64_t)h * moff(4);
+      const uint64_t m0 = (st ? mS0[1] : mS0[0]) + half, m1 = (st ? mS1[1] : mS1[0]) + half;
       if (issuer) {
+        // a thread of slice `part` packed its 16 columns into the first 8 of them: reduction step k reads column 16*k
         if (MODE == 0) {
 #pragma unroll
-          for (int k = 0; k < kB / 16; ++k)   // dV += P^T dO: 16 queries per step
-            umma_ts(tmem + kColAcc0, tmem + kColS + 32u * (uint32_t)(k >> 1) + 8u * (uint32_t)(k & 1), mdesc(sS1(st), k),
-                    id_g, !(first && k == 0));
+          for (int k = 0; k < (int)kSub / 16; ++k)   // dV += P^T dO: 16 queries per step
+            umma_ts(tmem + kColAcc0, tmem + kColS + kSub * bf + 16u * (uint32_t)k, m1 + moff(k), id_g, !(first && k == 0));
 #pragma unroll
-          for (int k = 0; k < kB / 16; ++k)   // dK += dS^T Q
-            umma_ts(tmem + kColAcc1, tmem + kColDP + 32u * (uint32_t)(k >> 1) + 8u * (uint32_t)(k & 1), mdesc(sS0(st), k),
-                    id_g, !(first && k == 0));
+          for (int k = 0; k < (int)kSub / 16; ++k)   // dK += dS^T Q
+            umma_ts(tmem + kColAcc1, tmem + kColDP + kSub * bf + 16u * (uint32_t)k, m0 + moff(k), id_g, !(first && k == 0));
         } else {
 #pragma unroll
-          for (int k = 0; k < kB / 16; ++k)   // dQ += dS K: 16 keys per step
-            umma_ts(tmem + kColAcc0, tmem + kColDP + 32u * (uint32_t)(k >> 1) + 8u * (uint32_t)(k & 1), mdesc(sS0(st), k),
-                    id_g, !(first && k == 0));
+          for (int k = 0; k < (int)kSub / 16; ++k)   // dQ += dS K: 16 keys per step
+            umma_ts(tmem + kColAcc0, tmem + kColDP + kSub * bf + 16u * (uint32_t)k, m0 + moff(k), id_g, !(first && k == 0));
         }
-        umma_commit(st_empty(st));   // the streamed pair's slot may be refilled
+        if (h == 1u) umma_commit(st_empty(st));   // both halves consumed: the streamed pair's slot may be refilled
       }
       __syncwarp();
     };
     uint32_t g = 0, n = 0;
-    for (int w = blockIdx.x; w < num_items; w += gridDim.x, ++n) {
+    for (int w = item_at(0); w < num_items; w = item_at(++n)) {
       const Item it = decode_item<MODE>(p, w, G);
-      const int N = it.n_iter;
+      const int N2 = 2 * it.n_iter;           // sub-pairs of this item (>= 2)
       mbar_wait(f_full, n & 1u);
-      issue_products(g, N == 1);
-      for (int t = 0; t < N; ++t, ++g) {
-        mbar_wait(pds_full, g & 1u);        // softmax warps are done with pair g: P, dS are in TMEM
+      issue_products(g, false);
+      issue_products(g + 1, N2 == 2);
+      for (int t2 = 0; t2 < N2; ++t2, ++g) {
+        mbar_wait(pds_full(g & 1u), (g >> 1) & 1u);   // softmax warps are done with sub-pair g: P, dS are in TMEM
         tc_fence_after();
-        if (t == 0 && n > 0) { mbar_wait(acc_free, (n - 1) & 1u); tc_fence_after(); }  // previous accumulators read out
-        issue_grads(g, t == 0);
-        if (t + 1 < N) issue_products(g + 1, t + 2 == N);
+        if (t2 == 0 && n > 0) { mbar_wait(acc_free, (n - 1) & 1u); tc_fence_after(); }  // previous accumulators read out
+        issue_grads(g, t2 == 0);
+        // the products of sub-pair g+2 replace P(g), dS(g) — in issue order after the UMMAs that read them — and run,
+        // with the gradients of g, while the softmax warps work on sub-pair g+1
+        if (t2 + 2 < N2) issue_products(g + 2, t2 + 3 == N2);
       }
       if (issuer) umma_commit(acc_full);
       __syncwarp();
     }
   } else if (warp >= 4) {
     // ================================ softmax / dS ================================
-    // Four warps per TMEM lane quarter; a thread owns one lane L (a key in MODE 0, a query in MODE 1) and the 32
-    // columns 32*part .. +31 (queries in MODE 0, keys in MODE 1).
+    // Four warps per TMEM lane quarter; a thread owns one lane L (a key in MODE 0, a query in MODE 1) and, in every
+    // sub-pair, the 16 columns 16*part .. +15 of the [128 x 64] buffer (queries in MODE 0, keys in MODE 1).
     const int quarter = warp & 3;
     const int part = (warp - 4) >> 2;
     const int L = quarter * 32 + lane;
     const int sm_tid = (warp - 4) * 32 + lane;             // 0..511 among the softmax warps
     const uint32_t t_lane = tmem + ((uint32_t)(quarter * 32) << 16);
-    const uint32_t t_s = t_lane + kColS + 32u * (uint32_t)part;
-    const uint32_t t_dp = t_lane + kColDP + 32u * (uint32_t)part;
     const f32x2_t sc2 = pk2(p.scale_log2, p.scale_log2);
     uint32_t g = 0, n = 0;
-    for (int w = blockIdx.x; w < num_items; w += gridDim.x, ++n) {
+    for (int w = item_at(0); w < num_items; w = item_at(++n)) {
       const Item it = decode_item<MODE>(p, w, G);
       // log-sum-exp and D of a query row; rows past the end of the sequence get lse = +inf: P = dS = 0
       auto row_stats = [&](int hq, int qt_, int r, float& lse_o, float& dl_o) {
@@ -246,80 +277,88 @@ attn_bwd_d128_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_co
           lse_o = __ldg(p.lse2 + idx); dl_o = __ldg(p.delta + idx);
         }
       };
-      // MODE 0: the statistics belong to the COLUMNS and change with every pair.  Threads 0..127 of the softmax
-      // warps fetch the next pair's values one pair ahead (global-memory latency off the critical path) and publish
-      // them in shared memory, double-buffered, at the start of the pair.
+      // MODE 0: the statistics belong to the COLUMNS and change with every streamed tile pair.  Threads 0..127 of the
+      // softmax warps fetch the next pair's values one pair ahead (global-memory latency off the critical path) and
+      // publish them in shared memory, double-buffered, when the pair starts.
       float lse = INFINITY, dl = 0.f, lse_next = INFINITY, dl_next = 0.f;
       if (MODE == 1) row_stats(it.hx, it.fixed_tile, L, lse, dl);
       else if (sm_tid < kB) row_stats(it.hk * G, it.fixed_tile, sm_tid, lse_next, dl_next);
-      for (int t = 0; t < it.n_iter; ++t, ++g) {
+      for (int t2 = 0; t2 < 2 * it.n_iter; ++t2, ++g) {
+        const int t = t2 >> 1, h = t2 & 1;               // streamed tile pair, half of it
+        const uint32_t pr = g >> 1, bf = g & 1u;
         int qt, kt;
         if (MODE == 0) { qt = it.fixed_tile + t % it.per_head; kt = it.fixed_tile; }
         else           { qt = it.fixed_tile; kt = t; }
         const bool diag = qt == kt;
-        const float* st_lse = stat + (g & 1u) * 2 * kB;
+        const float* st_lse = stat + (pr & 1u) * 2 * kB + 64 * h;
         const float* st_dl = st_lse + kB;
-        if (MODE == 0) {
+        if (MODE == 0 && h == 0) {
           if (sm_tid < kB) {
-            stat[(g & 1u) * 2 * kB + sm_tid] = lse_next;
-            stat[(g & 1u) * 2 * kB + kB + sm_tid] = dl_next;
+            stat[(pr & 1u) * 2 * kB + sm_tid] = lse_next;
+            stat[(pr & 1u) * 2 * kB + kB + sm_tid] = dl_next;
             if (t + 1 < it.n_iter)
               row_stats(it.hk * G + (t + 1) / it.per_head, it.fixed_tile + (t + 1) % it.per_head, sm_tid, lse_next, dl_next);
           }
           named_bar_sync(1, 512);   // the 16 softmax warps: this pair's statistics are visible
         }
-        // ---- phase A: P = exp2(S*c - lse) for this thread's 32 columns (kept in registers for phase B) ----
-        f32x2_t P2[16];
-        mbar_wait(s_full, g & 1u);
-        tc_fence_after();
-        {
-          uint32_t rs[32];
-          tmem_ld32(t_s, rs);
-          tmem_wait_ld();
+        const uint32_t t_s = t_lane + kColS + kSub * bf + 16u * (uint32_t)part;
+        const uint32_t t_dp = t_lane + kColDP + kSub * bf + 16u * (uint32_t)part;
+        const int c0 = 64 * h + 16 * part;               // first of this thread's columns, as a row of the streamed tile
+        // ---- phase A: P = exp2(S*c - lse) for this thread's 16 columns (kept in registers for phase B) ----
+        f32x2_t P2[8];
+        float cl[16], cd[16];                            // MODE 0: this thread's 16 column statistics (four 16-byte loads each)
+        if (MODE == 0) {
 #pragma unroll
-          for (int i = 0; i < 32; i += 2) {
-            const int c = 32 * part + i;
-            f32x2_t nl2;
-            if (MODE == 0) nl2 = pk2(-st_lse[c], -st_lse[c + 1]); else nl2 = pk2(-lse, -lse);
-            float e0, e1;
-            upk2(fma2(pk2(__uint_as_float(rs[i]), __uint_as_float(rs[i + 1])), sc2, nl2), e0, e1);
-            float p0 = ex2(e0), p1 = ex2(e1);   // lse = +inf (row past the sequence): exp2(-inf) = 0
-            if (diag) {                        // warp-uniform; causal: key index > query index contributes nothing
-              const bool m0 = MODE == 0 ? (L > c) : (c > L);
-              const bool m1 = MODE == 0 ? (L > c + 1) : (c + 1 > L);
-              if (m0) p0 = 0.f;
-              if (m1) p1 = 0.f;
-            }
-            P2[i >> 1] = pk2(p0, p1);
+          for (int v = 0; v < 4; ++v) {
+            const float4 a = *reinterpret_cast<const float4*>(st_lse + 16 * part + 4 * v);
+            const float4 d = *reinterpret_cast<const float4*>(st_dl + 16 * part + 4 * v);
+            cl[4 * v] = a.x; cl[4 * v + 1] = a.y; cl[4 * v + 2] = a.z; cl[4 * v + 3] = a.w;
+            cd[4 * v] = d.x; cd[4 * v + 1] = d.y; cd[4 * v + 2] = d.z; cd[4 * v + 3] = d.w;
           }
         }
-        if (MODE == 0) {   // P^T as bf16 over this thread's own first 16 score columns: A operand of dV += P^T dO
-          uint32_t wp[16];
+        mbar_wait(sdp_full(bf), (g >> 1) & 1u);
+        tc_fence_after();
+        uint32_t rs[16], rd[16];
+        tmem_ld16(t_s, rs);
+        tmem_ld16(t_dp, rd);
+        tmem_wait_ld();
 #pragma unroll
-          for (int i = 0; i < 16; ++i) wp[i] = f32x2_to_bf16x2(P2[i]);
-          tmem_st16(t_s, wp);
+        for (int i = 0; i < 16; i += 2) {
+          const int c = c0 + i;
+          f32x2_t nl2;
+          if (MODE == 0) nl2 = pk2(-cl[i], -cl[i + 1]); else nl2 = pk2(-lse, -lse);
+          float e0, e1;
+          upk2(fma2(pk2(__uint_as_float(rs[i]), __uint_as_float(rs[i + 1])), sc2, nl2), e0, e1);
+          float p0 = ex2(e0), p1 = ex2(e1);   // lse = +inf (row past the sequence): exp2(-inf) = 0
+          if (diag) {                        // warp-uniform; causal: key index > query index contributes nothing
+            const bool m0 = MODE == 0 ? (L > c) : (c > L);
+            const bool m1 = MODE == 0 ? (L > c + 1) : (c + 1 > L);
+            if (m0) p0 = 0.f;
+            if (m1) p1 = 0.f;
+          }
+          P2[i >> 1] = pk2(p0, p1);
+        }
+        if (MODE == 0) {   // P^T as bf16 over this thread's own first 8 score columns: A operand of dV += P^T dO
+          uint32_t wp[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) wp[i] = f32x2_to_bf16x2(P2[i]);
+          tmem_st8(t_s, wp);
         }
         // ---- phase B: dS' = P * (dP - D) (the softmax scale multiplies the dK / dQ accumulators once, at the end) ----
-        mbar_wait(dp_full, g & 1u);
-        tc_fence_after();
         {
-          uint32_t rd[32];
-          tmem_ld32(t_dp, rd);
-          tmem_wait_ld();
-          uint32_t wd[16];
+          uint32_t wd[8];
 #pragma unroll
-          for (int i = 0; i < 16; ++i) {
-            const int c = 32 * part + 2 * i;
+          for (int i = 0; i < 8; ++i) {
             f32x2_t dl2;
-            if (MODE == 0) dl2 = pk2(st_dl[c], st_dl[c + 1]); else dl2 = pk2(dl, dl);
+            if (MODE == 0) dl2 = pk2(cd[2 * i], cd[2 * i + 1]); else dl2 = pk2(dl, dl);
             wd[i] = f32x2_to_bf16x2(mul2(P2[i], sub2(pk2(__uint_as_float(rd[2 * i]), __uint_as_float(rd[2 * i + 1])), dl2)));
           }
-          tmem_st16(t_dp, wd);
+          tmem_st8(t_dp, wd);
         }
         tmem_wait_st();
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(pds_full);
+        if (lane == 0) mbar_arrive(pds_full(bf));
       }
       // ---- accumulators -> (x softmax scale for dK, dQ) -> bf16 -> the gradient buffer ----
       mbar_wait(acc_full, n & 1u);
