@@ -336,8 +336,10 @@ def run_ours(args) -> None:
     if rank == 0:
         sampler.start()
     launches0 = ops.LAUNCHES
+    bytes0 = sync.bytes_reduced if sync is not None else 0
     ms = timed(step_resident, args.steps)
     launches = ops.LAUNCHES - launches0
+    exchanged = (sync.bytes_reduced - bytes0) // args.steps if sync is not None else 0
     ms_e2e = timed(step_host, args.steps)
     clocks = sampler.stop() if rank == 0 else None
     tokens = world * BATCH * SEQ * args.steps
@@ -350,6 +352,20 @@ def run_ours(args) -> None:
     torch.cuda.synchronize()
     prof, ops.PROFILE = ops.PROFILE, None
     pk = peaks()
+    # N > 1: what the gradient exchange costs the step — the same timed loop with the exchange switched off (the ranks
+    # then drift apart numerically, so this runs last, after every number that is reported as a result)
+    exchange = None
+    if world > 1 and sync is not None:
+        eng.grad_sync = None
+        step_resident(0)
+        ms_local = timed(step_resident, args.steps)
+        eng.grad_sync = sync
+        exchange = {"ms_per_step_without_exchange": ms_local / args.steps,
+                    "exposed_exchange_ms": (ms - ms_local) / args.steps,
+                    "all_reduces_per_step": len(sync.buckets) if not full else None,
+                    "gradient_bytes_per_step": exchanged,
+                    "note": "difference of two timed loops of the same steps (max over ranks each); includes the skew "
+                            "between ranks that the all-reduce makes visible"}
     classes = {}
     for name, evs in prof.items():
         t_ms = sum(e[0].elapsed_time(e[1]) for e in evs)
@@ -435,6 +451,8 @@ def run_ours(args) -> None:
     }
     if parity is not None:
         line["dp_parity"] = parity
+    if exchange is not None:
+        line["exchange"] = exchange
     if extras is not None:
         line["configs_extra"] = extras
     print(json.dumps(line), flush=True)

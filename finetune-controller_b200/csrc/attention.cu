@@ -244,12 +244,18 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm, const AttnParams p) {
     const bool issuer = elect_one();
     const uint32_t id_s = idesc(kBK, 0, 0);   // S: N = 128 keys, K-major B (K_j rows = keys, d_head contiguous)
     const uint32_t id_pv = idesc(kDH, 0, 1);  // PV: N = d_head, MN-major B (V_j rows = keys = reduction index)
+    // Shared-memory descriptors are built once per tile; a UMMA's descriptor is that base plus a compile-time offset in
+    // the 16-byte units of its address field (all tiles lie below 256 KB: the add never carries out of the field) —
+    // the single issuing thread sits on the critical path of every kv tile.
+    const uint64_t dQ[2] = {sdesc(sQ, 16, 1024), sdesc(sQ + kQBytes, 16, 1024)};
+    const uint64_t dK[2] = {sdesc(sK, 16, 1024), sdesc(sK + kKVBytes, 16, 1024)};
+    const uint64_t dV[2] = {sdesc(sV, kBoxBytes, 1024), sdesc(sV + kKVBytes, kBoxBytes, 1024)};
+    auto koff = [](int k) { return (uint64_t)((((uint32_t)(k >> 2) * kBoxBytes) + 32u * (uint32_t)(k & 3)) >> 4); };
     auto issue_s = [&](int g, int st) {    // S_g = Q_g K^T
+      const uint64_t a = g ? dQ[1] : dQ[0], b = st ? dK[1] : dK[0];
       if (issuer) {
 #pragma unroll
-        for (int k = 0; k < kDH / 16; ++k)
-          umma(tmem + kColS + 128u * g, sdesc(sQ + g * kQBytes + (k >> 2) * kBoxBytes + 32 * (k & 3), 16, 1024),
-               sdesc(sK + st * kKVBytes + (k >> 2) * kBoxBytes + 32 * (k & 3), 16, 1024), id_s, k > 0);
+        for (int k = 0; k < kDH / 16; ++k) umma(tmem + kColS + 128u * g, a + koff(k), b + koff(k), id_s, k > 0);
         umma_commit(s_full(g));
       }
       __syncwarp();
@@ -263,7 +269,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm, const AttnParams p) {
 #pragma unroll
         for (int k = 0; k < kBK / 16; ++k)
           umma_ts(tmem + kColPV + (uint32_t)kDH * g, tmem + kColP + C::kStrideP * g + 8u * k,
-                  sdesc(sV + st * kKVBytes + 2048 * k, kBoxBytes, 1024), id_pv, !(first && k == 0));
+                  (st ? dV[1] : dV[0]) + (uint64_t)(128 * k), id_pv, !(first && k == 0));
 #endif
         umma_commit(pv_full(g));
       }
