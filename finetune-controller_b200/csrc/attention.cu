@@ -28,7 +28,7 @@ namespace {
 using namespace b200ft_attn;
 
 constexpr int kBQ = 128, kBK = 128;
-constexpr int kThreads = 384;
+constexpr int kThreads = 640;                  // warps 0-2 TMA / UMMA / TMEM, 4-19 softmax (two threads per query row)
 constexpr int kStages = 2;
 constexpr int kBoxBytes = 128 * 64 * 2;         // one TMA box: 128 rows x 64 columns, 128B-swizzled = 16 KB
 constexpr int kTmemCols = 512;
@@ -42,14 +42,20 @@ template <int DH> struct Cfg {
   static constexpr int kQBytes = kBQ * DH * 2;          // 16 / 32 KB per query tile
   static constexpr int kKVBytes = kBK * DH * 2;
   static constexpr int kTiles = 2 * kQBytes + 2 * kStages * kKVBytes;   // 96 / 192 KB
-  static constexpr int kSmemBytes = kTiles + 256;       // + barriers; no alignment slack (the kernel checks the base)
+  static constexpr int kOffXch = kTiles + 256;          // after the barriers: row statistics exchanged between the two
+                                                        // threads of a query row, [slot][group][half][128] fp32
+  static constexpr int kSmemBytes = kOffXch + 2 * 2 * 2 * 128 * 4;   // no alignment slack (the kernel checks the base)
   static constexpr bool kAliasP = DH == 128;
   static constexpr uint32_t kColS = 0, kColPV = 256;
   static constexpr uint32_t kColP = kAliasP ? 0u : 384u;
   static constexpr uint32_t kStrideP = kAliasP ? 128u : 64u;   // column distance between P_A and P_B
+  // P holds 128 keys as 64 packed columns.  In its own region they are contiguous (keys 64h.. of half h at column 32h).
+  // Written over S, half h of a row (the thread that owns score columns 64h .. 64h+63) keeps its 32 packed columns
+  // inside its own score columns, at 64h, so that no thread overwrites scores its partner has yet to read.
+  static constexpr uint32_t kHalfP = kAliasP ? 64u : 32u;      // column distance between the two halves of a P row
 };
 #ifndef B200FT_ATTN_SWEEP_LD
-#define B200FT_ATTN_SWEEP_LD 64
+#define B200FT_ATTN_SWEEP_LD 32
 #endif
 constexpr int kSweepLd = B200FT_ATTN_SWEEP_LD;  // 32, 64 or 128
 constexpr float kRescaleThreshold = 8.0f;       // log2 units: p stays below 2^8
@@ -65,11 +71,11 @@ struct AttnParams {
 
 
 
-// One sweep over a 128-key score tile of this thread's query row: p = exp2(s*scale - m_ref) -> bf16 P in
+// One sweep over this thread's NC score columns (t_s, t_p and kbase already point at them) of its query row: p = exp2(s*scale - m_ref) -> bf16 P in
 // TMEM, row sum and raw row max returned.  DIAG tiles mask keys beyond the query position; the other
 // tiles carry no masking code at all.  Before the first store into P the previous tile's P V UMMA must
 // have finished reading it (pv_bar / pv_parity; skipped when wait_pv is false).
-template <bool DIAG>
+template <bool DIAG, int NC>
 __device__ __forceinline__ void softmax_sweep(uint32_t t_s, uint32_t t_p, float scale_log2, float m_ref, int kbase,
                                               int qrow, bool wait_pv, uint32_t pv_bar, uint32_t pv_parity,
                                               float& sum_out, float& max_out) {
@@ -82,7 +88,7 @@ __device__ __forceinline__ void softmax_sweep(uint32_t t_s, uint32_t t_p, float 
   // kSweepLd score columns are requested per TMEM round trip (one tcgen05.wait::ld each): with one softmax warp
   // per query group and scheduler, every round trip is exposed latency
 #pragma unroll
-  for (int cc = 0; cc < kBK / kSweepLd; ++cc) {
+  for (int cc = 0; cc < NC / kSweepLd; ++cc) {
     uint32_t rr[kSweepLd];
 #pragma unroll
     for (int q = 0; q < kSweepLd / 32; ++q) tmem_ld32(t_s + kSweepLd * cc + 32 * q, rr + 32 * q);
@@ -181,7 +187,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm, const AttnParams p) {
       mbar_init(k_full(s), 1); mbar_init(k_empty(s), 1); mbar_init(v_full(s), 1); mbar_init(v_empty(s), 1);
     }
     for (int g = 0; g < 2; ++g) {
-      mbar_init(s_full(g), 1); mbar_init(s_free(g), 4); mbar_init(p_full(g), 4); mbar_init(pv_full(g), 1);
+      mbar_init(s_full(g), 1); mbar_init(s_free(g), 8); mbar_init(p_full(g), 8); mbar_init(pv_full(g), 1);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -268,7 +274,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm, const AttnParams p) {
 #ifndef B200FT_EXP_NO_PV   // bottleneck experiment (tools/attn_exp.py): skip the P V UMMAs, wrong numbers
 #pragma unroll
         for (int k = 0; k < kBK / 16; ++k)
-          umma_ts(tmem + kColPV + (uint32_t)kDH * g, tmem + kColP + C::kStrideP * g + 8u * k,
+          umma_ts(tmem + kColPV + (uint32_t)kDH * g,
+                  tmem + kColP + C::kStrideP * g + C::kHalfP * (uint32_t)(k >> 2) + 8u * (uint32_t)(k & 3),
                   (st ? dV[1] : dV[0]) + (uint64_t)(128 * k), id_pv, !(first && k == 0));
 #endif
         umma_commit(pv_full(g));
@@ -360,13 +367,34 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm, const AttnParams p) {
     kc += (uint32_t)n_kv; cA += (uint32_t)nA; cB += (uint32_t)nB;
     }  // items
   } else if (warp >= 4) {
-    // ================================ softmax, one thread per query row ================================
-    const int g = (warp - 4) >> 2;                // 0 = tile A, 1 = tile B
+    // ================================ softmax, TWO threads per query row ================================
+    // 16 warps: group g (query tile A / B) x half (score columns 64*half .. +63 of the row) x TMEM lane quarter.  Four
+    // softmax warps per scheduler hide each other's tcgen05.ld / MUFU / tcgen05.st latencies (with one thread per
+    // row — two warps per scheduler — a kv tile took ~2500 cycles against 1024 of MUFU work).  The two threads of a row
+    // keep separate partial row sums (added once per item) and exchange their half-row maxima through shared memory,
+    // double-buffered, with one 64-thread named barrier per exchange, so both work against the same reference.
+    const int idx = warp - 4;
+    const int g = (idx >> 2) & 1;                 // 0 = tile A, 1 = tile B
+    const int half = idx >> 3;                    // which 64 score columns of the row
     const int quarter = warp & 3;                 // TMEM lanes this warp may touch
     const int row = quarter * 32 + lane;          // row within the query tile
-    const uint32_t t_s = tmem + ((uint32_t)(quarter * 32) << 16) + kColS + 128u * g;
-    const uint32_t t_pv = tmem + ((uint32_t)(quarter * 32) << 16) + kColPV + (uint32_t)kDH * g;
-    const uint32_t t_p = tmem + ((uint32_t)(quarter * 32) << 16) + kColP + C::kStrideP * g;
+    const uint32_t t_lane = tmem + ((uint32_t)(quarter * 32) << 16);
+    const uint32_t t_s = t_lane + kColS + 128u * g + 64u * half;                        // my 64 score columns
+    const uint32_t t_p = t_lane + kColP + C::kStrideP * g + C::kHalfP * half;           // my 32 packed P columns
+    const uint32_t t_pv = t_lane + kColPV + (uint32_t)kDH * g + (uint32_t)(kDH / 2) * half;   // my half of the O columns
+    float* xch = reinterpret_cast<float*>(smem_raw + C::kOffXch);
+    const int bar_id = 1 + g * 4 + quarter;       // the two warps that share these 32 rows
+    uint32_t xn = 0;                              // exchanges done (slot = xn & 1)
+    // value of the other half of my row for v (max or sum): write mine, meet the partner warp, read theirs.  Slot
+    // xn & 1 is rewritten two exchanges later, after a barrier the partner reaches only past its read of this one.
+    auto exchange = [&](float v) -> float {
+      float* slot = xch + (xn & 1u) * 512 + g * 256;
+      slot[half * 128 + row] = v;
+      asm volatile("bar.sync %0, 64;" ::"r"(bar_id) : "memory");
+      const float o = slot[(half ^ 1) * 128 + row];
+      ++xn;
+      return o;
+    };
     uint32_t cg = 0;                              // tiles this group has processed so far
     uint32_t n = 0;
     for (int w = item_at(0); w < num_items; w = item_at(++n)) {
@@ -376,19 +404,19 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm, const AttnParams p) {
     const int qt = g ? it.qtB : it.qtA;
     const int n_mine = g ? it.nB : it.nA;
     const int qrow = qt * kBQ + row;              // position in the sequence
-    float m_ref = -INFINITY, l = 0.f;
+    float m_ref = -INFINITY, l = 0.f;             // l: partial row sum over my columns
     for (int j = 0; j < n_mine; ++j) {
       const uint32_t par = (cg + (uint32_t)j) & 1u;
       mbar_wait(s_full(g), par);
       tc_fence_after();
       const bool diag = (j == qt);
-      const int kbase = j * kBK;
-      // rescale this warp's rows of O in TMEM by alpha (rows whose reference stays pass alpha = 1).  Only legal while
-      // no P V UMMA of this query tile is in flight: those of tile j-1 have retired, those of tile j are not issued
-      // before p_full.
+      const int kbase = j * kBK + 64 * half;      // first key of my columns
+      // rescale my columns of this warp's rows of O in TMEM by alpha (rows whose reference stays pass alpha = 1).
+      // Only legal while no P V UMMA of this query tile is in flight: those of tile j-1 have retired, those of tile
+      // j are not issued before p_full.
       auto rescale_o = [&](float alpha) {
 #pragma unroll
-        for (int c = 0; c < kDH / 32; ++c) {
+        for (int c = 0; c < kDH / 64; ++c) {
           uint32_t r[32];
           tmem_ld32(t_pv + 32 * c, r);
           tmem_wait_ld();
@@ -403,22 +431,29 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm, const AttnParams p) {
         // read-only pass for the row maximum: always on the first tile (no reference yet), and on every tile when P
         // overwrites S (the reference has to be settled before the scores are destroyed)
         float mx0 = -INFINITY;
-#pragma unroll
-        for (int c = 0; c < kBK / 32; ++c) {
-          uint32_t r[32];
-          tmem_ld32(t_s + 32 * c, r);
+        {
+          uint32_t r[64];
+          tmem_ld32(t_s, r);
+          tmem_ld32(t_s + 32, r + 32);
           tmem_wait_ld();
+          float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};   // independent chains
+          if (diag) {            // warp-uniform: only the diagonal tile carries masking code
 #pragma unroll
-          for (int i = 0; i < 32; ++i)
-            mx0 = fmaxf(mx0, (diag && kbase + 32 * c + i > qrow) ? -INFINITY : __uint_as_float(r[i]));
+            for (int i = 0; i < 64; ++i) m4[i & 3] = fmaxf(m4[i & 3], (kbase + i > qrow) ? -INFINITY : __uint_as_float(r[i]));
+          } else {
+#pragma unroll
+            for (int i = 0; i < 64; ++i) m4[i & 3] = fmaxf(m4[i & 3], __uint_as_float(r[i]));
+          }
+          mx0 = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3]));
         }
+        mx0 = fmaxf(mx0, exchange(mx0));           // whole-row maximum
         if (j == 0) {
           m_ref = mx0 * p.scale_log2;
         } else {
           // lazy rescaling, decided up front: keep the old reference unless this row's max outgrew it by 2^8.
           // s_full(j) was committed after P V (j-1) in issue order, so O is quiescent here.
           const bool grow = mx0 * p.scale_log2 > m_ref + kRescaleThreshold;
-          if (__any_sync(0xffffffffu, grow)) {
+          if (__any_sync(0xffffffffu, grow)) {     // same rows, same maxima: the partner warp decides alike
             float alpha = 1.f;
             if (grow) {
               const float m_new = mx0 * p.scale_log2;
@@ -434,13 +469,14 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm, const AttnParams p) {
       bool first_pass = true;
       while (true) {
         const bool wait_pv = first_pass && j > 0;
-        if (diag) softmax_sweep<true>(t_s, t_p, p.scale_log2, m_ref, kbase, qrow, wait_pv, pv_full(g), par ^ 1u, sum, mx);
-        else      softmax_sweep<false>(t_s, t_p, p.scale_log2, m_ref, kbase, qrow, wait_pv, pv_full(g), par ^ 1u, sum, mx);
+        if (diag) softmax_sweep<true, 64>(t_s, t_p, p.scale_log2, m_ref, kbase, qrow, wait_pv, pv_full(g), par ^ 1u, sum, mx);
+        else      softmax_sweep<false, 64>(t_s, t_p, p.scale_log2, m_ref, kbase, qrow, wait_pv, pv_full(g), par ^ 1u, sum, mx);
         first_pass = false;
         if (C::kAliasP) break;   // the reference was settled before the sweep; the scores are gone now
+        mx = fmaxf(mx, exchange(mx));              // whole-row maximum
         // lazy rescaling: keep the old reference unless this row's max outgrew it by 2^8
         const bool grow = mx * p.scale_log2 > m_ref + kRescaleThreshold;
-        if (!__any_sync(0xffffffffu, grow)) break;
+        if (!__any_sync(0xffffffffu, grow)) break; // same rows, same maxima: the partner warp decides alike
         float alpha = 1.f;
         if (grow) {
           const float m_new = mx * p.scale_log2;
@@ -457,13 +493,14 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm, const AttnParams p) {
       if (lane == 0) { mbar_arrive(s_free(g)); mbar_arrive(p_full(g)); }
     }
     if (n_mine > 0) {
-      // ---- all P V UMMAs of the item have retired: normalise O, write it and the log-sum-exp ----
+      // ---- all P V UMMAs of the item have retired: normalise my half of O, write it and the log-sum-exp ----
       mbar_wait(pv_full(g), (cg + (uint32_t)n_mine - 1u) & 1u);
       tc_fence_after();
+      l += exchange(l);                            // whole-row sum
       const float inv_l = 1.f / l;
-      __nv_bfloat16* dst = p.out + ((int64_t)b * p.seq + qrow) * p.ld_out + h * kDH;
+      __nv_bfloat16* dst = p.out + ((int64_t)b * p.seq + qrow) * p.ld_out + h * kDH + (kDH / 2) * half;
 #pragma unroll
-      for (int c = 0; c < kDH / 32; ++c) {   // 32 columns (64 bytes of output) per TMEM round trip
+      for (int c = 0; c < kDH / 64; ++c) {   // 32 columns (64 bytes of output) per TMEM round trip
         uint32_t r[32];
         float o[32];
         tmem_ld32(t_pv + 32 * c, r);
@@ -475,7 +512,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm, const AttnParams p) {
           for (int v = 0; v < 4; ++v) *reinterpret_cast<uint4*>(dst + 32 * c + 8 * v) = pack8(o + 8 * v);
         }
       }
-      if (qrow < p.seq) p.lse2[(int64_t)bh * p.seq + qrow] = m_ref + log2f(l);
+      if (half == 0 && qrow < p.seq) p.lse2[(int64_t)bh * p.seq + qrow] = m_ref + log2f(l);
     }
     cg += (uint32_t)n_mine;
     }  // items
