@@ -54,10 +54,6 @@ template <int DH> struct Cfg {
   // inside its own score columns, at 64h, so that no thread overwrites scores its partner has yet to read.
   static constexpr uint32_t kHalfP = kAliasP ? 64u : 32u;      // column distance between the two halves of a P row
 };
-#ifndef B200FT_ATTN_SWEEP_LD
-#define B200FT_ATTN_SWEEP_LD 32
-#endif
-constexpr int kSweepLd = B200FT_ATTN_SWEEP_LD;  // 32, 64 or 128
 constexpr float kRescaleThreshold = 8.0f;       // log2 units: p stays below 2^8
 
 struct AttnParams {
@@ -70,64 +66,6 @@ struct AttnParams {
 };
 
 
-
-// One sweep over this thread's NC score columns (t_s, t_p and kbase already point at them) of its query row: p = exp2(s*scale - m_ref) -> bf16 P in
-// TMEM, row sum and raw row max returned.  DIAG tiles mask keys beyond the query position; the other
-// tiles carry no masking code at all.  Before the first store into P the previous tile's P V UMMA must
-// have finished reading it (pv_bar / pv_parity; skipped when wait_pv is false).
-template <bool DIAG, int NC>
-__device__ __forceinline__ void softmax_sweep(uint32_t t_s, uint32_t t_p, float scale_log2, float m_ref, int kbase,
-                                              int qrow, bool wait_pv, uint32_t pv_bar, uint32_t pv_parity,
-                                              float& sum_out, float& max_out) {
-  const f32x2_t sc2 = pk2(scale_log2, scale_log2);
-  const f32x2_t nm2 = pk2(-m_ref, -m_ref);
-  // four independent accumulator chains each for the row sum and the row max: with two warps per
-  // scheduler a single 64-deep dependent chain cannot be hidden
-  f32x2_t sa[4] = {pk2(0.f, 0.f), pk2(0.f, 0.f), pk2(0.f, 0.f), pk2(0.f, 0.f)};
-  float ma[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
-  // kSweepLd score columns are requested per TMEM round trip (one tcgen05.wait::ld each): with one softmax warp
-  // per query group and scheduler, every round trip is exposed latency
-#pragma unroll
-  for (int cc = 0; cc < NC / kSweepLd; ++cc) {
-    uint32_t rr[kSweepLd];
-#pragma unroll
-    for (int q = 0; q < kSweepLd / 32; ++q) tmem_ld32(t_s + kSweepLd * cc + 32 * q, rr + 32 * q);
-    tmem_wait_ld();
-#pragma unroll
-    for (int q = 0; q < kSweepLd / 32; ++q) {
-      const int c = cc * (kSweepLd / 32) + q;
-      const uint32_t* r = rr + 32 * q;
-      uint32_t w[16];
-#pragma unroll
-      for (int i = 0; i < 32; i += 2) {
-        float s0 = __uint_as_float(r[i]), s1 = __uint_as_float(r[i + 1]);
-        if (DIAG) {
-          if (kbase + 32 * c + i > qrow) s0 = -INFINITY;
-          if (kbase + 32 * c + i + 1 > qrow) s1 = -INFINITY;
-        }
-        const int a = (i >> 1) & 3;
-        ma[a] = fmaxf(ma[a], fmaxf(s0, s1));
-        float e0, e1;
-        upk2(fma2(pk2(s0, s1), sc2, nm2), e0, e1);
-        const float p0 = ex2(e0), p1 = ex2(e1);  // exp2(-inf) = 0 for masked keys
-        sa[a] = add2(sa[a], pk2(p0, p1));
-        w[i >> 1] = pack_bf16x2(p0, p1);
-      }
-      if (c == 0 && wait_pv) {
-        mbar_wait(pv_bar, pv_parity);
-        tc_fence_after();
-      }
-#ifdef B200FT_EXP_NO_PSTORE
-      if (w[0] == 0x12345678u)   // practically never
-#endif
-      tmem_st16(t_p + 16 * c, w);  // keys 32c .. 32c+31 of this row = 16 packed columns of P
-    }
-  }
-  max_out = fmaxf(fmaxf(ma[0], ma[1]), fmaxf(ma[2], ma[3]));
-  float s_lo, s_hi;
-  upk2(add2(add2(sa[0], sa[1]), add2(sa[2], sa[3])), s_lo, s_hi);
-  sum_out = s_lo + s_hi;
-}
 
 // Work item: (pair of query tiles, batch, head), heaviest pairs (most kv tiles) first.
 struct FwdItem {
@@ -416,81 +354,93 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm, const AttnParams p) {
       // j are not issued before p_full.
       auto rescale_o = [&](float alpha) {
 #pragma unroll
-        for (int c = 0; c < kDH / 64; ++c) {
-          uint32_t r[32];
-          tmem_ld32(t_pv + 32 * c, r);
+        for (int c = 0; c < kDH / 32; ++c) {     // 16 columns per round trip: the 64 scores stay in registers meanwhile
+          uint32_t o16[16];
+          tmem_ld16(t_pv + 16 * c, o16);
           tmem_wait_ld();
 #pragma unroll
-          for (int i = 0; i < 32; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * alpha);
-          tmem_st16(t_pv + 32 * c, r);
-          tmem_st16(t_pv + 32 * c + 16, r + 16);
+          for (int i = 0; i < 16; ++i) o16[i] = __float_as_uint(__uint_as_float(o16[i]) * alpha);
+          tmem_st16(t_pv + 16 * c, o16);
         }
         tmem_wait_st();
       };
-      if (j == 0 || C::kAliasP) {
-        // read-only pass for the row maximum: always on the first tile (no reference yet), and on every tile when P
-        // overwrites S (the reference has to be settled before the scores are destroyed)
-        float mx0 = -INFINITY;
-        {
-          uint32_t r[64];
-          tmem_ld32(t_s, r);
-          tmem_ld32(t_s + 32, r + 32);
-          tmem_wait_ld();
-          float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};   // independent chains
-          if (diag) {            // warp-uniform: only the diagonal tile carries masking code
-#pragma unroll
-            for (int i = 0; i < 64; ++i) m4[i & 3] = fmaxf(m4[i & 3], (kbase + i > qrow) ? -INFINITY : __uint_as_float(r[i]));
-          } else {
-#pragma unroll
-            for (int i = 0; i < 64; ++i) m4[i & 3] = fmaxf(m4[i & 3], __uint_as_float(r[i]));
-          }
-          mx0 = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3]));
-        }
-        mx0 = fmaxf(mx0, exchange(mx0));           // whole-row maximum
-        if (j == 0) {
-          m_ref = mx0 * p.scale_log2;
-        } else {
-          // lazy rescaling, decided up front: keep the old reference unless this row's max outgrew it by 2^8.
-          // s_full(j) was committed after P V (j-1) in issue order, so O is quiescent here.
-          const bool grow = mx0 * p.scale_log2 > m_ref + kRescaleThreshold;
-          if (__any_sync(0xffffffffu, grow)) {     // same rows, same maxima: the partner warp decides alike
-            float alpha = 1.f;
-            if (grow) {
-              const float m_new = mx0 * p.scale_log2;
-              alpha = ex2(m_ref - m_new);
-              l *= alpha;
-              m_ref = m_new;
-            }
-            rescale_o(alpha);
-          }
-        }
+      // ---- my 64 scores -> registers, ONCE.  tcgen05.ld moves 64 bytes per clock per SM: reading a 128 x 128 fp32
+      // score tile costs 1024 cycles, as much as its exponentials, so a second read (a separate row-maximum pass, or a
+      // repeated sweep) doubles the kernel's longest resource ----
+      uint32_t r[64];
+      tmem_ld32(t_s, r);
+      tmem_ld32(t_s + 32, r + 32);
+      tmem_wait_ld();
+      if (!C::kAliasP) {
+        // the scores are in registers: S_g(j+1) may be issued while this tile is exponentiated
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(s_free(g));
       }
-      float sum, mx;
-      bool first_pass = true;
-      while (true) {
-        const bool wait_pv = first_pass && j > 0;
-        if (diag) softmax_sweep<true, 64>(t_s, t_p, p.scale_log2, m_ref, kbase, qrow, wait_pv, pv_full(g), par ^ 1u, sum, mx);
-        else      softmax_sweep<false, 64>(t_s, t_p, p.scale_log2, m_ref, kbase, qrow, wait_pv, pv_full(g), par ^ 1u, sum, mx);
-        first_pass = false;
-        if (C::kAliasP) break;   // the reference was settled before the sweep; the scores are gone now
-        mx = fmaxf(mx, exchange(mx));              // whole-row maximum
-        // lazy rescaling: keep the old reference unless this row's max outgrew it by 2^8
+      float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};   // independent chains
+      if (diag) {            // warp-uniform: only the diagonal tile carries masking code
+#pragma unroll
+        for (int i = 0; i < 64; ++i) {
+          if (kbase + i > qrow) r[i] = 0xff800000u;   // -inf: exp2 gives 0
+          m4[i & 3] = fmaxf(m4[i & 3], __uint_as_float(r[i]));
+        }
+      } else {
+#pragma unroll
+        for (int i = 0; i < 64; ++i) m4[i & 3] = fmaxf(m4[i & 3], __uint_as_float(r[i]));
+      }
+      float mx = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3]));
+      mx = fmaxf(mx, exchange(mx));                // whole-row maximum
+      if (!C::kAliasP && j > 0) {
+        // P has its own columns here: the P V UMMAs of tile j-1 must have read them (and left O quiescent) before P
+        // is rewritten or O rescaled.  (Written over S, both follow from s_full(j): it was committed after P V (j-1).)
+        mbar_wait(pv_full(g), par ^ 1u);
+        tc_fence_after();
+      }
+      if (j == 0) {
+        m_ref = mx * p.scale_log2;
+      } else {
+        // lazy rescaling: keep the old reference unless this row's max outgrew it by 2^8 (p stays below 2^8)
         const bool grow = mx * p.scale_log2 > m_ref + kRescaleThreshold;
-        if (!__any_sync(0xffffffffu, grow)) break; // same rows, same maxima: the partner warp decides alike
-        float alpha = 1.f;
-        if (grow) {
-          const float m_new = mx * p.scale_log2;
-          alpha = ex2(m_ref - m_new);
-          l *= alpha;
-          m_ref = m_new;
+        if (__any_sync(0xffffffffu, grow)) {       // same rows, same maxima: the partner warp decides alike
+          float alpha = 1.f;
+          if (grow) {
+            const float m_new = mx * p.scale_log2;
+            alpha = ex2(m_ref - m_new);
+            l *= alpha;
+            m_ref = m_new;
+          }
+          rescale_o(alpha);
         }
-        if (j > 0) rescale_o(alpha);   // rare (the sweep waited for the P V UMMAs of tile j-1)
       }
-      l += sum;
+      // ---- p = exp2(s*scale - m_ref): bf16 P into TMEM (A operand of the P V UMMA), partial row sum ----
+      {
+        const f32x2_t sc2 = pk2(p.scale_log2, p.scale_log2);
+        const f32x2_t nm2 = pk2(-m_ref, -m_ref);
+        f32x2_t sa[2] = {pk2(0.f, 0.f), pk2(0.f, 0.f)};
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {              // 16 keys = 8 packed columns per store
+          uint32_t w[8];
+#pragma unroll
+          for (int i = 0; i < 16; i += 2) {
+            float e0, e1;
+            upk2(fma2(pk2(__uint_as_float(r[16 * c + i]), __uint_as_float(r[16 * c + i + 1])), sc2, nm2), e0, e1);
+            const float p0 = ex2(e0), p1 = ex2(e1);   // exp2(-inf) = 0 for masked keys
+            sa[(i >> 1) & 1] = add2(sa[(i >> 1) & 1], pk2(p0, p1));
+            w[i >> 1] = pack_bf16x2(p0, p1);
+          }
+          tmem_st8(t_p + 8 * c, w);
+        }
+        float s_lo, s_hi;
+        upk2(add2(sa[0], sa[1]), s_lo, s_hi);
+        l += s_lo + s_hi;
+      }
       tmem_wait_st();
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) { mbar_arrive(s_free(g)); mbar_arrive(p_full(g)); }
+      if (lane == 0) {
+        if (C::kAliasP) mbar_arrive(s_free(g));
+        mbar_arrive(p_full(g));
+      }
     }
     if (n_mine > 0) {
       // ---- all P V UMMAs of the item have retired: normalise my half of O, write it and the log-sum-exp ----
