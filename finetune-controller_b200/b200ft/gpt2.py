@@ -322,16 +322,24 @@ class GPT2LoRAStep(StepHostMixin, OwnAttentionMixin):
             # attention branch
             ops.gemm(dx1, W["attn_proj.w"], self.da)
             dq, dk, dv = self._attn_bwd(l, self.da)
-            # adapter gradients (dB = U^T dqkv, dU = s dqkv B^T, dA^T = dU^T h1) and d ln1, with
-            # dqkv = [dq | dk | dv] never materialised: each third is its own K segment / column block
+            # adapter gradients (dB = U^T dqkv, dU = s dqkv B^T, dA^T = dU^T h1) and d ln1
             d = D.d_model
             gB, Bsh, Wqkv = self.gB_all[rows], self.B_sh[rows], W["c_attn.w"]
-            for i, g in enumerate((dq, dk, dv)):
-                ops.lora_grad(self.U[l], g, gB[:, i * d:(i + 1) * d], r=R_PAD, cols=d)
-            ops.gemm(dq, Bsh[:, :d], self.dU, a2=dk, b2=Bsh[:, d:2 * d], more=[(dv, Bsh[:, 2 * d:])], alpha=s)
-            ops.lora_grad(self.dU, self.h1[l], self.gAt_all[rows], r=R_PAD, cols=d)
-            ops.gemm(dq, Wqkv[:, :d], self.dln, a2=dk, b2=Wqkv[:, d:2 * d],
-                     more=[(dv, Wqkv[:, 2 * d:]), (self.dU, self.A_sh[:, rows])])
+            if self.attention == "own":
+                # the own kernels leave dq | dk | dv side by side in one [tokens, 3d] buffer: one contraction each
+                dqkv = self.dqkv
+                ops.lora_grad(self.U[l], dqkv, gB, r=R_PAD, cols=3 * d)
+                ops.gemm(dqkv, Bsh, self.dU, alpha=s)
+                ops.lora_grad(self.dU, self.h1[l], self.gAt_all[rows], r=R_PAD, cols=d)
+                ops.gemm(dqkv, Wqkv, self.dln, a2=self.dU, b2=self.A_sh[:, rows])
+            else:
+                # the library hands back three separate buffers: each third is its own K segment / column block
+                for i, g in enumerate((dq, dk, dv)):
+                    ops.lora_grad(self.U[l], g, gB[:, i * d:(i + 1) * d], r=R_PAD, cols=d)
+                ops.gemm(dq, Bsh[:, :d], self.dU, a2=dk, b2=Bsh[:, d:2 * d], more=[(dv, Bsh[:, 2 * d:])], alpha=s)
+                ops.lora_grad(self.dU, self.h1[l], self.gAt_all[rows], r=R_PAD, cols=d)
+                ops.gemm(dq, Wqkv[:, :d], self.dln, a2=dk, b2=Wqkv[:, d:2 * d],
+                         more=[(dv, Wqkv[:, 2 * d:]), (self.dU, self.A_sh[:, rows])])
             ops.layernorm_bwd_dx(self.dln, self.x[l], W["ln1.g"], *self.st1[l], dx0, dres=dx1)
             dx, dx0 = dx0, dx
             if self.grad_sync is not None:

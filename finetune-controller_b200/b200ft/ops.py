@@ -309,7 +309,7 @@ def attn_bwd(qkv, out, dout, lse2, workspace, dqkv, *, batch, seq, n_head, n_kv_
                                     dout.stride(0), _p(lse2), _p(workspace), workspace.numel(), _p(dqkv), dqkv.stride(0),
                                     batch, seq, n_head, n_kv_head, d_head, scale,
                                     _lib.ATTN_BWD_DETERMINISTIC if deterministic else 0, _stream()), "attn_bwd")
-    LAUNCHES += 3
+    LAUNCHES += 3 if (deterministic or d_head == 128) else 2   # delta + (dK|dV, dQ) or delta + fused
     return dqkv
 
 

@@ -2,7 +2,9 @@
 // from the fused [tokens, q|k|v] projection buffer, o / do from [tokens, heads*64] buffers and the forward's
 // per-row log-sum-exp, and writes dq | dk | dv into a buffer with the projection's own column layout.
 //
-// Three launches:
+// Launches: delta, then either MODE 2 — the default: MODE 0's work item, which also forms the dQ partial of every
+// tile pair (dS K_j) and reduce-adds it, scaled and rounded to bf16, into the pre-zeroed q columns of the gradient
+// buffer by TMA (5 tile GEMMs per pair, S / dP / exponentials computed once) — or MODE 0 + MODE 1 (deterministic):
 //   delta     D[row] = sum_d do[row,d] * o[row,d]                              (one warp per token)
 //   MODE 0    one CTA per (kv tile j, batch, kv head): K_j, V_j resident; streams (Q_i, dO_i) over the q heads
 //             of the group and the q tiles i >= j; dV_j += P^T dO_i and dK_j += dS^T Q_i accumulate in TMEM
@@ -77,24 +79,6 @@ attn_delta_kernel(const __nv_bfloat16* __restrict__ o, int64_t ld_o, const __nv_
     acc += __shfl_xor_sync(0xffffffffu, acc, 4);
     if (kUPH == 16) acc += __shfl_xor_sync(0xffffffffu, acc, 8);
     if (u < units && (lane & (kUPH - 1)) == 0) delta[((int64_t)b * n_head + u / kUPH) * seq + t] = acc;
-  }
-}
-
-// ------------------------------------------------------------------------------------------------
-// dq (bf16, into the gradient buffer's q columns) = scale * fp32 accumulator; 8 elements per thread
-__global__ void __launch_bounds__(256)
-attn_dq_convert_kernel(const float* __restrict__ acc, __nv_bfloat16* __restrict__ dqkv, int64_t ld_d, int q_off,
-                       int64_t rows, int cols, float scale) {
-  const int vpr = cols >> 3;
-  const int64_t total = rows * vpr;
-  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
-    const int64_t r = i / vpr;
-    const int v = (int)(i % vpr);
-    const float4 a = *reinterpret_cast<const float4*>(acc + r * cols + 8 * v);
-    const float4 b = *reinterpret_cast<const float4*>(acc + r * cols + 8 * v + 4);
-    float f8[8] = {a.x * scale, a.y * scale, a.z * scale, a.w * scale, b.x * scale, b.y * scale, b.z * scale, b.w * scale};
-    *reinterpret_cast<uint4*>(dqkv + r * ld_d + q_off + 8 * v) = pack8(f8);
   }
 }
 
@@ -336,8 +320,8 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
         st_shared_v4(base + tile_off + unit * 16u, wv[4 * u], wv[4 * u + 1], wv[4 * u + 2], wv[4 * u + 3]);
       }
     };
-    // MODE 2: dQ partial of pair gg -> swizzled staging tile -> TMA reduce-add into the fp32 dQ accumulator
-    // [batch][seq][heads*64]; rows past the end of the sequence are clipped by TMA.  Slices 0 and 1 do it (32 rows x
+    // MODE 2: dQ partial of pair gg -> staging tile -> TMA reduce-add (bf16) into the q columns of the gradient buffer
+    // [batch][seq][columns], which the host zeroed; rows past the end of the sequence are clipped by TMA.  Slices 0 and 1 do it (32 rows x
     // 32 columns per warp); the other two warps of the quarter run ahead into the next pair's exponentials.
     const uint32_t stage_dq = raw + kOffDQ + (uint32_t)((part & 1) * 4 + quarter) * 4096u;
     auto drain_dq = [&](uint32_t gg, int hq, int qt, int bb) {
@@ -357,16 +341,21 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
       if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // the previous reduce has read the tile
       __syncwarp();
       if (lane == 0) mbar_arrive(dq_free(bq));
+      // x softmax scale, to bf16: the partial is ADDED in bf16 straight into the q columns of the gradient buffer
+      // (a 32 x 32 bf16 tile, 64-byte rows, unswizzled)
+      uint32_t wq[16];
 #pragma unroll
-      for (int u = 0; u < 8; ++u)
-        st_shared_v4(stage_dq + (uint32_t)lane * 128u + ((((uint32_t)u) ^ (uint32_t)(lane & 7)) << 4), r[4 * u], r[4 * u + 1],
-                     r[4 * u + 2], r[4 * u + 3]);
+      for (int i = 0; i < 16; ++i)
+        wq[i] = pack_bf16x2(__uint_as_float(r[2 * i]) * p.scale, __uint_as_float(r[2 * i + 1]) * p.scale);
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        st_shared_v4(stage_dq + (uint32_t)lane * 64u + ((uint32_t)u << 4), wq[4 * u], wq[4 * u + 1], wq[4 * u + 2], wq[4 * u + 3]);
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
       __syncwarp();
       if (lane == 0) {
         asm volatile(
             "cp.reduce.async.bulk.tensor.3d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3, %4}], [%1];"
-            ::"l"(reinterpret_cast<uint64_t>(&tm_dq)), "r"(stage_dq), "r"(hq * kDH + 32 * part),
+            ::"l"(reinterpret_cast<uint64_t>(&tm_dq)), "r"(stage_dq), "r"(p.q_off + hq * kDH + 32 * part),
               "r"(qt * kB + 32 * quarter), "r"(bb) : "memory");
         asm volatile("cp.async.bulk.commit_group;" ::: "memory");
       }
@@ -518,14 +507,14 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
 
 }  // namespace
 
-// workspace: delta [batch*n_head*seq] fp32 | dQ accumulator [batch*seq, n_head*64] fp32 (fused d_head-64 path only)
+// workspace: delta [batch*n_head*seq] fp32
 static size_t delta_bytes(int batch, int seq, int n_head) {
   return (((size_t)batch * n_head * seq * sizeof(float)) + 255) & ~(size_t)255;
 }
 
 extern "C" size_t b200ft_attn_bwd_workspace_bytes(int batch, int seq, int n_head, int d_head) {
-  if (d_head == 128) return delta_bytes(batch, seq, n_head);   // two-kernel form: no fp32 dQ accumulator
-  return delta_bytes(batch, seq, n_head) + (size_t)batch * seq * n_head * d_head * sizeof(float);
+  (void)d_head;
+  return delta_bytes(batch, seq, n_head);
 }
 
 extern "C" int b200ft_attn_bwd(const void* qkv, int64_t ld, int q_off, int k_off, int v_off, const void* out,
@@ -549,13 +538,12 @@ extern "C" int b200ft_attn_bwd(const void* qkv, int64_t ld, int q_off, int k_off
   // d_head 128: always the two-kernel form (dK|dV per kv tile, dQ per q tile; no atomics, bit-reproducible) of
   // attention_bwd_d128.cu — TMEM has no room for a dQ partial beside S, dP, dK and dV at that head size
   const bool split = (flags & B200FT_ATTN_BWD_DETERMINISTIC) != 0 || d_head == 128;
-  const size_t need = split ? delta_bytes(batch, seq, n_head) : b200ft_attn_bwd_workspace_bytes(batch, seq, n_head, d_head);
+  const size_t need = delta_bytes(batch, seq, n_head);
   if (workspace_bytes < need) {
     b200ft_set_error("attn_bwd: workspace %zu < %zu", workspace_bytes, need);
     return B200FT_ERR_WORKSPACE;
   }
   float* delta = (float*)workspace;
-  float* dq_acc = (float*)((uint8_t*)workspace + delta_bytes(batch, seq, n_head));
   EncodeTiledFn enc = encode_fn();
   if (!enc) { b200ft_set_error("attn_bwd: cuTensorMapEncodeTiled unavailable"); return B200FT_ERR_UNSUPPORTED; }
   CUtensorMap tm_qkv, tm_do, tm_dq;
@@ -565,13 +553,14 @@ extern "C" int b200ft_attn_bwd(const void* qkv, int64_t ld, int q_off, int k_off
   if (rc) return rc;
   tm_dq = tm_do;  // unused by the split kernels
   if (!split) {
-    // fp32 accumulator as [batch][seq][heads*64], boxes of 32 columns x 32 rows, 128B swizzle
-    cuuint64_t dims[3] = {(cuuint64_t)n_head * kDH, (cuuint64_t)seq, (cuuint64_t)batch};
-    cuuint64_t strides[2] = {(cuuint64_t)n_head * kDH * 4, (cuuint64_t)n_head * kDH * 4 * (cuuint64_t)seq};
+    // the gradient buffer itself as [batch][seq][columns] bf16, boxes of 32 columns x 32 rows, unswizzled: the dQ
+    // partials are reduce-added into its q columns in bf16 (one rounding per visible kv tile: T/128 of them per element)
+    cuuint64_t dims[3] = {(cuuint64_t)ld_dqkv, (cuuint64_t)seq, (cuuint64_t)batch};
+    cuuint64_t strides[2] = {(cuuint64_t)ld_dqkv * 2, (cuuint64_t)ld_dqkv * 2 * (cuuint64_t)seq};
     cuuint32_t box[3] = {32, 32, 1};
     cuuint32_t estr[3] = {1, 1, 1};
-    CUresult r = enc(&tm_dq, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, dq_acc, dims, strides, box, estr,
-                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+    CUresult r = enc(&tm_dq, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, dqkv, dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) { b200ft_set_error("attn_bwd: cuTensorMapEncodeTiled(dq) failed (%d)", (int)r); return B200FT_ERR_ARG; }
   }
@@ -619,13 +608,9 @@ extern "C" int b200ft_attn_bwd(const void* qkv, int64_t ld, int q_off, int k_off
     B200FT_LAUNCH_CHECK();
     return 0;
   }
-  B200FT_CUDA(cudaMemsetAsync(dq_acc, 0, (size_t)rows * n_head * kDH * sizeof(float), st));
+  // zero the q columns (a strided DMA fill, no kernel); dk | dv are written whole by the kernel
+  B200FT_CUDA(cudaMemset2DAsync((__nv_bfloat16*)dqkv + q_off, (size_t)ld_dqkv * 2, 0, (size_t)n_head * kDH * 2, (size_t)rows, st));
   attn_bwd_kernel<2><<<grid0, kThreads, kSmemBytes, st>>>(tm_qkv, tm_do, tm_dq, p);
-  B200FT_LAUNCH_CHECK();
-  const int cols = n_head * kDH;
-  int64_t want = (rows * (cols / 8) + 255) / 256;
-  const int blocks = (int)(want > B200FT_NUM_SMS * 16 ? B200FT_NUM_SMS * 16 : want);
-  attn_dq_convert_kernel<<<blocks, 256, 0, st>>>(dq_acc, (__nv_bfloat16*)dqkv, ld_dqkv, q_off, rows, cols, scale);
   B200FT_LAUNCH_CHECK();
   return 0;
 }

@@ -228,13 +228,14 @@ int b200ft_attn_fwd(const void* qkv, int64_t ld, int q_off, int k_off, int v_off
  * column h*d_head; lse2 is the forward's output.  dqkv [batch*seq, ld_dqkv] receives dq of head h at
  * q_off + h*d_head and dk / dv of kv head g at k_off / v_off + g*d_head (summed over the q heads of the
  * group), i.e. the column layout of the fused projection output itself; every element of those
- * column ranges is written.  d_head must be 64; other sizes return B200FT_ERR_UNSUPPORTED.
- * workspace: 256-byte aligned scratch of b200ft_attn_bwd_workspace_bytes() bytes (row sums of
- * dout*out, and the fp32 dQ accumulator of the default path).
- * flags = 0: one fused kernel per (kv tile, batch, kv head) computes dK, dV in TMEM and adds its dQ
- * partials into the fp32 accumulator with TMA reduce-add (summation order varies run to run in the
- * last bits of dq).  flags = B200FT_ATTN_BWD_DETERMINISTIC: two kernels (dK|dV, then dQ), no atomics,
- * bit-reproducible, ~1.4x the time. */
+ * column ranges is written.  d_head must be 64 or 128; other sizes return B200FT_ERR_UNSUPPORTED.
+ * workspace: 256-byte aligned scratch of b200ft_attn_bwd_workspace_bytes() bytes (row sums of dout*out).
+ * d_head 64, flags = 0: one fused kernel per (kv tile, batch, kv head) computes dK, dV in TMEM and adds
+ * its dQ partials, already scaled and rounded to bf16, into the (pre-zeroed) q columns of dqkv with TMA
+ * reduce-add: one bf16 rounding per visible kv tile, summation order varying run to run in the last bits
+ * of dq.  flags = B200FT_ATTN_BWD_DETERMINISTIC: two kernels (dK|dV, then dQ accumulated in fp32 in TMEM),
+ * no atomics, bit-reproducible, ~1.3x the time.  d_head 128 always runs its two-kernel form
+ * (bit-reproducible). */
 #define B200FT_ATTN_BWD_DETERMINISTIC 1
 size_t b200ft_attn_bwd_workspace_bytes(int batch, int seq, int n_head, int d_head);
 int b200ft_attn_bwd(const void* qkv, int64_t ld, int q_off, int k_off, int v_off, const void* out,

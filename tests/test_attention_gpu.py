@@ -146,11 +146,14 @@ def test_attn_bwd_deterministic_path_is_bit_reproducible():
         ops.attn_bwd(qd, out, dod, lse2, ws, dqkv, deterministic=True, **kw)
         res.append(dqkv.clone())
     assert torch.equal(res[0], res[1])
-    # the fused default: dk, dv are exact too, dq differs only in the summation order of its fp32 partials
-    fused = torch.zeros(B * T, ld, dtype=torch.bfloat16, device=DEV)
+    # the fused default: dk, dv are exact too; dq is summed from bf16-rounded partials (one per visible kv tile, here
+    # up to 3), in an order that varies from run to run
+    fused = torch.full((B * T, ld), float("nan"), dtype=torch.bfloat16, device=DEV)
     ops.attn_bwd(qd, out, dod, lse2, ws, fused, **kw)
     assert torch.equal(fused[:, H * dh:], res[0][:, H * dh:])
-    torch.testing.assert_close(fused[:, : H * dh].float(), res[0][:, : H * dh].float(), rtol=2 ** -7, atol=1e-3)
+    a, r = fused[:, : H * dh].float(), res[0][:, : H * dh].float()
+    assert float((a - r).norm() / r.norm()) <= 2 ** -7
+    torch.testing.assert_close(a, r, rtol=2 ** -5, atol=2e-3 * float(r.abs().max()))
 
 
 @pytest.mark.parametrize("dh", [64, 128])
