@@ -289,7 +289,7 @@ def run_ours(args) -> None:
     if world > 1 and full:
         k = args.nccl_ctas
         sync = ddp.BucketedGradSync(n_layer, n_buckets=n_layer, group=ddp.overlap_group(k) if k > 0 else None,
-                                    reserve_ctas=k, use_tail_group=True)
+                                    reserve_ctas=k, use_tail_group=True, tail_layers=args.tail_layers)
     elif world > 1:
         sync = ddp.BucketedGradSync(n_layer, n_buckets=1)   # the whole flat adapter gradient: ONE all-reduce per step
     # random-init weights; B drawn at random (not PEFT's zero) so every gradient path carries data
@@ -553,6 +553,8 @@ def main():
     ap.add_argument("--nccl-ctas", type=int, default=8,
                     help="full-parameter workloads: CTAs of the overlapped all-reduce (and SMs x2 left free by the "
                          "backward GEMMs); 0 = default communicator, no reservation")
+    ap.add_argument("--tail-layers", type=int, default=1,
+                    help="full-parameter workloads: buckets of the bottom N layers go out on the full-width communicator")
     ap.add_argument("--attention", default="auto", choices=["auto", "own", "sdpa"],
                     help="own: this repo's tcgen05 attention kernels (d_head 64 and 128), i.e. a step with no library "
                          "kernel in it; sdpa: torch SDPA (cuDNN, library; A/B measurements); auto = own where built")

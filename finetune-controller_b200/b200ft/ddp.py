@@ -78,10 +78,13 @@ class BucketedGradSync:
     backward GEMMs (0 = none)."""
 
     def __init__(self, n_layer: int, n_buckets: int = 2, group=None, tail_group=None, reserve_ctas: int = 0,
-                 use_tail_group: bool = False):
+                 use_tail_group: bool = False, tail_layers: int = 1):
         self.buckets = layer_buckets(n_layer, n_buckets)
         self.group = group
         self.tail_group = tail_group if use_tail_group else group
+        # buckets that start below this layer go out on the tail group: backward has little left to overlap them with,
+        # and the CTA-limited communicator by then carries a backlog
+        self.tail_layers = max(1, tail_layers)
         self.reserve_ctas = reserve_ctas
         self.pending = []
         self.bytes_reduced = 0
@@ -92,7 +95,7 @@ class BucketedGradSync:
             return
         for lo, hi in self.buckets:
             if l == lo:  # backward walks l downward: reaching `lo` completes the bucket
-                grp = self.tail_group if lo == 0 else self.group
+                grp = self.tail_group if lo < self.tail_layers else self.group
                 for t in engine.grad_views(lo, hi):
                     self.pending.append(dist.all_reduce(t, op=dist.ReduceOp.SUM, group=grp, async_op=True))
                     self.bytes_reduced += t.numel() * t.element_size()

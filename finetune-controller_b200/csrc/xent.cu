@@ -95,46 +95,55 @@ softmax_xent_kernel(__nv_bfloat16* __restrict__ logits, int64_t rows, int vocab,
   if (valid) {
     // ---- sweep 1: online max / sum in the log2 domain, kUnroll independent 16-byte loads in
     // flight per thread (the running max is revisited once per 8*kUnroll elements) ----
+    // Packed math throughout: the maximum on bf16 pairs (HMNMX2), then per pair two unpack ops, one FFMA2, two MUFU and
+    // one FADD2 — half the issue slots of the scalar form, which matters inside a step, where the SM clock sits at
+    // the power cap and this kernel's issue rate, not HBM, sets its time.
     MS acc{-INFINITY, 0.f};
+    const f32x2_t l2e2 = pk2(kLog2e, kLog2e);
     for (int i0 = threadIdx.x; i0 < nvec; i0 += kThreads * kUnroll) {
       uint4 q[kUnroll];
 #pragma unroll
-      for (int u = 0; u < kUnroll; ++u) {
+      for (int u = 0; u < kUnroll; ++u) {   // all loads of the iteration in flight before the first use
         const int i = i0 + u * kThreads;
+        q[u] = make_uint4(0xff80ff80u, 0xff80ff80u, 0xff80ff80u, 0xff80ff80u);   // (-inf, -inf) pairs in bf16
         if (i < nvec) q[u] = ld_cg16(z + ((int64_t)i << 3));
       }
-      float f[kUnroll][8];
-      float vmax = -INFINITY;
+      uint32_t mx2 = 0xff80ff80u;
 #pragma unroll
       for (int u = 0; u < kUnroll; ++u) {
-        const int i = i0 + u * kThreads;
-        const int c0 = i << 3;
-        if (i < nvec) {
-          unpack8(q[u], f[u]);
-          if (c0 + 8 <= vocab) {
+        const int c0 = (i0 + u * kThreads) << 3;
+        if (c0 + 8 > vocab && c0 < (nvec << 3)) {  // the vector straddling (or beyond) the vocabulary: padding -> -inf
+          uint32_t* w = reinterpret_cast<uint32_t*>(&q[u]);
 #pragma unroll
-            for (int j = 0; j < 8; ++j) { f[u][j] *= kLog2e; vmax = fmaxf(vmax, f[u][j]); }
-          } else {  // the vector straddling (or beyond) the end of the vocabulary
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              f[u][j] = (c0 + j < vocab) ? f[u][j] * kLog2e : -INFINITY;
-              vmax = fmaxf(vmax, f[u][j]);
-            }
+          for (int j = 0; j < 4; ++j) {
+            if (c0 + 2 * j >= vocab) w[j] = (w[j] & 0xffff0000u) | 0xff80u;
+            if (c0 + 2 * j + 1 >= vocab) w[j] = (w[j] & 0x0000ffffu) | 0xff800000u;
           }
-        } else {
-#pragma unroll
-          for (int j = 0; j < 8; ++j) f[u][j] = -INFINITY;
         }
+        mx2 = bf16x2_max(bf16x2_max(mx2, q[u].x), bf16x2_max(q[u].y, bf16x2_max(q[u].z, q[u].w)));
       }
+      const float vmax = fmaxf(bf16lo(mx2), bf16hi(mx2)) * kLog2e;
       if (vmax > acc.m) {  // rare after the first few iterations
         acc.s *= ex2_approx(acc.m - vmax);  // ex2(-inf) = 0 on the first hit
         acc.m = vmax;
       }
       if (acc.m != -INFINITY) {
+        const f32x2_t nm2 = pk2(-acc.m, -acc.m);
+        f32x2_t s2a = pk2(0.f, 0.f), s2b = pk2(0.f, 0.f);
 #pragma unroll
-        for (int u = 0; u < kUnroll; ++u)
+        for (int u = 0; u < kUnroll; ++u) {
+          const uint32_t* w = reinterpret_cast<const uint32_t*>(&q[u]);
 #pragma unroll
-          for (int j = 0; j < 8; ++j) acc.s += ex2_approx(f[u][j] - acc.m);
+          for (int j = 0; j < 4; ++j) {
+            float lo, hi;
+            upk2(fma2(bf16x2_to_f32x2(w[j]), l2e2, nm2), lo, hi);
+            const f32x2_t e = pk2(ex2_approx(lo), ex2_approx(hi));   // padding: exp2(-inf) = 0
+            if (j & 1) s2b = add2(s2b, e); else s2a = add2(s2a, e);
+          }
+        }
+        float s_lo, s_hi;
+        upk2(add2(s2a, s2b), s_lo, s_hi);
+        acc.s += s_lo + s_hi;
       }
     }
 #pragma unroll
@@ -165,6 +174,7 @@ softmax_xent_kernel(__nv_bfloat16* __restrict__ logits, int64_t rows, int vocab,
   const float lse2 = valid ? s_lse2 : 0.f;
   const int tcol = valid ? (int)tgt : -1;
   if (valid) {
+    const f32x2_t l2e2s = pk2(kLog2e, kLog2e), nl2 = pk2(-lse2, -lse2), sc2 = pk2(scale, scale);
     for (int i0 = threadIdx.x; i0 < nvec; i0 += kThreads * kUnroll) {
       uint4 q[kUnroll];
 #pragma unroll
@@ -177,19 +187,28 @@ softmax_xent_kernel(__nv_bfloat16* __restrict__ logits, int64_t rows, int vocab,
         const int i = i0 + u * kThreads;
         if (i < nvec) {
           const int c0 = i << 3;
-          float f[8];
-          unpack8(q[u], f);
+          const uint32_t* w = reinterpret_cast<const uint32_t*>(&q[u]);
+          uint4 o;
+          uint32_t* ow = reinterpret_cast<uint32_t*>(&o);
+          if ((tcol >= c0 && tcol < c0 + 8) || c0 + 8 > vocab) {   // the vector holding the target, or padding: scalar
+            float f[8];
+            unpack8(q[u], f);
 #pragma unroll
-          for (int j = 0; j < 8; ++j) f[j] = ex2_approx(f[j] * kLog2e - lse2) * scale;
-          if (tcol >= c0 && tcol < c0 + 8) {
+            for (int j = 0; j < 8; ++j) {
+              f[j] = ex2_approx(f[j] * kLog2e - lse2) * scale;
+              if (c0 + j == tcol) f[j] -= scale;
+              if (c0 + j >= vocab) f[j] = 0.f;
+            }
+            o = pack8(f);
+          } else {
 #pragma unroll
-            for (int j = 0; j < 8; ++j) if (c0 + j == tcol) f[j] -= scale;
+            for (int j = 0; j < 4; ++j) {
+              float lo, hi;
+              upk2(fma2(bf16x2_to_f32x2(w[j]), l2e2s, nl2), lo, hi);
+              ow[j] = f32x2_to_bf16x2(mul2(pk2(ex2_approx(lo), ex2_approx(hi)), sc2));
+            }
           }
-          if (c0 + 8 > vocab) {
-#pragma unroll
-            for (int j = 0; j < 8; ++j) if (c0 + j >= vocab) f[j] = 0.f;
-          }
-          st_stream16(z + ((int64_t)i << 3), pack8(f));
+          st_stream16(z + ((int64_t)i << 3), o);
         }
       }
     }
@@ -486,29 +505,45 @@ int launch_xent(void* logits, int64_t rows, int vocab, int64_t ld, const int64_t
   // Two-sweep kernel.  Its second sweep must find the row in L2 (126 MB): rows in flight = CTAs per SM x 148.  Rows up to
   // ~105 KB run 8 CTAs of 256 threads per SM; longer rows run 512-thread CTAs whose number per SM is capped, by a dynamic
   // shared-memory request they do not use, so that the rows in flight stay below ~120 MB.
-  // Measured at V = 128256 (256 KB rows), 512 threads: 1 / 2 / 3 CTAs per SM 3500 / 4480-4600 / 4740-4860 GB/s; the
-  // uncapped 8 x 256 threads (303 MB in flight, third sweep from HBM) 4270-4370.  V = 50257: 8 x 256 threads (119 MB in
-  // flight) 5089, 4 x 512 threads 4247.
+  // Measured at V = 128256 (256 KB rows), GB/s: 512 threads x 1 / 2 / 3 CTAs per SM 3500-3630 / 4480-4630 / 4250-4860 (114 MB
+  // in flight: fits L2 on some boxes and runs, not on others); 1024 threads x 2 4200-4320; the uncapped 303 MB in
+  // flight (third sweep from HBM) 4270-4370.  V = 50257: 256 threads x 4 per SM 5150, x 8 5250.  Rule: rows in flight
+  // <= 90 MB.
   const int64_t row_bytes = ld * 2;
-  int64_t cap = (120ll << 20) / (row_bytes * B200FT_NUM_SMS);
+  int64_t cap = (90ll << 20) / (row_bytes * B200FT_NUM_SMS);
   static const int force_cap = getenv("B200FT_XENT_CAP") ? atoi(getenv("B200FT_XENT_CAP")) : 0;   // experiments
   if (force_cap > 0) cap = force_cap;
   if (row_bytes * 8 * B200FT_NUM_SMS <= (126ll << 20) || force_cap >= 8) {
-    softmax_xent_kernel<256><<<(unsigned)rows, 256, 0, st>>>((__nv_bfloat16*)logits, rows, vocab, ld, targets,
-                                                            ignore_index, grad_scale, loss_out, ws);
+    static thread_local int attr_dev3 = -1;
+    int dev3 = -1;
+    B200FT_CUDA(cudaGetDevice(&dev3));
+    if (dev3 != attr_dev3) {
+      B200FT_CUDA(cudaFuncSetAttribute(softmax_xent_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+      attr_dev3 = dev3;
+    }
+    const int ctas256 = 8;   // measured at V = 50257 (119 MB in flight): 8 per SM 5250 GB/s, 6 4700, 4 5150
+    softmax_xent_kernel<256><<<(unsigned)rows, 256, 220 * 1024 / ctas256 - 2048, st>>>(
+        (__nv_bfloat16*)logits, rows, vocab, ld, targets, ignore_index, grad_scale, loss_out, ws);
   } else {
     if (cap < 1) cap = 1;
     if (cap > 3) cap = 3;
     const int pad = (int)(220 * 1024 / cap) - 2048;
+    static const int force_threads = getenv("B200FT_XENT_THREADS") ? atoi(getenv("B200FT_XENT_THREADS")) : 0;   // experiments
+    const int threads = force_threads ? force_threads : 512;   // 1024-thread CTAs measured 7 % slower at the same bytes in flight
     static thread_local int attr_dev2 = -1;
     int dev = -1;
     B200FT_CUDA(cudaGetDevice(&dev));
     if (dev != attr_dev2) {
       B200FT_CUDA(cudaFuncSetAttribute(softmax_xent_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+      B200FT_CUDA(cudaFuncSetAttribute(softmax_xent_kernel<1024>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
       attr_dev2 = dev;
     }
-    softmax_xent_kernel<512><<<(unsigned)rows, 512, pad, st>>>((__nv_bfloat16*)logits, rows, vocab, ld, targets,
-                                                              ignore_index, grad_scale, loss_out, ws);
+    if (threads == 1024)
+      softmax_xent_kernel<1024><<<(unsigned)rows, 1024, pad, st>>>((__nv_bfloat16*)logits, rows, vocab, ld, targets,
+                                                                  ignore_index, grad_scale, loss_out, ws);
+    else
+      softmax_xent_kernel<512><<<(unsigned)rows, 512, pad, st>>>((__nv_bfloat16*)logits, rows, vocab, ld, targets,
+                                                                ignore_index, grad_scale, loss_out, ws);
   }
   B200FT_LAUNCH_CHECK();
   return 0;
