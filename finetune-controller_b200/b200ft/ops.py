@@ -336,7 +336,7 @@ def rmsnorm_bwd_dgamma(dy, x, rstd, dgamma):
 
 
 def embed_bwd(ids, dx, dwte, *, vocab):
-    """dwte[ids] += dx (bf16 atomics)."""
+    """dwte[ids] += dx: rows of one id summed in fp32, added to the bf16 table row once (no atomics, reproducible)."""
     global LAUNCHES
     _need_cuda(ids, dx, dwte)
     rows, d = dx.shape

@@ -44,18 +44,99 @@ rmsnorm_dgamma_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16*
   }
 }
 
-// dwte[ids[r], :] += dx[r, :]; one warp per token row, bf16x2 atomics (rows of the same token collide)
-__global__ void __launch_bounds__(256)
+// dwte[ids[r], :] += dx[r, :] without atomics and with fp32 accumulation.  One CTA per token row r.  The CTA first
+// looks for an EARLIER row with the same id: if there is one, that row's CTA (the id's "leader") does the work and this
+// one leaves.  A leader gathers every later row with its id (ascending), adds their dx rows in fp32 registers — each
+// thread owns 8 columns per pass — and adds the sum to the table row once, in bf16: one rounding however often a
+// token occurs (real text repeats some ids hundreds of times per step; bf16 atomics would drop the small addends and
+// depend on arrival order), and the same bits every run.  Scanning the ids costs rows^2 * 8 bytes of L2 reads in
+// total: 134 MB at the 4096 rows of a full-parameter micro-batch.
+constexpr int kEmbThreads = 256;
+constexpr int kEmbMaxDup = 2048;   // duplicates of one id gathered per pass of the list (more: further passes)
+constexpr int kEmbVec = 4;         // 16-byte vectors per thread: d <= 256 * 4 * 8 = 8192
+
+__global__ void __launch_bounds__(kEmbThreads)
 embed_bwd_kernel(const int64_t* __restrict__ ids, const __nv_bfloat16* __restrict__ dx,
                  __nv_bfloat16* __restrict__ dwte, int64_t rows, int d, int vocab) {
-  const int64_t row = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
-  if (row >= rows) return;
-  const int lane = threadIdx.x & 31;
-  int64_t id = ids[row];
-  id = id < 0 ? 0 : (id >= vocab ? vocab - 1 : id);  // same clamp as the forward gather
-  const __nv_bfloat162* src = reinterpret_cast<const __nv_bfloat162*>(dx + row * d);
-  __nv_bfloat162* dst = reinterpret_cast<__nv_bfloat162*>(dwte + id * d);
-  for (int i = lane; i < (d >> 1); i += 32) atomicAdd(dst + i, src[i]);
+  __shared__ int s_found;
+  __shared__ int s_cnt;
+  __shared__ int s_list[kEmbMaxDup];
+  __shared__ int s_warp[kEmbThreads / 32];
+  const int64_t row = blockIdx.x;
+  const int tid = threadIdx.x;
+  auto clamp = [&](int64_t id) { return id < 0 ? (int64_t)0 : (id >= vocab ? (int64_t)vocab - 1 : id); };  // as the forward gather
+  const int64_t id = clamp(ids[row]);
+  if (tid == 0) { s_found = 0; s_cnt = 0; }
+  __syncthreads();
+  // ---- an earlier row with this id?  (chunked so that the CTA can stop at the first hit)
+  for (int64_t base = 0; base < row; base += kEmbThreads * 8) {
+    int hit = 0;
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      const int64_t r = base + (int64_t)u * kEmbThreads + tid;
+      if (r < row && clamp(ids[r]) == id) hit = 1;
+    }
+    if (hit) s_found = 1;
+    __syncthreads();
+    if (s_found) return;
+  }
+  // ---- leader: this row, then every later row with the same id, kEmbMaxDup of them per pass of the list, in
+  // ascending order; the fp32 sums stay in registers across the passes (a thread owns up to kEmbVec 16-byte vectors)
+  const int nvec = d >> 3;
+  float acc[kEmbVec][8];
+#pragma unroll
+  for (int vi = 0; vi < kEmbVec; ++vi)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[vi][j] = 0.f;
+  int64_t next = row;            // first row not yet looked at
+  while (next < rows) {
+    __syncthreads();
+    if (tid == 0) s_cnt = 0;
+    __syncthreads();
+    // gather matches in [next, rows) until the list is full; a chunk is taken whole or not at all, so order is kept
+    int64_t base = next;
+    for (; base < rows; base += kEmbThreads) {
+      if (s_cnt + kEmbThreads > kEmbMaxDup) break;
+      const int64_t r = base + tid;
+      const bool m = r < rows && (r == row || clamp(ids[r]) == id);
+      // ordered compaction inside the chunk: warp ballots + a prefix over the 8 warps
+      const unsigned bal = __ballot_sync(0xffffffffu, m);
+      if ((tid & 31) == 0) s_warp[tid >> 5] = __popc(bal);
+      __syncthreads();
+      int off = s_cnt;
+      for (int w = 0; w < (tid >> 5); ++w) off += s_warp[w];
+      if (m) s_list[off + __popc(bal & ((1u << (tid & 31)) - 1u))] = (int)(r - row);
+      __syncthreads();
+      if (tid == 0) { int t = 0; for (int w = 0; w < kEmbThreads / 32; ++w) t += s_warp[w]; s_cnt += t; }
+      __syncthreads();
+    }
+    next = base;
+    const int cnt = s_cnt;
+#pragma unroll
+    for (int vi = 0; vi < kEmbVec; ++vi) {
+      const int v0 = tid + vi * kEmbThreads;
+      if (v0 < nvec) {
+        for (int k = 0; k < cnt; ++k) {
+          float f[8];
+          unpack8(ld_stream16(dx + (row + s_list[k]) * d + (v0 << 3)), f);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) acc[vi][j] += f[j];
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int vi = 0; vi < kEmbVec; ++vi) {
+    const int v0 = tid + vi * kEmbThreads;
+    if (v0 < nvec) {
+      __nv_bfloat16* dst = dwte + id * d + (v0 << 3);
+      float t[8];
+      unpack8(*reinterpret_cast<const uint4*>(dst), t);   // what is there already (a tied lm_head's gradient)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) t[j] += acc[vi][j];
+      *reinterpret_cast<uint4*>(dst) = pack8(t);
+    }
+  }
 }
 
 }  // namespace
@@ -83,8 +164,10 @@ extern "C" int b200ft_rmsnorm_bwd_dgamma(const void* dy, const void* x, const fl
 
 extern "C" int b200ft_embed_bwd(const int64_t* ids, const void* dx, void* dwte, int64_t rows, int d, int vocab,
                                 void* stream) {
-  B200FT_CHECK_ARG(ids && dx && dwte && rows > 0 && d > 0 && d % 2 == 0 && vocab > 0, "embed_bwd: bad arguments");
-  embed_bwd_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, (cudaStream_t)stream>>>(
+  B200FT_CHECK_ARG(ids && dx && dwte && rows > 0 && rows < (1ll << 31) && d > 0 && d % 8 == 0 && d <= 8192 && vocab > 0 &&
+                       ((uintptr_t)dx | (uintptr_t)dwte) % 16 == 0,
+                   "embed_bwd: rows=%lld d=%d (d must be a multiple of 8 and <= 8192, buffers 16-byte aligned)", (long long)rows, d);
+  embed_bwd_kernel<<<(unsigned)rows, kEmbThreads, 0, (cudaStream_t)stream>>>(
       ids, (const __nv_bfloat16*)dx, (__nv_bfloat16*)dwte, rows, d, vocab);
   B200FT_LAUNCH_CHECK();
   return 0;

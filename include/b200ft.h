@@ -255,8 +255,10 @@ int b200ft_embed_fwd(const int64_t* ids, const void* wte, const void* wpe, void*
  * these two cover what is not a GEMM.  Oracle: autograd of oracle/llama_lora_ref.py rmsnorm() /
  * F.embedding under FullOracleTrainer.
  *   rmsnorm_bwd_dgamma: dgamma[c] += sum_r dy[r,c] * x[r,c] * rstd[r]   (fp32 atomics: zero it first)
- *   embed_bwd:          dwte[ids[r], :] += dx[r, :]                      (bf16x2 atomics into the
- *                       bf16 gradient table; ids clamped to [0, vocab) like b200ft_embed_fwd)
+ *   embed_bwd:          dwte[ids[r], :] += dx[r, :]   (no atomics: the first row of every id sums all rows
+ *                       of that id in fp32 and adds the sum to the bf16 table row once — one rounding however
+ *                       often a token repeats, bit-reproducible; ids clamped to [0, vocab) like b200ft_embed_fwd;
+ *                       d a multiple of 8)
  * --------------------------------------------------------------------------------------- */
 int b200ft_rmsnorm_bwd_dgamma(const void* dy, const void* x, const float* rstd, float* dgamma,
                               int64_t rows, int d, void* stream);
