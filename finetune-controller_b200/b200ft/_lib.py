@@ -1,7 +1,7 @@
 """ctypes binding of libb200ft.so (the C ABI declared in include/b200ft.h).
 
-There is no fallback: if the shared library has not been built (``__graft_entry__.build()``
-or ``make -C finetune-controller_b200/csrc``) importing an op raises, and every op raises on
+There is no fallback: if the shared library has not been built (``__graft_entry__.build()``, i.e. one
+``nvcc -gencode arch=compute_100a,code=sm_100a -shared`` over ``csrc/*.cu``) importing an op raises, and every op raises on
 a non-zero return code with the library's own error string.
 """
 from __future__ import annotations

@@ -83,11 +83,17 @@ class StepHostMixin:
         torch.cuda.current_stream().synchronize()
         return float(self._loss_host[0])
 
+    def state_parts(self) -> tuple[dict, dict]:
+        """(small metadata dict, {name: DEVICE tensor}) — everything needed to continue training.  The payload writes
+        the tensors one at a time, so the host never holds more than one of them (train.save_state)."""
+        meta = {"step": self.step_count, "r": self.lora.r, "alpha": self.lora.alpha, "n_layer": self.dims.n_layer,
+                "d_model": self.dims.d_model}
+        return meta, {"P": self.P, "m": self.Mo, "v": self.Vo}
+
     def state_dict(self) -> dict:
-        """Everything needed to continue training: fp32 master adapters, Adam moments, step."""
-        return {"P": self.P.detach().cpu(), "m": self.Mo.detach().cpu(),
-                "v": self.Vo.detach().cpu(), "step": self.step_count,
-                "r": self.lora.r, "alpha": self.lora.alpha, "n_layer": self.dims.n_layer, "d_model": self.dims.d_model}
+        """state_parts() as one dict of CPU tensors (tests, small models)."""
+        meta, tensors = self.state_parts()
+        return {**meta, **{k: t.detach().cpu() for k, t in tensors.items()}}
 
     def load_state_dict(self, st: dict) -> None:
         want = (self.lora.r, self.dims.n_layer, self.dims.d_model)

@@ -179,11 +179,11 @@ class LlamaFullStep(StepHostMixin, OwnAttentionMixin):
             out += [self.dW["embed"].view(-1), self.Gn]
         return out
 
-    def state_dict(self) -> dict:
-        return {"P": self.P.detach().cpu(), "m": self.Mo.detach().cpu(),
-                "v": self.Vo.detach().cpu(), "Pn": self.Pn.detach().cpu(),
-                "mn": self.Mn.detach().cpu(), "vn": self.Vn.detach().cpu(),
-                "step": self.step_count, "mode": "full", "n_layer": self.dims.n_layer, "d_model": self.dims.d_model}
+    def state_parts(self) -> tuple[dict, dict]:
+        """(metadata, {name: DEVICE tensor}): 12 bytes per parameter — 96 GB for Llama-3-8B, which is why the payload
+        writes the tensors one at a time (train.save_state) instead of building one host dict."""
+        meta = {"step": self.step_count, "mode": "full", "n_layer": self.dims.n_layer, "d_model": self.dims.d_model}
+        return meta, {"P": self.P, "m": self.Mo, "v": self.Vo, "Pn": self.Pn, "mn": self.Mn, "vn": self.Vn}
 
     def load_state_dict(self, st: dict) -> None:
         if st.get("mode") != "full" or st["P"].numel() != self.P.numel() or st["Pn"].numel() != self.Pn.numel():

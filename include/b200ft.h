@@ -97,7 +97,7 @@ typedef struct b200ft_gemm_args {
   int32_t max_ctas;               /* 0 = one per SM */
   int32_t split_k;                /* ATOMIC_F32_T only: 0 = choose, else number of K splits */
   int32_t cta_group;              /* 0 = choose; 1 = one CTA per 128 x block_n tile; 2 = CTA pair per
-                                     256 x block_n tile (K-major operands, non-atomic epilogue only) */
+                                     256 x block_n tile (K-major or MN-major operands; non-atomic epilogues only) */
 } b200ft_gemm_args;
 
 int b200ft_gemm_bf16(const b200ft_gemm_args* args_host, void* stream);

@@ -144,5 +144,5 @@ def test_resources_and_patterns_fit_the_deployer(plugin_cls):
     # AWS_JOB_SYNC_INTERVAL by the sidecar (PyTorchJobDeployer.py:122-139)
     sys.path.insert(0, os.path.join(ROOT, "finetune-controller_b200"))
     from b200ft.train import STATE_FILE
-    for kept_local in (STATE_FILE, STATE_FILE + ".tmp"):
+    for kept_local in (STATE_FILE, STATE_FILE + ".tmp", STATE_FILE + ".P.000000100", STATE_FILE + ".vn.000000100"):
         assert not any(fnmatch.fnmatch(kept_local, pat) for pat in inst.store_asset_patterns), kept_local
