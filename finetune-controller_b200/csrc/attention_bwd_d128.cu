@@ -113,7 +113,7 @@ attn_bwd_d128_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_co
   if (warp == 1 && lane == 0) {
     mbar_init(f_full, 1); mbar_init(f_empty, 1);
     for (uint32_t s = 0; s < kRing; ++s) { mbar_init(st_full(s), 1); mbar_init(st_empty(s), 1); }
-    mbar_init(sdp_full(0), 1); mbar_init(sdp_full(1), 1); mbar_init(pds_full(0), 16); mbar_init(pds_full(1), 16);
+    mbar_init(sdp_full(0), 1); mbar_init(sdp_full(1), 1); mbar_init(pds_full(0), 8); mbar_init(pds_full(1), 8);
     mbar_init(acc_full, 1); mbar_init(acc_free, 16);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -219,18 +219,19 @@ attn_bwd_d128_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_co
       const uint64_t half = (uint64_t)h * moff(4);
       const uint64_t m0 = (st ? mS0[1] : mS0[0]) + half, m1 = (st ? mS1[1] : mS1[0]) + half;
       if (issuer) {
-        // a thread of slice `part` packed its 16 columns into the first 8 of them: reduction step k reads column 16*k
+        // a thread packed its 32 columns into the first 16 of them: reduction step k (16 rows) reads its A operand at
+        // column 32*(k/2) + 8*(k%2) of the buffer
         if (MODE == 0) {
 #pragma unroll
           for (int k = 0; k < (int)kSub / 16; ++k)   // dV += P^T dO: 16 queries per step
-            umma_ts(tmem + kColAcc0, tmem + kColS + kSub * bf + 16u * (uint32_t)k, m1 + moff(k), id_g, !(first && k == 0));
+            umma_ts(tmem + kColAcc0, tmem + kColS + kSub * bf + 32u * (uint32_t)(k >> 1) + 8u * (uint32_t)(k & 1), m1 + moff(k), id_g, !(first && k == 0));
 #pragma unroll
           for (int k = 0; k < (int)kSub / 16; ++k)   // dK += dS^T Q
-            umma_ts(tmem + kColAcc1, tmem + kColDP + kSub * bf + 16u * (uint32_t)k, m0 + moff(k), id_g, !(first && k == 0));
+            umma_ts(tmem + kColAcc1, tmem + kColDP + kSub * bf + 32u * (uint32_t)(k >> 1) + 8u * (uint32_t)(k & 1), m0 + moff(k), id_g, !(first && k == 0));
         } else {
 #pragma unroll
           for (int k = 0; k < (int)kSub / 16; ++k)   // dQ += dS K: 16 keys per step
-            umma_ts(tmem + kColAcc0, tmem + kColDP + kSub * bf + 16u * (uint32_t)k, m0 + moff(k), id_g, !(first && k == 0));
+            umma_ts(tmem + kColAcc0, tmem + kColDP + kSub * bf + 32u * (uint32_t)(k >> 1) + 8u * (uint32_t)(k & 1), m0 + moff(k), id_g, !(first && k == 0));
         }
         if (h == 1u) umma_commit(st_empty(st));   // both halves consumed: the streamed pair's slot may be refilled
       }
@@ -257,15 +258,25 @@ attn_bwd_d128_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_co
     }
   } else if (warp >= 4) {
     // ================================ softmax / dS ================================
-    // Four warps per TMEM lane quarter; a thread owns one lane L (a key in MODE 0, a query in MODE 1) and, in every
-    // sub-pair, the 16 columns 16*part .. +15 of the [128 x 64] buffer (queries in MODE 0, keys in MODE 1).
+    // Two COHORTS of eight warps: cohort c works on the sub-pairs with g & 1 == c, i.e. on S / dP buffer c, always the
+    // same half (rows 64c .. 64c+63) of every streamed tile pair.  tcgen05.ld moves 64 bytes per clock per SM, so reading
+    // the [128 x 64] fp32 S and dP of a sub-pair costs 1024 cycles — as long as its UMMAs.  With all sixteen warps on the
+    // same sub-pair they read together and then compute together (2140 cycles per sub-pair measured); staggered, one
+    // cohort's reads run under the other's exponentials.  Inside a cohort: two warps per TMEM lane quarter; a thread
+    // owns one lane L (a key in MODE 0, a query in MODE 1) and the 32 columns 32*part .. +31 of its buffer.
+    const int idx = warp - 4;
+    const int cohort = idx >> 3;
     const int quarter = warp & 3;
-    const int part = (warp - 4) >> 2;
+    const int part = (idx >> 2) & 1;
+    const int part4 = idx >> 2;                            // 0..3: the accumulator slice this warp writes out per item
     const int L = quarter * 32 + lane;
-    const int sm_tid = (warp - 4) * 32 + lane;             // 0..511 among the softmax warps
+    const int co_tid = (idx & 7) * 32 + lane;              // 0..255 inside the cohort
     const uint32_t t_lane = tmem + ((uint32_t)(quarter * 32) << 16);
+    const uint32_t bf = (uint32_t)cohort;
+    const uint32_t t_s = t_lane + kColS + kSub * bf + 32u * (uint32_t)part;
+    const uint32_t t_dp = t_lane + kColDP + kSub * bf + 32u * (uint32_t)part;
     const f32x2_t sc2 = pk2(p.scale_log2, p.scale_log2);
-    uint32_t g = 0, n = 0;
+    uint32_t gp = 0, n = 0;                                // gp: tile PAIRS done so far (this cohort's sub-pair is 2*gp + cohort)
     for (int w = item_at(0); w < num_items; w = item_at(++n)) {
       const Item it = decode_item<MODE>(p, w, G);
       // log-sum-exp and D of a query row; rows past the end of the sequence get lse = +inf: P = dS = 0
@@ -273,87 +284,80 @@ attn_bwd_d128_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_co
         const int qr = qt_ * kB + r;
         lse_o = INFINITY; dl_o = 0.f;
         if (qr < p.seq) {
-          const int64_t idx = ((int64_t)it.b * p.n_head + hq) * p.seq + qr;
-          lse_o = __ldg(p.lse2 + idx); dl_o = __ldg(p.delta + idx);
+          const int64_t idx2 = ((int64_t)it.b * p.n_head + hq) * p.seq + qr;
+          lse_o = __ldg(p.lse2 + idx2); dl_o = __ldg(p.delta + idx2);
         }
       };
-      // MODE 0: the statistics belong to the COLUMNS and change with every streamed tile pair.  Threads 0..127 of the
-      // softmax warps fetch the next pair's values one pair ahead (global-memory latency off the critical path) and
-      // publish them in shared memory, double-buffered, when the pair starts.
+      // MODE 0: the statistics belong to the COLUMNS and change with every streamed tile pair.  Threads 0..63 of a
+      // cohort fetch the values of ITS 64 query rows one pair ahead (global-memory latency off the critical path) and
+      // publish them in shared memory, double-buffered, when the pair starts (one 256-thread named barrier per cohort).
       float lse = INFINITY, dl = 0.f, lse_next = INFINITY, dl_next = 0.f;
       if (MODE == 1) row_stats(it.hx, it.fixed_tile, L, lse, dl);
-      else if (sm_tid < kB) row_stats(it.hk * G, it.fixed_tile, sm_tid, lse_next, dl_next);
-      for (int t2 = 0; t2 < 2 * it.n_iter; ++t2, ++g) {
-        const int t = t2 >> 1, h = t2 & 1;               // streamed tile pair, half of it
-        const uint32_t pr = g >> 1, bf = g & 1u;
+      else if (co_tid < 64) row_stats(it.hk * G, it.fixed_tile, 64 * cohort + co_tid, lse_next, dl_next);
+      for (int t = 0; t < it.n_iter; ++t, ++gp) {
         int qt, kt;
         if (MODE == 0) { qt = it.fixed_tile + t % it.per_head; kt = it.fixed_tile; }
         else           { qt = it.fixed_tile; kt = t; }
         const bool diag = qt == kt;
-        const float* st_lse = stat + (pr & 1u) * 2 * kB + 64 * h;
-        const float* st_dl = st_lse + kB;
-        if (MODE == 0 && h == 0) {
-          if (sm_tid < kB) {
-            stat[(pr & 1u) * 2 * kB + sm_tid] = lse_next;
-            stat[(pr & 1u) * 2 * kB + kB + sm_tid] = dl_next;
-            if (t + 1 < it.n_iter)
-              row_stats(it.hk * G + (t + 1) / it.per_head, it.fixed_tile + (t + 1) % it.per_head, sm_tid, lse_next, dl_next);
-          }
-          named_bar_sync(1, 512);   // the 16 softmax warps: this pair's statistics are visible
-        }
-        const uint32_t t_s = t_lane + kColS + kSub * bf + 16u * (uint32_t)part;
-        const uint32_t t_dp = t_lane + kColDP + kSub * bf + 16u * (uint32_t)part;
-        const int c0 = 64 * h + 16 * part;               // first of this thread's columns, as a row of the streamed tile
-        // ---- phase A: P = exp2(S*c - lse) for this thread's 16 columns (kept in registers for phase B) ----
-        f32x2_t P2[8];
-        float cl[16], cd[16];                            // MODE 0: this thread's 16 column statistics (four 16-byte loads each)
+        float* st_lse = stat + (gp & 1u) * 2 * kB + 64 * cohort;     // this cohort's 64 columns
+        float* st_dl = st_lse + kB;
         if (MODE == 0) {
-#pragma unroll
-          for (int v = 0; v < 4; ++v) {
-            const float4 a = *reinterpret_cast<const float4*>(st_lse + 16 * part + 4 * v);
-            const float4 d = *reinterpret_cast<const float4*>(st_dl + 16 * part + 4 * v);
-            cl[4 * v] = a.x; cl[4 * v + 1] = a.y; cl[4 * v + 2] = a.z; cl[4 * v + 3] = a.w;
-            cd[4 * v] = d.x; cd[4 * v + 1] = d.y; cd[4 * v + 2] = d.z; cd[4 * v + 3] = d.w;
+          if (co_tid < 64) {
+            st_lse[co_tid] = lse_next;
+            st_dl[co_tid] = dl_next;
+            if (t + 1 < it.n_iter)
+              row_stats(it.hk * G + (t + 1) / it.per_head, it.fixed_tile + (t + 1) % it.per_head, 64 * cohort + co_tid,
+                        lse_next, dl_next);
           }
+          named_bar_sync(1 + cohort, 256);   // the cohort's eight warps: this pair's statistics are visible
         }
-        mbar_wait(sdp_full(bf), (g >> 1) & 1u);
+        const int c0 = 64 * cohort + 32 * part;          // first of this thread's columns, as a row of the streamed tile
+        // ---- phase A: P = exp2(S*c - lse) for this thread's 32 columns (kept in registers for phase B) ----
+        f32x2_t P2[16];
+        mbar_wait(sdp_full(bf), gp & 1u);
         tc_fence_after();
-        uint32_t rs[16], rd[16];
-        tmem_ld16(t_s, rs);
-        tmem_ld16(t_dp, rd);
-        tmem_wait_ld();
+        {
+          uint32_t rs[32];
+          tmem_ld32(t_s, rs);
+          tmem_wait_ld();
 #pragma unroll
-        for (int i = 0; i < 16; i += 2) {
-          const int c = c0 + i;
-          f32x2_t nl2;
-          if (MODE == 0) nl2 = pk2(-cl[i], -cl[i + 1]); else nl2 = pk2(-lse, -lse);
-          float e0, e1;
-          upk2(fma2(pk2(__uint_as_float(rs[i]), __uint_as_float(rs[i + 1])), sc2, nl2), e0, e1);
-          float p0 = ex2(e0), p1 = ex2(e1);   // lse = +inf (row past the sequence): exp2(-inf) = 0
-          if (diag) {                        // warp-uniform; causal: key index > query index contributes nothing
-            const bool m0 = MODE == 0 ? (L > c) : (c > L);
-            const bool m1 = MODE == 0 ? (L > c + 1) : (c + 1 > L);
-            if (m0) p0 = 0.f;
-            if (m1) p1 = 0.f;
+          for (int i = 0; i < 32; i += 2) {
+            const int c = c0 + i;
+            f32x2_t nl2;
+            if (MODE == 0) { const float2 a = *reinterpret_cast<const float2*>(st_lse + 32 * part + i); nl2 = pk2(-a.x, -a.y); }
+            else nl2 = pk2(-lse, -lse);
+            float e0, e1;
+            upk2(fma2(pk2(__uint_as_float(rs[i]), __uint_as_float(rs[i + 1])), sc2, nl2), e0, e1);
+            float p0 = ex2(e0), p1 = ex2(e1);   // lse = +inf (row past the sequence): exp2(-inf) = 0
+            if (diag) {                        // warp-uniform; causal: key index > query index contributes nothing
+              const bool m0 = MODE == 0 ? (L > c) : (c > L);
+              const bool m1 = MODE == 0 ? (L > c + 1) : (c + 1 > L);
+              if (m0) p0 = 0.f;
+              if (m1) p1 = 0.f;
+            }
+            P2[i >> 1] = pk2(p0, p1);
           }
-          P2[i >> 1] = pk2(p0, p1);
         }
-        if (MODE == 0) {   // P^T as bf16 over this thread's own first 8 score columns: A operand of dV += P^T dO
-          uint32_t wp[8];
+        if (MODE == 0) {   // P^T as bf16 over this thread's own first 16 score columns: A operand of dV += P^T dO
+          uint32_t wp[16];
 #pragma unroll
-          for (int i = 0; i < 8; ++i) wp[i] = f32x2_to_bf16x2(P2[i]);
-          tmem_st8(t_s, wp);
+          for (int i = 0; i < 16; ++i) wp[i] = f32x2_to_bf16x2(P2[i]);
+          tmem_st16(t_s, wp);
         }
         // ---- phase B: dS' = P * (dP - D) (the softmax scale multiplies the dK / dQ accumulators once, at the end) ----
         {
-          uint32_t wd[8];
+          uint32_t rd[32];
+          tmem_ld32(t_dp, rd);
+          tmem_wait_ld();
+          uint32_t wd[16];
 #pragma unroll
-          for (int i = 0; i < 8; ++i) {
+          for (int i = 0; i < 16; ++i) {
             f32x2_t dl2;
-            if (MODE == 0) dl2 = pk2(cd[2 * i], cd[2 * i + 1]); else dl2 = pk2(dl, dl);
+            if (MODE == 0) { const float2 a = *reinterpret_cast<const float2*>(st_dl + 32 * part + 2 * i); dl2 = pk2(a.x, a.y); }
+            else dl2 = pk2(dl, dl);
             wd[i] = f32x2_to_bf16x2(mul2(P2[i], sub2(pk2(__uint_as_float(rd[2 * i]), __uint_as_float(rd[2 * i + 1])), dl2)));
           }
-          tmem_st8(t_dp, wd);
+          tmem_st16(t_dp, wd);
         }
         tmem_wait_st();
         tc_fence_before();
@@ -366,9 +370,9 @@ attn_bwd_d128_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_co
       const int orow = it.fixed_tile * kB + L;   // key row (MODE 0) or query row (MODE 1)
       if (MODE == 0) {
         // slices 0, 1 write the two 64-column halves of dV (accumulator 0), slices 2, 3 those of dK (accumulator 1)
-        const uint32_t t_acc = t_lane + ((part >> 1) == 0 ? kColAcc0 : kColAcc1) + 64u * (uint32_t)(part & 1);
-        const int col = ((part >> 1) == 0 ? p.v_off : p.k_off) + it.hk * kDH + 64 * (part & 1);
-        const float oscale = (part >> 1) == 0 ? 1.f : p.scale;
+        const uint32_t t_acc = t_lane + ((part4 >> 1) == 0 ? kColAcc0 : kColAcc1) + 64u * (uint32_t)(part4 & 1);
+        const int col = ((part4 >> 1) == 0 ? p.v_off : p.k_off) + it.hk * kDH + 64 * (part4 & 1);
+        const float oscale = (part4 >> 1) == 0 ? 1.f : p.scale;
         uint32_t r[64];
         tmem_ld32(t_acc, r);
         tmem_ld32(t_acc + 32, r + 32);
@@ -389,13 +393,13 @@ attn_bwd_d128_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_co
       } else {
         // dQ: the four slices write 32 columns each
         uint32_t r[32];
-        tmem_ld32(t_lane + kColAcc0 + 32u * (uint32_t)part, r);
+        tmem_ld32(t_lane + kColAcc0 + 32u * (uint32_t)part4, r);
         tmem_wait_ld();
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(acc_free);
         if (orow < p.seq) {
-          __nv_bfloat16* dst = p.dqkv + ((int64_t)it.b * p.seq + orow) * p.ld_d + p.q_off + it.hx * kDH + 32 * part;
+          __nv_bfloat16* dst = p.dqkv + ((int64_t)it.b * p.seq + orow) * p.ld_d + p.q_off + it.hx * kDH + 32 * part4;
 #pragma unroll
           for (int v = 0; v < 4; ++v) {
             float fv[8];
