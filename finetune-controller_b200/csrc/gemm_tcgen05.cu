@@ -767,9 +767,11 @@ int choose_block_n(int M, int N, int units, int tile_m) {
   double best_cost = -1.0;
   // time ~ waves x per-tile time; per FLOP a narrower tile re-reads more of A from L2 and keeps the
   // tensor pipe less busy (measured on the step's shapes, profiles/README.md): relative efficiency
-  // 1.0 / 0.90 / 0.75 for BN = 256 / 192 / 128.  A narrower tile only wins when it saves a whole wave.
+  // 1.0 / 0.82 / 0.68 for BN = 256 / 192 / 128.  A narrower tile only wins when it saves more than a whole wave:
+  // at 32768 x 768 (384 tiles of BN 256 = 5.2 waves of 74 pairs, 512 of BN 192 = 6.9) BN 256 is still the faster one
+  // (K = 768 / 2320 / 3072: 38.0 / 98.1 / 120.1 us against 41.8 / 109.0 / 129.4 with BN 192; profiles/r02_gemm_probe_bn.log).
   const int bns[3] = {256, 192, 128};
-  const double eff[3] = {1.0, 0.90, 0.75};
+  const double eff[3] = {1.0, 0.82, 0.68};
   for (int i = 0; i < 3; ++i) {
     const int bn = bns[i];
     long tiles = (long)tiles_m * ((N + bn - 1) / bn);
