@@ -118,6 +118,9 @@ int b200ft_lora_grad(const void* s, int64_t ld_s, int r, const void* t, int64_t 
  * oracle/gpt2_lora_ref.py:softmax_xent_ref).  logits bf16 [rows, ld], the first `vocab`
  * columns valid; overwritten in place with d(loss)/d(logits) * grad_scale (padding columns
  * and ignored rows get 0).  loss_out[0] = mean over rows whose target != ignore_index.
+ * A target outside [0, vocab) other than ignore_index is treated like an ignored one (no loss, zero
+ * gradient row, not counted in the mean) and counted in 32-bit scratch word 2, which the host may read
+ * after the call has completed (word 0: number of valid targets).
  * Scratch: b200ft_softmax_xent_workspace_bytes(rows) bytes.
  * ------------------------------------------------------------------------------------- */
 size_t b200ft_softmax_xent_workspace_bytes(int64_t rows);
@@ -216,7 +219,7 @@ int b200ft_swiglu_bwd_act(const void* dact, const void* gate_up, void* dgate_up,
  * q starts at column q_off + h*d_head, kv head g at k_off + g*d_head / v_off + g*d_head, with
  * g = h / (n_head / n_kv_head) (grouped-query attention).  out [batch*seq, ld_out] receives head h
  * at column h*d_head; lse2 [batch*n_head, seq] receives max + log2(sum) of the scaled scores in
- * the log2 domain (what the backward needs).  d_head = 64 only; other sizes return
+ * the log2 domain (what the backward needs).  d_head = 64 or 128; other sizes return
  * B200FT_ERR_UNSUPPORTED.  seq may be ragged (not a multiple of the 128-row tile).
  * ------------------------------------------------------------------------------------- */
 int b200ft_attn_fwd(const void* qkv, int64_t ld, int q_off, int k_off, int v_off, void* out, int64_t ld_out,
