@@ -25,6 +25,7 @@ __global__ void __launch_bounds__(256)
 adamw_kernel(float* __restrict__ p, float* __restrict__ m, float* __restrict__ v,
              const void* __restrict__ g, __nv_bfloat16* __restrict__ shadow, int64_t n,
              AdamScalars s, const float* __restrict__ grad_scale_dev) {
+  grid_dep_sync();
   if (grad_scale_dev) s.grad_scale *= __ldg(grad_scale_dev);
   const int64_t nvec = n >> 3;  // 8 elements per thread per iteration
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
@@ -74,6 +75,7 @@ template <bool G_BF16>
 __global__ void __launch_bounds__(256)
 sumsq_kernel(const void* __restrict__ g, int64_t n, float* __restrict__ partials,
              unsigned int* __restrict__ ticket, float* __restrict__ out) {
+  grid_dep_sync();
   float acc = 0.f;
   const int64_t nvec = n >> 3;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
@@ -124,6 +126,7 @@ sumsq_kernel(const void* __restrict__ g, int64_t n, float* __restrict__ partials
 }
 
 __global__ void clip_coef_kernel(const float* norm_sq, float max_norm, float pre_scale, float* coef) {
+  grid_dep_sync();
   float nrm = sqrtf(norm_sq[0]) * pre_scale;
   coef[0] = fminf(1.f, max_norm / (nrm + 1e-6f));
 }
@@ -165,9 +168,9 @@ extern "C" int b200ft_adamw_step_limited(float* p, float* m, float* v, const voi
   if (max_blocks > 0 && blocks > max_blocks) blocks = max_blocks;
   cudaStream_t st = (cudaStream_t)stream;
   if (g_is_bf16)
-    adamw_kernel<true><<<blocks, 256, 0, st>>>(p, m, v, g, (__nv_bfloat16*)shadow_bf16, n, s, grad_scale_dev);
+    launch_k(adamw_kernel<true>, blocks, 256, 0, st, p, m, v, g, (__nv_bfloat16*)shadow_bf16, n, s, grad_scale_dev);
   else
-    adamw_kernel<false><<<blocks, 256, 0, st>>>(p, m, v, g, (__nv_bfloat16*)shadow_bf16, n, s, grad_scale_dev);
+    launch_k(adamw_kernel<false>, blocks, 256, 0, st, p, m, v, g, (__nv_bfloat16*)shadow_bf16, n, s, grad_scale_dev);
   B200FT_LAUNCH_CHECK();
   return 0;
 }
@@ -190,15 +193,15 @@ extern "C" int b200ft_gradnorm_sq(const void* g, int g_is_bf16, int64_t n, float
   B200FT_CUDA(cudaMemsetAsync(ticket, 0, sizeof(unsigned int), st));
   int64_t want = ((n >> 3) + 255) / 256;
   int blocks = (int)(want < 1 ? 1 : (want > kSumsqBlocks ? kSumsqBlocks : want));
-  if (g_is_bf16) sumsq_kernel<true><<<blocks, 256, 0, st>>>(g, n, partials, ticket, out_sq);
-  else sumsq_kernel<false><<<blocks, 256, 0, st>>>(g, n, partials, ticket, out_sq);
+  if (g_is_bf16) launch_k(sumsq_kernel<true>, blocks, 256, 0, st, g, n, partials, ticket, out_sq);
+  else launch_k(sumsq_kernel<false>, blocks, 256, 0, st, g, n, partials, ticket, out_sq);
   B200FT_LAUNCH_CHECK();
   return 0;
 }
 
 extern "C" int b200ft_clip_coef(const float* norm_sq, float max_norm, float pre_scale, float* coef, void* stream) {
   B200FT_CHECK_ARG(norm_sq && coef && max_norm > 0.f, "clip_coef: bad arguments");
-  clip_coef_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(norm_sq, max_norm, pre_scale, coef);
+  launch_k(clip_coef_kernel, 1, 1, 0, (cudaStream_t)stream, norm_sq, max_norm, pre_scale, coef);
   B200FT_LAUNCH_CHECK();
   return 0;
 }

@@ -137,6 +137,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm, const AttnParams p) {
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot_ptr;
+  grid_dep_sync();  // the prologue above overlaps the previous kernel's tail; global memory only from here on
 
   // Persistent launches deal the items (heaviest first) out in a snake: round n hands item n*grid + b to CTA b when n
   // is even and n*grid + (grid-1-b) when n is odd; with one CTA per item (grid = items) only round 0 exists.
@@ -519,8 +520,7 @@ extern "C" int b200ft_attn_fwd(const void* qkv, int64_t ld, int q_off, int k_off
   // placement balances the very unequal items better than the static walk (T >= 2048: 2-3 % faster).
   const bool persistent = p.nq_tiles <= 8 && items > B200FT_NUM_SMS;
   const unsigned grid = (unsigned)(persistent ? B200FT_NUM_SMS : items);
-  if (d_head == 64) attn_fwd_kernel<64><<<grid, kThreads, Cfg<64>::kSmemBytes, (cudaStream_t)stream>>>(tm, p);
-  else              attn_fwd_kernel<128><<<grid, kThreads, Cfg<128>::kSmemBytes, (cudaStream_t)stream>>>(tm, p);
-  B200FT_LAUNCH_CHECK();
+  if (d_head == 64) B200FT_CUDA(launch_k(attn_fwd_kernel<64>, grid, kThreads, Cfg<64>::kSmemBytes, (cudaStream_t)stream, tm, p));
+  else              B200FT_CUDA(launch_k(attn_fwd_kernel<128>, grid, kThreads, Cfg<128>::kSmemBytes, (cudaStream_t)stream, tm, p));
   return 0;
 }

@@ -59,6 +59,7 @@ __global__ void __launch_bounds__(256)
 attn_delta_kernel(const __nv_bfloat16* __restrict__ o, int64_t ld_o, const __nv_bfloat16* __restrict__ dout,
                   int64_t ld_do, float* __restrict__ delta, int batch, int seq, int n_head) {
   constexpr int kUPH = DH / 8;                                        // 16-byte units per head: 8 or 16 lanes
+  grid_dep_sync();
   const int64_t tok = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);   // b * seq + t
   if (tok >= (int64_t)batch * seq) return;
   const int lane = threadIdx.x & 31;
@@ -156,6 +157,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot_ptr;
+  grid_dep_sync();  // the prologue above overlaps the previous kernel's tail; global memory only from here on
 
   // Items are sorted heaviest first and dealt out in a snake: round n hands item n*grid + b to CTA b when n is even and
   // n*grid + (grid-1-b) when n is odd, so a CTA that drew a heavy item in one round draws a light one in the next.
@@ -583,34 +585,27 @@ extern "C" int b200ft_attn_bwd(const void* qkv, int64_t ld, int q_off, int k_off
   cudaStream_t st = (cudaStream_t)stream;
   const int64_t rows = (int64_t)batch * seq;
   if (d_head == 128) {
-    attn_delta_kernel<128><<<(unsigned)((rows + 7) / 8), 256, 0, st>>>((const __nv_bfloat16*)out, ld_out,
-                                                                       (const __nv_bfloat16*)dout, ld_dout, delta,
-                                                                       batch, seq, n_head);
-    B200FT_LAUNCH_CHECK();
+    B200FT_CUDA(launch_k(attn_delta_kernel<128>, (unsigned)((rows + 7) / 8), 256, 0, st, (const __nv_bfloat16*)out, ld_out,
+                         (const __nv_bfloat16*)dout, ld_dout, delta, batch, seq, n_head));
     Bwd128Args a;
     a.batch = batch; a.seq = seq; a.n_head = n_head; a.n_kv_head = n_kv_head;
     a.q_off = q_off; a.k_off = k_off; a.v_off = v_off; a.scale = scale;
     a.lse2 = lse2; a.delta = delta; a.dqkv = (__nv_bfloat16*)dqkv; a.ld_d = ld_dqkv;
     return launch_bwd_d128(tm_qkv, tm_do, a, st);
   }
-  attn_delta_kernel<64><<<(unsigned)((rows + 7) / 8), 256, 0, st>>>((const __nv_bfloat16*)out, ld_out,
-                                                                    (const __nv_bfloat16*)dout, ld_dout, delta, batch,
-                                                                    seq, n_head);
-  B200FT_LAUNCH_CHECK();
+  B200FT_CUDA(launch_k(attn_delta_kernel<64>, (unsigned)((rows + 7) / 8), 256, 0, st, (const __nv_bfloat16*)out, ld_out,
+                       (const __nv_bfloat16*)dout, ld_dout, delta, batch, seq, n_head));
   // persistent: one CTA per SM walks the work items (heaviest first, round-robin)
   const int items0 = p.n_tiles * batch * n_kv_head, items1 = p.n_tiles * batch * n_head;
   const unsigned grid0 = (unsigned)(items0 < B200FT_NUM_SMS ? items0 : B200FT_NUM_SMS);
   if (split) {
-    attn_bwd_kernel<0><<<grid0, kThreads, kSmemBytes, st>>>(tm_qkv, tm_do, tm_dq, p);
-    B200FT_LAUNCH_CHECK();
-    attn_bwd_kernel<1><<<(unsigned)(items1 < B200FT_NUM_SMS ? items1 : B200FT_NUM_SMS), kThreads, kSmemBytes, st>>>(
-        tm_qkv, tm_do, tm_dq, p);
-    B200FT_LAUNCH_CHECK();
+    B200FT_CUDA(launch_k(attn_bwd_kernel<0>, grid0, kThreads, kSmemBytes, st, tm_qkv, tm_do, tm_dq, p));
+    B200FT_CUDA(launch_k(attn_bwd_kernel<1>, (unsigned)(items1 < B200FT_NUM_SMS ? items1 : B200FT_NUM_SMS), kThreads,
+                         kSmemBytes, st, tm_qkv, tm_do, tm_dq, p));
     return 0;
   }
   // zero the q columns (a strided DMA fill, no kernel); dk | dv are written whole by the kernel
   B200FT_CUDA(cudaMemset2DAsync((__nv_bfloat16*)dqkv + q_off, (size_t)ld_dqkv * 2, 0, (size_t)n_head * kDH * 2, (size_t)rows, st));
-  attn_bwd_kernel<2><<<grid0, kThreads, kSmemBytes, st>>>(tm_qkv, tm_do, tm_dq, p);
-  B200FT_LAUNCH_CHECK();
+  B200FT_CUDA(launch_k(attn_bwd_kernel<2>, grid0, kThreads, kSmemBytes, st, tm_qkv, tm_do, tm_dq, p));
   return 0;
 }

@@ -125,6 +125,7 @@ attn_bwd_d128_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_co
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot_ptr;
+  grid_dep_sync();  // the prologue above overlaps the previous kernel's tail; global memory only from here on
 
   // Items are sorted heaviest first and dealt out in a snake: round n hands item n*grid + b to CTA b when n is even and
   // n*grid + (grid-1-b) when n is odd, so a CTA that drew a heavy item in one round draws a light one in the next.
@@ -440,11 +441,9 @@ int b200ft_attn::launch_bwd_d128(const CUtensorMap& tm_qkv, const CUtensorMap& t
   }
   // persistent: one CTA per SM walks the work items (heaviest first, round-robin)
   const int items0 = p.n_tiles * a.batch * a.n_kv_head, items1 = p.n_tiles * a.batch * a.n_head;
-  attn_bwd_d128_kernel<0><<<(unsigned)(items0 < B200FT_NUM_SMS ? items0 : B200FT_NUM_SMS), kThreads, kSmemBytes, st>>>(
-      tm_qkv, tm_do, p);
-  B200FT_LAUNCH_CHECK();
-  attn_bwd_d128_kernel<1><<<(unsigned)(items1 < B200FT_NUM_SMS ? items1 : B200FT_NUM_SMS), kThreads, kSmemBytes, st>>>(
-      tm_qkv, tm_do, p);
-  B200FT_LAUNCH_CHECK();
+  B200FT_CUDA(launch_k(attn_bwd_d128_kernel<0>, (unsigned)(items0 < B200FT_NUM_SMS ? items0 : B200FT_NUM_SMS), kThreads,
+                       kSmemBytes, st, tm_qkv, tm_do, p));
+  B200FT_CUDA(launch_k(attn_bwd_d128_kernel<1>, (unsigned)(items1 < B200FT_NUM_SMS ? items1 : B200FT_NUM_SMS), kThreads,
+                       kSmemBytes, st, tm_qkv, tm_do, p));
   return 0;
 }

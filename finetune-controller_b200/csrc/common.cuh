@@ -49,9 +49,40 @@ void b200ft_set_error(const char* fmt, ...);
   } while (0)
 
 // ----------------------------------------------------------------------------------
+// kernel launch: one path for every kernel of the library
+// ----------------------------------------------------------------------------------
+#ifdef __CUDACC__
+bool b200ft_pdl_enabled();  // abi.cu: B200FT_PDL=0 in the environment turns programmatic dependent launch off
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_k(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                            Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = b200ft_pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, args...);
+}
+#endif
+
+// ----------------------------------------------------------------------------------
 // device helpers
 // ----------------------------------------------------------------------------------
 #ifdef __CUDACC__
+
+// Programmatic dependent launch.  Every kernel of the library is launched with the programmatic-stream-serialization
+// attribute (launch_k below): its CTAs may be scheduled while the previous kernel of the stream is still draining, so
+// that block dispatch and the prologue (barrier init, TMEM allocation, descriptor prefetch) run under the predecessor's
+// tail instead of after it.  grid_dep_sync() is the point up to which that is safe: it returns once the
+// predecessor grid has completed and its writes are visible, and then lets the NEXT kernel's CTAs be scheduled.
+// Nothing before it may read or write global memory.  Without the launch attribute both instructions are no-ops.
+__device__ __forceinline__ void grid_dep_sync() {
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
 
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll

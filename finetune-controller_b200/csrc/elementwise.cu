@@ -10,6 +10,7 @@ __global__ void __launch_bounds__(256)
 embed_fwd_kernel(const int64_t* __restrict__ ids, const __nv_bfloat16* __restrict__ wte,
                  const __nv_bfloat16* __restrict__ wpe, __nv_bfloat16* __restrict__ x, int64_t rows,
                  int seq, int d, int vocab) {
+  grid_dep_sync();
   const int64_t row = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
   if (row >= rows) return;
   const int lane = threadIdx.x & 31;
@@ -37,6 +38,7 @@ embed_fwd_kernel(const int64_t* __restrict__ ids, const __nv_bfloat16* __restric
 __global__ void __launch_bounds__(256)
 transpose_bf16_kernel(const __nv_bfloat16* __restrict__ in, int64_t ld_in, __nv_bfloat16* __restrict__ out,
                       int64_t ld_out, int rows, int cols) {
+  grid_dep_sync();
   __shared__ __nv_bfloat16 tile[32][34];
   const int c0 = blockIdx.x * 32, r0 = blockIdx.y * 32;
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
@@ -55,6 +57,7 @@ transpose_bf16_kernel(const __nv_bfloat16* __restrict__ in, int64_t ld_in, __nv_
 
 __global__ void __launch_bounds__(256)
 cast_f32_bf16_kernel(const float* __restrict__ in, __nv_bfloat16* __restrict__ out, int64_t n) {
+  grid_dep_sync();
   const int64_t nvec = n >> 3;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += stride) {
@@ -74,7 +77,7 @@ extern "C" int b200ft_embed_fwd(const int64_t* ids, const void* wte, const void*
   B200FT_CHECK_ARG(ids && wte && x, "embed_fwd: null buffer");
   B200FT_CHECK_ARG(rows > 0 && seq > 0 && d > 0 && d % 8 == 0 && vocab > 0,
                    "embed_fwd: rows=%lld seq=%d d=%d vocab=%d", (long long)rows, seq, d, vocab);
-  embed_fwd_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, (cudaStream_t)stream>>>(
+  launch_k(embed_fwd_kernel, (unsigned)((rows + 7) / 8), 256, 0, (cudaStream_t)stream,
       ids, (const __nv_bfloat16*)wte, (const __nv_bfloat16*)wpe, (__nv_bfloat16*)x, rows, seq, d, vocab);
   B200FT_LAUNCH_CHECK();
   return 0;
@@ -86,7 +89,7 @@ extern "C" int b200ft_transpose_bf16(const void* in, int64_t ld_in, void* out, i
                    "transpose_bf16: rows=%d cols=%d ld_in=%lld ld_out=%lld", rows, cols,
                    (long long)ld_in, (long long)ld_out);
   dim3 grid((cols + 31) / 32, (rows + 31) / 32);
-  transpose_bf16_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(
+  launch_k(transpose_bf16_kernel, grid, 256, 0, (cudaStream_t)stream,
       (const __nv_bfloat16*)in, ld_in, (__nv_bfloat16*)out, ld_out, rows, cols);
   B200FT_LAUNCH_CHECK();
   return 0;
@@ -104,7 +107,7 @@ extern "C" int b200ft_cast_f32_to_bf16(const float* in, void* out, int64_t n, vo
   if (n == 0) return 0;
   int64_t want = ((n >> 3) + 255) / 256;
   int blocks = (int)(want < 1 ? 1 : (want > B200FT_NUM_SMS * 8 ? B200FT_NUM_SMS * 8 : want));
-  cast_f32_bf16_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(in, (__nv_bfloat16*)out, n);
+  launch_k(cast_f32_bf16_kernel, blocks, 256, 0, (cudaStream_t)stream, in, (__nv_bfloat16*)out, n);
   B200FT_LAUNCH_CHECK();
   return 0;
 }

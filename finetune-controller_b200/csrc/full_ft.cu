@@ -13,6 +13,7 @@ __global__ void __launch_bounds__(256)
 rmsnorm_dgamma_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
                       const float* __restrict__ rstd, float* __restrict__ dgamma, int64_t rows, int d,
                       int64_t rows_per_block) {
+  grid_dep_sync();
   __shared__ float part[8][256 + 8];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int c = blockIdx.x * 256 + 8 * lane;
@@ -58,6 +59,7 @@ constexpr int kEmbVec = 4;         // 16-byte vectors per thread: d <= 256 * 4 *
 __global__ void __launch_bounds__(kEmbThreads)
 embed_bwd_kernel(const int64_t* __restrict__ ids, const __nv_bfloat16* __restrict__ dx,
                  __nv_bfloat16* __restrict__ dwte, int64_t rows, int d, int vocab) {
+  grid_dep_sync();
   __shared__ int s_found;
   __shared__ int s_cnt;
   __shared__ int s_list[kEmbMaxDup];
@@ -156,7 +158,7 @@ extern "C" int b200ft_rmsnorm_bwd_dgamma(const void* dy, const void* x, const fl
   if (chunks > 65535) chunks = 65535;
   const int64_t rpb = (rows + chunks - 1) / chunks;
   dim3 grid(col_blocks, (unsigned)((rows + rpb - 1) / rpb));
-  rmsnorm_dgamma_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(
+  launch_k(rmsnorm_dgamma_kernel, grid, 256, 0, (cudaStream_t)stream,
       (const __nv_bfloat16*)dy, (const __nv_bfloat16*)x, rstd, dgamma, rows, d, rpb);
   B200FT_LAUNCH_CHECK();
   return 0;
@@ -167,7 +169,7 @@ extern "C" int b200ft_embed_bwd(const int64_t* ids, const void* dx, void* dwte, 
   B200FT_CHECK_ARG(ids && dx && dwte && rows > 0 && rows < (1ll << 31) && d > 0 && d % 8 == 0 && d <= 8192 && vocab > 0 &&
                        ((uintptr_t)dx | (uintptr_t)dwte) % 16 == 0,
                    "embed_bwd: rows=%lld d=%d (d must be a multiple of 8 and <= 8192, buffers 16-byte aligned)", (long long)rows, d);
-  embed_bwd_kernel<<<(unsigned)rows, kEmbThreads, 0, (cudaStream_t)stream>>>(
+  launch_k(embed_bwd_kernel, (unsigned)rows, kEmbThreads, 0, (cudaStream_t)stream,
       ids, (const __nv_bfloat16*)dx, (__nv_bfloat16*)dwte, rows, d, vocab);
   B200FT_LAUNCH_CHECK();
   return 0;

@@ -524,6 +524,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ TmapPack maps, const GemmParams
   else cluster_sync_all();  // the peer's barriers must be initialised before anything remote touches them
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot_ptr;
+  grid_dep_sync();  // everything above ran under the previous kernel's tail; global memory is touched only below
 
   const int num_work = p.tiles_m * p.tiles_n * p.splits;
   const int kb_total = p.kb_prefix[p.nseg];
@@ -934,8 +935,7 @@ extern "C" int b200ft_gemm_bf16(const b200ft_gemm_args* a, void* stream) {
   const int num_work = p.tiles_m * p.tiles_n * p.splits;
   if (cg == 1) {
     const int grid = num_work < ctas_max ? num_work : ctas_max;
-    gemm_bf16_tcgen05_kernel<1><<<grid, kThreads, kSmemBytes, (cudaStream_t)stream>>>(maps, p);
-    B200FT_LAUNCH_CHECK();
+    B200FT_CUDA(launch_k(gemm_bf16_tcgen05_kernel<1>, grid, kThreads, kSmemBytes, (cudaStream_t)stream, maps, p));
     return 0;
   }
   // cta_group::2: clusters of two CTAs (one TPC); work items go to pairs
@@ -947,10 +947,12 @@ extern "C" int b200ft_gemm_bf16(const b200ft_gemm_args* a, void* stream) {
   cfg.blockDim = dim3(kThreads);
   cfg.dynamicSmemBytes = kSmemBytes;
   cfg.stream = (cudaStream_t)stream;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
-  cfg.attrs = attr; cfg.numAttrs = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr; cfg.numAttrs = b200ft_pdl_enabled() ? 2 : 1;
   B200FT_CUDA(cudaLaunchKernelEx(&cfg, gemm_bf16_tcgen05_kernel<2>, maps, p));
   return 0;
 }

@@ -20,6 +20,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32, VPL <= 4 ? 4 : 1)
 layernorm_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ gamma,
                      const float* __restrict__ beta, __nv_bfloat16* __restrict__ y,
                      float* __restrict__ mean, float* __restrict__ rstd, int64_t rows, int d, float eps) {
+  grid_dep_sync();
   const int lane = threadIdx.x & 31;
   const int64_t row0 = ((int64_t)blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5)) * kRowsPerWarp;
   if (row0 >= rows) return;
@@ -93,6 +94,7 @@ layernorm_bwd_dx_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat1
                         const float* __restrict__ gamma, const float* __restrict__ mean,
                         const float* __restrict__ rstd, const __nv_bfloat16* __restrict__ dres,
                         __nv_bfloat16* __restrict__ dx, int64_t rows, int d) {
+  grid_dep_sync();
   const int lane = threadIdx.x & 31;
   const int64_t row0 = ((int64_t)blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5)) * kRowsPerWarp;
   if (row0 >= rows) return;
@@ -193,8 +195,8 @@ extern "C" int b200ft_layernorm_fwd(const void* x, const float* gamma, const flo
   unsigned blocks = (unsigned)((rows + rows_per_block - 1) / rows_per_block);
   int vpl = vpl_for(d);
 #define CALL(V)                                                                                     \
-  layernorm_fwd_kernel<V><<<blocks, kWarpsPerBlock * 32, 0, st>>>(                                   \
-      (const __nv_bfloat16*)x, gamma, beta, (__nv_bfloat16*)y, mean, rstd, rows, d, eps)
+  launch_k(layernorm_fwd_kernel<V>, blocks, kWarpsPerBlock * 32, 0, st,                              \
+           (const __nv_bfloat16*)x, gamma, beta, (__nv_bfloat16*)y, mean, rstd, rows, d, eps)
   LN_DISPATCH(vpl, CALL)
 #undef CALL
   B200FT_LAUNCH_CHECK();
@@ -212,9 +214,9 @@ extern "C" int b200ft_layernorm_bwd_dx(const void* dy, const void* x, const floa
   unsigned blocks = (unsigned)((rows + rows_per_block - 1) / rows_per_block);
   int vpl = vpl_for(d);
 #define CALL(V)                                                                                     \
-  layernorm_bwd_dx_kernel<V><<<blocks, kWarpsPerBlock * 32, 0, st>>>(                                \
-      (const __nv_bfloat16*)dy, (const __nv_bfloat16*)x, gamma, mean, rstd, (const __nv_bfloat16*)dres, \
-      (__nv_bfloat16*)dx, rows, d)
+  launch_k(layernorm_bwd_dx_kernel<V>, blocks, kWarpsPerBlock * 32, 0, st,                           \
+           (const __nv_bfloat16*)dy, (const __nv_bfloat16*)x, gamma, mean, rstd, (const __nv_bfloat16*)dres, \
+           (__nv_bfloat16*)dx, rows, d)
   LN_DISPATCH(vpl, CALL)
 #undef CALL
   B200FT_LAUNCH_CHECK();

@@ -16,6 +16,7 @@ template <int VPL, int kRowsPerWarp>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32)
 rmsnorm_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ gamma,
                    __nv_bfloat16* __restrict__ y, float* __restrict__ rstd, int64_t rows, int d, float eps) {
+  grid_dep_sync();
   const int lane = threadIdx.x & 31;
   const int64_t row0 = ((int64_t)blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5)) * kRowsPerWarp;
   if (row0 >= rows) return;
@@ -70,6 +71,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32)
 rmsnorm_bwd_dx_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
                       const float* __restrict__ gamma, const float* __restrict__ rstd,
                       const __nv_bfloat16* __restrict__ dres, __nv_bfloat16* __restrict__ dx, int64_t rows, int d) {
+  grid_dep_sync();
   const int lane = threadIdx.x & 31;
   const int64_t row0 = ((int64_t)blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5)) * kRowsPerWarp;
   if (row0 >= rows) return;
@@ -153,6 +155,7 @@ template <int VPL>
 __global__ void __launch_bounds__(kWideThreads)
 rmsnorm_fwd_wide_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ gamma,
                         __nv_bfloat16* __restrict__ y, float* __restrict__ rstd, int d, float eps) {
+  grid_dep_sync();
   __shared__ float red[4];
   const int64_t row = blockIdx.x;
   const int nvec = d >> 3;
@@ -193,6 +196,7 @@ __global__ void __launch_bounds__(kWideThreads)
 rmsnorm_bwd_dx_wide_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
                            const float* __restrict__ gamma, const float* __restrict__ rstd,
                            const __nv_bfloat16* __restrict__ dres, __nv_bfloat16* __restrict__ dx, int d) {
+  grid_dep_sync();
   __shared__ float red[4];
   const int64_t row = blockIdx.x;
   const int nvec = d >> 3;
@@ -260,15 +264,15 @@ extern "C" int b200ft_rmsnorm_fwd(const void* x, const float* gamma, void* y, fl
     const int wv = ((d >> 3) + kWideThreads - 1) / kWideThreads;
     const __nv_bfloat16* xi = (const __nv_bfloat16*)x;
     __nv_bfloat16* yo = (__nv_bfloat16*)y;
-    if (wv <= 2) rmsnorm_fwd_wide_kernel<2><<<(unsigned)rows, kWideThreads, 0, st>>>(xi, gamma, yo, rstd, d, eps);
-    else rmsnorm_fwd_wide_kernel<4><<<(unsigned)rows, kWideThreads, 0, st>>>(xi, gamma, yo, rstd, d, eps);
+    if (wv <= 2) launch_k(rmsnorm_fwd_wide_kernel<2>, (unsigned)rows, kWideThreads, 0, st, xi, gamma, yo, rstd, d, eps);
+    else launch_k(rmsnorm_fwd_wide_kernel<4>, (unsigned)rows, kWideThreads, 0, st, xi, gamma, yo, rstd, d, eps);
     B200FT_LAUNCH_CHECK();
     return 0;
   }
   int vpl = vpl_for(d);
 #define CALL(V, R)                                                                                  \
-  rmsnorm_fwd_kernel<V, R><<<(unsigned)((rows + kWarpsPerBlock * R - 1) / (kWarpsPerBlock * R)),      \
-                             kWarpsPerBlock * 32, 0, st>>>((const __nv_bfloat16*)x, gamma,           \
+  launch_k(rmsnorm_fwd_kernel<V, R>, (unsigned)((rows + kWarpsPerBlock * R - 1) / (kWarpsPerBlock * R)), \
+                             kWarpsPerBlock * 32, 0, st, (const __nv_bfloat16*)x, gamma,           \
                                                            (__nv_bfloat16*)y, rstd, rows, d, eps)
   RMS_DISPATCH(vpl, CALL)
 #undef CALL
@@ -286,15 +290,15 @@ extern "C" int b200ft_rmsnorm_bwd_dx(const void* dy, const void* x, const float*
     const int wv = ((d >> 3) + kWideThreads - 1) / kWideThreads;
     const __nv_bfloat16 *dyi = (const __nv_bfloat16*)dy, *xi = (const __nv_bfloat16*)x, *ri = (const __nv_bfloat16*)dres;
     __nv_bfloat16* o = (__nv_bfloat16*)dx;
-    if (wv <= 2) rmsnorm_bwd_dx_wide_kernel<2><<<(unsigned)rows, kWideThreads, 0, st>>>(dyi, xi, gamma, rstd, ri, o, d);
-    else rmsnorm_bwd_dx_wide_kernel<4><<<(unsigned)rows, kWideThreads, 0, st>>>(dyi, xi, gamma, rstd, ri, o, d);
+    if (wv <= 2) launch_k(rmsnorm_bwd_dx_wide_kernel<2>, (unsigned)rows, kWideThreads, 0, st, dyi, xi, gamma, rstd, ri, o, d);
+    else launch_k(rmsnorm_bwd_dx_wide_kernel<4>, (unsigned)rows, kWideThreads, 0, st, dyi, xi, gamma, rstd, ri, o, d);
     B200FT_LAUNCH_CHECK();
     return 0;
   }
   int vpl = vpl_for(d);
 #define CALL(V, R)                                                                                     \
-  rmsnorm_bwd_dx_kernel<V, R><<<(unsigned)((rows + kWarpsPerBlock * R - 1) / (kWarpsPerBlock * R)),      \
-                                kWarpsPerBlock * 32, 0, st>>>(                                          \
+  launch_k(rmsnorm_bwd_dx_kernel<V, R>, (unsigned)((rows + kWarpsPerBlock * R - 1) / (kWarpsPerBlock * R)), \
+                                kWarpsPerBlock * 32, 0, st,                                           \
       (const __nv_bfloat16*)dy, (const __nv_bfloat16*)x, gamma, rstd, (const __nv_bfloat16*)dres,       \
       (__nv_bfloat16*)dx, rows, d)
   RMS_DISPATCH(vpl, CALL)

@@ -11,6 +11,7 @@ namespace {
 __global__ void __launch_bounds__(256)
 rope_kernel(__nv_bfloat16* __restrict__ x, int64_t ld, int64_t rows, int seq, int n_heads, int dh,
             const float* __restrict__ cos_t, const float* __restrict__ sin_t, float sign) {
+  grid_dep_sync();
   const int half = dh >> 1;
   const int vph = half >> 3;  // 8-wide vectors per half head
   const int64_t per_row = (int64_t)n_heads * vph;
@@ -47,6 +48,7 @@ __device__ __forceinline__ float sigmoid_f(float x) { return __fdividef(1.f, 1.f
 // gu [rows, 2*ff]: gate in columns [0, ff), up in [ff, 2*ff).  act = silu(gate) * up.
 __global__ void __launch_bounds__(256)
 swiglu_fwd_kernel(const __nv_bfloat16* __restrict__ gu, __nv_bfloat16* __restrict__ act, int64_t rows, int ff) {
+  grid_dep_sync();
   const int vpr = ff >> 3;
   const int64_t total = rows * vpr;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
@@ -66,6 +68,7 @@ swiglu_fwd_kernel(const __nv_bfloat16* __restrict__ gu, __nv_bfloat16* __restric
 __global__ void __launch_bounds__(256)
 swiglu_bwd_kernel(const __nv_bfloat16* __restrict__ dact, const __nv_bfloat16* __restrict__ gu,
                   __nv_bfloat16* __restrict__ dgu, __nv_bfloat16* __restrict__ act, int64_t rows, int ff) {
+  grid_dep_sync();
   const int vpr = ff >> 3;
   const int64_t total = rows * vpr;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
@@ -99,7 +102,7 @@ extern "C" int b200ft_rope_inplace(void* x, int64_t ld, int64_t rows, int seq, i
                    "rope: rows=%lld seq=%d heads=%d d_head=%d ld=%lld (d_head %% 16 == 0, ld %% 8 == 0)",
                    (long long)rows, seq, n_heads, d_head, (long long)ld);
   const int64_t total = rows * n_heads * (d_head / 16);
-  rope_kernel<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+  launch_k(rope_kernel, (unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream,
       (__nv_bfloat16*)x, ld, rows, seq, n_heads, d_head, cos_table, sin_table, backward ? -1.f : 1.f);
   B200FT_LAUNCH_CHECK();
   return 0;
@@ -111,7 +114,7 @@ extern "C" int b200ft_swiglu_fwd(const void* gate_up, void* act, int64_t rows, i
   const int64_t total = rows * (d_ff / 8);
   int64_t want = (total + 255) / 256;
   int blocks = (int)(want > B200FT_NUM_SMS * 16 ? B200FT_NUM_SMS * 16 : want);
-  swiglu_fwd_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)gate_up, (__nv_bfloat16*)act, rows, d_ff);
+  launch_k(swiglu_fwd_kernel, blocks, 256, 0, (cudaStream_t)stream, (const __nv_bfloat16*)gate_up, (__nv_bfloat16*)act, rows, d_ff);
   B200FT_LAUNCH_CHECK();
   return 0;
 }
@@ -128,7 +131,7 @@ extern "C" int b200ft_swiglu_bwd_act(const void* dact, const void* gate_up, void
   const int64_t total = rows * (d_ff / 8);
   int64_t want = (total + 255) / 256;
   int blocks = (int)(want > B200FT_NUM_SMS * 16 ? B200FT_NUM_SMS * 16 : want);
-  swiglu_bwd_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)dact, (const __nv_bfloat16*)gate_up,
+  launch_k(swiglu_bwd_kernel, blocks, 256, 0, (cudaStream_t)stream, (const __nv_bfloat16*)dact, (const __nv_bfloat16*)gate_up,
                                                                (__nv_bfloat16*)dgate_up, (__nv_bfloat16*)act, rows, d_ff);
   B200FT_LAUNCH_CHECK();
   return 0;

@@ -35,6 +35,7 @@ constexpr float kLn2 = 0.6931471805599453f;
 __global__ void __launch_bounds__(256)
 count_valid_kernel(const int64_t* __restrict__ targets, int64_t rows, int64_t ignore_index, int vocab,
                    unsigned int* __restrict__ ws) {
+  grid_dep_sync();
   // single CTA: rows is at most a few 10^5, this is ~1 us and keeps the count exact
   unsigned int c = 0, bad = 0;
   for (int64_t i = threadIdx.x; i < rows; i += blockDim.x) {
@@ -82,6 +83,7 @@ __global__ void __launch_bounds__(kThreads)
 softmax_xent_kernel(__nv_bfloat16* __restrict__ logits, int64_t rows, int vocab, int64_t ld,
                     const int64_t* __restrict__ targets, int64_t ignore_index, float grad_scale,
                     float* __restrict__ loss_out, unsigned int* __restrict__ ws) {
+  grid_dep_sync();
   const int64_t row = blockIdx.x;
   __nv_bfloat16* z = logits + row * ld;
   const int nvec = (int)(ld >> 3);  // the whole padded row is rewritten
@@ -275,6 +277,7 @@ __global__ void __launch_bounds__(kCThreads, 1)
 softmax_xent_staged_kernel(__nv_bfloat16* __restrict__ logits, int64_t rows, int vocab, int64_t ld,
                            const int64_t* __restrict__ targets, int64_t ignore_index, float grad_scale,
                            float* __restrict__ loss_out, unsigned int* __restrict__ ws) {
+  grid_dep_sync();
   extern __shared__ __align__(128) uint8_t cx_smem[];
   __shared__ __align__(8) unsigned long long full_bar[kCStages];
   __shared__ float red_m[kCThreads / 32], red_s[kCThreads / 32];
@@ -466,6 +469,7 @@ softmax_xent_staged_kernel(__nv_bfloat16* __restrict__ logits, int64_t rows, int
 
 __global__ void shift_targets_kernel(const int64_t* __restrict__ labels, int64_t* __restrict__ targets,
                                      int64_t total, int seq, int64_t ignore_index) {
+  grid_dep_sync();
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= total) return;
   int t = (int)(i % seq);
@@ -478,7 +482,7 @@ namespace {
 // Both entry points launch through here.  ws: the scratch words described at the top of the file.
 int launch_xent(void* logits, int64_t rows, int vocab, int64_t ld, const int64_t* targets, int64_t ignore_index,
                 float grad_scale, float* loss_out, unsigned int* ws, cudaStream_t st) {
-  count_valid_kernel<<<1, 256, 0, st>>>(targets, rows, ignore_index, vocab, ws);
+  launch_k(count_valid_kernel, 1, 256, 0, st, targets, rows, ignore_index, vocab, ws);
   B200FT_LAUNCH_CHECK();
   const int64_t nvec = ld >> 3;
   static const bool legacy = getenv("B200FT_XENT_LEGACY") != nullptr;   // A/B measurements: two-sweep kernel only
@@ -497,7 +501,7 @@ int launch_xent(void* logits, int64_t rows, int vocab, int64_t ld, const int64_t
       attr_dev = dev;
     }
     const unsigned grid = (unsigned)(rows < B200FT_NUM_SMS ? rows : B200FT_NUM_SMS);   // persistent, one CTA per SM
-    softmax_xent_staged_kernel<<<grid, kCThreads, kCSmemBytes, st>>>((__nv_bfloat16*)logits, rows, vocab, ld, targets,
+    launch_k(softmax_xent_staged_kernel, grid, kCThreads, kCSmemBytes, st, (__nv_bfloat16*)logits, rows, vocab, ld, targets,
                                                                      ignore_index, grad_scale, loss_out, ws);
     B200FT_LAUNCH_CHECK();
     return 0;
@@ -522,7 +526,7 @@ int launch_xent(void* logits, int64_t rows, int vocab, int64_t ld, const int64_t
       attr_dev3 = dev3;
     }
     const int ctas256 = 8;   // measured at V = 50257 (119 MB in flight): 8 per SM 5250 GB/s, 6 4700, 4 5150
-    softmax_xent_kernel<256><<<(unsigned)rows, 256, 220 * 1024 / ctas256 - 2048, st>>>(
+    launch_k(softmax_xent_kernel<256>, (unsigned)rows, 256, 220 * 1024 / ctas256 - 2048, st,
         (__nv_bfloat16*)logits, rows, vocab, ld, targets, ignore_index, grad_scale, loss_out, ws);
   } else {
     if (cap < 1) cap = 1;
@@ -539,10 +543,10 @@ int launch_xent(void* logits, int64_t rows, int vocab, int64_t ld, const int64_t
       attr_dev2 = dev;
     }
     if (threads == 1024)
-      softmax_xent_kernel<1024><<<(unsigned)rows, 1024, pad, st>>>((__nv_bfloat16*)logits, rows, vocab, ld, targets,
+      launch_k(softmax_xent_kernel<1024>, (unsigned)rows, 1024, pad, st, (__nv_bfloat16*)logits, rows, vocab, ld, targets,
                                                                   ignore_index, grad_scale, loss_out, ws);
     else
-      softmax_xent_kernel<512><<<(unsigned)rows, 512, pad, st>>>((__nv_bfloat16*)logits, rows, vocab, ld, targets,
+      launch_k(softmax_xent_kernel<512>, (unsigned)rows, 512, pad, st, (__nv_bfloat16*)logits, rows, vocab, ld, targets,
                                                                 ignore_index, grad_scale, loss_out, ws);
   }
   B200FT_LAUNCH_CHECK();
@@ -637,7 +641,7 @@ extern "C" int b200ft_shift_targets(const int64_t* labels, int64_t* targets, int
                                     int64_t ignore_index, void* stream) {
   B200FT_CHECK_ARG(labels && targets && batch > 0 && seq > 0, "shift_targets: bad arguments");
   int64_t total = batch * seq;
-  shift_targets_kernel<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+  launch_k(shift_targets_kernel, (unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream,
       labels, targets, total, seq, ignore_index);
   B200FT_LAUNCH_CHECK();
   return 0;
