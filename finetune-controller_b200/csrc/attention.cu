@@ -54,7 +54,15 @@ template <int DH> struct Cfg {
   // inside its own score columns, at 64h, so that no thread overwrites scores its partner has yet to read.
   static constexpr uint32_t kHalfP = kAliasP ? 64u : 32u;      // column distance between the two halves of a P row
 };
-constexpr float kRescaleThreshold = 8.0f;       // log2 units: p stays below 2^8
+constexpr float kRescaleThreshold = 8.0f;
+
+#ifdef B200FT_ATTN_TIMING   // per-phase clock readings of CTA 0 (tools/attn_timing.py); never defined in the shipped build
+__device__ long long g_tlog[2][4096][2];
+__device__ int g_tcnt[2];
+#define TLOG(role, tag) do { if (blockIdx.x == 0) { int i__ = g_tcnt[role]++; if (i__ < 4096) { g_tlog[role][i__][0] = (tag); g_tlog[role][i__][1] = clock64(); } } } while (0)
+#else
+#define TLOG(role, tag) do { } while (0)
+#endif       // log2 units: p stays below 2^8
 
 struct AttnParams {
   int batch, seq, n_head, n_kv_head;
@@ -272,26 +280,33 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm, const AttnParams p) {
         // order, so the new scores land after P has been read); while tile A's softmax works on S_A(j+1) the
         // tensor core runs P_B V(j) and S_B(j+1)
         if (j < nA) {
+          if (issuer) TLOG(1, 10);
           mbar_wait(p_full(0), parA);
           tc_fence_after();
+          if (issuer) TLOG(1, 11);
           issue_pv(0, st, j == 0);
         }
         if (j + 1 < nA) {
           mbar_wait(k_full(nst), nph); k_next_ready = true;
           mbar_wait(s_free(0), parA);
           tc_fence_after();
+          if (issuer) TLOG(1, 12);
           issue_s(0, nst);
         }
         if (j < nB) {
+          if (issuer) TLOG(1, 13);
           mbar_wait(p_full(1), parB);
           tc_fence_after();
+          if (issuer) TLOG(1, 14);
           issue_pv(1, st, j == 0);
         }
         if (j + 1 < nB) {
           if (!k_next_ready) mbar_wait(k_full(nst), nph);
           mbar_wait(s_free(1), parB);
           tc_fence_after();
+          if (issuer) TLOG(1, 15);
           issue_s(1, nst);
+          if (issuer) TLOG(1, 16);
         }
       }
       if (issuer) umma_commit(v_empty(st));
@@ -346,8 +361,11 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm, const AttnParams p) {
     float m_ref = -INFINITY, l = 0.f;             // l: partial row sum over my columns
     for (int j = 0; j < n_mine; ++j) {
       const uint32_t par = (cg + (uint32_t)j) & 1u;
+      const bool tl = (warp == 4 && lane == 0);
+      if (tl) TLOG(0, 0);
       mbar_wait(s_full(g), par);
       tc_fence_after();
+      if (tl) TLOG(0, 1);
       const bool diag = (j == qt);
       const int kbase = j * kBK + 64 * half;      // first key of my columns
       // rescale my columns of this warp's rows of O in TMEM by alpha (rows whose reference stays pass alpha = 1).
@@ -372,6 +390,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm, const AttnParams p) {
       tmem_ld32(t_s, r);
       tmem_ld32(t_s + 32, r + 32);
       tmem_wait_ld();
+      if (tl) TLOG(0, 2);
       if (!C::kAliasP) {
         // the scores are in registers: S_g(j+1) may be issued while this tile is exponentiated
         tc_fence_before();
@@ -390,7 +409,9 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm, const AttnParams p) {
         for (int i = 0; i < 64; ++i) m4[i & 3] = fmaxf(m4[i & 3], __uint_as_float(r[i]));
       }
       float mx = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3]));
+      if (tl) TLOG(0, 3);
       mx = fmaxf(mx, exchange(mx));                // whole-row maximum
+      if (tl) TLOG(0, 4);
       if (!C::kAliasP && j > 0) {
         // P has its own columns here: the P V UMMAs of tile j-1 must have read them (and left O quiescent) before P
         // is rewritten or O rescaled.  (Written over S, both follow from s_full(j): it was committed after P V (j-1).)
@@ -435,6 +456,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm, const AttnParams p) {
         upk2(add2(sa[0], sa[1]), s_lo, s_hi);
         l += s_lo + s_hi;
       }
+      if (tl) TLOG(0, 5);
       tmem_wait_st();
       tc_fence_before();
       __syncwarp();
@@ -442,6 +464,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm, const AttnParams p) {
         if (C::kAliasP) mbar_arrive(s_free(g));
         mbar_arrive(p_full(g));
       }
+      if (tl) TLOG(0, 6);
     }
     if (n_mine > 0) {
       // ---- all P V UMMAs of the item have retired: normalise my half of O, write it and the log-sum-exp ----
@@ -524,3 +547,17 @@ extern "C" int b200ft_attn_fwd(const void* qkv, int64_t ld, int q_off, int k_off
   else              B200FT_CUDA(launch_k(attn_fwd_kernel<128>, grid, kThreads, Cfg<128>::kSmemBytes, (cudaStream_t)stream, tm, p));
   return 0;
 }
+
+#ifdef B200FT_ATTN_TIMING
+extern "C" int b200ft_debug_attn_timing(long long* log_out, int* counts_out, int reset) {
+  if (reset) {
+    int z[2] = {0, 0};
+    B200FT_CUDA(cudaMemcpyToSymbol(g_tcnt, z, sizeof(z)));
+    return 0;
+  }
+  B200FT_CUDA(cudaDeviceSynchronize());
+  B200FT_CUDA(cudaMemcpyFromSymbol(log_out, g_tlog, sizeof(long long) * 2 * 4096 * 2));
+  B200FT_CUDA(cudaMemcpyFromSymbol(counts_out, g_tcnt, sizeof(int) * 2));
+  return 0;
+}
+#endif
