@@ -302,17 +302,20 @@ class LlamaLoRAStep(StepHostMixin, OwnAttentionMixin):
             # attention branch
             ops.gemm(dx1, W["oT"], self.da)
             dq, dk, dv = self._attn_bwd(l, self.da)
-            ops.rope_inplace(dq, self.cos, self.sin, seq=self.T, n_heads=D.n_head, d_head=D.d_head, backward=True)
-            ops.rope_inplace(dk, self.cos, self.sin, seq=self.T, n_heads=D.n_kv_head, d_head=D.d_head, backward=True)
-            # adapters: dBq = Uq^T dq, dBv = Uv^T dv, dU = s [dq Bq^T | dv Bv^T], dA = dU^T h1
+            if self.attention == "own":   # dq | dk | dv are one buffer: one launch rotates the q and k heads back
+                ops.rope_inplace(self.dqkv, self.cos, self.sin, seq=self.T, n_heads=D.n_head + D.n_kv_head,
+                                 d_head=D.d_head, backward=True)
+            else:
+                ops.rope_inplace(dq, self.cos, self.sin, seq=self.T, n_heads=D.n_head, d_head=D.d_head, backward=True)
+                ops.rope_inplace(dk, self.cos, self.sin, seq=self.T, n_heads=D.n_kv_head, d_head=D.d_head, backward=True)
+            # adapters: dBq = Uq^T dq, dBv = Uv^T dv, dU = s [dq Bq^T | dv Bv^T], dA = dU^T h1.  The q and v adapters
+            # of a layer are stacked (rows 0..15 | 16..31 of the layer's block, the other adapter's rows zero in Bq / Bv),
+            # so dU and dA take one launch each for both adapters.
             Uq, Uv = self.U[l][:, :R_PAD], self.U[l][:, R_PAD:]
-            dUq, dUv = self.dU[:, :R_PAD], self.dU[:, R_PAD:]
             ops.lora_grad(Uq, dq, self.gBq_all[o: o + R_PAD], r=R_PAD, cols=Nq)
             ops.lora_grad(Uv, dv, self.gBv_all[o + R_PAD: o + A_BLK], r=R_PAD, cols=Nkv)
-            ops.gemm(dq, self.Bq_sh[o: o + R_PAD], dUq, alpha=s)
-            ops.gemm(dv, self.Bv_sh[o + R_PAD: o + A_BLK], dUv, alpha=s)
-            ops.lora_grad(dUq, self.h1[l], self.gAt_all[o: o + R_PAD], r=R_PAD, cols=d)
-            ops.lora_grad(dUv, self.h1[l], self.gAt_all[o + R_PAD: o + A_BLK], r=R_PAD, cols=d)
+            ops.gemm(dq, self.Bq_sh[blk], self.dU, alpha=s, a2=dv, b2=self.Bv_sh[blk])
+            ops.lora_grad(self.dU, self.h1[l], self.gAt_all[blk], r=A_BLK, cols=d)
             WT = W["qkvT"]
             ops.gemm(dq, WT[:, :Nq], self.dln, a2=dk, b2=WT[:, Nq: Nq + Nkv],
                      more=[(dv, WT[:, Nq + Nkv:]), (self.dU, self.A_T[:, blk])])

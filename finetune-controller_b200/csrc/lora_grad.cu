@@ -1,5 +1,5 @@
 // Adapter-gradient contraction over the token dimension:
-//   out[i, c] += alpha * sum_m S[m, i] * T[m, c]        i < r (8 or 16), c < cols
+//   out[i, c] += alpha * sum_m S[m, i] * T[m, c]        i < r (8, 16, or 32 = two stacked adapters), c < cols
 // used for dB = (s*X*A)^T * dY  (S = U, T = dY) and dA^T = dU^T * X  (S = dU, T = X).
 //
 // Both operands have the reduction index (tokens) as their slow dimension.  That is exactly
@@ -15,7 +15,7 @@ extern "C" int b200ft_lora_grad(const void* s, int64_t ld_s, int r, const void* 
                                 int cols, int64_t m, float* out, int64_t ld_out, float alpha,
                                 void* stream) {
   B200FT_CHECK_ARG(s && t && out, "lora_grad: null buffer");
-  B200FT_CHECK_ARG((r == 8 || r == 16) && ld_s >= r && ld_s % 8 == 0, "lora_grad: r=%d ld_s=%lld (r in {8,16}, ld_s %% 8 == 0)",
+  B200FT_CHECK_ARG((r == 8 || r == 16 || r == 32) && ld_s >= r && ld_s % 8 == 0, "lora_grad: r=%d ld_s=%lld (r in {8,16,32}, ld_s %% 8 == 0)",
                    r, (long long)ld_s);
   B200FT_CHECK_ARG(cols > 0 && ld_t >= cols && ld_t % 8 == 0 && ld_out >= cols && m > 0 && m < (1ll << 31),
                    "lora_grad: cols=%d ld_t=%lld ld_out=%lld m=%lld", cols, (long long)ld_t,

@@ -105,7 +105,7 @@ int b200ft_gemm_bf16(const b200ft_gemm_args* args_host, void* stream);
 /* ---------------------------------------------------------------------------------------
  * Adapter-gradient contraction over tokens (dB = s*(XA)^T*dY,
  * dA = X^T*(s*dY*B^T)):   out[i, c] += alpha * sum_m S[m, i] * T[m, c],  i < r, c < cols.
- * S, T bf16; out fp32 [r, ld_out], accumulated into (zero it first).  r = 8 or 16; ld_s, ld_t
+ * S, T bf16; out fp32 [r, ld_out], accumulated into (zero it first).  r = 8, 16 or 32 (two stacked adapters); ld_s, ld_t
  * multiples of 8.  Runs on the tcgen05 GEMM (both operands MN-major, split-K over tokens,
  * ATOMIC_F32_T epilogue): the sum order across splits is not fixed, results are reproducible
  * to fp32 rounding, not bitwise.

@@ -232,10 +232,10 @@ def test_embed_transpose_cast(ops):
     assert torch.equal(o.cpu(), f.to(torch.bfloat16))
 
 
-@pytest.mark.parametrize("M,r,cols", [(300, 16, 192), (1000, 8, 768), (130, 16, 2304)])
+@pytest.mark.parametrize("M,r,cols", [(300, 16, 192), (1000, 8, 768), (130, 16, 2304), (4096, 32, 4096), (700, 32, 2048)])
 def test_lora_grad(ops, M, r, cols):
     g = torch.Generator().manual_seed(M)
-    S = bf16_round(torch.randn(M, 16, generator=g))
+    S = bf16_round(torch.randn(M, max(16, r), generator=g))
     T = bf16_round(torch.randn(M, cols, generator=g))
     out = torch.zeros(r, cols, device=DEV)
     ops.lora_grad(S.to(DEV, torch.bfloat16), T.to(DEV, torch.bfloat16), out, r=r, cols=cols, alpha=2.0)
