@@ -93,6 +93,7 @@ SIGNATURES = {
     "b200ft_transpose_bf16": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_int, c_int, c_void_p]),
     "b200ft_cast_f32_to_bf16": (c_int, [c_void_p, c_void_p, c_int64, c_void_p]),
     "b200ft_zero": (c_int, [c_void_p, c_size_t, c_void_p]),
+    "b200ft_set_dependent_launch": (c_int, [c_int]),
 }
 
 _lib = None

@@ -284,6 +284,8 @@ class LlamaFullStep(StepHostMixin, OwnAttentionMixin):
     def backward(self) -> None:
         D, W, dW = self.dims, self.W, self.dW
         L, mc = D.n_layer, self.bwd_ctas
+        if mc:   # SMs are left to an all-reduce on another stream: the next kernel's CTAs must not be parked on them
+            ops.set_dependent_launch(False)
         ops.zero(self.Gn)
         dx, dx1, dx0 = self.dxs
         # lm_head: dW = dlogits^T . hf (both MN-major), dhf = dlogits . W_head (B MN-major)
@@ -376,5 +378,7 @@ class LlamaFullStep(StepHostMixin, OwnAttentionMixin):
         self.backward()
         if self.grad_sync is not None:
             self.grad_sync(self, -1)
+        if self.bwd_ctas:
+            ops.set_dependent_launch(True)
         self.optimizer_step()
         return self.loss

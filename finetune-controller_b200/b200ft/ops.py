@@ -366,6 +366,11 @@ def zero(t):
     return t
 
 
+def set_dependent_launch(enabled: bool) -> bool:
+    """Programmatic dependent launch on / off for every later launch of this process; returns the previous setting."""
+    return bool(lib().b200ft_set_dependent_launch(int(bool(enabled))))
+
+
 def cast_f32_to_bf16(inp, out):
     global LAUNCHES
     _need_cuda(inp, out)

@@ -279,6 +279,14 @@ int b200ft_cast_f32_to_bf16(const float* in, void* out, int64_t n, void* stream)
  * the step's "zero_grad").  A DMA memset, no kernel launch.  No counterpart in the reference (no compute there). */
 int b200ft_zero(void* ptr, size_t bytes, void* stream);
 
+/* Programmatic dependent launch, process-wide (default on; B200FT_PDL=0 in the environment forces it off).  With it on,
+ * the CTAs of a kernel are dispatched while the previous kernel of the stream drains and wait, resident, for it to
+ * finish.  Turn it off around work that shares the GPU with a kernel on ANOTHER stream which needs SMs of its own — the
+ * data-parallel step does so for the backward pass whose GEMMs leave SMs to an overlapped all-reduce: resident, waiting
+ * CTAs would take exactly those SMs (measured, 2 x B200, Llama-3-8B full-parameter step: 259.8 -> 263.3 ms).
+ * Returns the previous setting.  No counterpart in the reference (no compute there). */
+int b200ft_set_dependent_launch(int enabled);
+
 #ifdef __cplusplus
 }
 #endif

@@ -401,3 +401,32 @@ def test_gemm_rejects_bad_arguments(ops):
     out = torch.zeros(128, 128, dtype=torch.bfloat16, device=DEV)
     with pytest.raises(B200FTError):
         ops.gemm(a, b, out)
+
+
+def test_dependent_launch_switch_changes_nothing_but_the_launch_attribute(ops):
+    """b200ft_set_dependent_launch: returns the previous setting; a chain of dependent kernels gives bit-identical
+    results with programmatic dependent launch on and off (every kernel waits for its predecessor before its first
+    global access)."""
+    g = torch.Generator().manual_seed(11)
+    x = torch.randn(4096, 768, generator=g).to(DEV, torch.bfloat16)
+    w = torch.randn(768, 768, generator=g).to(DEV, torch.bfloat16) * 0.05
+    gam, bet = torch.ones(768, device=DEV), torch.zeros(768, device=DEV)
+    outs = []
+    prev = ops.set_dependent_launch(True)
+    try:
+        for on in (True, False, True):
+            assert ops.set_dependent_launch(on) in (True, False)
+            y = torch.empty_like(x); z = torch.empty_like(x)
+            mean = torch.empty(4096, device=DEV); rstd = torch.empty(4096, device=DEV)
+            cur = x
+            for _ in range(6):   # LayerNorm -> GEMM -> LayerNorm -> ... : each launch consumes its predecessor's output
+                ops.layernorm_fwd(cur, gam, bet, y, mean, rstd, 1e-5)
+                ops.gemm(y, w, z)
+                cur = z
+            outs.append(z.clone())
+        assert ops.set_dependent_launch(False) is True
+        assert ops.set_dependent_launch(True) is False
+    finally:
+        ops.set_dependent_launch(prev)
+    assert torch.equal(outs[0], outs[1]) and torch.equal(outs[0], outs[2])
+    assert torch.isfinite(outs[0].float()).all()
