@@ -373,12 +373,47 @@ class LlamaFullStep(StepHostMixin, OwnAttentionMixin):
             ops.adamw_step(self.P, self.Mo, self.Vo, self.G, shadow=self.S, **kw)
         ops.adamw_step(self.Pn, self.Mn, self.Vn, self.Gn, **kw)
 
+    def _optimizer_step_behind_exchange(self) -> bool:
+        """Data-parallel step whose buckets are single layers and whose update needs no global norm: instead of waiting
+        for the whole exchange and then updating everything, walk the buckets in the order they were sent (top layer
+        first), make the stream wait for THAT bucket's all-reduce and update that layer.  What is left of the exchange
+        when backward ends (8 x B200, Llama-3-8B: ~20 ms of a 16 GB exchange that backward cannot hide completely)
+        then runs under the update of the layers that were reduced long ago.  Returns False when it does not apply."""
+        sync = self.grad_sync
+        L = self.dims.n_layer
+        if (sync is None or self.overlap_opt or self.opt.max_grad_norm > 0 or not hasattr(sync, "buckets")
+                or len(sync.buckets) != L or not sync.pending):
+            return False
+        works = list(sync.pending)
+        n_expected = sum(len(self.grad_views(lo, hi)) for lo, hi in sync.buckets)
+        if len(works) != n_expected:
+            return False
+        self.step_count += 1
+        kw = self._adam_kw(self.step_count)
+        i = 0
+        for lo, hi in sync.buckets:                 # issue order = completion order on the communicator's stream
+            n = len(self.grad_views(lo, hi))
+            for w in works[i: i + n]:
+                w.wait()                            # stream-level wait; the host runs ahead
+            i += n
+            a, b = self.layer_off[lo], self.layer_off[hi]
+            ops.adamw_step(self.P[a:b], self.Mo[a:b], self.Vo[a:b], self.G[a:b], shadow=self.S[a:b], **kw)
+        sync.pending.clear()
+        for a, b in ((0, self.layer_off[0]), (self.layer_off[-1], self.n_mat)):   # embedding table, untied lm_head
+            if b > a:
+                ops.adamw_step(self.P[a:b], self.Mo[a:b], self.Vo[a:b], self.G[a:b], shadow=self.S[a:b], **kw)
+        ops.adamw_step(self.Pn, self.Mn, self.Vn, self.Gn, **kw)
+        return True
+
     def step(self, ids: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:
         self.forward_loss(ids, labels)
         self.backward()
-        if self.grad_sync is not None:
-            self.grad_sync(self, -1)
-        if self.bwd_ctas:
+        if not self._optimizer_step_behind_exchange():
+            if self.grad_sync is not None:
+                self.grad_sync(self, -1)
+            if self.bwd_ctas:
+                ops.set_dependent_launch(True)
+            self.optimizer_step()
+        elif self.bwd_ctas:
             ops.set_dependent_launch(True)
-        self.optimizer_step()
         return self.loss
