@@ -591,6 +591,7 @@ extern "C" int b200ft_attn_bwd(const void* qkv, int64_t ld, int q_off, int k_off
     a.batch = batch; a.seq = seq; a.n_head = n_head; a.n_kv_head = n_kv_head;
     a.q_off = q_off; a.k_off = k_off; a.v_off = v_off; a.scale = scale;
     a.lse2 = lse2; a.delta = delta; a.dqkv = (__nv_bfloat16*)dqkv; a.ld_d = ld_dqkv;
+    a.qkv = (const __nv_bfloat16*)qkv; a.ld_qkv = ld; a.dout = (const __nv_bfloat16*)dout; a.ld_dout = ld_dout;
     return launch_bwd_d128(tm_qkv, tm_do, a, st);
   }
   B200FT_CUDA(launch_k(attn_delta_kernel<64>, (unsigned)((rows + 7) / 8), 256, 0, st, (const __nv_bfloat16*)out, ld_out,

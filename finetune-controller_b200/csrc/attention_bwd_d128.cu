@@ -12,7 +12,8 @@
 //   MODE 1  dQ        work item (q tile i, batch, head): Q_i, dO_i resident; streams (K_j, V_j), j <= i.
 //           S = Q_i K_j^T, dP = dO_i V_j^T (lanes = queries); dQ_i += dS K_j.  lse / D are per thread.
 //
-// In both: product A operand = resident tile (K-major), B = streamed tile (K-major); gradient A = bf16 P / dS in
+// In both: product A operand = resident tile (K-major; MODE 1 keeps Q_i, dO_i in the TMEM columns of the second
+// accumulator, which that kernel does not need, and reads them from there), B = streamed tile (K-major); gradient A = bf16 P / dS in
 // TMEM, B = streamed tile read MN-major ([128 rows = reduction index] x [d_head], two 64-column boxes).  No atomics,
 // no fp32 scratch: results are bit-reproducible.  TMEM: S 2 x 64 columns at 0 | dP 2 x 64 at 128 | acc0 256..383 |
 // acc1 384..511; a thread of slice `part` owns columns 16*part..+15 of an S / dP buffer and writes its 16 bf16 results
@@ -40,6 +41,14 @@ constexpr int kSmemBytes = kOffBar + 256;     // 194.25 KB
 constexpr uint32_t kSub = 64;                 // streamed rows per sub-pair: S / dP are [128 x 64] and double-buffered
 constexpr uint32_t kColS = 0, kColDP = 128, kColAcc0 = 256, kColAcc1 = 384;   // S, dP: two buffers of 64 columns each
 
+#ifdef B200FT_ATTN_TIMING   // per-phase clock readings of CTA 0 (tools/attn_timing.py); never defined in the shipped build
+__device__ long long g_blog[2][2][4096][2];   // [MODE][role]
+__device__ int g_bcnt[2][2];
+#define BLOG(role, tag) do { if (blockIdx.x == 0) { int i__ = g_bcnt[MODE][role]++; if (i__ < 4096) { g_blog[MODE][role][i__][0] = (tag); g_blog[MODE][role][i__][1] = clock64(); } } } while (0)
+#else
+#define BLOG(role, tag) do { } while (0)
+#endif
+
 struct Params {
   int batch, seq, n_head, n_kv_head;
   int q_off, k_off, v_off;
@@ -48,6 +57,8 @@ struct Params {
   const float* lse2;
   const float* delta;
   __nv_bfloat16* dqkv; int64_t ld_d;
+  const __nv_bfloat16* qkv; int64_t ld_qkv;
+  const __nv_bfloat16* dout; int64_t ld_do;
 };
 
 // Work item of a CTA.  MODE 0: (kv tile ascending, batch, kv head); MODE 1: (q tile descending, batch, head):
@@ -111,7 +122,7 @@ attn_bwd_d128_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_co
   const int num_items = p.n_tiles * p.batch * (MODE == 0 ? p.n_kv_head : p.n_head);
 
   if (warp == 1 && lane == 0) {
-    mbar_init(f_full, 1); mbar_init(f_empty, 1);
+    mbar_init(f_full, MODE == 1 ? 16 : 1); mbar_init(f_empty, 1);   // MODE 1: the sixteen softmax warps fill the resident operands
     for (uint32_t s = 0; s < kRing; ++s) { mbar_init(st_full(s), 1); mbar_init(st_empty(s), 1); }
     mbar_init(sdp_full(0), 1); mbar_init(sdp_full(1), 1); mbar_init(pds_full(0), 8); mbar_init(pds_full(1), 8);
     mbar_init(acc_full, 1); mbar_init(acc_free, 16);
@@ -147,18 +158,15 @@ attn_bwd_d128_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_co
     uint32_t g = 0, n = 0;
     for (int w = item_at(0); w < num_items; w = item_at(++n)) {
       const Item it = decode_item<MODE>(p, w, G);
-      if (n > 0) mbar_wait(f_empty, (n - 1) & 1u);   // the previous item's last dP UMMAs have read the resident pair
-      if (issuer) {
-        mbar_expect_tx(f_full, 2 * kTile);
-        if (MODE == 0) {
+      if (MODE == 0) {   // (MODE 1 keeps its resident Q_i, dO_i in TMEM: written by the softmax warps)
+        if (n > 0) mbar_wait(f_empty, (n - 1) & 1u);   // the previous item's last dP UMMAs have read the resident pair
+        if (issuer) {
+          mbar_expect_tx(f_full, 2 * kTile);
           load_tile(sF0, &tm_qkv, p.k_off + it.hk * kDH, it.fixed_tile * kB, it.b, f_full);
           load_tile(sF1, &tm_qkv, p.v_off + it.hk * kDH, it.fixed_tile * kB, it.b, f_full);
-        } else {
-          load_tile(sF0, &tm_qkv, p.q_off + it.hx * kDH, it.fixed_tile * kB, it.b, f_full);
-          load_tile(sF1, &tm_do, it.hx * kDH, it.fixed_tile * kB, it.b, f_full);
         }
+        __syncwarp();
       }
-      __syncwarp();
       for (int t = 0; t < it.n_iter; ++t, ++g) {
         const uint32_t st = g % kRing;
         mbar_wait(st_empty(st), ((g / kRing) & 1u) ^ 1u);
@@ -206,10 +214,20 @@ attn_bwd_d128_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_co
       const uint64_t rows = (uint64_t)(h * ((kSub * 128u) >> 4));   // 64 rows further into each box of the streamed tiles
       const uint64_t b0 = (st ? kS0[1] : kS0[0]) + rows, b1 = (st ? kS1[1] : kS1[0]) + rows;
       if (issuer) {
+        if (MODE == 0) {
 #pragma unroll
-        for (int k = 0; k < kDH / 16; ++k) umma(tmem + kColS + kSub * bf, kF0 + koff(k), b0 + koff(k), id_kk, k > 0);
+          for (int k = 0; k < kDH / 16; ++k) umma(tmem + kColS + kSub * bf, kF0 + koff(k), b0 + koff(k), id_kk, k > 0);
 #pragma unroll
-        for (int k = 0; k < kDH / 16; ++k) umma(tmem + kColDP + kSub * bf, kF1 + koff(k), b1 + koff(k), id_kk, k > 0);
+          for (int k = 0; k < kDH / 16; ++k) umma(tmem + kColDP + kSub * bf, kF1 + koff(k), b1 + koff(k), id_kk, k > 0);
+        } else {
+          // A operands Q_i, dO_i from TMEM (the second accumulator's columns, free in this kernel): a [128 x 64 x 16]
+          // UMMA with both operands in shared memory reads 6 KB per 32 cycles of tensor time — 1.5 x what an SM's
+          // shared memory delivers (measured: 75 cycles per UMMA); with A in TMEM it reads 2 KB
+#pragma unroll
+          for (int k = 0; k < kDH / 16; ++k) umma_ts(tmem + kColS + kSub * bf, tmem + kColAcc1 + 8u * (uint32_t)k, b0 + koff(k), id_kk, k > 0);
+#pragma unroll
+          for (int k = 0; k < kDH / 16; ++k) umma_ts(tmem + kColDP + kSub * bf, tmem + kColAcc1 + 64u + 8u * (uint32_t)k, b1 + koff(k), id_kk, k > 0);
+        }
         umma_commit(sdp_full(bf));
         if (last_of_item) umma_commit(f_empty);   // nothing of this item reads the resident pair any more
       }
@@ -246,13 +264,17 @@ attn_bwd_d128_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_co
       issue_products(g, false);
       issue_products(g + 1, N2 == 2);
       for (int t2 = 0; t2 < N2; ++t2, ++g) {
+        if (issuer) BLOG(1, 10);
         mbar_wait(pds_full(g & 1u), (g >> 1) & 1u);   // softmax warps are done with sub-pair g: P, dS are in TMEM
         tc_fence_after();
         if (t2 == 0 && n > 0) { mbar_wait(acc_free, (n - 1) & 1u); tc_fence_after(); }  // previous accumulators read out
+        if (issuer) BLOG(1, 11);
         issue_grads(g, t2 == 0);
+        if (issuer) BLOG(1, 12);
         // the products of sub-pair g+2 replace P(g), dS(g) — in issue order after the UMMAs that read them — and run,
         // with the gradients of g, while the softmax warps work on sub-pair g+1
         if (t2 + 2 < N2) issue_products(g + 2, t2 + 3 == N2);
+        if (issuer) BLOG(1, 13);
       }
       if (issuer) umma_commit(acc_full);
       __syncwarp();
@@ -293,7 +315,32 @@ attn_bwd_d128_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_co
       // cohort fetch the values of ITS 64 query rows one pair ahead (global-memory latency off the critical path) and
       // publish them in shared memory, double-buffered, when the pair starts (one 256-thread named barrier per cohort).
       float lse = INFINITY, dl = 0.f, lse_next = INFINITY, dl_next = 0.f;
-      if (MODE == 1) row_stats(it.hx, it.fixed_tile, L, lse, dl);
+      if (MODE == 1) {
+        // resident operands -> TMEM: this thread's lane is query row L; slices 0, 1 carry the two halves of its Q row,
+        // slices 2, 3 those of its dO row (64 elements = 32 packed columns each), straight from global memory
+        const int qr = it.fixed_tile * kB + L;
+        uint32_t a[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) a[i] = 0u;
+        if (qr < p.seq) {
+          const __nv_bfloat16* src = part4 < 2
+              ? p.qkv + ((int64_t)it.b * p.seq + qr) * p.ld_qkv + p.q_off + it.hx * kDH + 64 * part4
+              : p.dout + ((int64_t)it.b * p.seq + qr) * p.ld_do + it.hx * kDH + 64 * (part4 - 2);
+#pragma unroll
+          for (int v = 0; v < 8; ++v) {
+            const uint4 q4 = __ldg(reinterpret_cast<const uint4*>(src) + v);
+            a[4 * v] = q4.x; a[4 * v + 1] = q4.y; a[4 * v + 2] = q4.z; a[4 * v + 3] = q4.w;
+          }
+        }
+        if (n > 0) { mbar_wait(f_empty, (n - 1) & 1u); tc_fence_after(); }   // the previous item's products have read theirs
+        tmem_st16(t_lane + kColAcc1 + 32u * (uint32_t)part4, a);
+        tmem_st16(t_lane + kColAcc1 + 32u * (uint32_t)part4 + 16u, a + 16);
+        tmem_wait_st();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(f_full);
+        row_stats(it.hx, it.fixed_tile, L, lse, dl);
+      }
       else if (co_tid < 64) row_stats(it.hk * G, it.fixed_tile, 64 * cohort + co_tid, lse_next, dl_next);
       for (int t = 0; t < it.n_iter; ++t, ++gp) {
         int qt, kt;
@@ -315,8 +362,11 @@ attn_bwd_d128_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_co
         const int c0 = 64 * cohort + 32 * part;          // first of this thread's columns, as a row of the streamed tile
         // ---- phase A: P = exp2(S*c - lse) for this thread's 32 columns (kept in registers for phase B) ----
         f32x2_t P2[16];
+        const bool tl = (warp == 4 && lane == 0);
+        if (tl) BLOG(0, 0);
         mbar_wait(sdp_full(bf), gp & 1u);
         tc_fence_after();
+        if (tl) BLOG(0, 1);
         {
           uint32_t rs[32];
           tmem_ld32(t_s, rs);
@@ -339,6 +389,7 @@ attn_bwd_d128_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_co
             P2[i >> 1] = pk2(p0, p1);
           }
         }
+        if (tl) BLOG(0, 2);
         if (MODE == 0) {   // P^T as bf16 over this thread's own first 16 score columns: A operand of dV += P^T dO
           uint32_t wp[16];
 #pragma unroll
@@ -360,10 +411,12 @@ attn_bwd_d128_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_co
           }
           tmem_st16(t_dp, wd);
         }
+        if (tl) BLOG(0, 3);
         tmem_wait_st();
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(pds_full(bf));
+        if (tl) BLOG(0, 4);
       }
       // ---- accumulators -> (x softmax scale for dK, dQ) -> bf16 -> the gradient buffer ----
       mbar_wait(acc_full, n & 1u);
@@ -431,6 +484,7 @@ int b200ft_attn::launch_bwd_d128(const CUtensorMap& tm_qkv, const CUtensorMap& t
   p.n_tiles = (a.seq + kB - 1) / kB;
   p.scale = a.scale; p.scale_log2 = a.scale * 1.4426950408889634f;
   p.lse2 = a.lse2; p.delta = a.delta; p.dqkv = a.dqkv; p.ld_d = a.ld_d;
+  p.qkv = a.qkv; p.ld_qkv = a.ld_qkv; p.dout = a.dout; p.ld_do = a.ld_dout;
   static thread_local int attr_dev = -1;
   int dev = -1;
   B200FT_CUDA(cudaGetDevice(&dev));
@@ -447,3 +501,17 @@ int b200ft_attn::launch_bwd_d128(const CUtensorMap& tm_qkv, const CUtensorMap& t
                        kSmemBytes, st, tm_qkv, tm_do, p));
   return 0;
 }
+
+#ifdef B200FT_ATTN_TIMING
+extern "C" int b200ft_debug_attn_bwd128_timing(long long* log_out, int* counts_out, int reset) {
+  if (reset) {
+    int z[4] = {0, 0, 0, 0};
+    B200FT_CUDA(cudaMemcpyToSymbol(g_bcnt, z, sizeof(z)));
+    return 0;
+  }
+  B200FT_CUDA(cudaDeviceSynchronize());
+  B200FT_CUDA(cudaMemcpyFromSymbol(log_out, g_blog, sizeof(long long) * 2 * 2 * 4096 * 2));
+  B200FT_CUDA(cudaMemcpyFromSymbol(counts_out, g_bcnt, sizeof(int) * 4));
+  return 0;
+}
+#endif

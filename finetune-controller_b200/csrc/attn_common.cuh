@@ -159,6 +159,8 @@ struct Bwd128Args {
   const float* lse2;     // [batch*n_head, seq], log2 domain incl. the softmax scale
   const float* delta;    // [batch*n_head, seq]
   __nv_bfloat16* dqkv; int64_t ld_d;
+  const __nv_bfloat16* qkv; int64_t ld_qkv;     // the same buffers the tensor maps describe: the dQ kernel reads the
+  const __nv_bfloat16* dout; int64_t ld_dout;   // rows of its resident Q / dO tile directly (A operands kept in TMEM)
 };
 int launch_bwd_d128(const CUtensorMap& tm_qkv, const CUtensorMap& tm_do, const Bwd128Args& a, cudaStream_t st);
 

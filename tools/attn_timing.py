@@ -39,3 +39,33 @@ for role in (0, 1):
     per = [int(ev[i, 1]) for i in range(lo, hi) if ev[i, 0] == (0 if role == 0 else 10)]
     if len(per) > 2:
         print(f"  period: {np.mean(np.diff(per)):.0f} clk")
+
+# ---- backward, d_head 128 (two kernels: MODE 0 = dK|dV, MODE 1 = dQ) ----
+if dh == 128 and hasattr(L, "b200ft_debug_attn_bwd128_timing"):
+    dout = torch.randn(B * T, H * dh, device=dev).to(torch.bfloat16)
+    dqkv = torch.empty(B * T, ld, dtype=torch.bfloat16, device=dev)
+    ws = ops.attn_bwd_workspace(B, T, H, dh, dev)
+    kw = dict(batch=B, seq=T, n_head=H, n_kv_head=KV, d_head=dh, q_off=0, k_off=H * dh, v_off=(H + KV) * dh, scale=1 / math.sqrt(dh))
+    for _ in range(3): ops.attn_bwd(qkv, out, dout, lse, ws, dqkv, **kw)
+    fn = L.b200ft_debug_attn_bwd128_timing
+    fn.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int]
+    blog = np.zeros((2, 2, 4096, 2), dtype=np.int64); bcnt = np.zeros((2, 2), dtype=np.int32)
+    fn(None, None, 1)
+    ops.attn_bwd(qkv, out, dout, lse, ws, dqkv, **kw)
+    fn(blog.ctypes.data_as(ctypes.c_void_p), bcnt.ctypes.data_as(ctypes.c_void_p), 0)
+    bn = {0: "wait S,dP", 1: "S,dP ready", 2: "P computed", 3: "dS computed", 4: "handed over",
+          10: "wait P,dS", 11: "P,dS ready", 12: "grads issued", 13: "products issued"}
+    for mode in (0, 1):
+        for role in (0, 1):
+            n = min(int(bcnt[mode, role]), 4096)
+            ev = blog[mode, role, :n]
+            print(f"--- backward MODE {mode} role {role}: {n} events")
+            lo, hi = n // 5, n - n // 10
+            acc = {}
+            for i in range(max(lo, 1), hi):
+                acc.setdefault((int(ev[i - 1, 0]), int(ev[i, 0])), []).append(int(ev[i, 1] - ev[i - 1, 1]))
+            for (a, b), v in sorted(acc.items()):
+                print(f"  {bn.get(a, a):>18} -> {bn.get(b, b):<18} mean {np.mean(v):7.0f}  min {np.min(v):6d}  max {np.max(v):6d}  n {len(v)}")
+            per = [int(ev[i, 1]) for i in range(lo, hi) if ev[i, 0] == (0 if role == 0 else 10)]
+            if len(per) > 2:
+                print(f"  period: {np.mean(np.diff(per)):.0f} clk")
