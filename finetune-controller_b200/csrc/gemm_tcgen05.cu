@@ -83,6 +83,14 @@ struct TmapPack {  // one __grid_constant__ block: TMA reads descriptors straigh
   CUtensorMap c, c2, aux;
 };
 
+#ifdef B200FT_ATTN_TIMING   // per-phase clock readings of CTA 0 (tools/gemm_timing.py); never defined in the shipped build
+__device__ long long g_glog[2][8192][2];
+__device__ int g_gcnt[2];
+#define GLOG(role, tag) do { if (blockIdx.x == 0) { int i__ = g_gcnt[role]++; if (i__ < 8192) { g_glog[role][i__][0] = (tag); g_glog[role][i__][1] = clock64(); } } } while (0)
+#else
+#define GLOG(role, tag) do { } while (0)
+#endif
+
 struct GemmParams {
   int M, N, BN;
   int nseg;                    // K segments: acc = sum_s A_s . B_s^T
@@ -359,8 +367,10 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtenso
       }
       epi_bar_sync();
     }
+    if (et == 0) GLOG(0, 30);
     mbar_wait(tfull0 + 8u * acc, acc_phase);
     tc_fence_after();
+    if (et == 0) GLOG(0, 31);
     const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * kAccStride);
     for (int c = h; c < nchunks; c += kWPQ) {
       const uint32_t b = seq & (kEpiBufs - 1);
@@ -459,6 +469,7 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtenso
         issue_aux(seq - 1 + kDepth);
       }
     }
+    if (et == 0) GLOG(0, 32);
     tc_fence_before();
     __syncwarp();
     if (lane == 0) {  // accumulator drained: tell the MMA issuer (it lives in CTA 0 of the pair)
@@ -621,15 +632,19 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ TmapPack maps, const GemmParams
       int acc = 0;
       uint32_t acc_phase = 0;
       for (int w = w_begin; w < num_work; w += w_stride) {
+        if (issuer) GLOG(1, 20);
         mbar_wait(tempty_bar(acc), acc_phase ^ 1u);
         tc_fence_after();
+        if (issuer) GLOG(1, 21);
         const uint32_t d_tmem = tmem_base + (uint32_t)(acc * kAccStride);
         const int kb_begin = (w % p.splits) * p.kb_per_split;
         const int kb_end = min(kb_total, kb_begin + p.kb_per_split);
         int seg = 0;
         for (int kb = kb_begin; kb < kb_end; ++kb) {
+          if (issuer) GLOG(1, 22);
           mbar_wait(full_bar(stage), phase);
           tc_fence_after();
+          if (issuer) GLOG(1, 23);
           while (kb >= p.kb_prefix[seg + 1]) ++seg;
           const bool seg2 = seg > 0;
           const int kleft = p.k[seg] - (kb - p.kb_prefix[seg]) * kBlockK;
@@ -956,3 +971,17 @@ extern "C" int b200ft_gemm_bf16(const b200ft_gemm_args* a, void* stream) {
   B200FT_CUDA(cudaLaunchKernelEx(&cfg, gemm_bf16_tcgen05_kernel<2>, maps, p));
   return 0;
 }
+
+#ifdef B200FT_ATTN_TIMING
+extern "C" int b200ft_debug_gemm_timing(long long* log_out, int* counts_out, int reset) {
+  if (reset) {
+    int z[2] = {0, 0};
+    B200FT_CUDA(cudaMemcpyToSymbol(g_gcnt, z, sizeof(z)));
+    return 0;
+  }
+  B200FT_CUDA(cudaDeviceSynchronize());
+  B200FT_CUDA(cudaMemcpyFromSymbol(log_out, g_glog, sizeof(long long) * 2 * 8192 * 2));
+  B200FT_CUDA(cudaMemcpyFromSymbol(counts_out, g_gcnt, sizeof(int) * 2));
+  return 0;
+}
+#endif
