@@ -334,18 +334,28 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtenso
   const uint32_t aux_bytes = 32u * CW * 2u;
   constexpr uint32_t kDepth = kEpiBufs - 1;  // operand prefetch distance, in chunks
 
-  // operand load of this warp's chunk number n (counted across all its tiles); lane 0 only
+  // operand load of this warp's chunk number n (counted across all its tiles); lane 0 only.  The chunks are requested
+  // strictly in order, so a cursor (work item, chunk within the tile, the tile's row / column origin) replaces the
+  // divisions that turn n into coordinates: done per chunk they cost the issuing lane ~800 cycles, a quarter of the
+  // chunk's time, and made the epilogues with a second operand slower than the K = 768 main loop they hide behind.
+  int pf_w = w_begin, pf_ci = 0, pf_r0 = 0, pf_c0 = 0;
+  bool pf_valid = false;
+  auto pf_tile = [&]() {
+    pf_valid = pf_w < num_work;
+    if (pf_valid) {
+      const int tile2 = pf_w / p.splits;
+      pf_r0 = tile_m_index(p, tile2) * (kBlockM * CG) + cta_rank * kBlockM + q * 32;
+      pf_c0 = tile_n_index(p, tile2) * BN + h * CW;
+    }
+  };
   auto issue_aux = [&](uint32_t n) {
-    const int ti = (int)n / cpw, ci = (int)n % cpw;
-    const int w2 = w_begin + ti * w_stride;
-    if (w2 >= num_work) return;
-    const int tile2 = w2 / p.splits;
-    const int r0 = tile_m_index(p, tile2) * (kBlockM * CG) + cta_rank * kBlockM + q * 32;
-    const int c0 = tile_n_index(p, tile2) * BN + (h + kWPQ * ci) * CW;
+    if (!pf_valid) return;
     const uint32_t b = n & (kEpiBufs - 1);
     mbar_expect_tx(abar + 8u * b, aux_bytes);
-    tma_load_2d(ebuf + b * kEpiBufBytes, tmAux, c0, r0, abar + 8u * b);
+    tma_load_2d(ebuf + b * kEpiBufBytes, tmAux, pf_c0 + kWPQ * CW * pf_ci, pf_r0, abar + 8u * b);
+    if (++pf_ci == cpw) { pf_ci = 0; pf_w += w_stride; pf_tile(); }
   };
+  if (has_aux && cpw > 0 && lane == 0) pf_tile();
   if (has_aux && cpw > 0 && lane == 0) {
     for (uint32_t n = 0; n < kDepth; ++n) issue_aux(n);
   }
@@ -393,13 +403,16 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtenso
         }
         continue;
       }
+      if (et == 0) GLOG(0, 33);
       if (has_aux) {
         mbar_wait(abar + 8u * b, (seq >> kEpiBufShift) & 1u);  // operand of this chunk has landed
+        if (et == 0) GLOG(0, 34);
       } else {
         if (lane == 0) tma_store_wait_read<kEpiBufs - 1>();  // the store 4 tiles back has drained this buffer
         __syncwarp();
       }
       tmem_wait_ld();
+      if (et == 0) GLOG(0, 35);
       // the arithmetic below runs on packed fp32 pairs (FFMA2/FMUL2/FADD2): half the issue slots
       const f32x2_t alpha2 = pk2(p.alpha, p.alpha);
 #pragma unroll
@@ -438,9 +451,11 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtenso
           r[v * 8 + 0] = packed.x; r[v * 8 + 1] = packed.y; r[v * 8 + 2] = packed.z; r[v * 8 + 3] = packed.w;
         }
       }
+      if (et == 0) GLOG(0, 36);
       fence_proxy_async_smem();
       __syncwarp();
       if (lane == 0) tma_store_2d(tmC, buf, colbase, row0);
+      if (et == 0) GLOG(0, 37);
       ++seq;
       if (p.epilogue == B200FT_EPI_GELU) {
         // second output: gelu of the bf16-ROUNDED pre-activation, so that backward (which only
@@ -466,7 +481,9 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtenso
         // chunk seq-1 was just stored; chunk seq+2 reuses the buffer of chunk seq-2, whose store
         // is older than the one just issued: allow only that newest store to be unread
         tma_store_wait_read<1>();
+        if (et == 0) GLOG(0, 38);
         issue_aux(seq - 1 + kDepth);
+        if (et == 0) GLOG(0, 39);
       }
     }
     if (et == 0) GLOG(0, 32);

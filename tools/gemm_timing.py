@@ -18,7 +18,7 @@ for _ in range(3): run()
 L = lib(); fn = L.b200ft_debug_gemm_timing; fn.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int]
 log = np.zeros((2, 8192, 2), dtype=np.int64); cnt = np.zeros(2, dtype=np.int32)
 fn(None, None, 1); run(); fn(log.ctypes.data_as(ctypes.c_void_p), cnt.ctypes.data_as(ctypes.c_void_p), 0)
-names = {20: "tile start", 21: "accumulator free", 22: "k-block start", 23: "operands landed", 30: "epi: wait acc", 31: "epi: acc ready", 32: "epi: tile drained"}
+names = {20: "tile start", 21: "accumulator free", 22: "k-block start", 23: "operands landed", 33: "chunk start", 34: "aux landed", 35: "acc in regs", 36: "math + sts done", 37: "store issued", 38: "older store read", 39: "next aux issued", 30: "epi: wait acc", 31: "epi: acc ready", 32: "epi: tile drained"}
 for role in (1, 0):
     n = min(int(cnt[role]), 8192); ev = log[role, :n]
     print(f"--- role {role} ({'issuer' if role else 'epilogue warp 0'}): {n} events, {int(ev[-1,1]-ev[0,1])} clk in all")
