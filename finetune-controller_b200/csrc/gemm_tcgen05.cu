@@ -87,8 +87,14 @@ struct TmapPack {  // one __grid_constant__ block: TMA reads descriptors straigh
 __device__ long long g_glog[2][8192][2];
 __device__ int g_gcnt[2];
 #define GLOG(role, tag) do { if (blockIdx.x == 0) { int i__ = g_gcnt[role]++; if (i__ < 8192) { g_glog[role][i__][0] = (tag); g_glog[role][i__][1] = clock64(); } } } while (0)
+#ifdef B200FT_GEMM_TIMING_FINE   // also per k-block and per epilogue chunk (each reading costs ~250 cycles itself)
+#define GLOG2(role, tag) GLOG(role, tag)
+#else
+#define GLOG2(role, tag) do { } while (0)
+#endif
 #else
 #define GLOG(role, tag) do { } while (0)
+#define GLOG2(role, tag) do { } while (0)
 #endif
 
 struct GemmParams {
@@ -318,7 +324,7 @@ __device__ __forceinline__ float4 lds_f4(uint32_t addr) {
 // second operand (residual / gelu') chunk n's operand is TMA-loaded into buffer n & 3 THREE chunks
 // ahead of its use — across tile boundaries — so that every warp keeps 6 KB (48 KB per SM) of
 // that stream in flight; the result is written over it in place and leaves by TMA store.
-template <int CW, int CG>
+template <int CW, int CG, int EPI>
 __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtensorMap* tmC, const CUtensorMap* tmC2,
                                               const CUtensorMap* tmAux, int q, int h, int lane, int et,
                                               uint32_t tmem_base, uint32_t ebuf, uint32_t sbias, uint32_t abar,
@@ -327,10 +333,17 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtenso
   const int BN = p.BN;
   const int nchunks = BN / CW;
   const int cpw = nchunks > h ? (nchunks - h + kWPQ - 1) / kWPQ : 0;  // chunks of a tile this warp owns
-  const bool has_aux = (p.epilogue == B200FT_EPI_RESIDUAL) || (p.epilogue == B200FT_EPI_DGELU);
-  const bool atomic_t = (p.epilogue == B200FT_EPI_ATOMIC_F32_T);
+  // The epilogue kind is a template parameter and alpha / bias are applied unconditionally (one FFMA2 per pair, the
+  // bias slice being zeros when there is none): run-time branches inside the per-vector arithmetic cut it into basic
+  // blocks the compiler cannot interleave, and with two epilogue warps per scheduler that dependent chain was the
+  // epilogue's time (ISETP / BRA / SEL were 17 % of the x GELU' kernel's instructions).
+  constexpr bool has_aux = (EPI == B200FT_EPI_RESIDUAL) || (EPI == B200FT_EPI_DGELU);
+  constexpr bool atomic_t = (EPI == B200FT_EPI_ATOMIC_F32_T);
   const bool has_bias = p.bias != nullptr;
-  const bool scale = p.alpha != 1.0f;
+  if (!has_bias && !atomic_t) {   // zeros once: the arithmetic below always adds the slice
+    if (et < kMaxBN) asm volatile("st.shared.f32 [%0], %1;" ::"r"(sbias + 4u * et), "f"(0.f) : "memory");
+    epi_bar_sync();
+  }
   const uint32_t aux_bytes = 32u * CW * 2u;
   constexpr uint32_t kDepth = kEpiBufs - 1;  // operand prefetch distance, in chunks
 
@@ -382,17 +395,14 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtenso
     tc_fence_after();
     if (et == 0) GLOG(0, 31);
     const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * kAccStride);
-    for (int c = h; c < nchunks; c += kWPQ) {
+    // One chunk: its accumulator columns are already in registers (r).
+    auto process_chunk = [&](const int c, uint32_t (&r)[CW]) {
       const uint32_t b = seq & (kEpiBufs - 1);
       const uint32_t buf = ebuf + b * kEpiBufBytes;
-      uint32_t r[CW];
-      if constexpr (CW == 32) tmem_ld32(t_row + c * CW, r);
-      else tmem_ld16(t_row + c * CW, r);
       const int colbase = n0 + c * CW;
       if (atomic_t) {
         // split-K partial: fp32 reduction into the transposed output (lanes = consecutive m,
         // so every red.global.add of a warp hits one 128-byte line)
-        tmem_wait_ld();
         const int mrow = row0 + lane;
         if (mrow < p.M) {
 #pragma unroll
@@ -401,18 +411,17 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtenso
               atomicAdd(p.cf + (int64_t)(colbase + j) * p.ldc + mrow, __uint_as_float(r[j]) * p.alpha);
           }
         }
-        continue;
+        return;
       }
-      if (et == 0) GLOG(0, 33);
+      if (et == 0) GLOG2(0, 33);
       if (has_aux) {
         mbar_wait(abar + 8u * b, (seq >> kEpiBufShift) & 1u);  // operand of this chunk has landed
-        if (et == 0) GLOG(0, 34);
+        if (et == 0) GLOG2(0, 34);
       } else {
         if (lane == 0) tma_store_wait_read<kEpiBufs - 1>();  // the store 4 tiles back has drained this buffer
         __syncwarp();
       }
-      tmem_wait_ld();
-      if (et == 0) GLOG(0, 35);
+      if (et == 0) GLOG2(0, 35);
       // the arithmetic below runs on packed fp32 pairs (FFMA2/FMUL2/FADD2): half the issue slots
       const f32x2_t alpha2 = pk2(p.alpha, p.alpha);
 #pragma unroll
@@ -421,21 +430,17 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtenso
 #pragma unroll
         for (int i = 0; i < 4; ++i)
           f[i] = pk2(__uint_as_float(r[v * 8 + 2 * i]), __uint_as_float(r[v * 8 + 2 * i + 1]));
-        if (scale) {
-#pragma unroll
-          for (int i = 0; i < 4; ++i) f[i] = mul2(f[i], alpha2);
-        }
-        if (has_bias) {
+        {
           const float4 b0 = lds_f4(sbias + 4u * (c * CW + v * 8));
           const float4 b1 = lds_f4(sbias + 4u * (c * CW + v * 8 + 4));
-          f[0] = add2(f[0], pk2(b0.x, b0.y)); f[1] = add2(f[1], pk2(b0.z, b0.w));
-          f[2] = add2(f[2], pk2(b1.x, b1.y)); f[3] = add2(f[3], pk2(b1.z, b1.w));
+          f[0] = fma2(f[0], alpha2, pk2(b0.x, b0.y)); f[1] = fma2(f[1], alpha2, pk2(b0.z, b0.w));
+          f[2] = fma2(f[2], alpha2, pk2(b1.x, b1.y)); f[3] = fma2(f[3], alpha2, pk2(b1.z, b1.w));
         }
         const uint32_t addr = epi_vec_addr<CW>(buf, lane, v);
         if (has_aux) {
           const uint4 aw = lds16(addr);
           const uint32_t a4[4] = {aw.x, aw.y, aw.z, aw.w};
-          if (p.epilogue == B200FT_EPI_RESIDUAL) {
+          if constexpr (EPI == B200FT_EPI_RESIDUAL) {
 #pragma unroll
             for (int i = 0; i < 4; ++i) f[i] = add2(f[i], bf16x2_to_f32x2(a4[i]));
           } else {
@@ -447,17 +452,17 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtenso
         packed.x = f32x2_to_bf16x2(f[0]); packed.y = f32x2_to_bf16x2(f[1]);
         packed.z = f32x2_to_bf16x2(f[2]); packed.w = f32x2_to_bf16x2(f[3]);
         sts16(addr, packed);
-        if (p.epilogue == B200FT_EPI_GELU) {  // keep the bf16-rounded pre-activation for pass 2
+        if constexpr (EPI == B200FT_EPI_GELU) {  // keep the bf16-rounded pre-activation for pass 2
           r[v * 8 + 0] = packed.x; r[v * 8 + 1] = packed.y; r[v * 8 + 2] = packed.z; r[v * 8 + 3] = packed.w;
         }
       }
-      if (et == 0) GLOG(0, 36);
+      if (et == 0) GLOG2(0, 36);
       fence_proxy_async_smem();
       __syncwarp();
       if (lane == 0) tma_store_2d(tmC, buf, colbase, row0);
-      if (et == 0) GLOG(0, 37);
+      if (et == 0) GLOG2(0, 37);
       ++seq;
-      if (p.epilogue == B200FT_EPI_GELU) {
+      if constexpr (EPI == B200FT_EPI_GELU) {
         // second output: gelu of the bf16-ROUNDED pre-activation, so that backward (which only
         // has the stored bf16 value) differentiates exactly the function applied here
         const uint32_t buf2 = ebuf + (seq & (kEpiBufs - 1)) * kEpiBufBytes;
@@ -481,10 +486,33 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtenso
         // chunk seq-1 was just stored; chunk seq+2 reuses the buffer of chunk seq-2, whose store
         // is older than the one just issued: allow only that newest store to be unread
         tma_store_wait_read<1>();
-        if (et == 0) GLOG(0, 38);
+        if (et == 0) GLOG2(0, 38);
         issue_aux(seq - 1 + kDepth);
-        if (et == 0) GLOG(0, 39);
+        if (et == 0) GLOG2(0, 39);
       }
+    };
+    // Software pipeline over this warp's chunks (h, h + kWPQ, ...): the tcgen05.ld of the next chunk is issued before
+    // the current one is processed, into the other register set (measured: ~1070 cycles per plain chunk of which the
+    // load's round trip was a third; the epilogues with arithmetic were slower than the K = 768 main loop they hide
+    // behind).  tcgen05.wait::ld waits for every outstanding load, hence the strict alternation.
+    auto load_chunk = [&](const int c, uint32_t (&r)[CW]) {
+      if constexpr (CW == 32) tmem_ld32(t_row + c * CW, r);
+      else tmem_ld16(t_row + c * CW, r);
+    };
+    uint32_t rA[CW], rB[CW];
+    int c = h;
+    if (c < nchunks) load_chunk(c, rA);
+    while (c < nchunks) {
+      tmem_wait_ld();
+      const int c1 = c + kWPQ;
+      if (c1 < nchunks) load_chunk(c1, rB);
+      process_chunk(c, rA);
+      if (c1 >= nchunks) break;
+      tmem_wait_ld();
+      const int c2 = c1 + kWPQ;
+      if (c2 < nchunks) load_chunk(c2, rA);
+      process_chunk(c1, rB);
+      c = c2;
     }
     if (et == 0) GLOG(0, 32);
     tc_fence_before();
@@ -658,10 +686,10 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ TmapPack maps, const GemmParams
         const int kb_end = min(kb_total, kb_begin + p.kb_per_split);
         int seg = 0;
         for (int kb = kb_begin; kb < kb_end; ++kb) {
-          if (issuer) GLOG(1, 22);
+          if (issuer) GLOG2(1, 22);
           mbar_wait(full_bar(stage), phase);
           tc_fence_after();
-          if (issuer) GLOG(1, 23);
+          if (issuer) GLOG2(1, 23);
           while (kb >= p.kb_prefix[seg + 1]) ++seg;
           const bool seg2 = seg > 0;
           const int kleft = p.k[seg] - (kb - p.kb_prefix[seg]) * kBlockK;
@@ -716,12 +744,27 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ TmapPack maps, const GemmParams
     const int h = ew >> 2;        // which of the quarter's warps
     const int et = threadIdx.x - 128;
     const uint32_t eb = sEpi + ew * kEpiBufs * kEpiBufBytes;
-    if (p.cw == 32)
-      epilogue_loop<32, CG>(p, &maps.c, &maps.c2, &maps.aux, q, h, lane, et, tmem_base, eb, sBias, aux_bar(ew, 0),
-                            tfull_bar(0), tempty_bar(0), num_work, w_begin, w_stride, cta_rank);
-    else
-      epilogue_loop<16, CG>(p, &maps.c, &maps.c2, &maps.aux, q, h, lane, et, tmem_base, eb, sBias, aux_bar(ew, 0),
-                            tfull_bar(0), tempty_bar(0), num_work, w_begin, w_stride, cta_rank);
+#define B200FT_EPI_CALL(CWV, E)                                                                                       \
+  epilogue_loop<CWV, CG, E>(p, &maps.c, &maps.c2, &maps.aux, q, h, lane, et, tmem_base, eb, sBias, aux_bar(ew, 0),    \
+                            tfull_bar(0), tempty_bar(0), num_work, w_begin, w_stride, cta_rank)
+    if (p.cw == 32) {
+      switch (p.epilogue) {
+        case B200FT_EPI_RESIDUAL: B200FT_EPI_CALL(32, B200FT_EPI_RESIDUAL); break;
+        case B200FT_EPI_GELU: B200FT_EPI_CALL(32, B200FT_EPI_GELU); break;
+        case B200FT_EPI_DGELU: B200FT_EPI_CALL(32, B200FT_EPI_DGELU); break;
+        case B200FT_EPI_ATOMIC_F32_T: B200FT_EPI_CALL(32, B200FT_EPI_ATOMIC_F32_T); break;
+        default: B200FT_EPI_CALL(32, B200FT_EPI_NONE); break;
+      }
+    } else {   // 16-column chunks: the N = 16 adapter GEMMs and the split-K adapter gradients
+      switch (p.epilogue) {
+        case B200FT_EPI_RESIDUAL: B200FT_EPI_CALL(16, B200FT_EPI_RESIDUAL); break;
+        case B200FT_EPI_GELU: B200FT_EPI_CALL(16, B200FT_EPI_GELU); break;
+        case B200FT_EPI_DGELU: B200FT_EPI_CALL(16, B200FT_EPI_DGELU); break;
+        case B200FT_EPI_ATOMIC_F32_T: B200FT_EPI_CALL(16, B200FT_EPI_ATOMIC_F32_T); break;
+        default: B200FT_EPI_CALL(16, B200FT_EPI_NONE); break;
+      }
+    }
+#undef B200FT_EPI_CALL
   }
 
   tc_fence_before();
