@@ -51,12 +51,11 @@ constexpr int kBlockK = 64;  // 64 bf16 = 128 B = one swizzle row
 constexpr int kMaxBN = 256;
 constexpr int kAStageBytes = kBlockM * kBlockK * 2;  // 16 KB
 constexpr int kTileBytes = 160 * 1024;  // operand ring
-template <int CG> struct RingCfg {
-  static constexpr int kStages = CG == 1 ? 3 : 5;
-  static constexpr int kBStageBytes = kMaxBN / CG * kBlockK * 2;  // 32 KB, or 16 KB (half of B per CTA)
-  static_assert(kStages * (kAStageBytes + kBStageBytes) <= kTileBytes, "ring size");
-};
-constexpr int kMaxStages = 5;
+// Ring depth and the B slab's size are per launch (GemmParams::n_stages, b_stage_bytes): a slab of B is BN / CG rows of
+// 128 bytes (K-major) or 8 KB per 64 columns (MN-major), so the 160 KB hold 3 stages at BN = 256 on one CTA, 5 on a
+// pair, and 6-8 for the N = 16 / 32 adapter GEMMs and gradient contractions — which stream [M x K] once and are bound
+// by the bytes they keep in flight (3 stages = 48 KB of A per SM measured 2.5-3.9 TB/s).
+constexpr int kMaxStages = 8;
 constexpr int kMaxSeg = 4;
 constexpr uint32_t kPeerBitMask = 0xFEFFFFFFu;  // clears the CTA-rank bit of a shared::cluster address -> CTA 0
 #ifndef B200FT_GEMM_EPI_WPQ
@@ -107,6 +106,7 @@ struct GemmParams {
   int raster_m;  // 1: consecutive work items walk the M tiles of one N tile (B streamed once, A resident in L2)
   int splits, kb_per_split;  // split-K: work item w -> (tile = w / splits, K slabs of split w % splits)
   int epilogue;
+  int n_stages, b_stage_bytes;   // operand ring: depth and bytes per B slab (A slabs are 16 KB)
   int cw;  // epilogue chunk width in columns: 64 (swizzled staging tile), 32 or 16 (dense)
   float alpha;
   const float* bias;
@@ -534,8 +534,8 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtenso
 template <int CG>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_bf16_tcgen05_kernel(const __grid_constant__ TmapPack maps, const GemmParams p) {
-  constexpr int kStages = RingCfg<CG>::kStages;
-  constexpr int kBStageBytes = RingCfg<CG>::kBStageBytes;
+  const int kStages = p.n_stages;
+  const uint32_t kBStageBytes = (uint32_t)p.b_stage_bytes;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
   const uint32_t base = (raw + 1023u) & ~1023u;  // identical in both CTAs of a pair (same kernel, same layout)
@@ -942,6 +942,16 @@ extern "C" int b200ft_gemm_bf16(const b200ft_gemm_args* a, void* stream) {
     if (force && (force[0] == 'm' || force[0] == 'n')) p.raster_m = force[0] == 'm';
   }
   p.epilogue = a->epilogue;
+  {
+    const int b_rows = BN / cg;
+    int b_stage = b_rows * kBlockK * 2;                                  // K-major slab (every segment after the first)
+    if (p.b_mn) { const int mn = (b_rows + 63) / 64 * 8192; if (mn > b_stage) b_stage = mn; }
+    b_stage = (b_stage + 1023) / 1024 * 1024;                            // 128B-swizzle atoms are 1024-byte aligned
+    int st = kTileBytes / (kAStageBytes + b_stage);
+    p.n_stages = st < 2 ? 2 : (st > kMaxStages ? kMaxStages : st);
+    p.b_stage_bytes = b_stage;
+    B200FT_CHECK_ARG(p.n_stages * (kAStageBytes + b_stage) <= kTileBytes, "gemm: operand ring does not fit (block_n=%d)", BN);
+  }
   p.alpha = a->alpha;
   p.bias = a->bias;
   p.aux = (const __nv_bfloat16*)a->aux; p.ld_aux = a->ld_aux;
