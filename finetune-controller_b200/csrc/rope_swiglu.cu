@@ -12,15 +12,16 @@ __global__ void __launch_bounds__(256)
 rope_kernel(__nv_bfloat16* __restrict__ x, int64_t ld, int64_t rows, int seq, int n_heads, int dh,
             const float* __restrict__ cos_t, const float* __restrict__ sin_t, float sign) {
   grid_dep_sync();
+  // flat index in 32 bits (the host checks rows * heads * vectors < 2^31): 64-bit divisions cost ~100 instructions each
   const int half = dh >> 1;
   const int vph = half >> 3;  // 8-wide vectors per half head
-  const int64_t per_row = (int64_t)n_heads * vph;
-  const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= rows * per_row) return;
-  const int64_t row = idx / per_row;
-  const int rem = (int)(idx % per_row);
-  const int head = rem / vph, vi = rem % vph;
-  const int pos = (int)(row % seq);
+  const unsigned per_row = (unsigned)(n_heads * vph);
+  const unsigned idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= (unsigned)rows * per_row) return;
+  const unsigned urow = idx / per_row, rem = idx - urow * per_row;
+  const int64_t row = urow;
+  const int head = (int)(rem / (unsigned)vph), vi = (int)rem - head * vph;
+  const int pos = (int)(urow % (unsigned)seq);
   __nv_bfloat16* p1 = x + row * ld + head * dh + (vi << 3);
   __nv_bfloat16* p2 = p1 + half;
   float a[8], b[8];
@@ -52,9 +53,14 @@ swiglu_fwd_kernel(const __nv_bfloat16* __restrict__ gu, __nv_bfloat16* __restric
   const int vpr = ff >> 3;
   const int64_t total = rows * vpr;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
-    const int64_t row = i / vpr;
-    const int v = (int)(i % vpr);
+  // (row, vector) advance with the grid stride: one division per thread, none per element
+  const int64_t i0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t step_rows = stride / vpr;
+  const int step_v = (int)(stride - step_rows * vpr);
+  int64_t row = i0 / vpr;
+  int v = (int)(i0 - row * vpr);
+  for (int64_t i = i0; i < total; i += stride, row += step_rows, v += step_v) {
+    if (v >= vpr) { v -= vpr; ++row; }
     float g[8], u[8], o[8];
     unpack8(ld_stream16(gu + row * 2 * ff + (v << 3)), g);
     unpack8(ld_stream16(gu + row * 2 * ff + ff + (v << 3)), u);
@@ -72,9 +78,14 @@ swiglu_bwd_kernel(const __nv_bfloat16* __restrict__ dact, const __nv_bfloat16* _
   const int vpr = ff >> 3;
   const int64_t total = rows * vpr;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
-    const int64_t row = i / vpr;
-    const int v = (int)(i % vpr);
+  // (row, vector) advance with the grid stride: one division per thread, none per element
+  const int64_t i0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t step_rows = stride / vpr;
+  const int step_v = (int)(stride - step_rows * vpr);
+  int64_t row = i0 / vpr;
+  int v = (int)(i0 - row * vpr);
+  for (int64_t i = i0; i < total; i += stride, row += step_rows, v += step_v) {
+    if (v >= vpr) { v -= vpr; ++row; }
     float g[8], u[8], d[8], dg[8], du[8], a[8];
     unpack8(ld_stream16(gu + row * 2 * ff + (v << 3)), g);
     unpack8(ld_stream16(gu + row * 2 * ff + ff + (v << 3)), u);
@@ -102,6 +113,7 @@ extern "C" int b200ft_rope_inplace(void* x, int64_t ld, int64_t rows, int seq, i
                    "rope: rows=%lld seq=%d heads=%d d_head=%d ld=%lld (d_head %% 16 == 0, ld %% 8 == 0)",
                    (long long)rows, seq, n_heads, d_head, (long long)ld);
   const int64_t total = rows * n_heads * (d_head / 16);
+  B200FT_CHECK_ARG(total < (1ll << 31), "rope: rows * heads * d_head / 16 = %lld does not fit 31 bits", (long long)total);
   launch_k(rope_kernel, (unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream,
       (__nv_bfloat16*)x, ld, rows, seq, n_heads, d_head, cos_table, sin_table, backward ? -1.f : 1.f);
   B200FT_LAUNCH_CHECK();
