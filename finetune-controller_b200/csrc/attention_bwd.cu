@@ -85,6 +85,14 @@ attn_delta_kernel(const __nv_bfloat16* __restrict__ o, int64_t ld_o, const __nv_
 
 // Work item of a CTA.  MODE 0: (kv tile ascending, batch, kv head); MODE 1: (q tile descending, batch, head):
 // heaviest first.  Every warp role walks the same item sequence w = blockIdx.x, += gridDim.x.
+#ifdef B200FT_ATTN_TIMING   // per-phase clock readings of CTA 0 (tools/attn_timing.py); never defined in the shipped build
+__device__ long long g_dlog[2][4096][2];
+__device__ int g_dcnt[2];
+#define DLOG(role, tag) do { if (MODE == 2 && blockIdx.x == 0) { int i__ = g_dcnt[role]++; if (i__ < 4096) { g_dlog[role][i__][0] = (tag); g_dlog[role][i__][1] = clock64(); } } } while (0)
+#else
+#define DLOG(role, tag) do { } while (0)
+#endif
+
 struct Item {
   int fixed_tile, b, hx, hk, per_head, n_iter;
 };
@@ -217,8 +225,12 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
       if (issuer) {
 #ifndef B200FT_EXP_NO_SDP
 #pragma unroll
+        // descriptors once per product, the k-th step's offset added to the address field (16-byte units; the tiles lie
+        // below 256 KB, so the add never carries out of it): the single issuing thread is on every pair's critical path
+        const uint64_t da = sdesc(aq, 16, 1024), db = sdesc(bk, 16, 1024);
+#pragma unroll
         for (int k = 0; k < kDH / 16; ++k)
-          umma(tmem + kColS + 128u * bf, sdesc(aq + 32 * k, 16, 1024), sdesc(bk + 32 * k, 16, 1024), id_s, k > 0);
+          umma(tmem + kColS + 128u * bf, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), id_s, k > 0);
 #endif
         umma_commit(s_full(bf));
       }
@@ -229,9 +241,10 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
       const uint32_t ado = MODE != 1 ? sS1(st) : sF1, bv = MODE != 1 ? sF1 : sS1(st);
       if (issuer) {
 #ifndef B200FT_EXP_NO_SDP
+        const uint64_t da = sdesc(ado, 16, 1024), db = sdesc(bv, 16, 1024);
 #pragma unroll
         for (int k = 0; k < kDH / 16; ++k)
-          umma(tmem + kColDP, sdesc(ado + 32 * k, 16, 1024), sdesc(bv + 32 * k, 16, 1024), id_s, k > 0);
+          umma(tmem + kColDP, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), id_s, k > 0);
 #endif
         umma_commit(dp_full);
         if (MODE != 2 && last_of_item) umma_commit(f_empty);   // nothing of this item reads the resident pair any more
@@ -243,14 +256,14 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
       if (issuer) {
 #ifndef B200FT_EXP_NO_GRADS   // bottleneck experiment: skip the gradient UMMAs (commits stay), wrong numbers
         if (MODE != 1) {
+          const uint64_t dp_ = sdesc(sP, 16384, 1024), dds = sdesc(sDS, 16384, 1024);
+          const uint64_t d1 = sdesc(sS1(st), 8192, 1024), d0 = sdesc(sS0(st), 8192, 1024);
 #pragma unroll
-          for (int k = 0; k < kB / 16; ++k)   // reduction over 16 query rows per step
-            umma(tmem + kColAcc0, sdesc(sP + 2048 * k, 16384, 1024), sdesc(sS1(st) + 2048 * k, 8192, 1024), id_g0,
-                 !(first && k == 0));
+          for (int k = 0; k < kB / 16; ++k)   // reduction over 16 query rows per step (2 KB = 128 units)
+            umma(tmem + kColAcc0, dp_ + (uint64_t)(128 * k), d1 + (uint64_t)(128 * k), id_g0, !(first && k == 0));
 #pragma unroll
           for (int k = 0; k < kB / 16; ++k)
-            umma(tmem + kColAcc1, sdesc(sDS + 2048 * k, 16384, 1024), sdesc(sS0(st) + 2048 * k, 8192, 1024), id_g0,
-                 !(first && k == 0));
+            umma(tmem + kColAcc1, dds + (uint64_t)(128 * k), d0 + (uint64_t)(128 * k), id_g0, !(first && k == 0));
         } else {
 #pragma unroll
           for (int k = 0; k < kB / 16; ++k)   // reduction over 16 keys per step: dS chunk k/4, 32 B per step inside
@@ -260,10 +273,10 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
         if (MODE == 2) {
           // dQ partial of this pair: 128 (queries) x 64 x 128 (keys), A = dS K-major, B = the resident K tile MN-major
           const uint32_t dq_col = kColDQ + 64u * (gg & 1u);
+          const uint64_t dds1 = sdesc(sDS, 16, 1024), dk1 = sdesc(sF0, 8192, 1024);
 #pragma unroll
           for (int k = 0; k < kB / 16; ++k)
-            umma(tmem + dq_col, sdesc(sDS + 16384 * (k >> 2) + 32 * (k & 3), 16, 1024),
-                 sdesc(sF0 + 2048 * k, 8192, 1024), id_g1, k > 0);
+            umma(tmem + dq_col, dds1 + (uint64_t)(1024 * (k >> 2) + 2 * (k & 3)), dk1 + (uint64_t)(128 * k), id_g1, k > 0);
         }
 #endif
         umma_commit(pds_free);      // P / dS tiles may be overwritten
@@ -283,13 +296,19 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
       issue_dp(g, N == 1);
       if (MODE != 2 && N > 1) issue_s(g + 1);
       for (int t = 0; t < N; ++t, ++g) {
+        if (issuer) DLOG(1, 10);
         if (MODE == 2 && t + 1 < N) issue_s(g + 1);   // waits for phase A of pair g; S is single-buffered here
+        if (issuer) DLOG(1, 11);
         mbar_wait(pds_full, g & 1u);        // softmax warps are done with pair g: P, dS in smem, dP read out
         tc_fence_after();
+        if (issuer) DLOG(1, 12);
         if (t + 1 < N) issue_dp(g + 1, t + 2 == N);
         if (t == 0 && n > 0) { mbar_wait(acc_free, (n - 1) & 1u); tc_fence_after(); }  // previous item's accumulators read out
+        if (issuer) DLOG(1, 13);
         if (MODE == 2 && g >= 2) { mbar_wait(dq_free(g & 1u), ((g >> 1) - 1) & 1u); tc_fence_after(); }
+        if (issuer) DLOG(1, 14);
         issue_grads(g, t == 0);
+        if (issuer) DLOG(1, 15);
         if (MODE != 2 && t + 2 < N) issue_s(g + 2);
       }
       if (issuer) {
@@ -369,9 +388,10 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
       // per-row log-sum-exp and D.  Rows past the end of the sequence get lse = +inf: P = dS = 0.  With the kv tile
       // fixed (MODE 0, 2) every pair has its own query rows: the values of pair t+1 are requested while pair t
       // is processed, so their global-memory latency is never on the critical path.
-      auto load_row_stats = [&](int t, float& lse_o, float& dl_o) {
-        const int hq = MODE == 1 ? it.hx : it.hk * G + t / it.per_head;
-        const int qt_ = MODE == 1 ? it.fixed_tile : it.fixed_tile + t % it.per_head;
+      // (head, q tile) of pair t = (it.hk * G + t / per_head, fixed_tile + t % per_head) when the kv tile is fixed: kept
+      // as counters that advance with t — the divisions, done per pair by each of the 512 threads, cost about as many
+      // instructions as the pair's arithmetic
+      auto load_row_stats = [&](int hq, int qt_, float& lse_o, float& dl_o) {
         const int qr = qt_ * kB + row;
         lse_o = INFINITY; dl_o = 0.f;
         if (qr < p.seq) {
@@ -380,13 +400,17 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
         }
       };
       float lse, dl, lse_next = INFINITY, dl_next = 0.f;
-      load_row_stats(0, lse, dl);
+      int hq_cur = MODE == 1 ? it.hx : it.hk * G, qt_cur = it.fixed_tile;   // pair t
+      int hq_prev = hq_cur, qt_prev = qt_cur;                               // pair t - 1 (for the dQ drain)
+      load_row_stats(hq_cur, qt_cur, lse, dl);
       for (int t = 0; t < it.n_iter; ++t, ++g) {
         int qt, kt;
+        int hq_next = hq_cur, qt_next = qt_cur + 1;                         // pair t + 1
         if (MODE != 1) {
-          qt = it.fixed_tile + t % it.per_head; kt = it.fixed_tile;
+          if (qt_next == it.fixed_tile + it.per_head) { qt_next = it.fixed_tile; ++hq_next; }
+          qt = qt_cur; kt = it.fixed_tile;
           if (t > 0) { lse = lse_next; dl = dl_next; }
-          if (t + 1 < it.n_iter) load_row_stats(t + 1, lse_next, dl_next);
+          if (t + 1 < it.n_iter) load_row_stats(hq_next, qt_next, lse_next, dl_next);
         } else {
           qt = it.fixed_tile; kt = t;
         }
@@ -398,8 +422,11 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
         const uint32_t t_s = t_lane + kColS + 128u * bf + 32u * part;
         // ---- phase A: P = exp2(S*c - lse) for this thread's 32 keys (kept in registers for phase B) ----
         f32x2_t P2[16];
+        const bool tl = (warp == 4 && lane == 0);
+        if (tl) DLOG(0, 0);
         mbar_wait(s_full(bf), MODE == 2 ? g & 1u : (g >> 1) & 1u);
         tc_fence_after();
+        if (tl) DLOG(0, 1);
         {
           uint32_t rs[32];
           tmem_ld32(t_s, rs);
@@ -425,16 +452,20 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(s_free(bf));          // the next S into this buffer may be issued
+        if (tl) DLOG(0, 2);
         if (MODE != 1) {
           if (g > 0) mbar_wait(pds_free, (g - 1) & 1u);  // the previous pair's gradient UMMAs are done with the tiles
+          if (tl) DLOG(0, 3);
           uint32_t wp[16];
 #pragma unroll
           for (int i = 0; i < 16; ++i) wp[i] = f32x2_to_bf16x2(P2[i]);
           store_slice(sP, wp);
         }
         // ---- phase B: dS' = P * (dP - D) ----
+        if (tl) DLOG(0, 4);
         mbar_wait(dp_full, g & 1u);
         tc_fence_after();
+        if (tl) DLOG(0, 5);
         {
           uint32_t rd[32];
           tmem_ld32(t_dp, rd);
@@ -450,11 +481,14 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy stores -> visible to the UMMAs
         __syncwarp();
         if (lane == 0) mbar_arrive(pds_full);
+        if (tl) DLOG(0, 6);
         if (drains && t > 0)   // the previous pair's dQ partial: its UMMAs ran while this pair was exponentiated
-          drain_dq(g - 1, it.hk * G + (t - 1) / it.per_head, it.fixed_tile + (t - 1) % it.per_head, it.b);
+          drain_dq(g - 1, hq_prev, qt_prev, it.b);
+        if (tl) DLOG(0, 7);
+        hq_prev = hq_cur; qt_prev = qt_cur;
+        hq_cur = hq_next; qt_cur = qt_next;
       }
-      if (drains)
-        drain_dq(g - 1, it.hk * G + (it.n_iter - 1) / it.per_head, it.fixed_tile + (it.n_iter - 1) % it.per_head, it.b);
+      if (drains) drain_dq(g - 1, hq_prev, qt_prev, it.b);
       // ---- accumulators -> (x softmax scale for dK) -> bf16 -> the gradient buffer ----
       mbar_wait(acc_full, n & 1u);
       tc_fence_after();
@@ -610,3 +644,17 @@ extern "C" int b200ft_attn_bwd(const void* qkv, int64_t ld, int q_off, int k_off
   B200FT_CUDA(launch_k(attn_bwd_kernel<2>, grid0, kThreads, kSmemBytes, st, tm_qkv, tm_do, tm_dq, p));
   return 0;
 }
+
+#ifdef B200FT_ATTN_TIMING
+extern "C" int b200ft_debug_attn_bwd64_timing(long long* log_out, int* counts_out, int reset) {
+  if (reset) {
+    int z[2] = {0, 0};
+    B200FT_CUDA(cudaMemcpyToSymbol(g_dcnt, z, sizeof(z)));
+    return 0;
+  }
+  B200FT_CUDA(cudaDeviceSynchronize());
+  B200FT_CUDA(cudaMemcpyFromSymbol(log_out, g_dlog, sizeof(long long) * 2 * 4096 * 2));
+  B200FT_CUDA(cudaMemcpyFromSymbol(counts_out, g_dcnt, sizeof(int) * 2));
+  return 0;
+}
+#endif

@@ -342,10 +342,13 @@ attn_bwd_d128_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_co
         row_stats(it.hx, it.fixed_tile, L, lse, dl);
       }
       else if (co_tid < 64) row_stats(it.hk * G, it.fixed_tile, 64 * cohort + co_tid, lse_next, dl_next);
+      int tq = 0, th = 0;   // MODE 0: t % per_head, t / per_head as counters (a division per pair in each of 512 threads otherwise)
       for (int t = 0; t < it.n_iter; ++t, ++gp) {
         int qt, kt;
-        if (MODE == 0) { qt = it.fixed_tile + t % it.per_head; kt = it.fixed_tile; }
+        if (MODE == 0) { qt = it.fixed_tile + tq; kt = it.fixed_tile; }
         else           { qt = it.fixed_tile; kt = t; }
+        int tqn = tq + 1, thn = th;
+        if (tqn == it.per_head) { tqn = 0; ++thn; }
         const bool diag = qt == kt;
         float* st_lse = stat + (gp & 1u) * 2 * kB + 64 * cohort;     // this cohort's 64 columns
         float* st_dl = st_lse + kB;
@@ -354,8 +357,7 @@ attn_bwd_d128_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_co
             st_lse[co_tid] = lse_next;
             st_dl[co_tid] = dl_next;
             if (t + 1 < it.n_iter)
-              row_stats(it.hk * G + (t + 1) / it.per_head, it.fixed_tile + (t + 1) % it.per_head, 64 * cohort + co_tid,
-                        lse_next, dl_next);
+              row_stats(it.hk * G + thn, it.fixed_tile + tqn, 64 * cohort + co_tid, lse_next, dl_next);
           }
           named_bar_sync(1 + cohort, 256);   // the cohort's eight warps: this pair's statistics are visible
         }
@@ -417,6 +419,7 @@ attn_bwd_d128_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_co
         __syncwarp();
         if (lane == 0) mbar_arrive(pds_full(bf));
         if (tl) BLOG(0, 4);
+        tq = tqn; th = thn;
       }
       // ---- accumulators -> (x softmax scale for dK, dQ) -> bf16 -> the gradient buffer ----
       mbar_wait(acc_full, n & 1u);

@@ -27,7 +27,8 @@ names = {0: "wait S", 1: "S ready", 2: "scores loaded", 3: "max found", 4: "exch
 for role in (0, 1):
     n = min(int(cnt[role]), 4096)
     ev = log[role, :n]
-    t0 = ev[0, 1]
+    if n == 0:
+        continue
     print(f"--- role {role}: {n} events")
     # per-tag mean delta to the previous event, over the steady state (skip first 20 %, last 10 %)
     lo, hi = n // 5, n - n // 10
@@ -69,3 +70,30 @@ if dh == 128 and hasattr(L, "b200ft_debug_attn_bwd128_timing"):
             per = [int(ev[i, 1]) for i in range(lo, hi) if ev[i, 0] == (0 if role == 0 else 10)]
             if len(per) > 2:
                 print(f"  period: {np.mean(np.diff(per)):.0f} clk")
+
+# ---- backward, d_head 64 (fused kernel, MODE 2) ----
+if dh == 64 and hasattr(L, "b200ft_debug_attn_bwd64_timing"):
+    dout = torch.randn(B * T, H * dh, device=dev).to(torch.bfloat16)
+    dqkv = torch.empty(B * T, ld, dtype=torch.bfloat16, device=dev)
+    ws = ops.attn_bwd_workspace(B, T, H, dh, dev)
+    kw = dict(batch=B, seq=T, n_head=H, n_kv_head=KV, d_head=dh, q_off=0, k_off=H * dh, v_off=(H + KV) * dh, scale=1 / math.sqrt(dh))
+    for _ in range(3): ops.attn_bwd(qkv, out, dout, lse, ws, dqkv, **kw)
+    fn = L.b200ft_debug_attn_bwd64_timing
+    fn.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int]
+    dlog = np.zeros((2, 4096, 2), dtype=np.int64); dcnt = np.zeros(2, dtype=np.int32)
+    fn(None, None, 1)
+    ops.attn_bwd(qkv, out, dout, lse, ws, dqkv, **kw)
+    fn(dlog.ctypes.data_as(ctypes.c_void_p), dcnt.ctypes.data_as(ctypes.c_void_p), 0)
+    dn = {0: "wait S", 1: "S ready", 2: "P computed, S freed", 3: "P/dS tiles free", 4: "P stored", 5: "dP ready", 6: "dS stored, handed over", 7: "dQ drained",
+          10: "pair start", 11: "S(next) issued", 12: "P,dS ready", 13: "dP(next) issued", 14: "dQ buffer free", 15: "grads issued"}
+    for role in (0, 1):
+        n = min(int(dcnt[role]), 4096); ev = dlog[role, :n]
+        print(f"--- backward d64 fused, role {role}: {n} events")
+        lo, hi = n // 5, n - n // 10
+        acc = {}
+        for i in range(max(lo, 1), hi):
+            acc.setdefault((int(ev[i - 1, 0]), int(ev[i, 0])), []).append(int(ev[i, 1] - ev[i - 1, 1]))
+        for (a, b), v in sorted(acc.items()):
+            print(f"  {dn.get(a, a):>24} -> {dn.get(b, b):<24} mean {np.mean(v):7.0f}  min {np.min(v):6d}  max {np.max(v):6d}  n {len(v)}")
+        per = [int(ev[i, 1]) for i in range(lo, hi) if ev[i, 0] == (0 if role == 0 else 10)]
+        if len(per) > 2: print(f"  period: {np.mean(np.diff(per)):.0f} clk")
