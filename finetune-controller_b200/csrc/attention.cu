@@ -36,6 +36,9 @@ constexpr int kTmemCols = 512;
 // pairs, 64 columns) in its own columns for DH = 64 and ON TOP OF S_g for DH = 128, where S (256) + O (256) fill
 // the 512 columns: the exponentials then overwrite the scores they came from, the row maximum is found in a
 // read-only pass first, and the issue order per query tile becomes P V (j) before S (j+1).
+#ifndef B200FT_ATTN_POLY_MASK
+#define B200FT_ATTN_POLY_MASK 3   // d_head 128: pairs whose index has these bits set take exp2 on the FMA pipe (3: one in four)
+#endif
 template <int DH> struct Cfg {
   static_assert(DH == 64 || DH == 128, "head sizes built: 64, 128");
   static constexpr int kBoxes = DH / 64;
@@ -46,6 +49,10 @@ template <int DH> struct Cfg {
                                                         // threads of a query row, [slot][group][half][128] fp32
   static constexpr int kSmemBytes = kOffXch + 2 * 2 * 2 * 128 * 4;   // no alignment slack (the kernel checks the base)
   static constexpr bool kAliasP = DH == 128;
+  // exp2 on the FMA pipe for part of the row.  Measured (us, 25 % of the pairs): 1 x 4096 x 32/8 d 128 149.6 -> 139.8, 2 x 4096
+  // 280.8 -> 273.7; d_head 64, where a tile has half the tensor work to hide the same exponentials and the softmax warps
+  // are short of issue slots: 4 x 2048 x 32/8 136 -> 140, 8 x 4096 x 12 331 -> 352.  So: d_head 128 only.
+  static constexpr int kPolyMask = DH == 128 ? B200FT_ATTN_POLY_MASK : 0xff;
   static constexpr uint32_t kColS = 0, kColPV = 256;
   static constexpr uint32_t kColP = kAliasP ? 0u : 384u;
   static constexpr uint32_t kStrideP = kAliasP ? 128u : 64u;   // column distance between P_A and P_B
@@ -444,9 +451,15 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm, const AttnParams p) {
           uint32_t w[8];
 #pragma unroll
           for (int i = 0; i < 16; i += 2) {
-            float e0, e1;
-            upk2(fma2(pk2(__uint_as_float(r[16 * c + i]), __uint_as_float(r[16 * c + i + 1])), sc2, nm2), e0, e1);
-            const float p0 = ex2(e0), p1 = ex2(e1);   // exp2(-inf) = 0 for masked keys
+            const f32x2_t e2 = fma2(pk2(__uint_as_float(r[16 * c + i]), __uint_as_float(r[16 * c + i + 1])), sc2, nm2);
+            float p0, p1;
+            if (((i >> 1) & C::kPolyMask) == C::kPolyMask) {   // compile-time: one pair in four on the FMA pipe (d_head 128)
+              upk2(exp2_fma2(e2), p0, p1);
+            } else {
+              float e0, e1;
+              upk2(e2, e0, e1);
+              p0 = ex2(e0); p1 = ex2(e1);               // exp2(-inf) = 0 for masked keys
+            }
             sa[(i >> 1) & 1] = add2(sa[(i >> 1) & 1], pk2(p0, p1));
             w[i >> 1] = pack_bf16x2(p0, p1);
           }

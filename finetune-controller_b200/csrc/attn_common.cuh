@@ -100,6 +100,37 @@ static __device__ __forceinline__ uint32_t idesc(int n, int a_mn, int b_mn) {
          ((uint32_t)(n >> 3) << 17) | (8u << 24);
 }
 
+// 2^x for a pair on the FMA pipe instead of the special-function unit (16 exponentials per clock and SM is the
+// forward kernel's longest resource at d_head 64): x = n + f with n = round(x) taken from the mantissa of x + 1.5 * 2^23,
+// 2^f on [-0.5, 0.5] by a degree-3 polynomial (relative error 1e-4: P is rounded to bf16, 4e-3, right after), 2^n added
+// into the exponent field.  x is clamped at -126: masked scores (-inf) and underflow give 2^-126, i.e. 0 in bf16.
+static __device__ __forceinline__ f32x2_t exp2_fma2(f32x2_t x) {
+  float x0, x1;
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(x0), "=f"(x1) : "l"(x));
+  x0 = fmaxf(x0, -126.f); x1 = fmaxf(x1, -126.f);
+  f32x2_t xc, t, f, q;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(xc) : "f"(x0), "f"(x1));
+  const float mg = 12582912.f;
+  f32x2_t magic, c0, c1, c2, c3;
+  asm("mov.b64 %0, {%1, %1};" : "=l"(magic) : "f"(mg));
+  asm("mov.b64 %0, {%1, %1};" : "=l"(c0) : "f"(0.99992454f));
+  asm("mov.b64 %0, {%1, %1};" : "=l"(c1) : "f"(0.69313675f));
+  asm("mov.b64 %0, {%1, %1};" : "=l"(c2) : "f"(0.24263948f));
+  asm("mov.b64 %0, {%1, %1};" : "=l"(c3) : "f"(0.05583828f));
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(t) : "l"(xc), "l"(magic));
+  asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(f) : "l"(t), "l"(magic));      // n as a float
+  asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(f) : "l"(xc), "l"(f));         // f = x - n
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(q) : "l"(c3), "l"(f), "l"(c2));
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(q) : "l"(q), "l"(f), "l"(c1));
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(q) : "l"(q), "l"(f), "l"(c0));
+  uint32_t q0, q1, t0, t1;
+  asm("mov.b64 {%0, %1}, %2;" : "=r"(q0), "=r"(q1) : "l"(q));
+  asm("mov.b64 {%0, %1}, %2;" : "=r"(t0), "=r"(t1) : "l"(t));
+  q0 += t0 << 23; q1 += t1 << 23;                                       // the low mantissa bits of t hold n (two's complement)
+  f32x2_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "r"(q0), "r"(q1));
+  return r;
+}
 static __device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t* w) {
   asm volatile(
       "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "

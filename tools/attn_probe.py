@@ -3,7 +3,8 @@ import math, os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, os.path.join(ROOT, "finetune-controller_b200"))
 import torch, torch.nn.functional as F
-from b200ft import ops
+from b200ft import ops, _lib
+if os.environ.get("B200FT_PROBE_LIB"): _lib.LIB_PATH = os.path.join(ROOT, os.environ["B200FT_PROBE_LIB"])  # variant build, measurement only
 dev = "cuda:0"
 def timeit(fn, n=20):
     for _ in range(3): fn()
