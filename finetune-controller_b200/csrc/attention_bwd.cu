@@ -34,7 +34,8 @@ constexpr int kRing = 3;                      // stream ring: pair g feeds its g
 constexpr int kOffS = 2 * kTile;              // ring stages of (tile0, tile1)
 constexpr int kOffP = kOffS + kRing * 2 * kTile;
 constexpr int kOffDS = kOffP + kPTile;
-constexpr int kOffDQ = kOffDS + kPTile;       // MODE 2: eight 4 KB staging tiles (32 rows x 32 fp32) for the dQ reduce
+constexpr int kOffDQ = kOffDS + kPTile;       // MODE 2: eight 2 KB staging tiles (32 rows x 32 bf16) for the dQ reduce,
+constexpr int kOffK1 = kOffDQ + 8 * 2048;     //         then the second buffer of the resident K tile (16 KB)
 constexpr int kOffBar = kOffDQ + 8 * 4096;    // 224 KB
 constexpr int kSmemBytes = kOffBar + 256;
 // S is double-buffered (+128) in the split modes; the fused mode keeps one S buffer and puts its two dQ-partial
@@ -141,7 +142,15 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
   const uint32_t acc_full = bars + 8u * 15, acc_free = bars + 8u * 16;
   auto dq_full = [&](uint32_t bf) { return bars + 8u * (17 + bf); };   // MODE 2: dQ partial of a pair is in TMEM
   auto dq_free = [&](uint32_t bf) { return bars + 8u * (19 + bf); };   //         ... and has been read out
-  const uint32_t tmem_slot = bars + 8u * 21;
+  // MODE 2: the resident K tile is double-buffered (item n uses buffer n & 1) and V is released after the item's last
+  // dP product, so that the next item's K and V are in shared memory when the current item ends.  At T = 1024 an item
+  // has 4.5 pairs on average, and reloading the resident pair after the last UMMA of an item (the dQ partials read K
+  // to the end) left the tensor core idle for ~4000 cycles at every boundary.
+  auto k_full = [&](uint32_t b) { return bars + 8u * (21 + b); };
+  auto k_empty = [&](uint32_t b) { return bars + 8u * (23 + b); };
+  const uint32_t v_full = bars + 8u * 25, v_empty = bars + 8u * 26;
+  const uint32_t sK1 = raw + kOffK1;
+  const uint32_t tmem_slot = bars + 8u * 27;
   volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - raw));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -155,6 +164,8 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
     mbar_init(dp_full, 1); mbar_init(pds_full, 16); mbar_init(pds_free, 1);
     mbar_init(acc_full, 1); mbar_init(acc_free, 16);
     for (uint32_t bf = 0; bf < 2; ++bf) { mbar_init(dq_full(bf), 1); mbar_init(dq_free(bf), 8); }
+    for (uint32_t b = 0; b < 2; ++b) { mbar_init(k_full(b), 1); mbar_init(k_empty(b), 1); }
+    mbar_init(v_full, 1); mbar_init(v_empty, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 2) {
@@ -180,8 +191,20 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
     uint32_t g = 0, n = 0;
     for (int w = item_at(0); w < num_items; w = item_at(++n)) {
       const Item it = decode_item<MODE>(p, w, G);
-      if (n > 0) mbar_wait(f_empty, (n - 1) & 1u);   // the previous item's last dP UMMAs have read the resident pair
-      if (issuer) {
+      if (MODE == 2) {
+        if (n == 0 && issuer) {
+          mbar_expect_tx(k_full(0), kTile);
+          tma_load_3d(sF0, &tm_qkv, p.k_off + it.hk * kDH, it.fixed_tile * kB, it.b, k_full(0));
+        }
+        if (n > 0) mbar_wait(v_empty, (n - 1) & 1u);   // the previous item's last dP product has read V
+        if (issuer) {
+          mbar_expect_tx(v_full, kTile);
+          tma_load_3d(sF1, &tm_qkv, p.v_off + it.hk * kDH, it.fixed_tile * kB, it.b, v_full);
+        }
+        __syncwarp();
+      }
+      if (MODE != 2 && n > 0) mbar_wait(f_empty, (n - 1) & 1u);   // the previous item's last dP UMMAs have read the resident pair
+      if (MODE != 2 && issuer) {
         mbar_expect_tx(f_full, 2 * kTile);
         if (MODE != 1) {
           tma_load_3d(sF0, &tm_qkv, p.k_off + it.hk * kDH, it.fixed_tile * kB, it.b, f_full);
@@ -208,6 +231,21 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
         }
         __syncwarp();
       }
+      if (MODE == 2) {
+        // K of the NEXT item into the other buffer, requested once this item's streamed tiles are all on their way
+        // (the producer runs up to three pairs ahead of the tensor core): the buffer's last user was item n - 1
+        const int w_next = item_at(n + 1);
+        if (w_next < num_items) {
+          const Item nx = decode_item<MODE>(p, w_next, G);
+          const uint32_t nb = (n + 1) & 1u;
+          if (n >= 1) mbar_wait(k_empty(nb), ((n - 1) >> 1) & 1u);
+          if (issuer) {
+            mbar_expect_tx(k_full(nb), kTile);
+            tma_load_3d(nb ? sK1 : sF0, &tm_qkv, p.k_off + nx.hk * kDH, nx.fixed_tile * kB, nx.b, k_full(nb));
+          }
+          __syncwarp();
+        }
+      }
     }
   } else if (warp == 1) {
     // ================================ MMA issuer ================================
@@ -215,16 +253,16 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
     const uint32_t id_s = idesc(kB, 0, 0);     // S, dP: 128 x 128 x 64, both operands K-major
     const uint32_t id_g0 = idesc(kDH, 1, 1);   // dV, dK: 128 (keys) x 64 x 128 (queries): A = P^T / dS^T, B = dO / Q, MN-major
     const uint32_t id_g1 = idesc(kDH, 0, 1);   // dQ: 128 (queries) x 64 x 128 (keys): A = dS K-major, B = K MN-major
+    uint32_t sK = sF0;                         // MODE 2: the current item's buffer of the resident K tile
     auto issue_s = [&](uint32_t gg) {          // S(gg) = Q K^T into S buffer gg & 1 (MODE 2: the only buffer)
       const uint32_t st = gg % kRing, bf = MODE == 2 ? 0u : gg & 1u;
       mbar_wait(st_full(st), (gg / kRing) & 1u);
       if (MODE == 2) { if (gg >= 1) mbar_wait(s_free(0), (gg - 1) & 1u); }   // phase A of the previous pair has read S
       else if (gg >= 2) mbar_wait(s_free(bf), ((gg >> 1) - 1) & 1u);         // phase A of pair gg-2 has read this buffer
       tc_fence_after();
-      const uint32_t aq = MODE != 1 ? sS0(st) : sF0, bk = MODE != 1 ? sF0 : sS0(st);
+      const uint32_t aq = MODE != 1 ? sS0(st) : sF0, bk = MODE != 1 ? sK : sS0(st);
       if (issuer) {
 #ifndef B200FT_EXP_NO_SDP
-#pragma unroll
         // descriptors once per product, the k-th step's offset added to the address field (16-byte units; the tiles lie
         // below 256 KB, so the add never carries out of it): the single issuing thread is on every pair's critical path
         const uint64_t da = sdesc(aq, 16, 1024), db = sdesc(bk, 16, 1024);
@@ -247,7 +285,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
           umma(tmem + kColDP, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), id_s, k > 0);
 #endif
         umma_commit(dp_full);
-        if (MODE != 2 && last_of_item) umma_commit(f_empty);   // nothing of this item reads the resident pair any more
+        if (last_of_item) umma_commit(MODE == 2 ? v_empty : f_empty);   // nothing of this item reads the resident pair (MODE 2: V) any more
       }
       __syncwarp();
     };
@@ -273,7 +311,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
         if (MODE == 2) {
           // dQ partial of this pair: 128 (queries) x 64 x 128 (keys), A = dS K-major, B = the resident K tile MN-major
           const uint32_t dq_col = kColDQ + 64u * (gg & 1u);
-          const uint64_t dds1 = sdesc(sDS, 16, 1024), dk1 = sdesc(sF0, 8192, 1024);
+          const uint64_t dds1 = sdesc(sDS, 16, 1024), dk1 = sdesc(sK, 8192, 1024);
 #pragma unroll
           for (int k = 0; k < kB / 16; ++k)
             umma(tmem + dq_col, dds1 + (uint64_t)(1024 * (k >> 2) + 2 * (k & 3)), dk1 + (uint64_t)(128 * k), id_g1, k > 0);
@@ -289,10 +327,12 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
     for (int w = item_at(0); w < num_items; w = item_at(++n)) {
       const Item it = decode_item<MODE>(p, w, G);
       const int N = it.n_iter;
-      mbar_wait(f_full, n & 1u);
+      if (MODE == 2) { sK = (n & 1u) ? sK1 : sF0; mbar_wait(k_full(n & 1u), (n >> 1) & 1u); }
+      else mbar_wait(f_full, n & 1u);
       // item prologue: S(first), dP(first), S(second).  The dP buffer is free: the previous item's last pair
       // was waited for below before its gradients were issued.
       issue_s(g);
+      if (MODE == 2) { mbar_wait(v_full, n & 1u); tc_fence_after(); }
       issue_dp(g, N == 1);
       if (MODE != 2 && N > 1) issue_s(g + 1);
       for (int t = 0; t < N; ++t, ++g) {
@@ -313,7 +353,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
       }
       if (issuer) {
         umma_commit(acc_full);
-        if (MODE == 2) umma_commit(f_empty);   // the dQ partials read the resident K tile to the end of the item
+        if (MODE == 2) umma_commit(k_empty(n & 1u));   // the dQ partials read the resident K tile to the end of the item
       }
       __syncwarp();
     }
@@ -344,7 +384,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
     // MODE 2: dQ partial of pair gg -> staging tile -> TMA reduce-add (bf16) into the q columns of the gradient buffer
     // [batch][seq][columns], which the host zeroed; rows past the end of the sequence are clipped by TMA.  Slices 0 and 1 do it (32 rows x
     // 32 columns per warp); the other two warps of the quarter run ahead into the next pair's exponentials.
-    const uint32_t stage_dq = raw + kOffDQ + (uint32_t)((part & 1) * 4 + quarter) * 4096u;
+    const uint32_t stage_dq = raw + kOffDQ + (uint32_t)((part & 1) * 4 + quarter) * 2048u;
     auto drain_dq = [&](uint32_t gg, int hq, int qt, int bb) {
       const uint32_t bq = gg & 1u;
       mbar_wait(dq_full(bq), (gg >> 1) & 1u);
