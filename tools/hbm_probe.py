@@ -5,7 +5,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, os.path.join(ROOT, "finetune-controller_b200"))
 import torch
 dev = "cuda:0"
-from b200ft import ops
+from b200ft import ops, _lib
+if os.environ.get("B200FT_PROBE_LIB"): _lib.LIB_PATH = os.path.join(ROOT, os.environ["B200FT_PROBE_LIB"])  # variant build, measurement only
 what = sys.argv[1]
 iters = int(sys.argv[2]) if len(sys.argv) > 2 else 5
 def run(fn, bytes_):
