@@ -6,28 +6,42 @@
 #include "common.cuh"
 #include "../../include/b200ft.h"
 
+#ifndef LN_BWD_PREFETCH_RES
+#define LN_BWD_PREFETCH_RES 1
+#endif
+#ifndef LN_BWD_BLOCKS
+#define LN_BWD_BLOCKS 2
+#endif
+#ifndef LN_FWD_ROWS
+#define LN_FWD_ROWS 2
+#endif
+#ifndef LN_FWD_BLOCKS
+#define LN_FWD_BLOCKS 4
+#endif
+
 namespace {
 
 constexpr int kWarpsPerBlock = 8;
-constexpr int kRowsPerWarp = 2;      // two rows in flight per warp: twice the bytes per SM in flight
+constexpr int kRowsPerWarp = 2;
+constexpr int kFwdRows = LN_FWD_ROWS;   // rows per warp in the forward kernel
 constexpr int kMaxVecPerLane = 32;   // d <= 32 lanes * 32 vectors * 8 = 8192
 
 // Rows are kept as the raw 16-byte bf16 vectors they were loaded as (4 registers per vector
 // instead of 8) and unpacked on the fly in each pass; all loads of both rows are issued before
 // the first reduction.
 template <int VPL>
-__global__ void __launch_bounds__(kWarpsPerBlock * 32, VPL <= 4 ? 4 : 1)
+__global__ void __launch_bounds__(kWarpsPerBlock * 32, VPL <= 4 ? LN_FWD_BLOCKS : 1)
 layernorm_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ gamma,
                      const float* __restrict__ beta, __nv_bfloat16* __restrict__ y,
                      float* __restrict__ mean, float* __restrict__ rstd, int64_t rows, int d, float eps) {
   grid_dep_sync();
   const int lane = threadIdx.x & 31;
-  const int64_t row0 = ((int64_t)blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5)) * kRowsPerWarp;
+  const int64_t row0 = ((int64_t)blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5)) * kFwdRows;
   if (row0 >= rows) return;
   const int nvec = d >> 3;
-  uint4 q[kRowsPerWarp][VPL];
+  uint4 q[kFwdRows][VPL];
 #pragma unroll
-  for (int r = 0; r < kRowsPerWarp; ++r) {
+  for (int r = 0; r < kFwdRows; ++r) {
     const bool live = row0 + r < rows;
 #pragma unroll
     for (int i = 0; i < VPL; ++i) {
@@ -35,9 +49,9 @@ layernorm_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restric
       q[r][i] = (live && vi < nvec) ? ld_stream16(x + (row0 + r) * d + (vi << 3)) : make_uint4(0u, 0u, 0u, 0u);
     }
   }
-  float mu[kRowsPerWarp], rs[kRowsPerWarp];
+  float mu[kFwdRows], rs[kFwdRows];
 #pragma unroll
-  for (int r = 0; r < kRowsPerWarp; ++r) {
+  for (int r = 0; r < kFwdRows; ++r) {
     float sum = 0.f;
 #pragma unroll
     for (int i = 0; i < VPL; ++i) {
@@ -49,7 +63,7 @@ layernorm_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restric
     mu[r] = warp_sum(sum) / (float)d;
   }
 #pragma unroll
-  for (int r = 0; r < kRowsPerWarp; ++r) {
+  for (int r = 0; r < kFwdRows; ++r) {
     float sq = 0.f;
 #pragma unroll
     for (int i = 0; i < VPL; ++i) {
@@ -74,7 +88,7 @@ layernorm_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restric
       const float gg[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
       const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
 #pragma unroll
-      for (int r = 0; r < kRowsPerWarp; ++r) {
+      for (int r = 0; r < kFwdRows; ++r) {
         if (row0 + r < rows) {
           float f[8], o[8];
           unpack8(q[r][i], f);
@@ -89,7 +103,7 @@ layernorm_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restric
 
 // dx = dres + rstd * (g*dy - mean(g*dy) - xhat * mean(g*dy*xhat))
 template <int VPL>
-__global__ void __launch_bounds__(kWarpsPerBlock * 32, VPL <= 4 ? 3 : 1)
+__global__ void __launch_bounds__(kWarpsPerBlock * 32, VPL <= 4 ? LN_BWD_BLOCKS : 1)
 layernorm_bwd_dx_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
                         const float* __restrict__ gamma, const float* __restrict__ mean,
                         const float* __restrict__ rstd, const __nv_bfloat16* __restrict__ dres,
@@ -100,6 +114,9 @@ layernorm_bwd_dx_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat1
   if (row0 >= rows) return;
   const int nvec = d >> 3;
   uint4 qdy[kRowsPerWarp][VPL], qx[kRowsPerWarp][VPL];
+#if LN_BWD_PREFETCH_RES
+  uint4 qr[kRowsPerWarp][VPL];
+#endif
   float mu[kRowsPerWarp], rs[kRowsPerWarp];
 #pragma unroll
   for (int r = 0; r < kRowsPerWarp; ++r) {
@@ -112,6 +129,9 @@ layernorm_bwd_dx_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat1
       const bool ok = live && vi < nvec;
       qdy[r][i] = ok ? ld_stream16(dy + (row0 + r) * d + (vi << 3)) : make_uint4(0u, 0u, 0u, 0u);
       qx[r][i] = ok ? ld_stream16(x + (row0 + r) * d + (vi << 3)) : make_uint4(0u, 0u, 0u, 0u);
+#if LN_BWD_PREFETCH_RES
+      qr[r][i] = (ok && dres) ? ld_stream16(dres + (row0 + r) * d + (vi << 3)) : make_uint4(0u, 0u, 0u, 0u);
+#endif
     }
   }
   float s1[kRowsPerWarp], s2[kRowsPerWarp];
@@ -160,7 +180,11 @@ layernorm_bwd_dx_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat1
           for (int j = 0; j < 8; ++j) o[j] = rs[r] * (a[j] * gg[j] - s1[r] - (b[j] - mu[r]) * rs[r] * s2[r]);
           if (dres) {
             float rr[8];
+#if LN_BWD_PREFETCH_RES
+            unpack8(qr[r][i], rr);
+#else
             unpack8(ld_stream16(dres + (row0 + r) * d + (vi << 3)), rr);
+#endif
 #pragma unroll
             for (int j = 0; j < 8; ++j) o[j] += rr[j];
           }
@@ -191,7 +215,7 @@ extern "C" int b200ft_layernorm_fwd(const void* x, const float* gamma, const flo
   B200FT_CHECK_ARG(rows > 0 && d > 0 && d % 8 == 0 && d <= 8 * 32 * kMaxVecPerLane,
                    "layernorm_fwd: rows=%lld d=%d (d must be a multiple of 8, <= 8192)", (long long)rows, d);
   cudaStream_t st = (cudaStream_t)stream;
-  const int64_t rows_per_block = (int64_t)kWarpsPerBlock * kRowsPerWarp;
+  const int64_t rows_per_block = (int64_t)kWarpsPerBlock * kFwdRows;
   unsigned blocks = (unsigned)((rows + rows_per_block - 1) / rows_per_block);
   int vpl = vpl_for(d);
 #define CALL(V)                                                                                     \
