@@ -16,7 +16,7 @@
 #define LN_FWD_ROWS 2
 #endif
 #ifndef LN_FWD_BLOCKS
-#define LN_FWD_BLOCKS 4
+#define LN_FWD_BLOCKS 3
 #endif
 
 namespace {
