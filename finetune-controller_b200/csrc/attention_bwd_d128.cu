@@ -315,30 +315,35 @@ attn_bwd_d128_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_co
       // cohort fetch the values of ITS 64 query rows one pair ahead (global-memory latency off the critical path) and
       // publish them in shared memory, double-buffered, when the pair starts (one 256-thread named barrier per cohort).
       float lse = INFINITY, dl = 0.f, lse_next = INFINITY, dl_next = 0.f;
-      if (MODE == 1) {
-        // resident operands -> TMEM: this thread's lane is query row L; slices 0, 1 carry the two halves of its Q row,
-        // slices 2, 3 those of its dO row (64 elements = 32 packed columns each), straight from global memory
-        const int qr = it.fixed_tile * kB + L;
+      // MODE 1, resident operands -> TMEM: this thread's lane is query row L; slices 0, 1 carry the two halves of its Q
+      // row, slices 2, 3 those of its dO row (64 elements = 32 packed columns each), straight from global memory.  Item
+      // n + 1's operands are written at the END of item n — as soon as its last products have read theirs, two
+      // sub-pairs before its gradients finish — so the tensor core goes from item to item without waiting for them.
+      auto fill_operands = [&](const Item& nx, uint32_t n_of) {
+        const int qr = nx.fixed_tile * kB + L;
         uint32_t a[32];
 #pragma unroll
         for (int i = 0; i < 32; ++i) a[i] = 0u;
         if (qr < p.seq) {
           const __nv_bfloat16* src = part4 < 2
-              ? p.qkv + ((int64_t)it.b * p.seq + qr) * p.ld_qkv + p.q_off + it.hx * kDH + 64 * part4
-              : p.dout + ((int64_t)it.b * p.seq + qr) * p.ld_do + it.hx * kDH + 64 * (part4 - 2);
+              ? p.qkv + ((int64_t)nx.b * p.seq + qr) * p.ld_qkv + p.q_off + nx.hx * kDH + 64 * part4
+              : p.dout + ((int64_t)nx.b * p.seq + qr) * p.ld_do + nx.hx * kDH + 64 * (part4 - 2);
 #pragma unroll
           for (int v = 0; v < 8; ++v) {
             const uint4 q4 = __ldg(reinterpret_cast<const uint4*>(src) + v);
             a[4 * v] = q4.x; a[4 * v + 1] = q4.y; a[4 * v + 2] = q4.z; a[4 * v + 3] = q4.w;
           }
         }
-        if (n > 0) { mbar_wait(f_empty, (n - 1) & 1u); tc_fence_after(); }   // the previous item's products have read theirs
+        if (n_of > 0) { mbar_wait(f_empty, (n_of - 1) & 1u); tc_fence_after(); }   // the previous item's products have read theirs
         tmem_st16(t_lane + kColAcc1 + 32u * (uint32_t)part4, a);
         tmem_st16(t_lane + kColAcc1 + 32u * (uint32_t)part4 + 16u, a + 16);
         tmem_wait_st();
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(f_full);
+      };
+      if (MODE == 1) {
+        if (n == 0) fill_operands(it, 0);
         row_stats(it.hx, it.fixed_tile, L, lse, dl);
       }
       else if (co_tid < 64) row_stats(it.hk * G, it.fixed_tile, 64 * cohort + co_tid, lse_next, dl_next);
@@ -420,6 +425,10 @@ attn_bwd_d128_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_co
         if (lane == 0) mbar_arrive(pds_full(bf));
         if (tl) BLOG(0, 4);
         tq = tqn; th = thn;
+      }
+      if (MODE == 1) {
+        const int w_next = item_at(n + 1);
+        if (w_next < num_items) fill_operands(decode_item<MODE>(p, w_next, G), n + 1);
       }
       // ---- accumulators -> (x softmax scale for dK, dQ) -> bf16 -> the gradient buffer ----
       mbar_wait(acc_full, n & 1u);
